@@ -1,0 +1,86 @@
+"""ctypes binding of libdepthb200.so (declared in include/depth_b200.h).
+
+The product path has NO fallback: if the shared library is missing or a call fails, a RuntimeError is
+raised.  torch is used only for device memory / streams; every entry point takes raw pointers.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libdepthb200.so")
+
+DE_DTYPE_BF16, DE_DTYPE_F32 = 0, 1
+ACT_NONE, ACT_RELU, ACT_GELU, ACT_RELU6 = 0, 1, 2, 3
+
+
+class DeGemm(C.Structure):
+    _fields_ = [
+        ("a_mode", C.c_int), ("a", C.c_void_p), ("lda", C.c_int64),
+        ("M", C.c_int), ("N", C.c_int), ("K", C.c_int),
+        ("B", C.c_int), ("H", C.c_int), ("W", C.c_int), ("Cin", C.c_int),
+        ("w", C.c_void_p), ("ldw", C.c_int64),
+        ("bias", C.c_void_p), ("bias_mod", C.c_int), ("act", C.c_int),
+        ("add1", C.c_void_p), ("add1_dtype", C.c_int), ("ld_add1", C.c_int64),
+        ("add1_rowmode", C.c_int), ("add1_pre", C.c_int),
+        ("add2", C.c_void_p),
+        ("out", C.c_void_p), ("out_dtype", C.c_int), ("ldo", C.c_int64),
+        ("out_relu", C.c_void_p),
+        ("out_rowmode", C.c_int), ("grp", C.c_int), ("pad", C.c_int), ("off", C.c_int),
+        ("ps_gh", C.c_int), ("ps_gw", C.c_int), ("ps_s", C.c_int), ("ps_cout", C.c_int),
+        ("head_w", C.c_void_p), ("head_b", C.c_float),
+        ("block_n", C.c_int),
+    ]
+
+
+# name -> (restype, argtypes); must list every symbol include/depth_b200.h declares
+SIGNATURES = {
+    "de_last_error": (C.c_char_p, []),
+    "de_version": (C.c_int, []),
+    "de_launch_count": (C.c_int64, []),
+    "de_get_size": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "de_cubic_taps": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
+    "de_preprocess": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_int, C.c_int,
+                                C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_int, C.c_void_p, C.c_void_p]),
+    "de_postprocess": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                 C.c_void_p, C.c_float, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "de_gemm": (C.c_int, [C.POINTER(DeGemm), C.c_void_p]),
+    "de_layernorm": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float,
+                               C.c_void_p, C.c_int64, C.c_void_p]),
+    "de_attention": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_void_p]),
+    "de_cast_tokens": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
+    "de_fill_cls": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "de_upsample2x": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "de_im2col3x3": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+}
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """Load (once) and type the shared library. Raises RuntimeError when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} is missing - build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(or depth_estimation_b200/csrc/build.sh). There is no CPU or PyTorch fallback.")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc != 0:
+        msg = load().de_last_error().decode(errors="replace")
+        raise RuntimeError(f"libdepthb200 {what} failed ({rc}): {msg}")
+
+
+def launch_count() -> int:
+    return int(load().de_launch_count())

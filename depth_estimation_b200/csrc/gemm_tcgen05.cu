@@ -1,0 +1,462 @@
+// Persistent, warp-specialised tcgen05 GEMM / implicit-GEMM 3x3 convolution for sm_100a.
+//
+//   warp 0      : TMA producer (one elected lane) - A and W tiles into a multi-stage smem ring
+//   warp 1      : MMA issuer (lane 0) - tcgen05.mma kind::f16, 128 x BN x 16 per instruction,
+//                 fp32 accumulators in TMEM, two accumulator stages so the next tile's main loop
+//                 overlaps this tile's epilogue
+//   warp 2      : TMEM allocator / deallocator
+//   warps 4..11 : epilogue - tcgen05.ld TMEM -> registers, fused bias / activation / residual adds /
+//                 row remaps (token offsets, pixel shuffle, conv tiles) / dual store / head dot
+//
+// Covers K2 patch-embed, K3 ViT linears, K4 reassemble (readout, 1x1, ConvT as
+// GEMM + pixel-shuffle), K5 3x3 convs as implicit GEMM (A tiles are TMA boxes of the NHWC activation
+// shifted per filter tap, halo zero-filled by TMA), K6 1x1 out_conv, K7 head, K9 1x1 MBConv convs.
+#include <cuda.h>
+
+#include "common.cuh"
+#include "depth_b200.h"
+#include "host_util.h"
+
+namespace deb {
+
+constexpr int BM = 128;
+constexpr int BK = 64;
+constexpr int kEpiWarps = 8;
+constexpr int kThreads = 128 + 32 * kEpiWarps;
+
+struct GemmParams {
+  int a_mode, M, N, num_k_blocks, m_tiles, n_tiles;
+  int H, W, bw, bh, tiles_x, tiles_y, cin_blocks;
+  // epilogue
+  const float* bias;
+  int bias_mod, act;
+  const void* add1;
+  int add1_dtype, add1_rowmode, add1_pre;
+  long long ld_add1;
+  const __nv_bfloat16* add2;
+  void* out;
+  int out_dtype;
+  long long ldo;
+  __nv_bfloat16* out_relu;
+  int out_rowmode, grp, pad, off;
+  int ps_gh, ps_gw, ps_s, ps_cout;
+  const float* head_w;
+  float head_b;
+};
+
+template <int BN>
+struct Cfg {
+  static constexpr int kABytes = BM * BK * 2;
+  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStagesRaw = (196 * 1024) / kStageBytes;
+  static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
+  static constexpr int kTmemCols = (2 * BN) < 32 ? 32 : 2 * BN;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+DEV float apply_act(float v, int act) {
+  if (act == DE_ACT_RELU) return fmaxf(v, 0.f);
+  if (act == DE_ACT_GELU) return gelu_erf(v);
+  if (act == DE_ACT_RELU6) return fminf(fmaxf(v, 0.f), 6.f);
+  return v;
+}
+
+template <int BN>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+  using C = Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + C::kStages * C::kABytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + C::kStages;
+  uint64_t* tfull = bars + 2 * C::kStages;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int num_tiles = p.m_tiles * p.n_tiles;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < C::kStages; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tfull[i], 1);
+      mbar_init(&tempty[i], kEpiWarps);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, C::kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------- TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      const uint32_t a_bytes = p.a_mode == 0 ? C::kABytes : p.bw * p.bh * BK * 2;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m_tile = tile / p.n_tiles, n_tile = tile % p.n_tiles;
+        int b = 0, y0 = 0, x0 = 0;
+        if (p.a_mode == 1) {
+          const int per_img = p.tiles_x * p.tiles_y;
+          b = m_tile / per_img;
+          const int t = m_tile % per_img;
+          y0 = (t / p.tiles_x) * p.bh;
+          x0 = (t % p.tiles_x) * p.bw;
+        }
+        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&full[stage], a_bytes + C::kBBytes);
+          if (p.a_mode == 0) {
+            tma_load_2d(sA + stage * C::kABytes, &tmA, &full[stage], kb * BK, m_tile * BM);
+          } else {
+            const int tap = kb / p.cin_blocks, cb = kb % p.cin_blocks;
+            tma_load_4d(sA + stage * C::kABytes, &tmA, &full[stage], cb * BK, x0 + (tap % 3) - 1, y0 + (tap / 3) - 1,
+                        b);
+          }
+          tma_load_2d(sB + stage * C::kBBytes, &tmB, &full[stage], kb * BK, n_tile * BN);
+          if (++stage == C::kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------- MMA issuer
+    constexpr uint32_t idesc = make_idesc_bf16(BM, BN);
+    int stage = 0;
+    uint32_t phase = 0;
+    int as = 0;
+    uint32_t aphase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      mbar_wait(&tempty[as], aphase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + as * BN;
+      for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+        mbar_wait(&full[stage], phase);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint64_t adesc = make_sw128_kmajor_desc(smem_u32(sA + stage * C::kABytes));
+          const uint64_t bdesc = make_sw128_kmajor_desc(smem_u32(sB + stage * C::kBBytes));
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+          }
+          umma_commit(&empty[stage]);
+          if (kb == p.num_k_blocks - 1) umma_commit(&tfull[as]);
+        }
+        __syncwarp();
+        if (++stage == C::kStages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      if (++as == 2) {
+        as = 0;
+        aphase ^= 1;
+      }
+    }
+  } else if (warp >= 4) {
+    // ------------------------------------------------------------- epilogue
+    const int q = warp & 3;                      // TMEM lane quadrant this warp may access
+    const int half = (warp - 4) >> 2;            // column half
+    constexpr int kChunks = BN / 32;
+    constexpr int kChunksPerHalf = kChunks >= 2 ? kChunks / 2 : 1;
+    const int c_begin = kChunks >= 2 ? half * kChunksPerHalf : 0;
+    const int c_end = kChunks >= 2 ? c_begin + kChunksPerHalf : (half == 0 ? 1 : 0);
+    const int r = q * 32 + lane;
+    const int bias_mod = p.bias_mod > 0 ? p.bias_mod : p.N;
+    int as = 0;
+    uint32_t aphase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int m_tile = tile / p.n_tiles, n_tile = tile % p.n_tiles;
+      // logical row index m of this thread's accumulator row, and validity
+      long long m;
+      bool valid;
+      if (p.a_mode == 0) {
+        m = static_cast<long long>(m_tile) * BM + r;
+        valid = m < p.M;
+      } else {
+        const int per_img = p.tiles_x * p.tiles_y;
+        const int b = m_tile / per_img, t = m_tile % per_img;
+        const int y = (t / p.tiles_x) * p.bh + r / p.bw, x = (t % p.tiles_x) * p.bw + r % p.bw;
+        valid = (r < p.bw * p.bh) && y < p.H && x < p.W;
+        m = (static_cast<long long>(b) * p.H + y) * p.W + x;
+      }
+      // storage row of out / add2 / out_relu
+      long long orow = m;
+      if (p.out_rowmode == 1) orow = m + (m / p.grp) * p.pad + p.off;
+      long long arow = orow;
+      if (p.add1_rowmode == 1) arow = m / p.grp;
+      else if (p.add1_rowmode == 2) arow = (m % p.grp) + p.off;
+      int ps_b = 0, ps_y = 0, ps_x = 0;
+      if (p.out_rowmode == 2) {
+        const int per = p.ps_gh * p.ps_gw;
+        ps_b = static_cast<int>(m / per);
+        const int t = static_cast<int>(m % per);
+        ps_y = t / p.ps_gw;
+        ps_x = t % p.ps_gw;
+      }
+
+      mbar_wait(&tfull[as], aphase);
+      tc_fence_after();
+      float head_acc = 0.f;
+      for (int c = c_begin; c < c_end; ++c) {
+        uint32_t acc[32];
+        __syncwarp();
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN + c * 32, acc);
+        tmem_ld_wait();
+        const int n0 = n_tile * BN + c * 32;
+        if (!valid || n0 >= p.N) continue;
+        long long obase;  // element offset of column n0 in out
+        int bcol = n0 % bias_mod;
+        if (p.out_rowmode == 2) {
+          const int g = n0 / p.ps_cout, co = n0 % p.ps_cout;
+          const int i = g / p.ps_s, j = g % p.ps_s;
+          obase = ((static_cast<long long>(ps_b) * p.ps_gh * p.ps_s + ps_y * p.ps_s + i) * (p.ps_gw * p.ps_s) +
+                   ps_x * p.ps_s + j) * p.ps_cout + co;
+        } else {
+          obase = orow * p.ldo + n0;
+        }
+        const int ncols = min(32, p.N - n0);  // multiple of 8
+#pragma unroll
+        for (int g8 = 0; g8 < 4; ++g8) {
+          if (g8 * 8 >= ncols) break;
+          float v[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(acc[g8 * 8 + j]);
+          if (p.bias) {
+            const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + bcol + g8 * 8));
+            const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + bcol + g8 * 8 + 4));
+            v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
+            v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
+          }
+          float a1[8];
+          if (p.add1) {
+            if (p.add1_dtype == DE_DTYPE_F32) {
+              const float* ap = reinterpret_cast<const float*>(p.add1) + arow * p.ld_add1 + n0 + g8 * 8;
+              const float4 t0 = *reinterpret_cast<const float4*>(ap);
+              const float4 t1 = *reinterpret_cast<const float4*>(ap + 4);
+              a1[0] = t0.x; a1[1] = t0.y; a1[2] = t0.z; a1[3] = t0.w;
+              a1[4] = t1.x; a1[5] = t1.y; a1[6] = t1.z; a1[7] = t1.w;
+            } else {
+              const __nv_bfloat16* ap = reinterpret_cast<const __nv_bfloat16*>(p.add1) + arow * p.ld_add1 + n0 + g8 * 8;
+              const uint4 t = *reinterpret_cast<const uint4*>(ap);
+              a1[0] = bf16_lo(t.x); a1[1] = bf16_hi(t.x); a1[2] = bf16_lo(t.y); a1[3] = bf16_hi(t.y);
+              a1[4] = bf16_lo(t.z); a1[5] = bf16_hi(t.z); a1[6] = bf16_lo(t.w); a1[7] = bf16_hi(t.w);
+            }
+            if (p.add1_pre) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] += a1[j];
+            }
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = apply_act(v[j], p.act);
+          if (p.add1 && !p.add1_pre) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] += a1[j];
+          }
+          if (p.add2) {
+            const uint4 t = *reinterpret_cast<const uint4*>(p.add2 + obase + g8 * 8);
+            v[0] += bf16_lo(t.x); v[1] += bf16_hi(t.x); v[2] += bf16_lo(t.y); v[3] += bf16_hi(t.y);
+            v[4] += bf16_lo(t.z); v[5] += bf16_hi(t.z); v[6] += bf16_lo(t.w); v[7] += bf16_hi(t.w);
+          }
+          if (p.head_w) {
+            const float4 w0 = __ldg(reinterpret_cast<const float4*>(p.head_w + n0 + g8 * 8));
+            const float4 w1 = __ldg(reinterpret_cast<const float4*>(p.head_w + n0 + g8 * 8 + 4));
+            head_acc += v[0] * w0.x + v[1] * w0.y + v[2] * w0.z + v[3] * w0.w + v[4] * w1.x + v[5] * w1.y +
+                        v[6] * w1.z + v[7] * w1.w;
+          } else if (p.out_dtype == DE_DTYPE_F32) {
+            float* op = reinterpret_cast<float*>(p.out) + obase + g8 * 8;
+            *reinterpret_cast<float4*>(op) = make_float4(v[0], v[1], v[2], v[3]);
+            *reinterpret_cast<float4*>(op + 4) = make_float4(v[4], v[5], v[6], v[7]);
+          } else {
+            uint4 o;
+            o.x = pack_bf16(v[0], v[1]); o.y = pack_bf16(v[2], v[3]);
+            o.z = pack_bf16(v[4], v[5]); o.w = pack_bf16(v[6], v[7]);
+            *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + obase + g8 * 8) = o;
+          }
+          if (p.out_relu) {
+            uint4 o;
+            o.x = pack_bf16(fmaxf(v[0], 0.f), fmaxf(v[1], 0.f)); o.y = pack_bf16(fmaxf(v[2], 0.f), fmaxf(v[3], 0.f));
+            o.z = pack_bf16(fmaxf(v[4], 0.f), fmaxf(v[5], 0.f)); o.w = pack_bf16(fmaxf(v[6], 0.f), fmaxf(v[7], 0.f));
+            *reinterpret_cast<uint4*>(p.out_relu + obase + g8 * 8) = o;
+          }
+        }
+      }
+      if (p.head_w && valid && c_end > c_begin) {
+        reinterpret_cast<float*>(p.out)[orow] = fmaxf(head_acc + p.head_b, 0.f);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[as]);
+      if (++as == 2) {
+        as = 0;
+        aphase ^= 1;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, C::kTmemCols);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+static bool make_map(CUtensorMap* map, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                     const uint32_t* box) {
+  auto fn = get_tensor_map_encoder();
+  if (!fn) return false;
+  uint32_t estr[5] = {1, 1, 1, 1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), dims, strides_bytes, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed with CUresult %d (rank %d, dims %llu %llu, box %u %u)", (int)r, rank,
+              (unsigned long long)dims[0], (unsigned long long)dims[1], box[0], box[1]);
+    return false;
+  }
+  return true;
+}
+
+// pick the (bw, bh) spatial box with bw*bh <= 128 that wastes the fewest accumulator rows
+static void pick_conv_box(int H, int W, int* bw_out, int* bh_out) {
+  double best = -1;
+  int bbw = 1, bbh = 1;
+  for (int bw = 1; bw <= 128 && bw <= W; ++bw) {
+    int bh = 128 / bw;
+    if (bh > H) bh = H;
+    if (bh < 1) continue;
+    const long long tiles = (long long)((W + bw - 1) / bw) * ((H + bh - 1) / bh);
+    const double eff = (double)H * W / (double)(tiles * 128);
+    if (eff > best + 1e-9) {
+      best = eff;
+      bbw = bw;
+      bbh = bh;
+    }
+  }
+  *bw_out = bbw;
+  *bh_out = bbh;
+}
+
+template <int BN>
+static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
+  using C = Cfg<BN>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(gemm)");
+    attr_set = true;
+  }
+  const int tiles = p.m_tiles * p.n_tiles;
+  const int grid = tiles < num_sms() ? tiles : num_sms();
+  gemm_kernel<BN><<<grid, kThreads, C::kSmemBytes, st>>>(ta, tb, p);
+  count_launch();
+  return cuda_check_launch("gemm_kernel");
+}
+
+}  // namespace deb
+
+extern "C" int de_gemm(const DeGemm* g, void* stream) {
+  using namespace deb;
+  if (!g || !g->a || !g->w || !g->out) return fail(DE_ERR_INVALID, "de_gemm: null pointer");
+  if (g->N % 8 != 0) return fail(DE_ERR_INVALID, "de_gemm: N=%d must be a multiple of 8", g->N);
+  GemmParams p{};
+  p.a_mode = g->a_mode;
+  p.N = g->N;
+  int bn = g->block_n;
+  if (bn == 0) bn = g->N >= 256 ? 256 : (g->N > 64 ? 128 : (g->N > 32 ? 64 : 32));
+  if (g->head_w && (g->N != 32 || bn != 32)) return fail(DE_ERR_INVALID, "de_gemm: head_w needs N == 32");
+  if (g->out_rowmode == 2 && (g->ps_cout % 32 != 0)) return fail(DE_ERR_INVALID, "de_gemm: ps_cout %% 32 != 0");
+  CUtensorMap ta, tb;
+  int64_t ktot;
+  if (g->a_mode == 0) {
+    if (g->K % 8 != 0 || g->lda % 8 != 0) return fail(DE_ERR_INVALID, "de_gemm: K and lda must be multiples of 8");
+    p.M = g->M;
+    p.m_tiles = (g->M + BM - 1) / BM;
+    p.num_k_blocks = (g->K + BK - 1) / BK;
+    ktot = g->K;
+    const uint64_t dims[2] = {(uint64_t)g->K, (uint64_t)g->M};
+    const uint64_t strides[1] = {(uint64_t)g->lda * 2};
+    const uint32_t box[2] = {BK, BM};
+    if (!make_map(&ta, g->a, 2, dims, strides, box)) return DE_ERR_CUDA;
+  } else if (g->a_mode == 1) {
+    if (g->Cin % 8 != 0) return fail(DE_ERR_INVALID, "de_gemm: Cin must be a multiple of 8");
+    p.H = g->H;
+    p.W = g->W;
+    pick_conv_box(g->H, g->W, &p.bw, &p.bh);
+    p.tiles_x = (g->W + p.bw - 1) / p.bw;
+    p.tiles_y = (g->H + p.bh - 1) / p.bh;
+    p.m_tiles = g->B * p.tiles_x * p.tiles_y;
+    p.cin_blocks = (g->Cin + BK - 1) / BK;
+    p.num_k_blocks = 9 * p.cin_blocks;
+    p.M = g->B * g->H * g->W;
+    ktot = (int64_t)9 * p.cin_blocks * BK;
+    const uint64_t dims[4] = {(uint64_t)g->Cin, (uint64_t)g->W, (uint64_t)g->H, (uint64_t)g->B};
+    const uint64_t strides[3] = {(uint64_t)g->Cin * 2, (uint64_t)g->W * g->Cin * 2, (uint64_t)g->H * g->W * g->Cin * 2};
+    const uint32_t box[4] = {BK, (uint32_t)p.bw, (uint32_t)p.bh, 1};
+    if (!make_map(&ta, g->a, 4, dims, strides, box)) return DE_ERR_CUDA;
+  } else {
+    return fail(DE_ERR_INVALID, "de_gemm: bad a_mode %d", g->a_mode);
+  }
+  if (g->ldw % 8 != 0 || g->ldw < ktot) return fail(DE_ERR_INVALID, "de_gemm: ldw=%lld too small / unaligned for K=%lld", (long long)g->ldw, (long long)ktot);
+  {
+    const uint64_t dims[2] = {(uint64_t)ktot, (uint64_t)g->N};
+    const uint64_t strides[1] = {(uint64_t)g->ldw * 2};
+    const uint32_t box[2] = {BK, (uint32_t)bn};
+    if (!make_map(&tb, g->w, 2, dims, strides, box)) return DE_ERR_CUDA;
+  }
+  p.n_tiles = (g->N + bn - 1) / bn;
+  p.bias = g->bias;
+  p.bias_mod = g->bias_mod;
+  p.act = g->act;
+  p.add1 = g->add1;
+  p.add1_dtype = g->add1_dtype;
+  p.add1_rowmode = g->add1_rowmode;
+  p.add1_pre = g->add1_pre;
+  p.ld_add1 = g->ld_add1;
+  p.add2 = reinterpret_cast<const __nv_bfloat16*>(g->add2);
+  p.out = g->out;
+  p.out_dtype = g->out_dtype;
+  p.ldo = g->ldo;
+  p.out_relu = reinterpret_cast<__nv_bfloat16*>(g->out_relu);
+  p.out_rowmode = g->out_rowmode;
+  p.grp = g->grp > 0 ? g->grp : 1;
+  p.pad = g->pad;
+  p.off = g->off;
+  p.ps_gh = g->ps_gh; p.ps_gw = g->ps_gw; p.ps_s = g->ps_s; p.ps_cout = g->ps_cout > 0 ? g->ps_cout : 1;
+  p.head_w = g->head_w;
+  p.head_b = g->head_b;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  switch (bn) {
+    case 256: return launch<256>(ta, tb, p, st);
+    case 128: return launch<128>(ta, tb, p, st);
+    case 64: return launch<64>(ta, tb, p, st);
+    case 32: return launch<32>(ta, tb, p, st);
+  }
+  return fail(DE_ERR_INVALID, "de_gemm: block_n %d not in {32,64,128,256}", bn);
+}

@@ -1,0 +1,189 @@
+// K8 - fused output stage (replaces /root/reference/depth_midas.py:28-33 and the metric tail of
+// /root/reference/face.py:106-108,137):
+//   prediction [B,h,w] -> bicubic (Keys A=-0.75, align_corners=False, ATen fp32 coordinate rule) to the
+//   source resolution [B,H,W] fp32, optionally also the bf16 "metric" map D*metric_scale (=D/2.54) and
+//   the interpolated values at a few (row,col) sample points (the iris centres).
+// One CTA per output tile: source window staged in smem, horizontal pass, vertical pass, 16-byte stores.
+#include "common.cuh"
+#include "depth_b200.h"
+#include "host_util.h"
+#include "resample_plan.h"
+
+namespace deb {
+
+struct PostParams {
+  const void* src;
+  int in_dtype;
+  int h, w, H, W;
+  const int32_t* xidx;
+  const float* xw;
+  const int32_t* yidx;
+  const float* yw;
+  float* out_map;
+  __nv_bfloat16* out_metric;
+  float metric_scale;
+  int TW, TH, max_rows, max_cols;
+};
+
+constexpr int kPostThreads = 256;
+
+DEV float load_pred(const void* src, int in_dtype, long long i) {
+  if (in_dtype == DE_DTYPE_F32) return __ldg(reinterpret_cast<const float*>(src) + i);
+  return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(src)[i]);
+}
+// fixed evaluation order so the tile kernel and the sample kernel agree bit for bit
+DEV float dot4(float a, float b, float c, float d, float4 w) {
+  float acc = a * w.x;
+  acc = fmaf(b, w.y, acc);
+  acc = fmaf(c, w.z, acc);
+  acc = fmaf(d, w.w, acc);
+  return acc;
+}
+
+__global__ void __launch_bounds__(kPostThreads) postprocess_kernel(const PostParams p) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  float* s_src = reinterpret_cast<float*>(smem);        // [max_rows][max_cols]
+  float* s_h = s_src + p.max_rows * p.max_cols;         // [max_rows][TW]
+  const int tid = threadIdx.x;
+  const int b = blockIdx.z;
+  const int ox0 = blockIdx.x * p.TW, oy0 = blockIdx.y * p.TH;
+  const int ncols = min(p.TW, p.W - ox0), nrows = min(p.TH, p.H - oy0);
+  const int xs = __ldg(p.xidx + ox0 * 4), xe = __ldg(p.xidx + (ox0 + ncols - 1) * 4 + 3);
+  const int ys = __ldg(p.yidx + oy0 * 4), ye = __ldg(p.yidx + (oy0 + nrows - 1) * 4 + 3);
+  const int nr = ye - ys + 1, nc = xe - xs + 1;
+  const long long fbase = (long long)b * p.h * p.w;
+
+  for (int i = tid; i < nr * nc; i += kPostThreads) {
+    const int rr = i / nc, cc = i % nc;
+    s_src[rr * p.max_cols + cc] = load_pred(p.src, p.in_dtype, fbase + (long long)(ys + rr) * p.w + xs + cc);
+  }
+  __syncthreads();
+  for (int i = tid; i < nr * ncols; i += kPostThreads) {
+    const int rr = i / ncols, c = i % ncols;
+    const int4 xi = __ldg(reinterpret_cast<const int4*>(p.xidx) + ox0 + c);
+    const float4 w = __ldg(reinterpret_cast<const float4*>(p.xw) + ox0 + c);
+    const float* row = s_src + rr * p.max_cols - xs;
+    s_h[rr * p.TW + c] = dot4(row[xi.x], row[xi.y], row[xi.z], row[xi.w], w);
+  }
+  __syncthreads();
+  // vertical pass: 4 adjacent columns per thread when the tile is 4-aligned
+  const int quads = (ncols + 3) >> 2;
+  for (int i = tid; i < nrows * quads; i += kPostThreads) {
+    const int cq = i % quads, ry = i / quads;
+    const int oy = oy0 + ry;
+    const int4 yi = __ldg(reinterpret_cast<const int4*>(p.yidx) + oy);
+    const float4 w = __ldg(reinterpret_cast<const float4*>(p.yw) + oy);
+    const float* r0 = s_h + (yi.x - ys) * p.TW;
+    const float* r1 = s_h + (yi.y - ys) * p.TW;
+    const float* r2 = s_h + (yi.z - ys) * p.TW;
+    const float* r3 = s_h + (yi.w - ys) * p.TW;
+    float v[4];
+    const int c0 = cq * 4;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int c = min(c0 + e, ncols - 1);
+      v[e] = dot4(r0[c], r1[c], r2[c], r3[c], w);
+    }
+    const long long o = ((long long)b * p.H + oy) * p.W + ox0 + c0;
+    const bool full = (c0 + 4 <= ncols) && ((o & 3) == 0);
+    if (p.out_map) {
+      if (full) {
+        *reinterpret_cast<float4*>(p.out_map + o) = make_float4(v[0], v[1], v[2], v[3]);
+      } else {
+        for (int e = 0; e < 4 && c0 + e < ncols; ++e) p.out_map[o + e] = v[e];
+      }
+    }
+    if (p.out_metric) {
+      if (full) {
+        uint2 m;
+        m.x = pack_bf16(v[0] * p.metric_scale, v[1] * p.metric_scale);
+        m.y = pack_bf16(v[2] * p.metric_scale, v[3] * p.metric_scale);
+        *reinterpret_cast<uint2*>(p.out_metric + o) = m;
+      } else {
+        for (int e = 0; e < 4 && c0 + e < ncols; ++e) p.out_metric[o + e] = __float2bfloat16(v[e] * p.metric_scale);
+      }
+    }
+  }
+}
+
+// out_samples[b, s] = interpolated value at output pixel (row, col) = sample_rc[b, s, :]
+__global__ void sample_kernel(const PostParams p, int B, const int32_t* sample_rc, int n_samples, float* out_samples) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * n_samples) return;
+  const int b = i / n_samples;
+  int row = sample_rc[i * 2], col = sample_rc[i * 2 + 1];
+  row = min(max(row, 0), p.H - 1);
+  col = min(max(col, 0), p.W - 1);
+  const int4 xi = __ldg(reinterpret_cast<const int4*>(p.xidx) + col);
+  const float4 wx = __ldg(reinterpret_cast<const float4*>(p.xw) + col);
+  const int4 yi = __ldg(reinterpret_cast<const int4*>(p.yidx) + row);
+  const float4 wy = __ldg(reinterpret_cast<const float4*>(p.yw) + row);
+  const long long fbase = (long long)b * p.h * p.w;
+  const int ys[4] = {yi.x, yi.y, yi.z, yi.w};
+  float hrow[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const long long rb = fbase + (long long)ys[k] * p.w;
+    hrow[k] = dot4(load_pred(p.src, p.in_dtype, rb + xi.x), load_pred(p.src, p.in_dtype, rb + xi.y),
+                   load_pred(p.src, p.in_dtype, rb + xi.z), load_pred(p.src, p.in_dtype, rb + xi.w), wx);
+  }
+  out_samples[i] = dot4(hrow[0], hrow[1], hrow[2], hrow[3], wy);
+}
+
+}  // namespace deb
+
+extern "C" int de_postprocess(const void* pred, int in_dtype, int B, int h, int w, int H, int W, float* out_map,
+                              void* out_metric, float metric_scale, const int32_t* sample_rc, int n_samples,
+                              float* out_samples, void* stream) {
+  using namespace deb;
+  if (!pred || B <= 0 || h <= 0 || w <= 0 || H <= 0 || W <= 0) return fail(DE_ERR_INVALID, "de_postprocess: bad args");
+  if (in_dtype != DE_DTYPE_F32 && in_dtype != DE_DTYPE_BF16) return fail(DE_ERR_INVALID, "de_postprocess: in_dtype");
+  const AxisTaps* tx = get_axis_taps(w, W, 1);
+  const AxisTaps* ty = get_axis_taps(h, H, 1);
+  if (!tx || !ty) return DE_ERR_CUDA;
+  PostParams p{};
+  p.src = pred; p.in_dtype = in_dtype;
+  p.h = h; p.w = w; p.H = H; p.W = W;
+  p.xidx = tx->d_idx; p.xw = tx->d_w; p.yidx = ty->d_idx; p.yw = ty->d_w;
+  p.out_map = out_map;
+  p.out_metric = reinterpret_cast<__nv_bfloat16*>(out_metric);
+  p.metric_scale = metric_scale;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (out_map || out_metric) {
+    static const int cand[][2] = {{128, 16}, {128, 8}, {64, 8}, {32, 8}, {32, 4}, {16, 2}, {4, 1}};
+    size_t smem = 0;
+    bool ok = false;
+    for (auto& c : cand) {
+      p.TW = c[0];
+      p.TH = c[1];
+      p.max_cols = tx->max_extent(p.TW);
+      p.max_rows = ty->max_extent(p.TH);
+      smem = sizeof(float) * ((size_t)p.max_rows * p.max_cols + (size_t)p.max_rows * p.TW);
+      if (smem <= 200 * 1024) {
+        ok = true;
+        break;
+      }
+    }
+    if (!ok) return fail(DE_ERR_UNSUPPORTED, "de_postprocess: resampling window too large");
+    if (smem > 48 * 1024) {
+      static bool configured = false;
+      if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(postprocess_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(postprocess)");
+        configured = true;
+      }
+    }
+    dim3 grid((W + p.TW - 1) / p.TW, (H + p.TH - 1) / p.TH, B);
+    postprocess_kernel<<<grid, kPostThreads, smem, st>>>(p);
+    count_launch();
+    int rc = cuda_check_launch("postprocess_kernel");
+    if (rc != DE_OK) return rc;
+  }
+  if (sample_rc && n_samples > 0 && out_samples) {
+    const int n = B * n_samples;
+    sample_kernel<<<(n + 127) / 128, 128, 0, st>>>(p, B, sample_rc, n_samples, out_samples);
+    count_launch();
+    return cuda_check_launch("sample_kernel");
+  }
+  return DE_OK;
+}

@@ -1,0 +1,205 @@
+"""Thin torch-tensor front-ends over the C ABI (include/depth_b200.h).  torch supplies device memory
+and the current stream only; every op below is one call into libdepthb200.so and raises on failure."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import ACT_GELU, ACT_NONE, ACT_RELU, ACT_RELU6, DE_DTYPE_BF16, DE_DTYPE_F32, DeGemm  # noqa: F401
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def _dt(t) -> int:
+    if t.dtype == torch.bfloat16:
+        return DE_DTYPE_BF16
+    if t.dtype == torch.float32:
+        return DE_DTYPE_F32
+    raise TypeError(f"unsupported dtype {t.dtype}")
+
+
+def _need_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("depth_estimation_b200 ops run on CUDA tensors only (no CPU fallback)")
+
+
+# ------------------------------------------------------------------------------- host helpers
+def get_size(width: int, height: int, model_type: str):
+    """(net_w, net_h) the reference transform would resize to (depth_midas.py:13-16,23)."""
+    dpt = model_type in ("DPT_Large", "DPT_Hybrid")
+    w, h = C.c_int(), C.c_int()
+    _lib.check(_lib.load().de_get_size(width, height, 384 if dpt else 256, 1 if dpt else 0, C.byref(w), C.byref(h)),
+               "de_get_size")
+    return w.value, h.value
+
+
+def cubic_taps(src: int, dst: int, mode: int):
+    idx = np.empty((dst, 4), dtype=np.int32)
+    w = np.empty((dst, 4), dtype=np.float32)
+    _lib.check(_lib.load().de_cubic_taps(src, dst, mode, idx.ctypes.data, w.ctypes.data), "de_cubic_taps")
+    return idx, w
+
+
+# ------------------------------------------------------------------------------- K1 / K8
+LAYOUT_NCHW_BF16, LAYOUT_PATCH16_BF16, LAYOUT_NCHW_F32 = 0, 1, 2
+
+
+def preprocess(frames_u8: torch.Tensor, net_h: int, net_w: int, mean, std, layout: int = LAYOUT_NCHW_BF16,
+               out: torch.Tensor | None = None) -> torch.Tensor:
+    """frames_u8: uint8 [B,H,W,3] BGR on the GPU (contiguous rows)."""
+    _need_cuda(frames_u8)
+    assert frames_u8.dtype == torch.uint8 and frames_u8.dim() == 4 and frames_u8.shape[3] == 3
+    assert frames_u8.stride(3) == 1 and frames_u8.stride(2) == 3
+    B, H, W, _ = frames_u8.shape
+    if out is None:
+        if layout == LAYOUT_NCHW_BF16:
+            out = torch.empty((B, 3, net_h, net_w), dtype=torch.bfloat16, device=frames_u8.device)
+        elif layout == LAYOUT_PATCH16_BF16:
+            out = torch.empty((B * (net_h // 16) * (net_w // 16), 768), dtype=torch.bfloat16, device=frames_u8.device)
+        else:
+            out = torch.empty((B, 3, net_h, net_w), dtype=torch.float32, device=frames_u8.device)
+    m = (C.c_float * 3)(*[float(v) for v in mean])
+    s = (C.c_float * 3)(*[float(v) for v in std])
+    _lib.check(_lib.load().de_preprocess(frames_u8.data_ptr(), B, H, W, frames_u8.stride(1), frames_u8.stride(0),
+                                         net_h, net_w, m, s, layout, out.data_ptr(), _stream()), "de_preprocess")
+    return out
+
+
+def postprocess(pred: torch.Tensor, H: int, W: int, want_map: bool = True, want_metric: bool = False,
+                metric_scale: float = 1.0 / 2.54, sample_rc: torch.Tensor | None = None,
+                out_map: torch.Tensor | None = None, out_metric: torch.Tensor | None = None):
+    """pred: [B,h,w] f32/bf16.  Returns (map f32 [B,H,W] | None, metric bf16 | None, samples f32 [B,S] | None)."""
+    _need_cuda(pred, sample_rc)
+    assert pred.dim() == 3 and pred.is_contiguous()
+    B, h, w = pred.shape
+    if want_map and out_map is None:
+        out_map = torch.empty((B, H, W), dtype=torch.float32, device=pred.device)
+    if want_metric and out_metric is None:
+        out_metric = torch.empty((B, H, W), dtype=torch.bfloat16, device=pred.device)
+    samples, ns = None, 0
+    if sample_rc is not None:
+        assert sample_rc.dtype == torch.int32 and sample_rc.is_contiguous() and sample_rc.shape[0] == B
+        ns = sample_rc.shape[1]
+        samples = torch.empty((B, ns), dtype=torch.float32, device=pred.device)
+    _lib.check(_lib.load().de_postprocess(pred.data_ptr(), _dt(pred), B, h, w, H, W, _ptr(out_map), _ptr(out_metric),
+                                          float(metric_scale), _ptr(sample_rc), ns, _ptr(samples), _stream()),
+               "de_postprocess")
+    return out_map, out_metric, samples
+
+
+# ------------------------------------------------------------------------------- GEMM / conv
+def gemm(a: torch.Tensor, w: torch.Tensor, out: torch.Tensor, *, M=None, N=None, K=None, bias=None, act=ACT_NONE,
+         add1=None, add1_rowmode=0, add1_pre=False, ld_add1=None, add2=None, out_relu=None, out_rowmode=0, grp=0,
+         pad=0, off=0, ldo=None, conv=None, pixel_shuffle=None, bias_mod=0, head=None, block_n=0):
+    """out = epilogue(a @ w.T) through de_gemm.  a: bf16 [M,K] (or NHWC [B,H,W,Cin] with conv=(B,H,W,Cin));
+    w: bf16 [N,K].  See include/depth_b200.h for the epilogue contract."""
+    _need_cuda(a, w, out, bias, add1, add2, out_relu)
+    assert a.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and w.dim() == 2 and w.stride(1) == 1
+    g = DeGemm()
+    g.a = a.data_ptr()
+    g.w = w.data_ptr()
+    g.ldw = w.stride(0)
+    g.N = int(N if N is not None else w.shape[0])
+    if conv is not None:
+        g.a_mode = 1
+        g.B, g.H, g.W, g.Cin = [int(v) for v in conv]
+        assert a.is_contiguous()
+    else:
+        g.a_mode = 0
+        assert a.dim() == 2 and a.stride(1) == 1
+        g.M = int(M if M is not None else a.shape[0])
+        g.K = int(K if K is not None else a.shape[1])
+        g.lda = a.stride(0)
+    if bias is not None:
+        assert bias.dtype == torch.float32
+        g.bias = bias.data_ptr()
+    g.bias_mod = int(bias_mod)
+    g.act = int(act)
+    if add1 is not None:
+        g.add1 = add1.data_ptr()
+        g.add1_dtype = _dt(add1)
+        g.ld_add1 = int(ld_add1 if ld_add1 is not None else add1.stride(-2))
+        g.add1_rowmode = int(add1_rowmode)
+        g.add1_pre = 1 if add1_pre else 0
+    if add2 is not None:
+        assert add2.dtype == torch.bfloat16
+        g.add2 = add2.data_ptr()
+    g.out = out.data_ptr()
+    g.out_dtype = _dt(out)
+    g.ldo = int(ldo if ldo is not None else (out.stride(-2) if out.dim() >= 2 else 1))
+    if out_relu is not None:
+        assert out_relu.dtype == torch.bfloat16
+        g.out_relu = out_relu.data_ptr()
+    g.out_rowmode = int(out_rowmode)
+    g.grp, g.pad, g.off = int(grp), int(pad), int(off)
+    if pixel_shuffle is not None:
+        g.out_rowmode = 2
+        g.ps_gh, g.ps_gw, g.ps_s, g.ps_cout = [int(v) for v in pixel_shuffle]
+    if head is not None:
+        hw, hb = head
+        assert hw.dtype == torch.float32 and out.dtype == torch.float32
+        g.head_w = hw.data_ptr()
+        g.head_b = float(hb)
+    g.block_n = int(block_n)
+    _lib.check(_lib.load().de_gemm(C.byref(g), _stream()), "de_gemm")
+    return out
+
+
+def layernorm(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float, out: torch.Tensor):
+    _need_cuda(x, gamma, beta, out)
+    assert x.dtype == torch.float32 and out.dtype == torch.bfloat16 and x.dim() == 2
+    _lib.check(_lib.load().de_layernorm(x.data_ptr(), x.stride(0), gamma.data_ptr(), beta.data_ptr(), x.shape[0],
+                                        x.shape[1], float(eps), out.data_ptr(), out.stride(0), _stream()),
+               "de_layernorm")
+    return out
+
+
+def attention(qkv: torch.Tensor, out: torch.Tensor, B: int, T: int, heads: int, scale: float):
+    _need_cuda(qkv, out)
+    assert qkv.dtype == torch.bfloat16 and out.dtype == torch.bfloat16 and qkv.is_contiguous() and out.is_contiguous()
+    _lib.check(_lib.load().de_attention(qkv.data_ptr(), out.data_ptr(), B, T, heads, float(scale), _stream()),
+               "de_attention")
+    return out
+
+
+def cast_tokens(x: torch.Tensor, out: torch.Tensor, grp: int = 0, skip: int = 0):
+    _need_cuda(x, out)
+    assert x.dtype == torch.float32 and out.dtype == torch.bfloat16 and x.dim() == 2 and out.is_contiguous()
+    _lib.check(_lib.load().de_cast_tokens(x.data_ptr(), x.stride(0), x.shape[0], x.shape[1], grp, skip,
+                                          out.data_ptr(), _stream()), "de_cast_tokens")
+    return out
+
+
+def fill_cls(x: torch.Tensor, B: int, T: int, cls: torch.Tensor, pos: torch.Tensor):
+    _need_cuda(x, cls, pos)
+    _lib.check(_lib.load().de_fill_cls(x.data_ptr(), x.stride(0), B, T, x.shape[1], cls.data_ptr(), pos.data_ptr(),
+                                       _stream()), "de_fill_cls")
+    return x
+
+
+def upsample2x(x: torch.Tensor, out: torch.Tensor, align_corners: bool):
+    """x: bf16 NHWC [B,H,W,C] -> out [B,2H,2W,C]."""
+    _need_cuda(x, out)
+    B, H, W, Cc = x.shape
+    assert x.dtype == torch.bfloat16 and x.is_contiguous() and out.is_contiguous()
+    _lib.check(_lib.load().de_upsample2x(x.data_ptr(), out.data_ptr(), B, H, W, Cc, 1 if align_corners else 0,
+                                         _stream()), "de_upsample2x")
+    return out
+
+
+def im2col3x3(x: torch.Tensor, out: torch.Tensor, stride: int):
+    _need_cuda(x, out)
+    B, H, W, Cc = x.shape
+    assert x.dtype == torch.bfloat16 and x.is_contiguous() and out.is_contiguous()
+    _lib.check(_lib.load().de_im2col3x3(x.data_ptr(), out.data_ptr(), B, H, W, Cc, stride, _stream()), "de_im2col3x3")
+    return out

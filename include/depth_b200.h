@@ -1,0 +1,142 @@
+/* depth_b200.h - C ABI of libdepthb200.so: the B200 (sm_100a) kernels behind the per-frame MiDaS
+ * depth path of juhoward/depth_estimation.
+ *
+ * The reference has no FFI of its own (it is pure Python): the boundary it offers is
+ * the Python class DepthEstimator (/root/reference/depth_midas.py:6-35 == midas.py:6-35).  Every entry
+ * point below replaces one slice of DepthEstimator.predict or of the un-vendored upstream modules it
+ * calls, and is bound with ctypes by depth_estimation_b200/_lib.py.
+ *
+ * Conventions: plain pointers + sizes, no torch types.  All data pointers are DEVICE pointers owned by
+ * the caller unless a parameter says "host".  Work is enqueued on `stream` (a cudaStream_t passed as
+ * void*), never synchronised.  Return value: 0 on success, negative DE_ERR_* otherwise;
+ * de_last_error() returns a thread-local message for the last failure.
+ */
+#ifndef DEPTH_B200_H_
+#define DEPTH_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DE_OK 0
+#define DE_ERR_INVALID (-1)
+#define DE_ERR_CUDA (-2)
+#define DE_ERR_UNSUPPORTED (-3)
+
+#define DE_DTYPE_BF16 0
+#define DE_DTYPE_F32 1
+
+#define DE_ACT_NONE 0
+#define DE_ACT_RELU 1
+#define DE_ACT_GELU 2  /* exact erf GELU (timm nn.GELU) */
+#define DE_ACT_RELU6 3
+
+const char* de_last_error(void);
+int de_version(void);
+/* Number of kernels this library has launched in the calling process (bench.py "gpu_launches"). */
+int64_t de_launch_count(void);
+
+/* ---- get_size: [UPSTREAM] midas/transforms.py Resize.get_size, reached from depth_midas.py:23.
+ * method 0 = "upper_bound" (small_transform, T=256), 1 = "minimal" (dpt_transform, T=384). */
+int de_get_size(int width, int height, int target, int method, int* net_w, int* net_h);
+
+/* ---- cubic tap tables (host): cv2.resize INTER_CUBIC coordinate rule (mode 0; used by the
+ * transform, depth_midas.py:23) or torch F.interpolate bicubic align_corners=False rule (mode 1;
+ * depth_midas.py:28-33).  idx: int32 [dst*4] border-clamped source indices, w: float [dst*4]. */
+int de_cubic_taps(int src, int dst, int mode, int32_t* idx_host, float* w_host);
+
+/* ---- K1: replaces depth_midas.py:22-23 (cvtColor BGR2RGB + upstream transform chain
+ * /255 -> Resize(INTER_CUBIC, multiple of 32) -> NormalizeImage -> PrepareForNet).
+ * bgr: uint8 [B,H,W,3] (row_stride bytes per row, frame_stride bytes per frame).
+ * Tap tables (de_cubic_taps mode 0) are built and cached inside the library per (H,W,net_h,net_w);
+ * the first call for a new shape allocates - warm up before CUDA-graph capture.
+ * mean/std: host float[3] in RGB order.
+ * layout 0: out = bf16 NCHW [B,3,net_h,net_w].
+ * layout 1: out = bf16 patch matrix [B*(net_h/16)*(net_w/16), 768], column = c*256+py*16+px
+ *           (the im2col of the ViT patch-embed conv, feeding de_gemm directly).
+ * layout 2: out = float32 NCHW (parity/debug). */
+int de_preprocess(const uint8_t* bgr, int B, int H, int W, int64_t row_stride, int64_t frame_stride,
+                  int net_h, int net_w, const float* mean_host, const float* std_host, int layout, void* out,
+                  void* stream);
+
+/* ---- K8: replaces depth_midas.py:28-33 (F.interpolate bicubic, align_corners=False, to the source
+ * resolution) fused with the metric tail of face.py:106-108,137 (ri_depth sampling, /2.54).
+ * pred: [B,h,w] (in_dtype bf16 or f32).  Tap tables (mode 1) cached inside the library.
+ * out_map: [B,H,W] f32 (may be NULL).  out_metric: [B,H,W] bf16 = map*metric_scale (may be NULL).
+ * sample_rc: int32 [B,n_samples,2] (row, col) device indices into the OUTPUT map (may be NULL);
+ * out_samples: float [B,n_samples] receives the interpolated value at those points. */
+int de_postprocess(const void* pred, int in_dtype, int B, int h, int w, int H, int W, float* out_map,
+                   void* out_metric, float metric_scale, const int32_t* sample_rc, int n_samples,
+                   float* out_samples, void* stream);
+
+/* ---- tcgen05 GEMM / implicit-GEMM convolution.  D = epilogue(A * Wt^T):
+ *   a_mode 0: A is a bf16 row-major matrix [M,K] (lda elements); K % 8 == 0.
+ *   a_mode 1: A is a bf16 NHWC activation [B,H,W,Cin]; 3x3, stride 1, pad 1 convolution; the weight
+ *             is [N, 9*cin_pad] with k = tap*cin_pad + ci (tap = kh*3+kw, cin_pad = ceil64(Cin)).
+ *   w: bf16 [N,K] row-major (ldw elements) - the torch Linear / flattened-conv layout.
+ * Epilogue, per output element (row m, column n), fp32:
+ *   v = acc + bias[n % bias_mod]; if (add1 && add1_pre) v += add1; v = act(v);
+ *   if (add1 && !add1_pre) v += add1; if (add2) v += add2; store(out); if (out_relu) store(relu(v)).
+ * Row maps (m -> storage row): out_rowmode 0: m; 1: m + (m/grp)*pad + off;
+ *   2: pixel shuffle (ConvTranspose k==s): rows are (b,y,x) on a gh x gw grid, columns are
+ *      (i,j,co); out is NHWC [B,gh*s,gw*s,cout].
+ * add1_rowmode 0: same storage row as out; 1: m / grp (per-group broadcast); 2: (m % grp) + off.
+ * head_w != NULL (requires N == 32): out is float [rows]; out[m] = relu(sum_n v[n]*head_w[n] + head_b). */
+typedef struct DeGemm {
+  int a_mode;
+  const void* a;
+  int64_t lda;
+  int M, N, K;
+  int B, H, W, Cin; /* a_mode 1 */
+  const void* w;
+  int64_t ldw;
+  const float* bias;
+  int bias_mod; /* 0 -> N */
+  int act;
+  const void* add1;
+  int add1_dtype;
+  int64_t ld_add1;
+  int add1_rowmode;
+  int add1_pre;
+  const void* add2; /* bf16, storage row of out, ld = ldo */
+  void* out;
+  int out_dtype;
+  int64_t ldo;
+  void* out_relu; /* bf16, same rows/ld as out */
+  int out_rowmode;
+  int grp, pad, off;
+  int ps_gh, ps_gw, ps_s, ps_cout; /* out_rowmode 2 */
+  const float* head_w;
+  float head_b;
+  int block_n; /* 0 = auto; else 32/64/128/256 */
+} DeGemm;
+int de_gemm(const DeGemm* g, void* stream);
+
+/* ---- LayerNorm over the last dim (eps given), fp32 in -> bf16 out (timm ViT norm1/norm2). */
+int de_layernorm(const float* x, int64_t ldx, const float* gamma, const float* beta, int rows, int dim,
+                 float eps, void* out_bf16, int64_t ldo, void* stream);
+
+/* ---- multi-head self-attention on a packed qkv buffer (timm Attention.forward):
+ * qkv: bf16 [B*T, 3*heads*64] (q | k | v, each heads x 64), out: bf16 [B*T, heads*64].
+ * softmax(q k^T * scale) v, non-causal, fp32 softmax. head_dim must be 64. */
+int de_attention(const void* qkv, void* out, int B, int T, int heads, float scale, void* stream);
+
+/* ---- small bandwidth kernels used between the GEMMs ---- */
+/* fp32 [rows, dim] (ldx) -> bf16 [rows', dim]: drops the first `skip` rows of every group of `grp`
+ * rows (cls token removal for the reassemble readout).  grp=0: plain cast. */
+int de_cast_tokens(const float* x, int64_t ldx, int rows, int dim, int grp, int skip, void* out_bf16,
+                   void* stream);
+/* x[b*T + 0, :] = cls[:] + pos[0, :] (fp32 token stream) */
+int de_fill_cls(float* x, int64_t ldx, int B, int T, int dim, const float* cls, const float* pos,
+                void* stream);
+/* bilinear x2 upsample NHWC bf16 [B,H,W,C] -> [B,2H,2W,C]; align_corners 1/0. */
+int de_upsample2x(const void* x, void* out, int B, int H, int W, int C, int align_corners, void* stream);
+/* im2col for 3x3 stride-s pad-1 (s=2 used by act_postprocess4) NHWC bf16 -> [B*Ho*Wo, 9*C]. */
+int de_im2col3x3(const void* x, void* out, int B, int H, int W, int C, int stride, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DEPTH_B200_H_ */

@@ -1,0 +1,319 @@
+"""GPU parity tests for the individual sm_100a kernels, called through the C ABI (ops.py -> ctypes).
+The checker is torch fp32 on the same (bf16-rounded) inputs, or the CPU oracle for K1/K8."""
+import math
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev():
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    return torch.device("cuda:0")
+
+
+def _rand(shape, dev, scale=1.0, seed=0):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    return (torch.randn(shape, generator=g) * scale).to(dev)
+
+
+def _relerr(a, b):
+    a, b = a.float(), b.float()
+    return ((a - b).abs().max() / (b.abs().max() + 1e-12)).item()
+
+
+# ------------------------------------------------------------------------------------ GEMM
+GEMM_CASES = [
+    # M, N, K, block_n
+    (128, 256, 64, 0),
+    (577, 1024, 1024, 0),
+    (577, 3072, 1024, 256),
+    (1000, 128, 192, 128),
+    (300, 96, 144, 0),
+    (4617, 64, 256, 64),
+    (50, 32, 64, 32),
+    (18464, 1024, 1024, 128),
+    (2308, 24, 144, 0),
+]
+
+
+@pytest.mark.parametrize("M,N,K,bn", GEMM_CASES)
+def test_gemm_plain(M, N, K, bn):
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    a = _rand((M, K), dev, seed=1).bfloat16()
+    w = _rand((N, K), dev, 0.05, seed=2).bfloat16()
+    out = torch.full((M, N), float("nan"), dtype=torch.float32, device=dev)
+    ops.gemm(a, w, out, block_n=bn)
+    torch.cuda.synchronize()
+    ref = a.float() @ w.float().t()
+    assert torch.isfinite(out).all()
+    assert _relerr(out, ref) < 2e-5, _relerr(out, ref)
+
+
+@pytest.mark.parametrize("act", [0, 1, 2, 3])
+def test_gemm_epilogue_bias_act_residual(act):
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    M, N, K = 700, 512, 320
+    a = _rand((M, K), dev, seed=3).bfloat16()
+    w = _rand((N, K), dev, 0.08, seed=4).bfloat16()
+    bias = _rand((N,), dev, seed=5)
+    res = _rand((M, N), dev, seed=6)
+    out = torch.empty((M, N), dtype=torch.float32, device=dev)
+    ops.gemm(a, w, out, bias=bias, act=act, add1=res)
+    v = a.float() @ w.float().t() + bias
+    v = {0: lambda t: t, 1: F.relu, 2: F.gelu, 3: F.relu6}[act](v) + res
+    torch.cuda.synchronize()
+    assert _relerr(out, v) < 2e-5
+    # bf16 output + pre-activation addend + relu copy
+    outb = torch.empty((M, N), dtype=torch.bfloat16, device=dev)
+    outr = torch.empty((M, N), dtype=torch.bfloat16, device=dev)
+    resb = res.bfloat16()
+    ops.gemm(a, w, outb, bias=bias, act=act, add1=resb, add1_pre=True, out_relu=outr)
+    v2 = {0: lambda t: t, 1: F.relu, 2: F.gelu, 3: F.relu6}[act](a.float() @ w.float().t() + bias + resb.float())
+    torch.cuda.synchronize()
+    assert _relerr(outb, v2) < 6e-3
+    assert torch.equal(outr, F.relu(outb.float()).bfloat16())
+
+
+def test_gemm_row_maps_tokens():
+    """patch-embed style: rows m=(b,p) -> b*(N+1)+1+p, addend = pos[1+p] broadcast over b."""
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    B, Np, D, K = 3, 36, 256, 768
+    a = _rand((B * Np, K), dev, seed=7).bfloat16()
+    w = _rand((D, K), dev, 0.05, seed=8).bfloat16()
+    bias = _rand((D,), dev, seed=9)
+    pos = _rand((Np + 1, D), dev, seed=10)
+    x = torch.zeros((B * (Np + 1), D), dtype=torch.float32, device=dev)
+    ops.gemm(a, w, x, bias=bias, add1=pos, add1_rowmode=2, out_rowmode=1, grp=Np, pad=1, off=1)
+    ref = (a.float() @ w.float().t() + bias).view(B, Np, D) + pos[1:][None]
+    torch.cuda.synchronize()
+    xv = x.view(B, Np + 1, D)
+    assert _relerr(xv[:, 1:], ref) < 2e-5
+    assert (xv[:, 0] == 0).all()
+    # per-group broadcast addend before the activation (readout: W_cls x_cls + b)
+    cb = _rand((B, D), dev, seed=11)
+    o = torch.empty((B * Np, D), dtype=torch.bfloat16, device=dev)
+    ops.gemm(a, w, o, act=2, add1=cb, add1_rowmode=1, add1_pre=True, grp=Np)
+    ref2 = F.gelu((a.float() @ w.float().t()).view(B, Np, D) + cb[:, None]).view(B * Np, D)
+    torch.cuda.synchronize()
+    assert _relerr(o, ref2) < 6e-3
+
+
+CONV_CASES = [
+    # B, H, W, Cin, Cout
+    (2, 12, 12, 256, 256),
+    (1, 24, 24, 1024, 256),
+    (2, 48, 48, 512, 256),
+    (1, 96, 96, 256, 256),
+    (1, 24, 42, 256, 256),
+    (1, 21, 12, 64, 128),
+    (2, 32, 40, 48, 64),
+    (1, 16, 16, 136, 256),
+    (1, 64, 64, 128, 32),
+]
+
+
+@pytest.mark.parametrize("B,H,W,Cin,Cout", CONV_CASES)
+def test_conv3x3_implicit_gemm(B, H, W, Cin, Cout):
+    from depth_estimation_b200 import ops
+    from depth_estimation_b200.weights import pack_conv3x3
+    dev = _dev()
+    x = _rand((B, Cin, H, W), dev, seed=12).bfloat16()
+    wt = _rand((Cout, Cin, 3, 3), dev, 0.05, seed=13).bfloat16()
+    bias = _rand((Cout,), dev, seed=14)
+    x_nhwc = x.permute(0, 2, 3, 1).contiguous()
+    wp = pack_conv3x3(wt)
+    out = torch.full((B, H, W, Cout), float("nan"), dtype=torch.float32, device=dev)
+    ops.gemm(x_nhwc, wp, out.view(-1, Cout), conv=(B, H, W, Cin), bias=bias, N=Cout)
+    ref = F.conv2d(x.float(), wt.float(), bias, padding=1).permute(0, 2, 3, 1)
+    torch.cuda.synchronize()
+    assert torch.isfinite(out).all()
+    assert _relerr(out, ref) < 2e-5, _relerr(out, ref)
+
+
+def test_conv3x3_rcu_epilogue():
+    """RCU tail: conv2(..)+bias + x + path, with raw and relu'd copies stored."""
+    from depth_estimation_b200 import ops
+    from depth_estimation_b200.weights import pack_conv3x3
+    dev = _dev()
+    B, H, W, Cc = 2, 24, 24, 256
+    x = _rand((B, H, W, Cc), dev, seed=15).bfloat16()
+    skip = _rand((B, H, W, Cc), dev, seed=16).bfloat16()
+    path = _rand((B, H, W, Cc), dev, seed=17).bfloat16()
+    wt = _rand((Cc, Cc, 3, 3), dev, 0.03, seed=18).bfloat16()
+    bias = _rand((Cc,), dev, seed=19)
+    out = torch.empty((B, H, W, Cc), dtype=torch.bfloat16, device=dev)
+    outr = torch.empty_like(out)
+    ops.gemm(x, pack_conv3x3(wt), out.view(-1, Cc), conv=(B, H, W, Cc), bias=bias, add1=skip.view(-1, Cc),
+             add2=path, out_relu=outr)
+    ref = F.conv2d(x.float().permute(0, 3, 1, 2), wt.float(), bias, padding=1).permute(0, 2, 3, 1) + skip.float() + path.float()
+    torch.cuda.synchronize()
+    assert _relerr(out, ref) < 6e-3
+    assert torch.equal(outr, F.relu(out.float()).bfloat16())
+
+
+@pytest.mark.parametrize("s,Cc", [(4, 256), (2, 512)])
+def test_conv_transpose_pixel_shuffle(s, Cc):
+    from depth_estimation_b200 import ops
+    from depth_estimation_b200.weights import pack_conv_transpose
+    dev = _dev()
+    B, gh, gw = 2, 6, 7
+    x = _rand((B, Cc, gh, gw), dev, seed=20).bfloat16()
+    wt = _rand((Cc, Cc, s, s), dev, 0.05, seed=21).bfloat16()     # [Cin, Cout, kh, kw]
+    bias = _rand((Cc,), dev, seed=22)
+    a = x.permute(0, 2, 3, 1).reshape(B * gh * gw, Cc).contiguous()
+    out = torch.full((B, gh * s, gw * s, Cc), float("nan"), dtype=torch.float32, device=dev)
+    ops.gemm(a, pack_conv_transpose(wt), out, bias=bias, bias_mod=Cc, pixel_shuffle=(gh, gw, s, Cc))
+    ref = F.conv_transpose2d(x.float(), wt.float(), bias, stride=s).permute(0, 2, 3, 1)
+    torch.cuda.synchronize()
+    assert torch.isfinite(out).all()
+    assert _relerr(out, ref) < 2e-5
+
+
+def test_head_dot():
+    from depth_estimation_b200 import ops
+    from depth_estimation_b200.weights import pack_conv3x3
+    dev = _dev()
+    B, H, W, Cin = 1, 64, 96, 128
+    x = _rand((B, H, W, Cin), dev, seed=23).bfloat16()
+    wt = _rand((32, Cin, 3, 3), dev, 0.05, seed=24).bfloat16()
+    bias = _rand((32,), dev, seed=25)
+    w2 = _rand((32,), dev, seed=26)
+    out = torch.empty((B, H, W), dtype=torch.float32, device=dev)
+    ops.gemm(x, pack_conv3x3(wt), out, conv=(B, H, W, Cin), bias=bias, act=1, head=(w2, 0.7), N=32)
+    t = F.relu(F.conv2d(x.float().permute(0, 3, 1, 2), wt.float(), bias, padding=1))
+    ref = F.relu((t * w2.view(1, 32, 1, 1)).sum(1) + 0.7)
+    torch.cuda.synchronize()
+    assert _relerr(out, ref) < 2e-5
+
+
+# ------------------------------------------------------------------------------------ others
+@pytest.mark.parametrize("dim", [768, 1024])
+def test_layernorm(dim):
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    x = _rand((1155, dim), dev, 2.0, seed=30) + 0.5
+    g, b = _rand((dim,), dev, seed=31), _rand((dim,), dev, seed=32)
+    out = torch.empty((1155, dim), dtype=torch.bfloat16, device=dev)
+    ops.layernorm(x, g, b, 1e-6, out)
+    ref = F.layer_norm(x, (dim,), g, b, 1e-6)
+    torch.cuda.synchronize()
+    assert _relerr(out, ref) < 5e-3
+
+
+@pytest.mark.parametrize("B,T,heads", [(2, 577, 16), (1, 1009, 12), (3, 64, 4), (1, 65, 2)])
+def test_attention(B, T, heads):
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    D = heads * 64
+    qkv = _rand((B * T, 3 * D), dev, 1.0, seed=33).bfloat16()
+    out = torch.full((B * T, D), float("nan"), dtype=torch.bfloat16, device=dev)
+    ops.attention(qkv, out, B, T, heads, 0.125)
+    q, k, v = qkv.float().view(B, T, 3, heads, 64).permute(2, 0, 3, 1, 4)
+    ref = F.scaled_dot_product_attention(q, k, v).transpose(1, 2).reshape(B * T, D)
+    torch.cuda.synchronize()
+    assert torch.isfinite(out.float()).all()
+    assert _relerr(out, ref) < 1.5e-2, _relerr(out, ref)
+
+
+@pytest.mark.parametrize("ac", [True, False])
+def test_upsample2x(ac):
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    x = _rand((2, 13, 21, 64), dev, seed=34).bfloat16()
+    out = torch.empty((2, 26, 42, 64), dtype=torch.bfloat16, device=dev)
+    ops.upsample2x(x, out, ac)
+    ref = F.interpolate(x.float().permute(0, 3, 1, 2), scale_factor=2, mode="bilinear", align_corners=ac).permute(0, 2, 3, 1)
+    torch.cuda.synchronize()
+    assert _relerr(out, ref) < 5e-3
+
+
+def test_im2col_cast_fill():
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    x = _rand((2, 24, 24, 64), dev, seed=35).bfloat16()
+    col = torch.empty((2 * 12 * 12, 9 * 64), dtype=torch.bfloat16, device=dev)
+    ops.im2col3x3(x, col, 2)
+    ref = F.unfold(x.float().permute(0, 3, 1, 2), 3, padding=1, stride=2)           # [B, C*9, L], (c, tap) order
+    ref = ref.view(2, 64, 9, 144).permute(0, 3, 2, 1).reshape(288, 576)
+    torch.cuda.synchronize()
+    assert torch.equal(col.float(), ref)
+    t = _rand((3 * 10, 128), dev, seed=36)
+    o = torch.empty((3 * 9, 128), dtype=torch.bfloat16, device=dev)
+    ops.cast_tokens(t, o, grp=10, skip=1)
+    torch.cuda.synchronize()
+    assert torch.equal(o, t.view(3, 10, 128)[:, 1:].reshape(27, 128).bfloat16())
+    cls, pos = _rand((128,), dev, seed=37), _rand((10, 128), dev, seed=38)
+    ops.fill_cls(t, 3, 10, cls, pos)
+    torch.cuda.synchronize()
+    assert torch.equal(t.view(3, 10, 128)[:, 0], (cls + pos[0]).expand(3, 128))
+
+
+# ------------------------------------------------------------------------------------ K1 / K8
+PRE_CASES = [(640, 480, "MiDaS_small"), (1280, 720, "MiDaS_small"), (1920, 1080, "DPT_Large"),
+             (384, 384, "DPT_Large"), (640, 480, "DPT_Hybrid"), (1280, 720, "DPT_Large"), (333, 517, "DPT_Hybrid")]
+
+
+@pytest.mark.parametrize("W,H,mt", PRE_CASES)
+@pytest.mark.parametrize("kind", ["U", "S"])
+def test_preprocess_vs_oracle(W, H, mt, kind):
+    from depth_estimation_b200 import ops
+    from oracle import transforms as T
+    from oracle.predict import synthetic_frame
+    dev = _dev()
+    frames = np.stack([synthetic_frame(W, H, 7, kind, i) for i in range(2)])
+    name = T.transform_name_for(mt)
+    _, _, mean, std = T.TRANSFORM_SPECS[name]
+    ref = np.concatenate([T.midas_transform_bgr(f, mt) for f in frames])          # fp32 [2,3,h,w]
+    nw, nh = ops.get_size(W, H, mt)
+    assert ref.shape[2:] == (nh, nw)
+    fr = torch.from_numpy(frames).to(dev)
+    o32 = ops.preprocess(fr, nh, nw, mean, std, ops.LAYOUT_NCHW_F32)
+    o16 = ops.preprocess(fr, nh, nw, mean, std, ops.LAYOUT_NCHW_BF16)
+    op = ops.preprocess(fr, nh, nw, mean, std, ops.LAYOUT_PATCH16_BF16)
+    torch.cuda.synchronize()
+    reft = torch.from_numpy(ref).to(dev)
+    assert (o32 - reft).abs().max().item() < 2e-5
+    # bf16 output within 1 bf16 ulp of bf16(oracle fp32)
+    refb = reft.bfloat16()
+    ulp = torch.maximum(refb.float().abs(), torch.tensor(2.0 ** -120, device=dev)) * 2.0 ** -7
+    assert ((o16.float() - refb.float()).abs() <= ulp).all()
+    assert (o16 != refb).float().mean().item() < 0.01
+    # patch layout is the same numbers rearranged: [B, gh, gw, c, py, px]
+    gh, gw = nh // 16, nw // 16
+    rearr = o16.view(2, 3, gh, 16, gw, 16).permute(0, 2, 4, 1, 3, 5).reshape(2 * gh * gw, 768)
+    assert torch.equal(op, rearr)
+
+
+POST_CASES = [(192, 256, 480, 640), (128, 256, 720, 1280), (384, 672, 1080, 1920), (384, 384, 384, 384), (384, 384, 100, 130)]
+
+
+@pytest.mark.parametrize("h,w,H,W", POST_CASES)
+def test_postprocess_vs_torch(h, w, H, W):
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    pred = _rand((2, h, w), dev, seed=40).abs() * 10
+    rc = torch.tensor([[[0, 0], [H - 1, W - 1], [H // 3, W // 2]], [[5, 7], [H // 2, 3], [H - 2, W - 3]]],
+                      dtype=torch.int32, device=dev)
+    omap, ometric, samples = ops.postprocess(pred, H, W, want_map=True, want_metric=True, sample_rc=rc)
+    ref = F.interpolate(pred.cpu().unsqueeze(1), size=(H, W), mode="bicubic", align_corners=False).squeeze(1).to(dev)
+    torch.cuda.synchronize()
+    assert _relerr(omap, ref) < 1e-5
+    assert torch.equal(ometric, (omap * (1.0 / 2.54)).bfloat16())
+    assert _relerr(ometric, ref / 2.54) < 1e-2          # north_star: bf16 metric depth within 1 %
+    for b in range(2):
+        for s in range(3):
+            r, c = rc[b, s].tolist()
+            assert samples[b, s].item() == omap[b, r, c].item()
+    # bf16 input path
+    omap2, _, _ = ops.postprocess(pred.bfloat16(), H, W)
+    ref2 = F.interpolate(pred.bfloat16().float().cpu().unsqueeze(1), size=(H, W), mode="bicubic", align_corners=False).squeeze(1).to(dev)
+    torch.cuda.synchronize()
+    assert _relerr(omap2, ref2) < 1e-5
