@@ -115,10 +115,10 @@ extern "C" int de_cubic_taps(int src, int dst, int mode, int32_t* idx, float* w)
       c[2] = ((A + 2) * (1 - x) - (A + 3)) * (1 - x) * (1 - x) + 1;
       c[3] = 1.f - c[0] - c[1] - c[2];
     } else {
-      // ATen UpSample.h: scale = (float)src/dst; real = scale*(d+0.5f)-0.5f (fp32, no clamp for cubic);
+      // ATen UpSample.h: scale = (float)src/dst; real = fma(scale, d+0.5f, -0.5f) (fp32, no clamp for cubic);
       // cubic_convolution2(x+1), cubic_convolution1(x), cubic_convolution1(1-x), cubic_convolution2(2-x)
       const float scale = (float)src / (float)dst;
-      const float f = scale * ((float)d + 0.5f) - 0.5f;
+      const float f = fmaf(scale, (float)d + 0.5f, -0.5f);  // ATen's kernels are built with FMA contraction
       s = (int)floorf(f);
       x = f - (float)s;
       const float x0 = x + 1.0f, x1 = x, x2 = 1.0f - x, x3 = 2.0f - x;

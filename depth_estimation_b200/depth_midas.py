@@ -1,0 +1,201 @@
+"""Drop-in for the reference's ``depth_midas.py`` / ``midas.py`` (byte-identical files): the same
+``DepthEstimator(model_type)`` / ``.predict(img) -> np.float32[H,W]`` surface
+(/root/reference/depth_midas.py:6-35), backed by the hand-written sm_100a kernels of libdepthb200.so.
+
+What changes underneath (and nothing else): cvtColor + the MiDaS transform chain (:22-23) is one fused
+kernel (K1), the hub model forward (:25-26) is the tcgen05 GEMM / implicit-conv / attention launch
+sequence in dpt.py / midas_small.py, and the bicubic resize back to the frame size (:28-33) is K8.  There
+is no CPU fallback: without a CUDA device or the built library the constructor raises.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import ops
+from .init import random_state_dict
+
+MODEL_TYPES = ("DPT_Large", "DPT_Hybrid", "MiDaS_small")
+_DPT_NORM = ((0.5, 0.5, 0.5), (0.5, 0.5, 0.5))
+_IMAGENET_NORM = ((0.485, 0.456, 0.406), (0.229, 0.224, 0.225))
+
+
+class _Transforms:
+    """Stand-in for the hub ``transforms`` namespace (depth_midas.py:12-16): the callables run K1 and
+    return the network input on the device (NCHW bf16 [1,3,h,w])."""
+
+    def __init__(self, owner):
+        self._o = owner
+        self.dpt_transform = lambda rgb: owner._transform_rgb(rgb, "DPT_Large")
+        self.small_transform = lambda rgb: owner._transform_rgb(rgb, "MiDaS_small")
+        self.default_transform = self.small_transform
+
+
+class DepthEstimator(object):
+    def __init__(self, model_type, *, weights=None, seed=0, device=None, use_cuda_graph=True):
+        """model_type: "DPT_Large" | "DPT_Hybrid" | "MiDaS_small" (anything else gets the small transform,
+        as at depth_midas.py:13-16, and is rejected by the model factory).
+        weights: upstream-format state_dict, a path to one (torch.load), or None for seeded random init."""
+        self.model_type = model_type
+        print(f'Loading model: {self.model_type}')
+        if not torch.cuda.is_available():
+            raise RuntimeError("depth_estimation_b200 needs a CUDA (sm_100a) device; there is no CPU path")
+        self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        ops._lib.load()
+        if weights is None:
+            weights = random_state_dict(model_type, seed)
+        elif isinstance(weights, str):
+            weights = torch.load(weights, map_location="cpu")
+        with torch.cuda.device(self.device):
+            self.estimator = _build_net(model_type, weights, self.device)
+        print('Loading transforms...')
+        self.midas_transforms = _Transforms(self)
+        if self.model_type == "DPT_Large" or self.model_type == "DPT_Hybrid":
+            self.transform = self.midas_transforms.dpt_transform
+            self._norm = _DPT_NORM
+        else:
+            self.transform = self.midas_transforms.small_transform
+            self._norm = _IMAGENET_NORM
+        self.use_cuda_graph = use_cuda_graph
+        self._plans = {}
+
+    # ------------------------------------------------------------------ reference surface
+    def predict(self, img):
+        """img: np.uint8 [H,W,3] BGR (cv2.VideoCapture frame).  Returns np.float32 [H,W] relative inverse
+        depth at source resolution, host memory, synchronous - as depth_midas.py:21-35."""
+        if not isinstance(img, np.ndarray) or img.ndim != 3 or img.shape[2] != 3 or img.dtype != np.uint8:
+            raise TypeError("predict expects a uint8 HxWx3 BGR numpy frame")
+        out = self.predict_batch(img[None])
+        return out[0]
+
+    # ------------------------------------------------------------------ supersets
+    def predict_batch(self, frames, samples_rc=None, want_metric=False):
+        """frames: np.uint8 [B,H,W,3] BGR (host).  Returns np.float32 [B,H,W]; with samples_rc
+        (int [B,S,2] (row,col)) returns (maps, samples[B,S]); with want_metric adds the bf16 metric map
+        (face.py:137, D/2.54) as a float32 array."""
+        frames = np.ascontiguousarray(frames)
+        B, H, W, _ = frames.shape
+        plan = self._plan(B, H, W, 0 if samples_rc is None else int(np.asarray(samples_rc).shape[1]), want_metric)
+        plan.h_in.numpy()[...] = frames
+        if samples_rc is not None:
+            plan.h_rc.numpy()[...] = np.asarray(samples_rc, dtype=np.int32)
+        with torch.cuda.device(self.device):
+            plan.run()
+            torch.cuda.current_stream().synchronize()
+        maps = plan.h_map.numpy().copy()
+        res = [maps]
+        if samples_rc is not None:
+            res.append(plan.h_samples.numpy().copy())
+        if want_metric:
+            res.append(plan.h_metric.float().numpy().copy())
+        return res[0] if len(res) == 1 else tuple(res)
+
+    def predict_device(self, frames_u8: torch.Tensor) -> torch.Tensor:
+        """Device-resident path: uint8 [B,H,W,3] BGR CUDA tensor -> fp32 [B,H,W] CUDA tensor (a buffer
+        owned by the estimator, overwritten by the next call).  No host copies, no sync."""
+        B, H, W, _ = frames_u8.shape
+        plan = self._plan(B, H, W, 0, False)
+        return plan.run_device(frames_u8)
+
+    # ------------------------------------------------------------------ internals
+    def _transform_rgb(self, rgb, mt):
+        """Reference-style transform(img): takes the RGB frame the reference passes (:22-23)."""
+        bgr = np.ascontiguousarray(rgb[:, :, ::-1])
+        H, W = bgr.shape[:2]
+        nw, nh = ops.get_size(W, H, mt)
+        mean, std = _DPT_NORM if mt in ("DPT_Large", "DPT_Hybrid") else _IMAGENET_NORM
+        with torch.cuda.device(self.device):
+            d = torch.from_numpy(bgr[None]).to(self.device)
+            return ops.preprocess(d, nh, nw, mean, std, ops.LAYOUT_NCHW_BF16)
+
+    def _plan(self, B, H, W, n_samples, want_metric):
+        key = (B, H, W, n_samples, want_metric)
+        p = self._plans.get(key)
+        if p is None:
+            with torch.cuda.device(self.device):
+                p = _Plan(self, B, H, W, n_samples, want_metric)
+            self._plans[key] = p
+        return p
+
+
+class _Plan:
+    """Static buffers + (optionally) a captured CUDA graph for one (B,H,W) geometry:
+    pinned host frame -> H2D -> K1 -> net -> K8 -> D2H pinned."""
+
+    def __init__(self, est: DepthEstimator, B, H, W, n_samples, want_metric):
+        self.est = est
+        dev = est.device
+        self.B, self.H, self.W = B, H, W
+        self.net_w, self.net_h = ops.get_size(W, H, est.model_type)
+        self.h_in = torch.empty((B, H, W, 3), dtype=torch.uint8).pin_memory()
+        self.d_in = torch.empty((B, H, W, 3), dtype=torch.uint8, device=dev)
+        self.d_map = torch.empty((B, H, W), dtype=torch.float32, device=dev)
+        self.h_map = torch.empty((B, H, W), dtype=torch.float32).pin_memory()
+        self.want_metric = want_metric
+        self.d_metric = torch.empty((B, H, W), dtype=torch.bfloat16, device=dev) if want_metric else None
+        self.h_metric = torch.empty((B, H, W), dtype=torch.bfloat16).pin_memory() if want_metric else None
+        self.n_samples = n_samples
+        if n_samples:
+            self.h_rc = torch.zeros((B, n_samples, 2), dtype=torch.int32).pin_memory()
+            self.d_rc = torch.zeros((B, n_samples, 2), dtype=torch.int32, device=dev)
+            self.h_samples = torch.empty((B, n_samples), dtype=torch.float32).pin_memory()
+        self.graph = None
+        self._dev_graph = None
+        self._warm = False
+
+    def _compute(self, src):
+        est = self.est
+        mean, std = est._norm
+        net = est.estimator
+        x = ops.preprocess(src, self.net_h, self.net_w, mean, std, net.preprocess_layout)
+        pred = net.forward(x, self.B, self.net_h, self.net_w)
+        rc = self.d_rc if self.n_samples else None
+        _, _, samples = ops.postprocess(pred, self.H, self.W, want_map=True, want_metric=self.want_metric,
+                                        sample_rc=rc, out_map=self.d_map, out_metric=self.d_metric)
+        return samples
+
+    def _body(self):
+        self.d_in.copy_(self.h_in, non_blocking=True)
+        if self.n_samples:
+            self.d_rc.copy_(self.h_rc, non_blocking=True)
+        samples = self._compute(self.d_in)
+        self.h_map.copy_(self.d_map, non_blocking=True)
+        if self.want_metric:
+            self.h_metric.copy_(self.d_metric, non_blocking=True)
+        if self.n_samples:
+            self.h_samples.copy_(samples, non_blocking=True)
+
+    def run(self):
+        if not self.est.use_cuda_graph:
+            self._body()
+            return
+        if self.graph is None:
+            # warm-up on a side stream (allocates work buffers / tap tables), then capture
+            s = torch.cuda.Stream()
+            s.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s):
+                self._body()
+            torch.cuda.current_stream().wait_stream(s)
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._body()
+            self.graph = g
+        self.graph.replay()
+
+    def run_device(self, frames_u8):
+        self._compute(frames_u8)
+        return self.d_map
+
+
+def _build_net(model_type, sd, device):
+    if model_type == "DPT_Large":
+        from .dpt import DPTLargeNet
+        return DPTLargeNet(sd, device)
+    if model_type == "DPT_Hybrid":
+        from .dpt_hybrid import DPTHybridNet
+        return DPTHybridNet(sd, device)
+    if model_type == "MiDaS_small":
+        from .midas_small import MidasSmallNet
+        return MidasSmallNet(sd, device)
+    raise ValueError(f"unknown model_type {model_type!r}; expected one of {MODEL_TYPES}")

@@ -283,7 +283,8 @@ def test_preprocess_vs_oracle(W, H, mt, kind):
     assert (o32 - reft).abs().max().item() < 2e-5
     # bf16 output within 1 bf16 ulp of bf16(oracle fp32)
     refb = reft.bfloat16()
-    ulp = torch.maximum(refb.float().abs(), torch.tensor(2.0 ** -120, device=dev)) * 2.0 ** -7
+    # (near zero the fp32 result itself may differ by ~2e-5 absolute, many "ulps" of a tiny number)
+    ulp = torch.clamp(refb.float().abs() * 2.0 ** -7, min=4e-5)
     assert ((o16.float() - refb.float()).abs() <= ulp).all()
     assert (o16 != refb).float().mean().item() < 0.01
     # patch layout is the same numbers rearranged: [B, gh, gw, c, py, px]
