@@ -1,0 +1,214 @@
+// Direct (CUDA-core) convolution kernels for the shapes that are not dense contractions:
+//   * the 3-channel stems (EfficientNet-Lite3 3x3 s2, ResNetV2 7x7 s2) - K = 27 / 147, reads the NCHW
+//     bf16 tensor K1 writes, emits NHWC bf16;
+//   * depthwise k3 / k5, stride 1 / 2, TF-"same" padding with folded BatchNorm + ReLU6 (MBConv middle),
+//     NHWC bf16, 8 channels (16 B) per thread, weights tap-major so every access is a coalesced 16-byte
+//     transaction - an HBM/L2 bandwidth kernel;
+//   * MaxPool 3x3 s2 TF-same (ResNetV2 stem).
+// Restates [UPSTREAM] geffnet Conv2dSame / timm StdConv2dSame+MaxPool2dSame padding rule:
+//   pad_total = max((ceil(i/s)-1)*s + k - i, 0), pad_before = pad_total / 2 (extra pixel bottom/right).
+#include "common.cuh"
+#include "depth_b200.h"
+#include "host_util.h"
+
+namespace deb {
+
+__host__ __device__ inline int same_pad_before(int in, int k, int s) {
+  const int out = (in + s - 1) / s;
+  int total = (out - 1) * s + k - in;
+  if (total < 0) total = 0;
+  return total / 2;
+}
+
+// ---------------------------------------------------------------- stem: NCHW bf16 (3 ch) -> NHWC bf16
+constexpr int kStemCo = 16;  // output channels per thread
+
+__global__ void __launch_bounds__(128) stem_conv_kernel(const __nv_bfloat16* __restrict__ x,
+                                                        const float* __restrict__ w,  // [Cout][k*k*3] (kh,kw,c)
+                                                        const float* __restrict__ bias, __nv_bfloat16* __restrict__ out,
+                                                        int B, int H, int W, int Cout, int k, int stride, int Ho, int Wo,
+                                                        int pad_y, int pad_x, int act) {
+  extern __shared__ float s_w[];  // [k*k*3][Cout] transposed for broadcast float4 reads
+  const int taps = k * k * 3;
+  for (int i = threadIdx.x; i < taps * Cout; i += blockDim.x) {
+    const int co = i % Cout, t = i / Cout;
+    s_w[i] = w[co * taps + t];
+  }
+  __syncthreads();
+  const int cgs = Cout / kStemCo;
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long long)B * Ho * Wo * cgs) return;
+  // pixel-major thread order (adjacent threads -> adjacent ox) keeps the input reads coalesced
+  const int ox = static_cast<int>(idx % Wo);
+  long long t = idx / Wo;
+  const int oy = static_cast<int>(t % Ho);
+  t /= Ho;
+  const int cg = static_cast<int>(t % cgs);
+  const int b = static_cast<int>(t / cgs);
+  float acc[kStemCo];
+#pragma unroll
+  for (int j = 0; j < kStemCo; ++j) acc[j] = bias ? bias[cg * kStemCo + j] : 0.f;
+  const __nv_bfloat16* xb = x + (long long)b * 3 * H * W;
+  for (int ky = 0; ky < k; ++ky) {
+    const int iy = oy * stride + ky - pad_y;
+    if (iy < 0 || iy >= H) continue;
+    for (int kx = 0; kx < k; ++kx) {
+      const int ix = ox * stride + kx - pad_x;
+      if (ix < 0 || ix >= W) continue;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const float v = __bfloat162float(xb[((long long)c * H + iy) * W + ix]);
+        const float4* wp = reinterpret_cast<const float4*>(s_w + ((ky * k + kx) * 3 + c) * Cout + cg * kStemCo);
+#pragma unroll
+        for (int j4 = 0; j4 < kStemCo / 4; ++j4) {
+          const float4 ww = wp[j4];
+          acc[j4 * 4 + 0] = fmaf(v, ww.x, acc[j4 * 4 + 0]);
+          acc[j4 * 4 + 1] = fmaf(v, ww.y, acc[j4 * 4 + 1]);
+          acc[j4 * 4 + 2] = fmaf(v, ww.z, acc[j4 * 4 + 2]);
+          acc[j4 * 4 + 3] = fmaf(v, ww.w, acc[j4 * 4 + 3]);
+        }
+      }
+    }
+  }
+  uint32_t o[kStemCo / 2];
+#pragma unroll
+  for (int j = 0; j < kStemCo / 2; ++j) {
+    float a = acc[2 * j], c = acc[2 * j + 1];
+    if (act == DE_ACT_RELU6) { a = fminf(fmaxf(a, 0.f), 6.f); c = fminf(fmaxf(c, 0.f), 6.f); }
+    else if (act == DE_ACT_RELU) { a = fmaxf(a, 0.f); c = fmaxf(c, 0.f); }
+    o[j] = pack_bf16(a, c);
+  }
+  uint4* op = reinterpret_cast<uint4*>(out + (((long long)b * Ho + oy) * Wo + ox) * Cout + cg * kStemCo);
+  op[0] = make_uint4(o[0], o[1], o[2], o[3]);
+  op[1] = make_uint4(o[4], o[5], o[6], o[7]);
+}
+
+// ---------------------------------------------------------------- depthwise, NHWC bf16
+template <int K>
+__global__ void __launch_bounds__(256) depthwise_kernel(const __nv_bfloat16* __restrict__ x,
+                                                        const __nv_bfloat16* __restrict__ w,  // [K*K][C] tap-major
+                                                        const float* __restrict__ bias, __nv_bfloat16* __restrict__ out,
+                                                        int B, int H, int W, int C, int stride, int Ho, int Wo, int pad_y,
+                                                        int pad_x, int act) {
+  const int cgs = C >> 3;
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long long)B * Ho * Wo * cgs) return;
+  const int c = static_cast<int>(idx % cgs) * 8;
+  long long t = idx / cgs;
+  const int ox = static_cast<int>(t % Wo);
+  t /= Wo;
+  const int oy = static_cast<int>(t % Ho);
+  const int b = static_cast<int>(t / Ho);
+  float acc[8];
+  {
+    const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias + c));
+    const float4 b1 = __ldg(reinterpret_cast<const float4*>(bias + c + 4));
+    acc[0] = b0.x; acc[1] = b0.y; acc[2] = b0.z; acc[3] = b0.w;
+    acc[4] = b1.x; acc[5] = b1.y; acc[6] = b1.z; acc[7] = b1.w;
+  }
+  const __nv_bfloat16* xb = x + (long long)b * H * W * C + c;
+#pragma unroll
+  for (int ky = 0; ky < K; ++ky) {
+    const int iy = oy * stride + ky - pad_y;
+    if (iy < 0 || iy >= H) continue;
+#pragma unroll
+    for (int kx = 0; kx < K; ++kx) {
+      const int ix = ox * stride + kx - pad_x;
+      if (ix < 0 || ix >= W) continue;
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(xb + ((long long)iy * W + ix) * C));
+      const uint4 ww = __ldg(reinterpret_cast<const uint4*>(w + (ky * K + kx) * C + c));
+      acc[0] = fmaf(bf16_lo(v.x), bf16_lo(ww.x), acc[0]); acc[1] = fmaf(bf16_hi(v.x), bf16_hi(ww.x), acc[1]);
+      acc[2] = fmaf(bf16_lo(v.y), bf16_lo(ww.y), acc[2]); acc[3] = fmaf(bf16_hi(v.y), bf16_hi(ww.y), acc[3]);
+      acc[4] = fmaf(bf16_lo(v.z), bf16_lo(ww.z), acc[4]); acc[5] = fmaf(bf16_hi(v.z), bf16_hi(ww.z), acc[5]);
+      acc[6] = fmaf(bf16_lo(v.w), bf16_lo(ww.w), acc[6]); acc[7] = fmaf(bf16_hi(v.w), bf16_hi(ww.w), acc[7]);
+    }
+  }
+  if (act == DE_ACT_RELU6) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = fminf(fmaxf(acc[j], 0.f), 6.f);
+  } else if (act == DE_ACT_RELU) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = fmaxf(acc[j], 0.f);
+  }
+  *reinterpret_cast<uint4*>(out + (((long long)b * Ho + oy) * Wo + ox) * C + c) =
+      make_uint4(pack_bf16(acc[0], acc[1]), pack_bf16(acc[2], acc[3]), pack_bf16(acc[4], acc[5]), pack_bf16(acc[6], acc[7]));
+}
+
+// ---------------------------------------------------------------- maxpool 3x3 s2 TF-same, NHWC bf16
+__global__ void maxpool3x3s2_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, int B, int H,
+                                    int W, int C, int Ho, int Wo, int pad_y, int pad_x) {
+  const int cgs = C >> 3;
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long long)B * Ho * Wo * cgs) return;
+  const int c = static_cast<int>(idx % cgs) * 8;
+  long long t = idx / cgs;
+  const int ox = static_cast<int>(t % Wo);
+  t /= Wo;
+  const int oy = static_cast<int>(t % Ho);
+  const int b = static_cast<int>(t / Ho);
+  float m[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) m[j] = -INFINITY;
+  for (int ky = 0; ky < 3; ++ky) {
+    const int iy = oy * 2 + ky - pad_y;
+    if (iy < 0 || iy >= H) continue;
+    for (int kx = 0; kx < 3; ++kx) {
+      const int ix = ox * 2 + kx - pad_x;
+      if (ix < 0 || ix >= W) continue;
+      const uint4 v = *reinterpret_cast<const uint4*>(x + (((long long)b * H + iy) * W + ix) * C + c);
+      m[0] = fmaxf(m[0], bf16_lo(v.x)); m[1] = fmaxf(m[1], bf16_hi(v.x));
+      m[2] = fmaxf(m[2], bf16_lo(v.y)); m[3] = fmaxf(m[3], bf16_hi(v.y));
+      m[4] = fmaxf(m[4], bf16_lo(v.z)); m[5] = fmaxf(m[5], bf16_hi(v.z));
+      m[6] = fmaxf(m[6], bf16_lo(v.w)); m[7] = fmaxf(m[7], bf16_hi(v.w));
+    }
+  }
+  *reinterpret_cast<uint4*>(out + (((long long)b * Ho + oy) * Wo + ox) * C + c) =
+      make_uint4(pack_bf16(m[0], m[1]), pack_bf16(m[2], m[3]), pack_bf16(m[4], m[5]), pack_bf16(m[6], m[7]));
+}
+
+}  // namespace deb
+
+using namespace deb;
+
+extern "C" int de_stem_conv(const void* x_nchw, const float* w, const float* bias, void* out_nhwc, int B, int H, int W,
+                            int Cout, int k, int stride, int act, void* stream) {
+  if (!x_nchw || !w || !out_nhwc || Cout % kStemCo != 0 || k < 1 || k > 7)
+    return fail(DE_ERR_INVALID, "de_stem_conv: bad args (Cout %% 16, k <= 7)");
+  const int Ho = (H + stride - 1) / stride, Wo = (W + stride - 1) / stride;
+  const long long n = (long long)B * Ho * Wo * (Cout / kStemCo);
+  const size_t smem = sizeof(float) * k * k * 3 * Cout;
+  stem_conv_kernel<<<(unsigned)((n + 127) / 128), 128, smem, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const __nv_bfloat16*>(x_nchw), w, bias, reinterpret_cast<__nv_bfloat16*>(out_nhwc), B, H, W, Cout,
+      k, stride, Ho, Wo, same_pad_before(H, k, stride), same_pad_before(W, k, stride), act);
+  count_launch();
+  return cuda_check_launch("stem_conv_kernel");
+}
+
+extern "C" int de_depthwise(const void* x, const void* w_tapmajor, const float* bias, void* out, int B, int H, int W,
+                            int C, int k, int stride, int act, void* stream) {
+  if (!x || !w_tapmajor || !bias || !out || C % 8 != 0) return fail(DE_ERR_INVALID, "de_depthwise: bad args (C %% 8)");
+  const int Ho = (H + stride - 1) / stride, Wo = (W + stride - 1) / stride;
+  const long long n = (long long)B * Ho * Wo * (C / 8);
+  const unsigned grid = (unsigned)((n + 255) / 256);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int py = same_pad_before(H, k, stride), px = same_pad_before(W, k, stride);
+  auto xp = reinterpret_cast<const __nv_bfloat16*>(x);
+  auto wp = reinterpret_cast<const __nv_bfloat16*>(w_tapmajor);
+  auto op = reinterpret_cast<__nv_bfloat16*>(out);
+  if (k == 3) depthwise_kernel<3><<<grid, 256, 0, st>>>(xp, wp, bias, op, B, H, W, C, stride, Ho, Wo, py, px, act);
+  else if (k == 5) depthwise_kernel<5><<<grid, 256, 0, st>>>(xp, wp, bias, op, B, H, W, C, stride, Ho, Wo, py, px, act);
+  else return fail(DE_ERR_UNSUPPORTED, "de_depthwise: k=%d (3 or 5)", k);
+  count_launch();
+  return cuda_check_launch("depthwise_kernel");
+}
+
+extern "C" int de_maxpool3x3s2(const void* x, void* out, int B, int H, int W, int C, void* stream) {
+  if (!x || !out || C % 8 != 0) return fail(DE_ERR_INVALID, "de_maxpool3x3s2: bad args");
+  const int Ho = (H + 1) / 2, Wo = (W + 1) / 2;
+  const long long n = (long long)B * Ho * Wo * (C / 8);
+  maxpool3x3s2_kernel<<<(unsigned)((n + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(out), B, H, W, C, Ho, Wo,
+      same_pad_before(H, 3, 2), same_pad_before(W, 3, 2));
+  count_launch();
+  return cuda_check_launch("maxpool3x3s2_kernel");
+}

@@ -70,7 +70,8 @@ def preprocess(frames_u8: torch.Tensor, net_h: int, net_w: int, mean, std, layou
             out = torch.empty((B, 3, net_h, net_w), dtype=torch.float32, device=frames_u8.device)
     m = (C.c_float * 3)(*[float(v) for v in mean])
     s = (C.c_float * 3)(*[float(v) for v in std])
-    _lib.check(_lib.load().de_preprocess(frames_u8.data_ptr(), B, H, W, frames_u8.stride(1), frames_u8.stride(0),
+    fstride = frames_u8.stride(0) if B > 1 else frames_u8.stride(1) * H
+    _lib.check(_lib.load().de_preprocess(frames_u8.data_ptr(), B, H, W, frames_u8.stride(1), fstride,
                                          net_h, net_w, m, s, layout, out.data_ptr(), _stream()), "de_preprocess")
     return out
 
@@ -202,4 +203,31 @@ def im2col3x3(x: torch.Tensor, out: torch.Tensor, stride: int):
     B, H, W, Cc = x.shape
     assert x.dtype == torch.bfloat16 and x.is_contiguous() and out.is_contiguous()
     _lib.check(_lib.load().de_im2col3x3(x.data_ptr(), out.data_ptr(), B, H, W, Cc, stride, _stream()), "de_im2col3x3")
+    return out
+
+
+def stem_conv(x_nchw: torch.Tensor, w: torch.Tensor, bias, out: torch.Tensor, k: int, stride: int, act: int):
+    """x: bf16 NCHW [B,3,H,W]; w: f32 [Cout, k*k*3]; out: bf16 NHWC."""
+    _need_cuda(x_nchw, w, bias, out)
+    B, _, H, W = x_nchw.shape
+    assert x_nchw.dtype == torch.bfloat16 and x_nchw.is_contiguous() and w.dtype == torch.float32
+    _lib.check(_lib.load().de_stem_conv(x_nchw.data_ptr(), w.data_ptr(), _ptr(bias), out.data_ptr(), B, H, W,
+                                        w.shape[0], k, stride, act, _stream()), "de_stem_conv")
+    return out
+
+
+def depthwise(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, out: torch.Tensor, k: int, stride: int, act: int):
+    """x: bf16 NHWC; w: bf16 [k*k, C]; bias f32 [C]."""
+    _need_cuda(x, w, bias, out)
+    B, H, W, Cc = x.shape
+    assert x.dtype == torch.bfloat16 and x.is_contiguous() and w.dtype == torch.bfloat16 and w.is_contiguous()
+    _lib.check(_lib.load().de_depthwise(x.data_ptr(), w.data_ptr(), bias.data_ptr(), out.data_ptr(), B, H, W, Cc, k,
+                                        stride, act, _stream()), "de_depthwise")
+    return out
+
+
+def maxpool3x3s2(x: torch.Tensor, out: torch.Tensor):
+    _need_cuda(x, out)
+    B, H, W, Cc = x.shape
+    _lib.check(_lib.load().de_maxpool3x3s2(x.data_ptr(), out.data_ptr(), B, H, W, Cc, _stream()), "de_maxpool3x3s2")
     return out

@@ -136,6 +136,18 @@ int de_upsample2x(const void* x, void* out, int B, int H, int W, int C, int alig
 /* im2col for 3x3 stride-s pad-1 (s=2 used by act_postprocess4) NHWC bf16 -> [B*Ho*Wo, 9*C]. */
 int de_im2col3x3(const void* x, void* out, int B, int H, int W, int C, int stride, void* stream);
 
+/* ---- direct (CUDA-core) convolutions for non-GEMM shapes; TF-"same" padding (geffnet Conv2dSame /
+ * timm StdConv2dSame, MaxPool2dSame): pad_total = max((ceil(i/s)-1)*s+k-i, 0), extra pixel bottom/right. */
+/* 3-channel stem: x NCHW bf16 [B,3,H,W] (K1 layout 0), w float [Cout][k*k*3] ((kh,kw,c) order, BN
+ * folded), bias float[Cout] or NULL -> NHWC bf16 [B,ceil(H/s),ceil(W/s),Cout]. Cout % 16 == 0. */
+int de_stem_conv(const void* x_nchw, const float* w, const float* bias, void* out_nhwc, int B, int H, int W,
+                 int Cout, int k, int stride, int act, void* stream);
+/* depthwise k in {3,5}: x NHWC bf16, w bf16 [k*k][C] (tap-major, BN folded), bias float[C]. */
+int de_depthwise(const void* x, const void* w_tapmajor, const float* bias, void* out, int B, int H, int W, int C,
+                 int k, int stride, int act, void* stream);
+/* MaxPool 3x3 stride 2 TF-same, NHWC bf16. */
+int de_maxpool3x3s2(const void* x, void* out, int B, int H, int W, int C, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
