@@ -318,3 +318,56 @@ def test_postprocess_vs_torch(h, w, H, W):
     ref2 = F.interpolate(pred.bfloat16().float().cpu().unsqueeze(1), size=(H, W), mode="bicubic", align_corners=False).squeeze(1).to(dev)
     torch.cuda.synchronize()
     assert _relerr(omap2, ref2) < 1e-5
+
+
+# ------------------------------------------------------------------------------------ direct convs
+def _tf_same_pad(x, k, s, value=0.0):
+    ih, iw = x.shape[-2:]
+    ph = max((math.ceil(ih / s) - 1) * s + k - ih, 0)
+    pw = max((math.ceil(iw / s) - 1) * s + k - iw, 0)
+    return F.pad(x, [pw // 2, pw - pw // 2, ph // 2, ph - ph // 2], value=value)
+
+
+@pytest.mark.parametrize("k,s,Cout,H,W", [(3, 2, 32, 192, 256), (7, 2, 64, 96, 130), (3, 2, 32, 37, 41)])
+def test_stem_conv(k, s, Cout, H, W):
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    x = _rand((2, 3, H, W), dev, seed=50).bfloat16()
+    w = _rand((Cout, 3, k, k), dev, 0.1, seed=51)
+    b = _rand((Cout,), dev, seed=52)
+    Ho, Wo = (H + s - 1) // s, (W + s - 1) // s
+    out = torch.empty((2, Ho, Wo, Cout), dtype=torch.bfloat16, device=dev)
+    ops.stem_conv(x, w.permute(0, 2, 3, 1).reshape(Cout, -1).contiguous(), b, out, k, s, ops.ACT_RELU6)
+    ref = F.relu6(F.conv2d(_tf_same_pad(x.float(), k, s), w, b, stride=s)).permute(0, 2, 3, 1)
+    torch.cuda.synchronize()
+    assert out.shape == ref.shape
+    assert _relerr(out, ref) < 5e-3
+
+
+@pytest.mark.parametrize("k,s,Cc,H,W", [(3, 1, 32, 96, 128), (3, 2, 144, 96, 128), (5, 2, 192, 48, 64), (5, 1, 816, 12, 16),
+                                        (5, 2, 816, 12, 16), (3, 1, 1392, 6, 8), (5, 2, 48, 9, 7)])
+def test_depthwise(k, s, Cc, H, W):
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    x = _rand((2, Cc, H, W), dev, seed=53).bfloat16()
+    w = _rand((Cc, 1, k, k), dev, 0.2, seed=54).bfloat16()
+    b = _rand((Cc,), dev, seed=55)
+    Ho, Wo = (H + s - 1) // s, (W + s - 1) // s
+    out = torch.empty((2, Ho, Wo, Cc), dtype=torch.bfloat16, device=dev)
+    ops.depthwise(x.permute(0, 2, 3, 1).contiguous(), w.reshape(Cc, k * k).t().contiguous(), b, out, k, s, ops.ACT_RELU6)
+    ref = F.relu6(F.conv2d(_tf_same_pad(x.float(), k, s), w.float(), b, stride=s, groups=Cc)).permute(0, 2, 3, 1)
+    torch.cuda.synchronize()
+    assert out.shape == ref.shape
+    assert _relerr(out, ref) < 5e-3
+
+
+def test_maxpool():
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    for H, W in ((192, 192), (35, 22)):
+        x = _rand((2, 64, H, W), dev, seed=56).bfloat16()
+        out = torch.empty((2, (H + 1) // 2, (W + 1) // 2, 64), dtype=torch.bfloat16, device=dev)
+        ops.maxpool3x3s2(x.permute(0, 2, 3, 1).contiguous(), out)
+        ref = F.max_pool2d(_tf_same_pad(x.float(), 3, 2, float("-inf")), 3, 2).permute(0, 2, 3, 1)
+        torch.cuda.synchronize()
+        assert torch.equal(out.float(), ref)
