@@ -120,9 +120,9 @@ __global__ void upsample2x_kernel(const __nv_bfloat16* __restrict__ x, __nv_bflo
   *reinterpret_cast<uint4*>(out + (((long long)b * OH + oy) * OW + ox) * C + c) = make_uint4(o[0], o[1], o[2], o[3]);
 }
 
-// ---------------------------------------------------------------- im2col 3x3, stride s, pad 1
+// ---------------------------------------------------------------- im2col 3x3, stride s, explicit pad
 __global__ void im2col3x3_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, int B, int H,
-                                 int W, int C, int stride, int Ho, int Wo) {
+                                 int W, int C, int stride, int pad_y, int pad_x, int Ho, int Wo) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const int cg = C >> 3;
   if (i >= (long long)B * Ho * Wo * 9 * cg) return;
@@ -134,11 +134,108 @@ __global__ void im2col3x3_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloa
   t /= Wo;
   const int oy = static_cast<int>(t % Ho);
   const int b = static_cast<int>(t / Ho);
-  const int iy = oy * stride + tap / 3 - 1, ix = ox * stride + tap % 3 - 1;
+  const int iy = oy * stride + tap / 3 - pad_y, ix = ox * stride + tap % 3 - pad_x;
   uint4 v = make_uint4(0, 0, 0, 0);
   if (iy >= 0 && iy < H && ix >= 0 && ix < W)
     v = *reinterpret_cast<const uint4*>(x + (((long long)b * H + iy) * W + ix) * C + c);
   *reinterpret_cast<uint4*>(out + (((long long)b * Ho + oy) * Wo + ox) * 9 * C + (long long)tap * C + c) = v;
+}
+
+// ---------------------------------------------------------------- spatial subsample (1x1 stride-2 conv input)
+__global__ void subsample_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, int B, int H,
+                                 int W, int C, int stride, int Ho, int Wo) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int cg = C >> 3;
+  if (i >= (long long)B * Ho * Wo * cg) return;
+  const int c = static_cast<int>(i % cg) * 8;
+  long long t = i / cg;
+  const int ox = static_cast<int>(t % Wo);
+  t /= Wo;
+  const int oy = static_cast<int>(t % Ho);
+  const int b = static_cast<int>(t / Ho);
+  *reinterpret_cast<uint4*>(out + (((long long)b * Ho + oy) * Wo + ox) * C + c) =
+      *reinterpret_cast<const uint4*>(x + (((long long)b * H + oy * stride) * W + ox * stride) * C + c);
+}
+
+// ---------------------------------------------------------------- GroupNorm (NHWC bf16), two passes
+// pass 1: per-(sample, group) sum / sum of squares, block partials -> double atomics
+__global__ void __launch_bounds__(256) groupnorm_stats_kernel(const __nv_bfloat16* __restrict__ x, int HW, int C,
+                                                              int groups, int px_per_block, double* __restrict__ stats) {
+  __shared__ float s_sum[64], s_sq[64];
+  const int b = blockIdx.y;
+  const int vec = C >> 3;                    // 8-channel vectors per pixel
+  const int lanes = 256 / vec;               // pixels processed concurrently
+  const int v = threadIdx.x % vec, pl = threadIdx.x / vec;
+  if (threadIdx.x < 64) { s_sum[threadIdx.x] = 0.f; s_sq[threadIdx.x] = 0.f; }
+  __syncthreads();
+  const int p0 = blockIdx.x * px_per_block;
+  const int p1 = min(p0 + px_per_block, HW);
+  float su[8], sq[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) su[j] = sq[j] = 0.f;
+  if (pl < lanes) {
+    for (int p = p0 + pl; p < p1; p += lanes) {
+      const uint4 t = *reinterpret_cast<const uint4*>(x + ((long long)b * HW + p) * C + v * 8);
+      const float f[8] = {bf16_lo(t.x), bf16_hi(t.x), bf16_lo(t.y), bf16_hi(t.y),
+                          bf16_lo(t.z), bf16_hi(t.z), bf16_lo(t.w), bf16_hi(t.w)};
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { su[j] += f[j]; sq[j] = fmaf(f[j], f[j], sq[j]); }
+    }
+    const int cpg = C / groups;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int g = (v * 8 + j) / cpg;
+      atomicAdd(&s_sum[g], su[j]);
+      atomicAdd(&s_sq[g], sq[j]);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < groups) {
+    atomicAdd(&stats[((long long)b * groups + threadIdx.x) * 2], (double)s_sum[threadIdx.x]);
+    atomicAdd(&stats[((long long)b * groups + threadIdx.x) * 2 + 1], (double)s_sq[threadIdx.x]);
+  }
+}
+
+// pass 2: y = act((x-mean)*rstd*gamma + beta [+ add])
+__global__ void groupnorm_apply_kernel(const __nv_bfloat16* __restrict__ x, const double* __restrict__ stats,
+                                       const float* __restrict__ gamma, const float* __restrict__ beta,
+                                       const __nv_bfloat16* __restrict__ add, __nv_bfloat16* __restrict__ out, int B,
+                                       int HW, int C, int groups, float eps, int act) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int vec = C >> 3;
+  if (i >= (long long)B * HW * vec) return;
+  const int c0 = static_cast<int>(i % vec) * 8;
+  const int b = static_cast<int>(i / ((long long)HW * vec));
+  const int cpg = C / groups;
+  const double n = (double)HW * cpg;
+  const uint4 t = *reinterpret_cast<const uint4*>(x + i * 8);
+  float f[8] = {bf16_lo(t.x), bf16_hi(t.x), bf16_lo(t.y), bf16_hi(t.y), bf16_lo(t.z), bf16_hi(t.z), bf16_lo(t.w), bf16_hi(t.w)};
+  float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  if (add) {
+    const uint4 u = *reinterpret_cast<const uint4*>(add + i * 8);
+    a[0] = bf16_lo(u.x); a[1] = bf16_hi(u.x); a[2] = bf16_lo(u.y); a[3] = bf16_hi(u.y);
+    a[4] = bf16_lo(u.z); a[5] = bf16_hi(u.z); a[6] = bf16_lo(u.w); a[7] = bf16_hi(u.w);
+  }
+  int gprev = -1;
+  float mean = 0.f, rstd = 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int g = (c0 + j) / cpg;
+    if (g != gprev) {
+      const double s = stats[((long long)b * groups + g) * 2], q = stats[((long long)b * groups + g) * 2 + 1];
+      const double m = s / n;
+      double var = q / n - m * m;
+      if (var < 0) var = 0;
+      mean = (float)m;
+      rstd = (float)(1.0 / sqrt(var + (double)eps));
+      gprev = g;
+    }
+    float y = (f[j] - mean) * rstd * __ldg(gamma + c0 + j) + __ldg(beta + c0 + j) + a[j];
+    if (act == DE_ACT_RELU) y = fmaxf(y, 0.f);
+    f[j] = y;
+  }
+  *reinterpret_cast<uint4*>(out + i * 8) =
+      make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
 }
 
 }  // namespace deb
@@ -194,12 +291,47 @@ extern "C" int de_upsample2x(const void* x, void* out, int B, int H, int W, int 
   return cuda_check_launch("upsample2x_kernel");
 }
 
-extern "C" int de_im2col3x3(const void* x, void* out, int B, int H, int W, int C, int stride, void* stream) {
-  if (!x || !out || C % 8 != 0 || stride < 1) return fail(DE_ERR_INVALID, "de_im2col3x3: bad args");
-  const int Ho = (H + 2 - 3) / stride + 1, Wo = (W + 2 - 3) / stride + 1;
+extern "C" int de_im2col3x3(const void* x, void* out, int B, int H, int W, int C, int stride, int pad_y, int pad_x,
+                            int Ho, int Wo, void* stream) {
+  if (!x || !out || C % 8 != 0 || stride < 1 || Ho < 1 || Wo < 1) return fail(DE_ERR_INVALID, "de_im2col3x3: bad args");
   const long long n = (long long)B * Ho * Wo * 9 * (C / 8);
   im2col3x3_kernel<<<(unsigned)((n + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(out), B, H, W, C, stride, Ho, Wo);
+      reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(out), B, H, W, C, stride, pad_y, pad_x,
+      Ho, Wo);
   count_launch();
   return cuda_check_launch("im2col3x3_kernel");
+}
+
+extern "C" int de_subsample(const void* x, void* out, int B, int H, int W, int C, int stride, void* stream) {
+  if (!x || !out || C % 8 != 0 || stride < 1) return fail(DE_ERR_INVALID, "de_subsample: bad args");
+  const int Ho = (H + stride - 1) / stride, Wo = (W + stride - 1) / stride;
+  const long long n = (long long)B * Ho * Wo * (C / 8);
+  subsample_kernel<<<(unsigned)((n + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(out), B, H, W, C, stride, Ho, Wo);
+  count_launch();
+  return cuda_check_launch("subsample_kernel");
+}
+
+extern "C" int de_groupnorm(const void* x, const float* gamma, const float* beta, const void* add, void* out, int B,
+                            int HW, int C, int groups, float eps, int act, void* stats_ws, void* stream) {
+  if (!x || !gamma || !beta || !out || !stats_ws) return fail(DE_ERR_INVALID, "de_groupnorm: null pointer");
+  if (C % 8 != 0 || C > 2048 || groups > 64 || groups < 1 || C % groups != 0 || 256 % (C / 8) != 0)
+    return fail(DE_ERR_UNSUPPORTED, "de_groupnorm: C=%d groups=%d unsupported", C, groups);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  cudaError_t e = cudaMemsetAsync(stats_ws, 0, sizeof(double) * 2 * B * groups, st);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(groupnorm stats)");
+  // enough blocks to fill the GPU even at B=1
+  int px_per_block = (HW + 147) / 148;
+  const int lanes = 256 / (C / 8);
+  if (px_per_block < lanes * 4) px_per_block = lanes * 4;
+  dim3 grid((HW + px_per_block - 1) / px_per_block, B);
+  groupnorm_stats_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(x), HW, C, groups, px_per_block,
+                                              reinterpret_cast<double*>(stats_ws));
+  count_launch();
+  const long long n = (long long)B * HW * (C / 8);
+  groupnorm_apply_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(
+      reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<const double*>(stats_ws), gamma, beta,
+      reinterpret_cast<const __nv_bfloat16*>(add), reinterpret_cast<__nv_bfloat16*>(out), B, HW, C, groups, eps, act);
+  count_launch();
+  return cuda_check_launch("groupnorm kernels");
 }

@@ -198,11 +198,33 @@ def upsample2x(x: torch.Tensor, out: torch.Tensor, align_corners: bool):
     return out
 
 
-def im2col3x3(x: torch.Tensor, out: torch.Tensor, stride: int):
+def im2col3x3(x: torch.Tensor, out: torch.Tensor, stride: int, pad=(1, 1), out_hw=None):
+    """NHWC bf16 -> [B*Ho*Wo, 9*C].  Default = torch Conv2d(k3, stride, padding=1) geometry."""
     _need_cuda(x, out)
     B, H, W, Cc = x.shape
+    if out_hw is None:
+        out_hw = ((H + 2 - 3) // stride + 1, (W + 2 - 3) // stride + 1)
     assert x.dtype == torch.bfloat16 and x.is_contiguous() and out.is_contiguous()
-    _lib.check(_lib.load().de_im2col3x3(x.data_ptr(), out.data_ptr(), B, H, W, Cc, stride, _stream()), "de_im2col3x3")
+    _lib.check(_lib.load().de_im2col3x3(x.data_ptr(), out.data_ptr(), B, H, W, Cc, stride, pad[0], pad[1], out_hw[0],
+                                        out_hw[1], _stream()), "de_im2col3x3")
+    return out
+
+
+def subsample(x: torch.Tensor, out: torch.Tensor, stride: int):
+    _need_cuda(x, out)
+    B, H, W, Cc = x.shape
+    _lib.check(_lib.load().de_subsample(x.data_ptr(), out.data_ptr(), B, H, W, Cc, stride, _stream()), "de_subsample")
+    return out
+
+
+def groupnorm(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, out: torch.Tensor, ws: torch.Tensor,
+              act: int = ACT_RELU, add: torch.Tensor | None = None, groups: int = 32, eps: float = 1e-5):
+    """x: bf16 NHWC [B,H,W,C]; ws: float64 scratch with >= 2*B*groups elements."""
+    _need_cuda(x, gamma, beta, out, ws, add)
+    B, H, W, Cc = x.shape
+    assert x.dtype == torch.bfloat16 and x.is_contiguous() and ws.dtype == torch.float64 and ws.numel() >= 2 * B * groups
+    _lib.check(_lib.load().de_groupnorm(x.data_ptr(), gamma.data_ptr(), beta.data_ptr(), _ptr(add), out.data_ptr(), B,
+                                        H * W, Cc, groups, float(eps), act, ws.data_ptr(), _stream()), "de_groupnorm")
     return out
 
 

@@ -133,8 +133,17 @@ int de_fill_cls(float* x, int64_t ldx, int B, int T, int dim, const float* cls, 
                 void* stream);
 /* bilinear x2 upsample NHWC bf16 [B,H,W,C] -> [B,2H,2W,C]; align_corners 1/0. */
 int de_upsample2x(const void* x, void* out, int B, int H, int W, int C, int align_corners, void* stream);
-/* im2col for 3x3 stride-s pad-1 (s=2 used by act_postprocess4) NHWC bf16 -> [B*Ho*Wo, 9*C]. */
-int de_im2col3x3(const void* x, void* out, int B, int H, int W, int C, int stride, void* stream);
+/* im2col for a 3x3 window, stride s, explicit leading pad: NHWC bf16 -> [B*Ho*Wo, 9*C], k = tap*C + c.
+ * torch Conv2d(k3,s2,p1) (act_postprocess4): pad 1, Ho = (H-1)/2+1.  TF-same s2 (ResNetV2): pad
+ * ((ceil(H/2)-1)*2+3-H)/2, Ho = ceil(H/2). */
+int de_im2col3x3(const void* x, void* out, int B, int H, int W, int C, int stride, int pad_y, int pad_x, int Ho,
+                 int Wo, void* stream);
+/* out[b,y,x,:] = x[b,y*s,x*s,:] (input gather of a 1x1 stride-s conv), NHWC bf16. */
+int de_subsample(const void* x, void* out, int B, int H, int W, int C, int stride, void* stream);
+/* GroupNorm over (HW, C/groups) per sample, NHWC bf16: out = act((x-mean)*rstd*gamma+beta [+ add]).
+ * stats_ws: device scratch of 2*B*groups doubles. (timm GroupNormAct, eps 1e-5, 32 groups.) */
+int de_groupnorm(const void* x, const float* gamma, const float* beta, const void* add, void* out, int B, int HW,
+                 int C, int groups, float eps, int act, void* stats_ws, void* stream);
 
 /* ---- direct (CUDA-core) convolutions for non-GEMM shapes; TF-"same" padding (geffnet Conv2dSame /
  * timm StdConv2dSame, MaxPool2dSame): pad_total = max((ceil(i/s)-1)*s+k-i, 0), extra pixel bottom/right. */

@@ -371,3 +371,38 @@ def test_maxpool():
         ref = F.max_pool2d(_tf_same_pad(x.float(), 3, 2, float("-inf")), 3, 2).permute(0, 2, 3, 1)
         torch.cuda.synchronize()
         assert torch.equal(out.float(), ref)
+
+
+@pytest.mark.parametrize("Cc,H,W,B", [(64, 96, 96, 1), (256, 48, 48, 2), (128, 24, 40, 2), (1024, 12, 12, 1), (512, 7, 9, 3)])
+@pytest.mark.parametrize("with_add", [False, True])
+def test_groupnorm(Cc, H, W, B, with_add):
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    x = (_rand((B, H, W, Cc), dev, 2.0, seed=60) + 0.7).bfloat16()
+    g, b = _rand((Cc,), dev, seed=61), _rand((Cc,), dev, seed=62)
+    add = _rand((B, H, W, Cc), dev, seed=63).bfloat16() if with_add else None
+    out = torch.empty_like(x)
+    ws = torch.zeros(2 * B * 32, dtype=torch.float64, device=dev)
+    ops.groupnorm(x, g, b, out, ws, act=ops.ACT_RELU, add=add)
+    ref = F.group_norm(x.float().permute(0, 3, 1, 2), 32, g, b, 1e-5).permute(0, 2, 3, 1)
+    if with_add:
+        ref = ref + add.float()
+    ref = F.relu(ref)
+    torch.cuda.synchronize()
+    assert _relerr(out, ref) < 6e-3
+
+
+def test_subsample_and_same_im2col():
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    x = _rand((2, 10, 14, 32), dev, seed=64).bfloat16()
+    o = torch.empty((2, 5, 7, 32), dtype=torch.bfloat16, device=dev)
+    ops.subsample(x, o, 2)
+    torch.cuda.synchronize()
+    assert torch.equal(o, x[:, ::2, ::2])
+    col = torch.empty((2 * 5 * 7, 9 * 32), dtype=torch.bfloat16, device=dev)
+    ops.im2col3x3(x, col, 2, pad=(0, 0), out_hw=(5, 7))            # TF-same, even input: pad (0 before, 1 after)
+    xp = F.pad(x.float().permute(0, 3, 1, 2), [0, 1, 0, 1])
+    ref = F.unfold(xp, 3, stride=2).view(2, 32, 9, 35).permute(0, 3, 2, 1).reshape(70, 288)
+    torch.cuda.synchronize()
+    assert torch.equal(col.float(), ref)
