@@ -179,13 +179,17 @@ def instrumented_step(est, frames_dev, B, H, W):
             return r
         setattr(ops, name, inner)
 
+    shapes = []
+
     def gemm_flops(a, w, out, **k):
         N = k.get("N") or w.shape[0]
         if k.get("conv") is not None:
             b, h, ww, cin = k["conv"]
+            shapes.append(("conv3x3", b * h * ww, N, 9 * cin, k.get("act", 0)))
             return 2.0 * b * h * ww * N * 9 * cin
         M = k.get("M") or a.shape[0]
         K = k.get("K") or a.shape[1]
+        shapes.append(("gemm", M, N, K, k.get("act", 0)))
         return 2.0 * M * N * K
 
     for n in ("preprocess", "postprocess", "layernorm", "attention", "cast_tokens", "fill_cls", "upsample2x",
@@ -200,11 +204,23 @@ def instrumented_step(est, frames_dev, B, H, W):
         for n, fn in orig.items():
             setattr(ops, n, fn)
     agg = {}
+    per_shape = {}
+    gi = 0
     for name, e0, e1, fl in rec:
         d = agg.setdefault(name, {"launches": 0, "ms": 0.0, "flops": 0.0})
         d["launches"] += 1
-        d["ms"] += e0.elapsed_time(e1)
+        ms = e0.elapsed_time(e1)
+        d["ms"] += ms
         d["flops"] += fl
+        if name == "gemm":
+            ps = per_shape.setdefault(shapes[gi], [0, 0.0, 0.0])
+            ps[0] += 1
+            ps[1] += ms
+            ps[2] += fl
+            gi += 1
+    if os.environ.get("BENCH_DETAIL"):
+        for k, (n, ms, fl) in sorted(per_shape.items(), key=lambda kv: -kv[1][1]):
+            print(f"  {k}: launches={n} ms={ms:.3f} TFLOP/s={fl / (ms * 1e-3) / 1e12 if ms > 0 else 0:.1f}", file=sys.stderr)
     return agg
 
 

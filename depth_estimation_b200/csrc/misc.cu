@@ -157,85 +157,112 @@ __global__ void subsample_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloa
       *reinterpret_cast<const uint4*>(x + (((long long)b * H + oy * stride) * W + ox * stride) * C + c);
 }
 
-// ---------------------------------------------------------------- GroupNorm (NHWC bf16), two passes
-// pass 1: per-(sample, group) sum / sum of squares, block partials -> double atomics
-__global__ void __launch_bounds__(256) groupnorm_stats_kernel(const __nv_bfloat16* __restrict__ x, int HW, int C,
-                                                              int groups, int px_per_block, double* __restrict__ stats) {
-  __shared__ float s_sum[64], s_sq[64];
+// ---------------------------------------------------------------- GroupNorm (NHWC bf16), deterministic
+// pass 1: per-block partial (sum, sumsq) per group, fixed-order reductions (no atomics: bf16 storage makes
+//         last-bit noise visible as rounding flips, so the statistics must be bit-reproducible)
+// pass 2: fixed-order sum over blocks -> (mean, rstd)
+// pass 3: y = act((x-mean)*rstd*gamma + beta [+ add]) -> bf16 (and optionally an fp32 copy)
+__global__ void __launch_bounds__(256) groupnorm_partial_kernel(const __nv_bfloat16* __restrict__ x, int HW, int C,
+                                                                int groups, int px_per_block,
+                                                                double* __restrict__ partial) {
+  __shared__ float s_su[256 * 8], s_sq[256 * 8];
   const int b = blockIdx.y;
   const int vec = C >> 3;                    // 8-channel vectors per pixel
   const int lanes = 256 / vec;               // pixels processed concurrently
   const int v = threadIdx.x % vec, pl = threadIdx.x / vec;
-  if (threadIdx.x < 64) { s_sum[threadIdx.x] = 0.f; s_sq[threadIdx.x] = 0.f; }
-  __syncthreads();
   const int p0 = blockIdx.x * px_per_block;
   const int p1 = min(p0 + px_per_block, HW);
   float su[8], sq[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) su[j] = sq[j] = 0.f;
-  if (pl < lanes) {
-    for (int p = p0 + pl; p < p1; p += lanes) {
-      const uint4 t = *reinterpret_cast<const uint4*>(x + ((long long)b * HW + p) * C + v * 8);
-      const float f[8] = {bf16_lo(t.x), bf16_hi(t.x), bf16_lo(t.y), bf16_hi(t.y),
-                          bf16_lo(t.z), bf16_hi(t.z), bf16_lo(t.w), bf16_hi(t.w)};
+  for (int p = p0 + pl; p < p1; p += lanes) {
+    const uint4 t = *reinterpret_cast<const uint4*>(x + ((long long)b * HW + p) * C + v * 8);
+    const float f[8] = {bf16_lo(t.x), bf16_hi(t.x), bf16_lo(t.y), bf16_hi(t.y),
+                        bf16_lo(t.z), bf16_hi(t.z), bf16_lo(t.w), bf16_hi(t.w)};
 #pragma unroll
-      for (int j = 0; j < 8; ++j) { su[j] += f[j]; sq[j] = fmaf(f[j], f[j], sq[j]); }
-    }
-    const int cpg = C / groups;
+    for (int j = 0; j < 8; ++j) { su[j] += f[j]; sq[j] = fmaf(f[j], f[j], sq[j]); }
+  }
+  // s_[pl][channel]
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int g = (v * 8 + j) / cpg;
-      atomicAdd(&s_sum[g], su[j]);
-      atomicAdd(&s_sq[g], sq[j]);
-    }
+  for (int j = 0; j < 8; ++j) {
+    s_su[pl * C + v * 8 + j] = su[j];
+    s_sq[pl * C + v * 8 + j] = sq[j];
   }
   __syncthreads();
   if (threadIdx.x < groups) {
-    atomicAdd(&stats[((long long)b * groups + threadIdx.x) * 2], (double)s_sum[threadIdx.x]);
-    atomicAdd(&stats[((long long)b * groups + threadIdx.x) * 2 + 1], (double)s_sq[threadIdx.x]);
+    const int cpg = C / groups, g = threadIdx.x;
+    double a = 0.0, q = 0.0;
+    for (int c = g * cpg; c < (g + 1) * cpg; ++c)
+      for (int l = 0; l < lanes; ++l) {
+        a += (double)s_su[l * C + c];
+        q += (double)s_sq[l * C + c];
+      }
+    double* o = partial + (((long long)b * gridDim.x + blockIdx.x) * groups + g) * 2;
+    o[0] = a;
+    o[1] = q;
   }
 }
 
-// pass 2: y = act((x-mean)*rstd*gamma + beta [+ add])
-__global__ void groupnorm_apply_kernel(const __nv_bfloat16* __restrict__ x, const double* __restrict__ stats,
+__global__ void groupnorm_finalize_kernel(const double* __restrict__ partial, int nblocks, int groups, double n,
+                                          float eps, float2* __restrict__ stats, int total) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;   // (b, g)
+  if (i >= total) return;
+  const int b = i / groups, g = i % groups;
+  double a = 0.0, q = 0.0;
+  for (int k = 0; k < nblocks; ++k) {
+    const double* o = partial + (((long long)b * nblocks + k) * groups + g) * 2;
+    a += o[0];
+    q += o[1];
+  }
+  const double m = a / n;
+  double var = q / n - m * m;
+  if (var < 0) var = 0;
+  stats[i] = make_float2((float)m, (float)(1.0 / sqrt(var + (double)eps)));
+}
+
+__global__ void groupnorm_apply_kernel(const __nv_bfloat16* __restrict__ x, const float2* __restrict__ stats,
                                        const float* __restrict__ gamma, const float* __restrict__ beta,
-                                       const __nv_bfloat16* __restrict__ add, __nv_bfloat16* __restrict__ out, int B,
-                                       int HW, int C, int groups, float eps, int act) {
+                                       const void* __restrict__ add, int add_dtype, __nv_bfloat16* __restrict__ out,
+                                       float* __restrict__ out_f32, int B, int HW, int C, int groups, int act) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const int vec = C >> 3;
   if (i >= (long long)B * HW * vec) return;
   const int c0 = static_cast<int>(i % vec) * 8;
   const int b = static_cast<int>(i / ((long long)HW * vec));
   const int cpg = C / groups;
-  const double n = (double)HW * cpg;
   const uint4 t = *reinterpret_cast<const uint4*>(x + i * 8);
   float f[8] = {bf16_lo(t.x), bf16_hi(t.x), bf16_lo(t.y), bf16_hi(t.y), bf16_lo(t.z), bf16_hi(t.z), bf16_lo(t.w), bf16_hi(t.w)};
   float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (add) {
-    const uint4 u = *reinterpret_cast<const uint4*>(add + i * 8);
-    a[0] = bf16_lo(u.x); a[1] = bf16_hi(u.x); a[2] = bf16_lo(u.y); a[3] = bf16_hi(u.y);
-    a[4] = bf16_lo(u.z); a[5] = bf16_hi(u.z); a[6] = bf16_lo(u.w); a[7] = bf16_hi(u.w);
+    if (add_dtype == DE_DTYPE_F32) {
+      const float4 u0 = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(add) + i * 8);
+      const float4 u1 = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(add) + i * 8 + 4);
+      a[0] = u0.x; a[1] = u0.y; a[2] = u0.z; a[3] = u0.w; a[4] = u1.x; a[5] = u1.y; a[6] = u1.z; a[7] = u1.w;
+    } else {
+      const uint4 u = *reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(add) + i * 8);
+      a[0] = bf16_lo(u.x); a[1] = bf16_hi(u.x); a[2] = bf16_lo(u.y); a[3] = bf16_hi(u.y);
+      a[4] = bf16_lo(u.z); a[5] = bf16_hi(u.z); a[6] = bf16_lo(u.w); a[7] = bf16_hi(u.w);
+    }
   }
   int gprev = -1;
-  float mean = 0.f, rstd = 0.f;
+  float2 st = make_float2(0.f, 0.f);
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     const int g = (c0 + j) / cpg;
     if (g != gprev) {
-      const double s = stats[((long long)b * groups + g) * 2], q = stats[((long long)b * groups + g) * 2 + 1];
-      const double m = s / n;
-      double var = q / n - m * m;
-      if (var < 0) var = 0;
-      mean = (float)m;
-      rstd = (float)(1.0 / sqrt(var + (double)eps));
+      st = __ldg(stats + b * groups + g);
       gprev = g;
     }
-    float y = (f[j] - mean) * rstd * __ldg(gamma + c0 + j) + __ldg(beta + c0 + j) + a[j];
+    float y = (f[j] - st.x) * st.y * __ldg(gamma + c0 + j) + __ldg(beta + c0 + j) + a[j];
     if (act == DE_ACT_RELU) y = fmaxf(y, 0.f);
     f[j] = y;
   }
   *reinterpret_cast<uint4*>(out + i * 8) =
       make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+  if (out_f32) {
+    *reinterpret_cast<float4*>(out_f32 + i * 8) = make_float4(f[0], f[1], f[2], f[3]);
+    *reinterpret_cast<float4*>(out_f32 + i * 8 + 4) = make_float4(f[4], f[5], f[6], f[7]);
+  }
 }
 
 }  // namespace deb
@@ -312,26 +339,33 @@ extern "C" int de_subsample(const void* x, void* out, int B, int H, int W, int C
   return cuda_check_launch("subsample_kernel");
 }
 
-extern "C" int de_groupnorm(const void* x, const float* gamma, const float* beta, const void* add, void* out, int B,
-                            int HW, int C, int groups, float eps, int act, void* stats_ws, void* stream) {
-  if (!x || !gamma || !beta || !out || !stats_ws) return fail(DE_ERR_INVALID, "de_groupnorm: null pointer");
+extern "C" int de_groupnorm(const void* x, const float* gamma, const float* beta, const void* add, int add_dtype,
+                            void* out, float* out_f32, int B, int HW, int C, int groups, float eps, int act,
+                            void* ws, int64_t ws_bytes, void* stream) {
+  if (!x || !gamma || !beta || !out || !ws) return fail(DE_ERR_INVALID, "de_groupnorm: null pointer");
   if (C % 8 != 0 || C > 2048 || groups > 64 || groups < 1 || C % groups != 0 || 256 % (C / 8) != 0)
     return fail(DE_ERR_UNSUPPORTED, "de_groupnorm: C=%d groups=%d unsupported", C, groups);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  cudaError_t e = cudaMemsetAsync(stats_ws, 0, sizeof(double) * 2 * B * groups, st);
-  if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(groupnorm stats)");
-  // enough blocks to fill the GPU even at B=1
-  int px_per_block = (HW + 147) / 148;
+  int px_per_block = (HW + 147) / 148;      // enough blocks to fill the GPU even at B=1
   const int lanes = 256 / (C / 8);
   if (px_per_block < lanes * 4) px_per_block = lanes * 4;
-  dim3 grid((HW + px_per_block - 1) / px_per_block, B);
-  groupnorm_stats_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(x), HW, C, groups, px_per_block,
-                                              reinterpret_cast<double*>(stats_ws));
+  const int nblocks = (HW + px_per_block - 1) / px_per_block;
+  const int64_t stats_bytes = (int64_t)sizeof(float2) * B * groups;
+  const int64_t need = stats_bytes + (int64_t)sizeof(double) * 2 * B * nblocks * groups + 16;
+  if (ws_bytes < need) return fail(DE_ERR_INVALID, "de_groupnorm: workspace %lld < %lld bytes", (long long)ws_bytes, (long long)need);
+  float2* stats = reinterpret_cast<float2*>(ws);
+  double* partial = reinterpret_cast<double*>(reinterpret_cast<char*>(ws) + ((stats_bytes + 15) / 16) * 16);
+  dim3 grid(nblocks, B);
+  groupnorm_partial_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(x), HW, C, groups, px_per_block,
+                                                partial);
+  count_launch();
+  groupnorm_finalize_kernel<<<(B * groups + 127) / 128, 128, 0, st>>>(partial, nblocks, groups,
+                                                                     (double)HW * (C / groups), eps, stats, B * groups);
   count_launch();
   const long long n = (long long)B * HW * (C / 8);
   groupnorm_apply_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(
-      reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<const double*>(stats_ws), gamma, beta,
-      reinterpret_cast<const __nv_bfloat16*>(add), reinterpret_cast<__nv_bfloat16*>(out), B, HW, C, groups, eps, act);
+      reinterpret_cast<const __nv_bfloat16*>(x), stats, gamma, beta, add, add_dtype,
+      reinterpret_cast<__nv_bfloat16*>(out), out_f32, B, HW, C, groups, act);
   count_launch();
   return cuda_check_launch("groupnorm kernels");
 }

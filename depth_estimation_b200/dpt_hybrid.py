@@ -66,7 +66,7 @@ class DPTHybridNet:
         self.dec = ScratchDecoder(sd, (256, 512, 768, 768), (256, 256, 256, 256), True, dev)
         self._bufs = {}
         self._x = {}
-        self._ws = torch.zeros(4096, dtype=torch.float64, device=dev)
+        self._ws = torch.zeros(4 << 20, dtype=torch.uint8, device=dev)
 
     def _buf(self, key, shape, dtype=torch.bfloat16):
         t = self._bufs.get(key)
@@ -75,12 +75,14 @@ class DPTHybridNet:
             self._bufs[key] = t
         return t
 
-    def _gn(self, x, nrm, key, act=ops.ACT_RELU, add=None):
+    def _gn(self, x, nrm, key, act=ops.ACT_RELU, add=None, want_f32=False):
         out = self._buf(key, tuple(x.shape))
-        assert 2 * x.shape[0] * 32 <= self._ws.numel()
-        return ops.groupnorm(x, nrm[0], nrm[1], out, self._ws, act=act, add=add)
+        o32 = self._buf((key, "f32"), tuple(x.shape), torch.float32) if want_f32 else None
+        ops.groupnorm(x, nrm[0], nrm[1], out, self._ws, act=act, add=add, out_f32=o32)
+        return out, o32
 
-    def _bottleneck(self, tag, blk: _Bottleneck, x, B, H, W):
+    def _bottleneck(self, tag, blk: _Bottleneck, x, x32, B, H, W):
+        """x: bf16 block input (GEMM operand); x32: the same tensor in fp32 (residual stream) or None."""
         s, mid, cout, cin = blk.stride, blk.mid, blk.cout, blk.cin
         Ho, Wo = (H + s - 1) // s, (W + s - 1) // s
         if blk.has_proj:
@@ -90,12 +92,12 @@ class DPTHybridNet:
                 ops.subsample(x, xs, s)
             d = self._buf((tag, "dc"), (B, Ho, Wo, cout))
             ops.gemm(xs.view(-1, cin), blk.wd, d.view(-1, cout))
-            shortcut = self._gn(d, blk.nd, (tag, "dn"), act=ops.ACT_NONE)
+            _, shortcut = self._gn(d, blk.nd, (tag, "dn"), act=ops.ACT_NONE, want_f32=True)
         else:
-            shortcut = x
+            shortcut = x32
         t = self._buf((tag, "c1"), (B, H, W, mid))
         ops.gemm(x.view(-1, cin), blk.w1, t.view(-1, mid))
-        t = self._gn(t, blk.n[0], (tag, "n1"))
+        t, _ = self._gn(t, blk.n[0], (tag, "n1"))
         u = self._buf((tag, "c2"), (B, Ho, Wo, mid))
         if s == 1:
             ops.gemm(t, blk.w2, u.view(-1, mid), conv=(B, H, W, mid), N=mid)
@@ -103,26 +105,27 @@ class DPTHybridNet:
             col = self._buf((tag, "col"), (B * Ho * Wo, 9 * mid))
             ops.im2col3x3(t, col, s, pad=(_same_pad_before(H, 3, s), _same_pad_before(W, 3, s)), out_hw=(Ho, Wo))
             ops.gemm(col, blk.w2, u.view(-1, mid))
-        u = self._gn(u, blk.n[1], (tag, "n2"))
+        u, _ = self._gn(u, blk.n[1], (tag, "n2"))
         v = self._buf((tag, "c3"), (B, Ho, Wo, cout))
         ops.gemm(u.view(-1, mid), blk.w3, v.view(-1, cout))
-        y = self._gn(v, blk.n[2], (tag, "n3"), act=ops.ACT_RELU, add=shortcut)
-        return y, Ho, Wo
+        y, y32 = self._gn(v, blk.n[2], (tag, "n3"), act=ops.ACT_RELU, add=shortcut, want_f32=True)
+        return y, y32, Ho, Wo
 
     def forward(self, x_nchw: torch.Tensor, B: int, net_h: int, net_w: int) -> torch.Tensor:
         """x_nchw: bf16 [B,3,net_h,net_w] from K1.  Returns fp32 [B, net_h, net_w] (>= 0)."""
         H, W = (net_h + 1) // 2, (net_w + 1) // 2
         s0 = self._buf(("stem", B, H, W), (B, H, W, 64))
         ops.stem_conv(x_nchw, self.stem_w, None, s0, 7, 2, ops.ACT_NONE)
-        s0 = self._gn(s0, self.stem_n, ("stemn", B, H, W))
+        s0, _ = self._gn(s0, self.stem_n, ("stemn", B, H, W))
         Hp, Wp = (H + 1) // 2, (W + 1) // 2
         x = self._buf(("pool", B, Hp, Wp), (B, Hp, Wp, 64))
         ops.maxpool3x3s2(s0, x)
         H, W = Hp, Wp
         stage_out = []
+        x32 = None
         for si, blocks in enumerate(self.stages):
             for bi, blk in enumerate(blocks):
-                x, H, W = self._bottleneck((si, bi, B, H, W), blk, x, B, H, W)
+                x, x32, H, W = self._bottleneck((si, bi, B, H, W), blk, x, x32, B, H, W)
             stage_out.append(x)
         gh, gw = net_h // 16, net_w // 16
         assert (H, W) == (gh, gw)

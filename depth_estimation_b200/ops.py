@@ -218,13 +218,16 @@ def subsample(x: torch.Tensor, out: torch.Tensor, stride: int):
 
 
 def groupnorm(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, out: torch.Tensor, ws: torch.Tensor,
-              act: int = ACT_RELU, add: torch.Tensor | None = None, groups: int = 32, eps: float = 1e-5):
-    """x: bf16 NHWC [B,H,W,C]; ws: float64 scratch with >= 2*B*groups elements."""
-    _need_cuda(x, gamma, beta, out, ws, add)
+              act: int = ACT_RELU, add: torch.Tensor | None = None, out_f32: torch.Tensor | None = None,
+              groups: int = 32, eps: float = 1e-5):
+    """x: bf16 NHWC [B,H,W,C]; ws: byte scratch (torch.uint8) - see include/depth_b200.h for the size."""
+    _need_cuda(x, gamma, beta, out, ws, add, out_f32)
     B, H, W, Cc = x.shape
-    assert x.dtype == torch.bfloat16 and x.is_contiguous() and ws.dtype == torch.float64 and ws.numel() >= 2 * B * groups
-    _lib.check(_lib.load().de_groupnorm(x.data_ptr(), gamma.data_ptr(), beta.data_ptr(), _ptr(add), out.data_ptr(), B,
-                                        H * W, Cc, groups, float(eps), act, ws.data_ptr(), _stream()), "de_groupnorm")
+    assert x.dtype == torch.bfloat16 and x.is_contiguous() and ws.dtype == torch.uint8
+    _lib.check(_lib.load().de_groupnorm(x.data_ptr(), gamma.data_ptr(), beta.data_ptr(), _ptr(add),
+                                        _dt(add) if add is not None else 0, out.data_ptr(), _ptr(out_f32), B, H * W,
+                                        Cc, groups, float(eps), act, ws.data_ptr(), ws.numel(), _stream()),
+               "de_groupnorm")
     return out
 
 

@@ -141,9 +141,13 @@ int de_im2col3x3(const void* x, void* out, int B, int H, int W, int C, int strid
 /* out[b,y,x,:] = x[b,y*s,x*s,:] (input gather of a 1x1 stride-s conv), NHWC bf16. */
 int de_subsample(const void* x, void* out, int B, int H, int W, int C, int stride, void* stream);
 /* GroupNorm over (HW, C/groups) per sample, NHWC bf16: out = act((x-mean)*rstd*gamma+beta [+ add]).
- * stats_ws: device scratch of 2*B*groups doubles. (timm GroupNormAct, eps 1e-5, 32 groups.) */
-int de_groupnorm(const void* x, const float* gamma, const float* beta, const void* add, void* out, int B, int HW,
-                 int C, int groups, float eps, int act, void* stats_ws, void* stream);
+ * add: bf16 or f32 (add_dtype), same shape, may be NULL.  out_f32: optional fp32 copy of the result (the
+ * ResNetV2 residual stream).  Deterministic (fixed-order reductions).  ws: device scratch of at least
+ * 8*B*groups + 16*B*groups*ceil(HW/max(ceil(HW/148), 4*256/(C/8))) + 32 bytes.
+ * (timm GroupNormAct, eps 1e-5, 32 groups.) */
+int de_groupnorm(const void* x, const float* gamma, const float* beta, const void* add, int add_dtype, void* out,
+                 float* out_f32, int B, int HW, int C, int groups, float eps, int act, void* ws, int64_t ws_bytes,
+                 void* stream);
 
 /* ---- direct (CUDA-core) convolutions for non-GEMM shapes; TF-"same" padding (geffnet Conv2dSame /
  * timm StdConv2dSame, MaxPool2dSame): pad_total = max((ceil(i/s)-1)*s+k-i, 0), extra pixel bottom/right. */

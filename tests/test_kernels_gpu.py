@@ -382,14 +382,19 @@ def test_groupnorm(Cc, H, W, B, with_add):
     g, b = _rand((Cc,), dev, seed=61), _rand((Cc,), dev, seed=62)
     add = _rand((B, H, W, Cc), dev, seed=63).bfloat16() if with_add else None
     out = torch.empty_like(x)
-    ws = torch.zeros(2 * B * 32, dtype=torch.float64, device=dev)
-    ops.groupnorm(x, g, b, out, ws, act=ops.ACT_RELU, add=add)
+    ws = torch.zeros(1 << 20, dtype=torch.uint8, device=dev)
+    o32 = torch.empty(x.shape, dtype=torch.float32, device=dev)
+    ops.groupnorm(x, g, b, out, ws, act=ops.ACT_RELU, add=add, out_f32=o32)
+    out_again = torch.empty_like(x)
+    ops.groupnorm(x, g, b, out_again, ws, act=ops.ACT_RELU, add=add.float() if with_add else None)
     ref = F.group_norm(x.float().permute(0, 3, 1, 2), 32, g, b, 1e-5).permute(0, 2, 3, 1)
     if with_add:
         ref = ref + add.float()
     ref = F.relu(ref)
     torch.cuda.synchronize()
     assert _relerr(out, ref) < 6e-3
+    assert _relerr(o32, ref) < 1e-4
+    assert torch.equal(out, out_again) and torch.equal(out, o32.bfloat16())      # deterministic
 
 
 def test_subsample_and_same_im2col():
