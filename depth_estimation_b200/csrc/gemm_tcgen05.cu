@@ -44,10 +44,11 @@ struct GemmParams {
   float head_b;
 };
 
-template <int BN>
+template <int BN, int CG>
 struct Cfg {
   static constexpr int kABytes = BM * BK * 2;
-  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kBRows = BN / CG;                 // rows of the W tile this CTA stages
+  static constexpr int kBBytes = kBRows * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStagesRaw = (196 * 1024) / kStageBytes;
   static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
@@ -62,10 +63,13 @@ DEV float apply_act(float v, int act) {
   return v;
 }
 
-template <int BN>
+// CG = 1: one CTA per 128 x BN tile.  CG = 2: a CTA pair (cluster of 2, cta_group::2) per 256 x BN tile -
+// each CTA stages its own 128 A rows and HALF of the W tile, one tcgen05.mma (M=256) drives both SMs, so
+// the L2->smem operand traffic per FLOP drops by a third and the W tile is fetched once per pair.
+template <int BN, int CG>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
-  using C = Cfg<BN>;
+  using C = Cfg<BN, CG>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
@@ -80,7 +84,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int num_tiles = p.m_tiles * p.n_tiles;
+  const uint32_t cta_rank = CG == 2 ? cluster_ctarank() : 0u;
+  const int unit = blockIdx.x / CG, num_units = gridDim.x / CG;
+  const int num_tiles = ((p.m_tiles + CG - 1) / CG) * p.n_tiles;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -93,46 +99,66 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);
-      mbar_init(&tempty[i], kEpiWarps);
+      mbar_init(&tempty[i], kEpiWarps * CG);
     }
     mbar_fence_init();
   }
   if (warp == 2) {
-    tmem_alloc(tmem_slot, C::kTmemCols);
-    tmem_relinquish();
+    if (CG == 2) {
+      tmem_alloc_cg2(tmem_slot, C::kTmemCols);
+      tmem_relinquish_cg2();
+    } else {
+      tmem_alloc(tmem_slot, C::kTmemCols);
+      tmem_relinquish();
+    }
   }
   tc_fence_before();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ------------------------------------------------------------- TMA producer
+    // ------------------------------------------------------------- TMA producer (one per CTA)
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
       const uint32_t a_bytes = p.a_mode == 0 ? C::kABytes : p.bw * p.bh * BK * 2;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m_tile = tile / p.n_tiles, n_tile = tile % p.n_tiles;
+      for (int tile = unit; tile < num_tiles; tile += num_units) {
+        const int m_tile = (tile / p.n_tiles) * CG + cta_rank, n_tile = tile % p.n_tiles;
         int b = 0, y0 = 0, x0 = 0;
         if (p.a_mode == 1) {
           const int per_img = p.tiles_x * p.tiles_y;
-          b = m_tile / per_img;
+          b = m_tile / per_img;                      // b >= B for the padding tile of an odd pair: TMA zero-fills
           const int t = m_tile % per_img;
           y0 = (t / p.tiles_x) * p.bh;
           x0 = (t % p.tiles_x) * p.bw;
         }
+        const int n_row = n_tile * BN + cta_rank * C::kBRows;
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
-          mbar_arrive_expect_tx(&full[stage], a_bytes + C::kBBytes);
-          if (p.a_mode == 0) {
-            tma_load_2d(sA + stage * C::kABytes, &tmA, &full[stage], kb * BK, m_tile * BM);
+          uint8_t* da = sA + stage * C::kABytes;
+          uint8_t* db = sB + stage * C::kBBytes;
+          if (CG == 1) {
+            mbar_arrive_expect_tx(&full[stage], a_bytes + C::kBBytes);
+            if (p.a_mode == 0) {
+              tma_load_2d(da, &tmA, &full[stage], kb * BK, m_tile * BM);
+            } else {
+              const int tap = kb / p.cin_blocks, cb = kb % p.cin_blocks;
+              tma_load_4d(da, &tmA, &full[stage], cb * BK, x0 + (tap % 3) - 1, y0 + (tap / 3) - 1, b);
+            }
+            tma_load_2d(db, &tmB, &full[stage], kb * BK, n_row);
           } else {
-            const int tap = kb / p.cin_blocks, cb = kb % p.cin_blocks;
-            tma_load_4d(sA + stage * C::kABytes, &tmA, &full[stage], cb * BK, x0 + (tap % 3) - 1, y0 + (tap / 3) - 1,
-                        b);
+            // both CTAs' bytes land on the LEADER's full barrier, which only the leader arms
+            if (cta_rank == 0) mbar_arrive_expect_tx(&full[stage], 2 * (a_bytes + C::kBBytes));
+            const uint32_t lead_full = mapa_u32(&full[stage], 0);
+            if (p.a_mode == 0) {
+              tma_load_2d_cg2(da, &tmA, lead_full, kb * BK, m_tile * BM);
+            } else {
+              const int tap = kb / p.cin_blocks, cb = kb % p.cin_blocks;
+              tma_load_4d_cg2(da, &tmA, lead_full, cb * BK, x0 + (tap % 3) - 1, y0 + (tap / 3) - 1, b);
+            }
+            tma_load_2d_cg2(db, &tmB, lead_full, kb * BK, n_row);
           }
-          tma_load_2d(sB + stage * C::kBBytes, &tmB, &full[stage], kb * BK, n_tile * BN);
           if (++stage == C::kStages) {
             stage = 0;
             phase ^= 1;
@@ -141,38 +167,46 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       }
     }
   } else if (warp == 1) {
-    // ------------------------------------------------------------- MMA issuer
-    constexpr uint32_t idesc = make_idesc_bf16(BM, BN);
-    int stage = 0;
-    uint32_t phase = 0;
-    int as = 0;
-    uint32_t aphase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      mbar_wait(&tempty[as], aphase ^ 1);
-      tc_fence_after();
-      const uint32_t d_tmem = tmem_base + as * BN;
-      for (int kb = 0; kb < p.num_k_blocks; ++kb) {
-        mbar_wait(&full[stage], phase);
+    // ------------------------------------------------------------- MMA issuer (leader CTA only)
+    if (cta_rank == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM * CG, BN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int as = 0;
+      uint32_t aphase = 0;
+      for (int tile = unit; tile < num_tiles; tile += num_units) {
+        mbar_wait(&tempty[as], aphase ^ 1);
         tc_fence_after();
-        if (lane == 0) {
-          const uint64_t adesc = make_sw128_kmajor_desc(smem_u32(sA + stage * C::kABytes));
-          const uint64_t bdesc = make_sw128_kmajor_desc(smem_u32(sB + stage * C::kBBytes));
+        const uint32_t d_tmem = tmem_base + as * BN;
+        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          if (lane == 0) {
+            const uint64_t adesc = make_sw128_kmajor_desc(smem_u32(sA + stage * C::kABytes));
+            const uint64_t bdesc = make_sw128_kmajor_desc(smem_u32(sB + stage * C::kBBytes));
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k) {
-            umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+            for (int k = 0; k < BK / 16; ++k) {
+              if (CG == 2) umma_bf16_cg2(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+              else umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+            }
+            if (CG == 2) {
+              umma_commit_cg2(&empty[stage], 3);
+              if (kb == p.num_k_blocks - 1) umma_commit_cg2(&tfull[as], 3);
+            } else {
+              umma_commit(&empty[stage]);
+              if (kb == p.num_k_blocks - 1) umma_commit(&tfull[as]);
+            }
           }
-          umma_commit(&empty[stage]);
-          if (kb == p.num_k_blocks - 1) umma_commit(&tfull[as]);
+          __syncwarp();
+          if (++stage == C::kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
         }
-        __syncwarp();
-        if (++stage == C::kStages) {
-          stage = 0;
-          phase ^= 1;
+        if (++as == 2) {
+          as = 0;
+          aphase ^= 1;
         }
-      }
-      if (++as == 2) {
-        as = 0;
-        aphase ^= 1;
       }
     }
   } else if (warp >= 4) {
@@ -187,8 +221,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const int bias_mod = p.bias_mod > 0 ? p.bias_mod : p.N;
     int as = 0;
     uint32_t aphase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int m_tile = tile / p.n_tiles, n_tile = tile % p.n_tiles;
+    for (int tile = unit; tile < num_tiles; tile += num_units) {
+      const int m_tile = (tile / p.n_tiles) * CG + cta_rank, n_tile = tile % p.n_tiles;
       // logical row index m of this thread's accumulator row, and validity
       long long m;
       bool valid;
@@ -199,7 +233,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         const int per_img = p.tiles_x * p.tiles_y;
         const int b = m_tile / per_img, t = m_tile % per_img;
         const int y = (t / p.tiles_x) * p.bh + r / p.bw, x = (t % p.tiles_x) * p.bw + r % p.bw;
-        valid = (r < p.bw * p.bh) && y < p.H && x < p.W;
+        valid = (m_tile < p.m_tiles) && (r < p.bw * p.bh) && y < p.H && x < p.W;
         m = (static_cast<long long>(b) * p.H + y) * p.W + x;
       }
       // storage row of out / add2 / out_relu
@@ -308,7 +342,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty[as]);
+      if (lane == 0) {
+        if (CG == 2 && cta_rank != 0) mbar_arrive_cluster(mapa_u32(&tempty[as], 0));
+        else mbar_arrive(&tempty[as]);
+      }
       if (++as == 2) {
         as = 0;
         aphase ^= 1;
@@ -317,10 +354,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all(); else __syncthreads();
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, C::kTmemCols);
+    if (CG == 2) tmem_dealloc_cg2(tmem_base, C::kTmemCols);
+    else tmem_dealloc(tmem_base, C::kTmemCols);
   }
 }
 
@@ -363,19 +401,33 @@ static void pick_conv_box(int H, int W, int* bw_out, int* bh_out) {
   *bh_out = bbh;
 }
 
-template <int BN>
+template <int BN, int CG>
 static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
-  using C = Cfg<BN>;
+  using C = Cfg<BN, CG>;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(gemm_kernel<BN, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(gemm)");
     attr_set = true;
   }
-  const int tiles = p.m_tiles * p.n_tiles;
-  const int grid = tiles < num_sms() ? tiles : num_sms();
-  gemm_kernel<BN><<<grid, kThreads, C::kSmemBytes, st>>>(ta, tb, p);
+  const int tiles = ((p.m_tiles + CG - 1) / CG) * p.n_tiles;
+  int units = num_sms() / CG;
+  if (tiles < units) units = tiles;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(units * CG);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = C::kSmemBytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CG;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_kernel<BN, CG>, ta, tb, p);
   count_launch();
+  if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(gemm_kernel)");
   return cuda_check_launch("gemm_kernel");
 }
 
@@ -392,6 +444,7 @@ extern "C" int de_gemm(const DeGemm* g, void* stream) {
   if (bn == 0) bn = g->N >= 256 ? 256 : (g->N > 64 ? 128 : (g->N > 32 ? 64 : 32));
   if (g->head_w && (g->N != 32 || bn != 32)) return fail(DE_ERR_INVALID, "de_gemm: head_w needs N == 32");
   if (g->out_rowmode == 2 && (g->ps_cout % 32 != 0)) return fail(DE_ERR_INVALID, "de_gemm: ps_cout %% 32 != 0");
+  int cg = g->cta_group;
   CUtensorMap ta, tb;
   int64_t ktot;
   if (g->a_mode == 0) {
@@ -427,7 +480,10 @@ extern "C" int de_gemm(const DeGemm* g, void* stream) {
   {
     const uint64_t dims[2] = {(uint64_t)ktot, (uint64_t)g->N};
     const uint64_t strides[1] = {(uint64_t)g->ldw * 2};
-    const uint32_t box[2] = {BK, (uint32_t)bn};
+    // pair mode: N a multiple of 256 and enough 256-row tile pairs to occupy the 74 SM pairs
+    if (cg == 0) cg = (bn == 256 && g->N % 256 == 0 && ((p.m_tiles + 1) / 2) * (g->N / 256) >= 64) ? 2 : 1;
+    if (cg == 2 && (bn != 256 || g->N % 256 != 0)) return fail(DE_ERR_INVALID, "de_gemm: cta_group 2 needs block_n 256 and N %% 256 == 0");
+    const uint32_t box[2] = {BK, (uint32_t)(bn / cg)};
     if (!make_map(&tb, g->w, 2, dims, strides, box)) return DE_ERR_CUDA;
   }
   p.n_tiles = (g->N + bn - 1) / bn;
@@ -453,10 +509,10 @@ extern "C" int de_gemm(const DeGemm* g, void* stream) {
   p.head_b = g->head_b;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   switch (bn) {
-    case 256: return launch<256>(ta, tb, p, st);
-    case 128: return launch<128>(ta, tb, p, st);
-    case 64: return launch<64>(ta, tb, p, st);
-    case 32: return launch<32>(ta, tb, p, st);
+    case 256: return cg == 2 ? launch<256, 2>(ta, tb, p, st) : launch<256, 1>(ta, tb, p, st);
+    case 128: return launch<128, 1>(ta, tb, p, st);
+    case 64: return launch<64, 1>(ta, tb, p, st);
+    case 32: return launch<32, 1>(ta, tb, p, st);
   }
   return fail(DE_ERR_INVALID, "de_gemm: block_n %d not in {32,64,128,256}", bn);
 }

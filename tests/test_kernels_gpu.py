@@ -106,6 +106,39 @@ def test_gemm_row_maps_tokens():
     assert _relerr(o, ref2) < 6e-3
 
 
+@pytest.mark.parametrize("M,N,K", [(256, 256, 64), (577, 1024, 1024), (18464, 3072, 1024), (1000, 512, 320), (4617, 256, 2304)])
+def test_gemm_cta_pair(M, N, K):
+    """cta_group::2 path: CTA pair per 256-row tile (odd 128-row tile counts included)."""
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    a = _rand((M, K), dev, seed=70).bfloat16()
+    w = _rand((N, K), dev, 0.05, seed=71).bfloat16()
+    bias = _rand((N,), dev, seed=72)
+    res = _rand((M, N), dev, seed=73)
+    out = torch.full((M, N), float("nan"), dtype=torch.float32, device=dev)
+    ops.gemm(a, w, out, bias=bias, add1=res, block_n=256, cta_group=2)
+    torch.cuda.synchronize()
+    ref = a.float() @ w.float().t() + bias + res
+    assert torch.isfinite(out).all()
+    assert _relerr(out, ref) < 2e-5, _relerr(out, ref)
+
+
+@pytest.mark.parametrize("B,H,W,Cin", [(3, 24, 24, 256), (1, 96, 96, 256), (5, 12, 12, 1024)])
+def test_conv3x3_cta_pair(B, H, W, Cin):
+    from depth_estimation_b200 import ops
+    from depth_estimation_b200.weights import pack_conv3x3
+    dev = _dev()
+    x = _rand((B, Cin, H, W), dev, seed=74).bfloat16()
+    wt = _rand((256, Cin, 3, 3), dev, 0.05, seed=75).bfloat16()
+    out = torch.full((B, H, W, 256), float("nan"), dtype=torch.float32, device=dev)
+    ops.gemm(x.permute(0, 2, 3, 1).contiguous(), pack_conv3x3(wt), out.view(-1, 256), conv=(B, H, W, Cin), N=256,
+             block_n=256, cta_group=2)
+    ref = F.conv2d(x.float(), wt.float(), None, padding=1).permute(0, 2, 3, 1)
+    torch.cuda.synchronize()
+    assert torch.isfinite(out).all()
+    assert _relerr(out, ref) < 2e-5
+
+
 CONV_CASES = [
     # B, H, W, Cin, Cout
     (2, 12, 12, 256, 256),
