@@ -23,6 +23,9 @@ constexpr int BM = 128;
 constexpr int BK = 64;
 constexpr int kEpiWarps = 8;
 constexpr int kThreads = 128 + 32 * kEpiWarps;
+constexpr int kStgStride = 36;                                  // floats per staged row (conflict-free float4 I/O)
+constexpr int kEpiWarpBytes = 32 * kStgStride * 4 + 2 * 32 * 8;   // staging tile + two int64 row tables
+constexpr int kSmemLimit = 232448;                              // 227 KB opt-in maximum per CTA
 
 struct GemmParams {
   int a_mode, M, N, num_k_blocks, m_tiles, n_tiles;
@@ -50,10 +53,11 @@ struct Cfg {
   static constexpr int kBRows = BN / CG;                 // rows of the W tile this CTA stages
   static constexpr int kBBytes = kBRows * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStagesRaw = (196 * 1024) / kStageBytes;
+  static constexpr int kEpiBytes = kEpiWarps * kEpiWarpBytes;
+  static constexpr int kStagesRaw = (kSmemLimit - 1024 - 256 - kEpiBytes) / kStageBytes;
   static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
   static constexpr int kTmemCols = (2 * BN) < 32 ? 32 : 2 * BN;
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/ + kEpiBytes;
 };
 
 DEV float apply_act(float v, int act) {
@@ -211,6 +215,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
   } else if (warp >= 4) {
     // ------------------------------------------------------------- epilogue
+    // TMEM -> registers (thread = accumulator row) -> per-warp smem staging tile -> re-read so that 8
+    // lanes cover 32 consecutive columns of one row: every global access (residual read, output write)
+    // is a fully used 64/128-byte row segment instead of 32 scattered 16-byte pieces.
     const int q = warp & 3;                      // TMEM lane quadrant this warp may access
     const int half = (warp - 4) >> 2;            // column half
     constexpr int kChunks = BN / 32;
@@ -219,132 +226,138 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const int c_end = kChunks >= 2 ? c_begin + kChunksPerHalf : (half == 0 ? 1 : 0);
     const int r = q * 32 + lane;
     const int bias_mod = p.bias_mod > 0 ? p.bias_mod : p.N;
+    uint8_t* epi = smem + C::kStages * C::kStageBytes + 256 + (warp - 4) * kEpiWarpBytes;
+    float* stg = reinterpret_cast<float*>(epi);                               // [32][36] fp32
+    long long* s_ro = reinterpret_cast<long long*>(epi + 32 * kStgStride * 4);  // out row offset (elements) or -1
+    long long* s_ar = s_ro + 32;                                              // add1 row offset (elements)
+    const int sub = lane >> 3, cc = (lane & 7) * 4;                           // read-back mapping
     int as = 0;
     uint32_t aphase = 0;
     for (int tile = unit; tile < num_tiles; tile += num_units) {
       const int m_tile = (tile / p.n_tiles) * CG + cta_rank, n_tile = tile % p.n_tiles;
-      // logical row index m of this thread's accumulator row, and validity
-      long long m;
-      bool valid;
-      if (p.a_mode == 0) {
-        m = static_cast<long long>(m_tile) * BM + r;
-        valid = m < p.M;
-      } else {
-        const int per_img = p.tiles_x * p.tiles_y;
-        const int b = m_tile / per_img, t = m_tile % per_img;
-        const int y = (t / p.tiles_x) * p.bh + r / p.bw, x = (t % p.tiles_x) * p.bw + r % p.bw;
-        valid = (m_tile < p.m_tiles) && (r < p.bw * p.bh) && y < p.H && x < p.W;
-        m = (static_cast<long long>(b) * p.H + y) * p.W + x;
+      {
+        // row-owner phase: logical row index m of accumulator row r, validity, storage offsets
+        long long m;
+        bool valid;
+        if (p.a_mode == 0) {
+          m = static_cast<long long>(m_tile) * BM + r;
+          valid = m < p.M;
+        } else {
+          const int per_img = p.tiles_x * p.tiles_y;
+          const int b = m_tile / per_img, t = m_tile % per_img;
+          const int y = (t / p.tiles_x) * p.bh + r / p.bw, x = (t % p.tiles_x) * p.bw + r % p.bw;
+          valid = (m_tile < p.m_tiles) && (r < p.bw * p.bh) && y < p.H && x < p.W;
+          m = (static_cast<long long>(b) * p.H + y) * p.W + x;
+        }
+        long long orow = m;
+        if (p.out_rowmode == 1) orow = m + (m / p.grp) * p.pad + p.off;
+        long long arow = orow;
+        if (p.add1_rowmode == 1) arow = m / p.grp;
+        else if (p.add1_rowmode == 2) arow = (m % p.grp) + p.off;
+        long long ro;
+        if (p.out_rowmode == 2) {
+          const int per = p.ps_gh * p.ps_gw;
+          const int ps_b = static_cast<int>(m / per), t = static_cast<int>(m % per);
+          const int ps_y = t / p.ps_gw, ps_x = t % p.ps_gw;
+          ro = ((static_cast<long long>(ps_b) * p.ps_gh * p.ps_s + ps_y * p.ps_s) * (p.ps_gw * p.ps_s) + ps_x * p.ps_s) *
+               p.ps_cout;
+        } else if (p.head_w) {
+          ro = orow;
+        } else {
+          ro = orow * p.ldo;
+        }
+        __syncwarp();
+        s_ro[lane] = valid ? ro : -1;
+        s_ar[lane] = arow * p.ld_add1;
       }
-      // storage row of out / add2 / out_relu
-      long long orow = m;
-      if (p.out_rowmode == 1) orow = m + (m / p.grp) * p.pad + p.off;
-      long long arow = orow;
-      if (p.add1_rowmode == 1) arow = m / p.grp;
-      else if (p.add1_rowmode == 2) arow = (m % p.grp) + p.off;
-      int ps_b = 0, ps_y = 0, ps_x = 0;
-      if (p.out_rowmode == 2) {
-        const int per = p.ps_gh * p.ps_gw;
-        ps_b = static_cast<int>(m / per);
-        const int t = static_cast<int>(m % per);
-        ps_y = t / p.ps_gw;
-        ps_x = t % p.ps_gw;
-      }
-
       mbar_wait(&tfull[as], aphase);
       tc_fence_after();
-      float head_acc = 0.f;
       for (int c = c_begin; c < c_end; ++c) {
         uint32_t acc[32];
-        __syncwarp();
+        __syncwarp();                            // previous chunk's read-back finished; row info visible
         tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN + c * 32, acc);
         tmem_ld_wait();
+        if (c == c_end - 1) {                    // accumulator fully drained into registers: release it early
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) {
+            if (CG == 2 && cta_rank != 0) mbar_arrive_cluster(mapa_u32(&tempty[as], 0));
+            else mbar_arrive(&tempty[as]);
+          }
+        }
+#pragma unroll
+        for (int j4 = 0; j4 < 8; ++j4)
+          *reinterpret_cast<float4*>(stg + lane * kStgStride + j4 * 4) =
+              make_float4(__uint_as_float(acc[j4 * 4]), __uint_as_float(acc[j4 * 4 + 1]),
+                          __uint_as_float(acc[j4 * 4 + 2]), __uint_as_float(acc[j4 * 4 + 3]));
+        __syncwarp();
         const int n0 = n_tile * BN + c * 32;
-        if (!valid || n0 >= p.N) continue;
-        long long obase;  // element offset of column n0 in out
-        int bcol = n0 % bias_mod;
+        if (n0 >= p.N) continue;
+        const bool col_ok = cc < p.N - n0;       // N % 8 == 0 and cc % 4 == 0: whole float4 in or out
+        long long colpart = n0 + cc;
         if (p.out_rowmode == 2) {
           const int g = n0 / p.ps_cout, co = n0 % p.ps_cout;
-          const int i = g / p.ps_s, j = g % p.ps_s;
-          obase = ((static_cast<long long>(ps_b) * p.ps_gh * p.ps_s + ps_y * p.ps_s + i) * (p.ps_gw * p.ps_s) +
-                   ps_x * p.ps_s + j) * p.ps_cout + co;
-        } else {
-          obase = orow * p.ldo + n0;
+          colpart = (static_cast<long long>(g / p.ps_s) * (p.ps_gw * p.ps_s) + g % p.ps_s) * p.ps_cout + co + cc;
         }
-        const int ncols = min(32, p.N - n0);  // multiple of 8
+        float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f), hw4 = bias4;
+        if (col_ok) {
+          if (p.bias) bias4 = __ldg(reinterpret_cast<const float4*>(p.bias + (n0 % bias_mod) + cc));
+          if (p.head_w) hw4 = __ldg(reinterpret_cast<const float4*>(p.head_w + n0 + cc));
+        }
 #pragma unroll
-        for (int g8 = 0; g8 < 4; ++g8) {
-          if (g8 * 8 >= ncols) break;
-          float v[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(acc[g8 * 8 + j]);
-          if (p.bias) {
-            const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + bcol + g8 * 8));
-            const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + bcol + g8 * 8 + 4));
-            v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
-            v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
-          }
-          float a1[8];
-          if (p.add1) {
+        for (int i = 0; i < 8; ++i) {
+          const int row = i * 4 + sub;
+          const long long ro = s_ro[row];
+          const bool live = col_ok && ro >= 0;
+          float4 v = *reinterpret_cast<const float4*>(stg + row * kStgStride + cc);
+          v.x += bias4.x; v.y += bias4.y; v.z += bias4.z; v.w += bias4.w;
+          float4 a1 = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (p.add1 && live) {
+            const long long ao = s_ar[row] + n0 + cc;
             if (p.add1_dtype == DE_DTYPE_F32) {
-              const float* ap = reinterpret_cast<const float*>(p.add1) + arow * p.ld_add1 + n0 + g8 * 8;
-              const float4 t0 = *reinterpret_cast<const float4*>(ap);
-              const float4 t1 = *reinterpret_cast<const float4*>(ap + 4);
-              a1[0] = t0.x; a1[1] = t0.y; a1[2] = t0.z; a1[3] = t0.w;
-              a1[4] = t1.x; a1[5] = t1.y; a1[6] = t1.z; a1[7] = t1.w;
+              a1 = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.add1) + ao);
             } else {
-              const __nv_bfloat16* ap = reinterpret_cast<const __nv_bfloat16*>(p.add1) + arow * p.ld_add1 + n0 + g8 * 8;
-              const uint4 t = *reinterpret_cast<const uint4*>(ap);
-              a1[0] = bf16_lo(t.x); a1[1] = bf16_hi(t.x); a1[2] = bf16_lo(t.y); a1[3] = bf16_hi(t.y);
-              a1[4] = bf16_lo(t.z); a1[5] = bf16_hi(t.z); a1[6] = bf16_lo(t.w); a1[7] = bf16_hi(t.w);
-            }
-            if (p.add1_pre) {
-#pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] += a1[j];
+              const uint2 t = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(p.add1) + ao);
+              a1 = make_float4(bf16_lo(t.x), bf16_hi(t.x), bf16_lo(t.y), bf16_hi(t.y));
             }
           }
-#pragma unroll
-          for (int j = 0; j < 8; ++j) v[j] = apply_act(v[j], p.act);
-          if (p.add1 && !p.add1_pre) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] += a1[j];
-          }
-          if (p.add2) {
-            const uint4 t = *reinterpret_cast<const uint4*>(p.add2 + obase + g8 * 8);
-            v[0] += bf16_lo(t.x); v[1] += bf16_hi(t.x); v[2] += bf16_lo(t.y); v[3] += bf16_hi(t.y);
-            v[4] += bf16_lo(t.z); v[5] += bf16_hi(t.z); v[6] += bf16_lo(t.w); v[7] += bf16_hi(t.w);
-          }
+          if (p.add1_pre) { v.x += a1.x; v.y += a1.y; v.z += a1.z; v.w += a1.w; }
+          v.x = apply_act(v.x, p.act); v.y = apply_act(v.y, p.act);
+          v.z = apply_act(v.z, p.act); v.w = apply_act(v.w, p.act);
+          if (!p.add1_pre) { v.x += a1.x; v.y += a1.y; v.z += a1.z; v.w += a1.w; }
           if (p.head_w) {
-            const float4 w0 = __ldg(reinterpret_cast<const float4*>(p.head_w + n0 + g8 * 8));
-            const float4 w1 = __ldg(reinterpret_cast<const float4*>(p.head_w + n0 + g8 * 8 + 4));
-            head_acc += v[0] * w0.x + v[1] * w0.y + v[2] * w0.z + v[3] * w0.w + v[4] * w1.x + v[5] * w1.y +
-                        v[6] * w1.z + v[7] * w1.w;
-          } else if (p.out_dtype == DE_DTYPE_F32) {
-            float* op = reinterpret_cast<float*>(p.out) + obase + g8 * 8;
-            *reinterpret_cast<float4*>(op) = make_float4(v[0], v[1], v[2], v[3]);
-            *reinterpret_cast<float4*>(op + 4) = make_float4(v[4], v[5], v[6], v[7]);
+            float d = v.x * hw4.x + v.y * hw4.y + v.z * hw4.z + v.w * hw4.w;
+            d += __shfl_xor_sync(0xffffffffu, d, 1);
+            d += __shfl_xor_sync(0xffffffffu, d, 2);
+            d += __shfl_xor_sync(0xffffffffu, d, 4);
+            if ((lane & 7) == 0 && ro >= 0) reinterpret_cast<float*>(p.out)[ro] = fmaxf(d + p.head_b, 0.f);
+            continue;
+          }
+          if (!live) continue;
+          const long long o = ro + colpart;
+          if (p.add2) {
+            const uint2 t = *reinterpret_cast<const uint2*>(p.add2 + o);
+            v.x += bf16_lo(t.x); v.y += bf16_hi(t.x); v.z += bf16_lo(t.y); v.w += bf16_hi(t.y);
+          }
+          if (p.out_dtype == DE_DTYPE_F32) {
+            *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + o) = v;
           } else {
-            uint4 o;
-            o.x = pack_bf16(v[0], v[1]); o.y = pack_bf16(v[2], v[3]);
-            o.z = pack_bf16(v[4], v[5]); o.w = pack_bf16(v[6], v[7]);
-            *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + obase + g8 * 8) = o;
+            *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.out) + o) =
+                make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
           }
           if (p.out_relu) {
-            uint4 o;
-            o.x = pack_bf16(fmaxf(v[0], 0.f), fmaxf(v[1], 0.f)); o.y = pack_bf16(fmaxf(v[2], 0.f), fmaxf(v[3], 0.f));
-            o.z = pack_bf16(fmaxf(v[4], 0.f), fmaxf(v[5], 0.f)); o.w = pack_bf16(fmaxf(v[6], 0.f), fmaxf(v[7], 0.f));
-            *reinterpret_cast<uint4*>(p.out_relu + obase + g8 * 8) = o;
+            *reinterpret_cast<uint2*>(p.out_relu + o) =
+                make_uint2(pack_bf16(fmaxf(v.x, 0.f), fmaxf(v.y, 0.f)), pack_bf16(fmaxf(v.z, 0.f), fmaxf(v.w, 0.f)));
           }
         }
       }
-      if (p.head_w && valid && c_end > c_begin) {
-        reinterpret_cast<float*>(p.out)[orow] = fmaxf(head_acc + p.head_b, 0.f);
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) {
-        if (CG == 2 && cta_rank != 0) mbar_arrive_cluster(mapa_u32(&tempty[as], 0));
-        else mbar_arrive(&tempty[as]);
+      if (c_end <= c_begin) {                    // idle column half (BN == 32): still hand the accumulator back
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          if (CG == 2 && cta_rank != 0) mbar_arrive_cluster(mapa_u32(&tempty[as], 0));
+          else mbar_arrive(&tempty[as]);
+        }
       }
       if (++as == 2) {
         as = 0;
