@@ -304,23 +304,35 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           if (p.bias) bias4 = __ldg(reinterpret_cast<const float4*>(p.bias + (n0 % bias_mod) + cc));
           if (p.head_w) hw4 = __ldg(reinterpret_cast<const float4*>(p.head_w + n0 + cc));
         }
+        // all global reads of the chunk are issued before any store (out may alias add1, so the compiler
+        // cannot hoist them itself): one memory round trip per chunk instead of eight
+        long long ro_[8];
+        float4 a1_[8];
+        uint2 a2_[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           const int row = i * 4 + sub;
-          const long long ro = s_ro[row];
-          const bool live = col_ok && ro >= 0;
-          float4 v = *reinterpret_cast<const float4*>(stg + row * kStgStride + cc);
-          v.x += bias4.x; v.y += bias4.y; v.z += bias4.z; v.w += bias4.w;
-          float4 a1 = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (p.add1 && live) {
+          ro_[i] = col_ok ? s_ro[row] : -1;
+          a1_[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+          a2_[i] = make_uint2(0u, 0u);
+          if (p.add1 && ro_[i] >= 0) {
             const long long ao = s_ar[row] + n0 + cc;
             if (p.add1_dtype == DE_DTYPE_F32) {
-              a1 = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.add1) + ao);
+              a1_[i] = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.add1) + ao);
             } else {
               const uint2 t = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(p.add1) + ao);
-              a1 = make_float4(bf16_lo(t.x), bf16_hi(t.x), bf16_lo(t.y), bf16_hi(t.y));
+              a1_[i] = make_float4(bf16_lo(t.x), bf16_hi(t.x), bf16_lo(t.y), bf16_hi(t.y));
             }
           }
+          if (p.add2 && ro_[i] >= 0) a2_[i] = *reinterpret_cast<const uint2*>(p.add2 + ro_[i] + colpart);
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int row = i * 4 + sub;
+          const long long ro = ro_[i];
+          float4 v = *reinterpret_cast<const float4*>(stg + row * kStgStride + cc);
+          v.x += bias4.x; v.y += bias4.y; v.z += bias4.z; v.w += bias4.w;
+          const float4 a1 = a1_[i];
           if (p.add1_pre) { v.x += a1.x; v.y += a1.y; v.z += a1.z; v.w += a1.w; }
           v.x = apply_act(v.x, p.act); v.y = apply_act(v.y, p.act);
           v.z = apply_act(v.z, p.act); v.w = apply_act(v.w, p.act);
@@ -330,15 +342,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             d += __shfl_xor_sync(0xffffffffu, d, 1);
             d += __shfl_xor_sync(0xffffffffu, d, 2);
             d += __shfl_xor_sync(0xffffffffu, d, 4);
-            if ((lane & 7) == 0 && ro >= 0) reinterpret_cast<float*>(p.out)[ro] = fmaxf(d + p.head_b, 0.f);
+            const long long hro = s_ro[row];
+            if ((lane & 7) == 0 && hro >= 0) reinterpret_cast<float*>(p.out)[hro] = fmaxf(d + p.head_b, 0.f);
             continue;
           }
-          if (!live) continue;
+          if (ro < 0) continue;
           const long long o = ro + colpart;
-          if (p.add2) {
-            const uint2 t = *reinterpret_cast<const uint2*>(p.add2 + o);
-            v.x += bf16_lo(t.x); v.y += bf16_hi(t.x); v.z += bf16_lo(t.y); v.w += bf16_hi(t.y);
-          }
+          v.x += bf16_lo(a2_[i].x); v.y += bf16_hi(a2_[i].x); v.z += bf16_lo(a2_[i].y); v.w += bf16_hi(a2_[i].y);
           if (p.out_dtype == DE_DTYPE_F32) {
             *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + o) = v;
           } else {
