@@ -24,7 +24,7 @@ constexpr int BK = 64;
 constexpr int kEpiWarps = 8;
 constexpr int kThreads = 128 + 32 * kEpiWarps;
 constexpr int kStgStride = 36;                                  // floats per staged row (conflict-free float4 I/O)
-constexpr int kEpiWarpBytes = 32 * kStgStride * 4 + 2 * 32 * 8;   // staging tile + two int64 row tables
+constexpr int kEpiWarpBytes = 32 * kStgStride * 4 + 2 * 32 * 8 + 4 * 32 * 4;   // staging tile + two int64 row tables + bias slice
 constexpr int kSmemLimit = 232448;                              // 227 KB opt-in maximum per CTA
 
 struct GemmParams {
@@ -45,6 +45,7 @@ struct GemmParams {
   int ps_gh, ps_gw, ps_s, ps_cout;
   const float* head_w;
   float head_b;
+  int debug;  // bit0: skip epilogue body (perf experiments only), bit1: skip global stores
 };
 
 template <int BN, int CG>
@@ -60,10 +61,35 @@ struct Cfg {
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/ + kEpiBytes;
 };
 
-DEV float apply_act(float v, int act) {
-  if (act == DE_ACT_RELU) return fmaxf(v, 0.f);
-  if (act == DE_ACT_GELU) return gelu_erf(v);
-  if (act == DE_ACT_RELU6) return fminf(fmaxf(v, 0.f), 6.f);
+// erf by Abramowitz-Stegun 7.1.26 (|abs err| <= 1.5e-7, branch-free: one rcp + one ex2) - far below the
+// bf16 rounding of the GELU output, and ~4x smaller than libdevice erff, which matters because the
+// epilogue's code footprint has to stay inside the instruction cache.
+DEV float fast_erf(float x) {
+  const float ax = fabsf(x);
+  float t;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, ax, 1.0f)));
+  float poly = fmaf(1.061405429f, t, -1.453152027f);
+  poly = fmaf(poly, t, 1.421413741f);
+  poly = fmaf(poly, t, -0.284496736f);
+  poly = fmaf(poly, t, 0.254829592f);
+  float e;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-1.4426950408889634f * ax * ax));
+  const float r = 1.0f - poly * t * e;
+  return copysignf(r, x);
+}
+// Kept out of line on purpose: one copy of the activation code per kernel instead of one per use.
+__device__ __noinline__ float4 apply_act4(float4 v, int act) {
+  if (act == DE_ACT_RELU) {
+    v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f);
+  } else if (act == DE_ACT_GELU) {
+    v.x = 0.5f * v.x * (1.0f + fast_erf(v.x * 0.70710678f));
+    v.y = 0.5f * v.y * (1.0f + fast_erf(v.y * 0.70710678f));
+    v.z = 0.5f * v.z * (1.0f + fast_erf(v.z * 0.70710678f));
+    v.w = 0.5f * v.w * (1.0f + fast_erf(v.w * 0.70710678f));
+  } else if (act == DE_ACT_RELU6) {
+    v.x = fminf(fmaxf(v.x, 0.f), 6.f); v.y = fminf(fmaxf(v.y, 0.f), 6.f);
+    v.z = fminf(fmaxf(v.z, 0.f), 6.f); v.w = fminf(fmaxf(v.w, 0.f), 6.f);
+  }
   return v;
 }
 
@@ -230,6 +256,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     float* stg = reinterpret_cast<float*>(epi);                               // [32][36] fp32
     long long* s_ro = reinterpret_cast<long long*>(epi + 32 * kStgStride * 4);  // out row offset (elements) or -1
     long long* s_ar = s_ro + 32;                                              // add1 row offset (elements)
+    float* s_bias = reinterpret_cast<float*>(s_ar + 32);                      // [kChunksPerHalf][32] bias slice
     const int sub = lane >> 3, cc = (lane & 7) * 4;                           // read-back mapping
     int as = 0;
     uint32_t aphase = 0;
@@ -270,8 +297,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         s_ro[lane] = valid ? ro : -1;
         s_ar[lane] = arow * p.ld_add1;
       }
+      // The tile's bias slice is fetched into this warp's smem BEFORE waiting for the accumulator: under
+      // saturating TMA traffic an L2 round trip costs thousands of cycles, so it overlaps the main loop.
+      if (p.bias) {
+        for (int ci = 0; ci < c_end - c_begin; ++ci) {
+          const int n = n_tile * BN + (c_begin + ci) * 32 + lane;
+          s_bias[ci * 32 + lane] = n < p.N ? __ldg(p.bias + (n % bias_mod)) : 0.f;
+        }
+      }
       mbar_wait(&tfull[as], aphase);
       tc_fence_after();
+#pragma unroll 1
       for (int c = c_begin; c < c_end; ++c) {
         uint32_t acc[32];
         __syncwarp();                            // previous chunk's read-back finished; row info visible
@@ -292,7 +328,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                           __uint_as_float(acc[j4 * 4 + 2]), __uint_as_float(acc[j4 * 4 + 3]));
         __syncwarp();
         const int n0 = n_tile * BN + c * 32;
-        if (n0 >= p.N) continue;
+        if (n0 >= p.N || (p.debug & 1)) continue;
         const bool col_ok = cc < p.N - n0;       // N % 8 == 0 and cc % 4 == 0: whole float4 in or out
         long long colpart = n0 + cc;
         if (p.out_rowmode == 2) {
@@ -300,10 +336,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           colpart = (static_cast<long long>(g / p.ps_s) * (p.ps_gw * p.ps_s) + g % p.ps_s) * p.ps_cout + co + cc;
         }
         float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f), hw4 = bias4;
-        if (col_ok) {
-          if (p.bias) bias4 = __ldg(reinterpret_cast<const float4*>(p.bias + (n0 % bias_mod) + cc));
-          if (p.head_w) hw4 = __ldg(reinterpret_cast<const float4*>(p.head_w + n0 + cc));
-        }
+        if (p.bias) bias4 = *reinterpret_cast<const float4*>(s_bias + (c - c_begin) * 32 + cc);
+        if (p.head_w && col_ok) hw4 = __ldg(reinterpret_cast<const float4*>(p.head_w + n0 + cc));
         // all global reads of the chunk are issued before any store (out may alias add1, so the compiler
         // cannot hoist them itself): one memory round trip per chunk instead of eight
         long long ro_[8];
@@ -334,8 +368,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           v.x += bias4.x; v.y += bias4.y; v.z += bias4.z; v.w += bias4.w;
           const float4 a1 = a1_[i];
           if (p.add1_pre) { v.x += a1.x; v.y += a1.y; v.z += a1.z; v.w += a1.w; }
-          v.x = apply_act(v.x, p.act); v.y = apply_act(v.y, p.act);
-          v.z = apply_act(v.z, p.act); v.w = apply_act(v.w, p.act);
+          if (p.act != DE_ACT_NONE) v = apply_act4(v, p.act);
           if (!p.add1_pre) { v.x += a1.x; v.y += a1.y; v.z += a1.z; v.w += a1.w; }
           if (p.head_w) {
             float d = v.x * hw4.x + v.y * hw4.y + v.z * hw4.z + v.w * hw4.w;
@@ -346,7 +379,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             if ((lane & 7) == 0 && hro >= 0) reinterpret_cast<float*>(p.out)[hro] = fmaxf(d + p.head_b, 0.f);
             continue;
           }
-          if (ro < 0) continue;
+          if (ro < 0 || (p.debug & 2)) continue;
           const long long o = ro + colpart;
           v.x += bf16_lo(a2_[i].x); v.y += bf16_hi(a2_[i].x); v.z += bf16_lo(a2_[i].y); v.w += bf16_hi(a2_[i].y);
           if (p.out_dtype == DE_DTYPE_F32) {
@@ -530,6 +563,7 @@ extern "C" int de_gemm(const DeGemm* g, void* stream) {
   p.ps_gh = g->ps_gh; p.ps_gw = g->ps_gw; p.ps_s = g->ps_s; p.ps_cout = g->ps_cout > 0 ? g->ps_cout : 1;
   p.head_w = g->head_w;
   p.head_b = g->head_b;
+  p.debug = g->debug;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   switch (bn) {
     case 256: return cg == 2 ? launch<256, 2>(ta, tb, p, st) : launch<256, 1>(ta, tb, p, st);

@@ -111,6 +111,7 @@ typedef struct DeGemm {
   const float* head_w;
   float head_b;
   int block_n; /* 0 = auto; else 32/64/128/256 */
+  int debug;     /* 0 in production; perf experiments: bit0 skip epilogue body, bit1 skip global stores */
   int cta_group; /* 0 = auto; 1 = one CTA per 128-row tile; 2 = CTA pair per 256-row tile (block_n 256) */
 } DeGemm;
 int de_gemm(const DeGemm* g, void* stream);
