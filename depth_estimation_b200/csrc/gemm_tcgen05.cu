@@ -48,17 +48,24 @@ struct GemmParams {
   int debug;  // bit0: skip epilogue body (perf experiments only), bit1: skip global stores
 };
 
-template <int BN, int CG>
+// EPI 0: "store" epilogue - bias + activation only, output tile staged in 128B-swizzled smem and written
+//        with TMA stores (no per-row address math, no LSU store traffic).
+// EPI 1: "general" epilogue - residual adds, row remaps, pixel shuffle, dual store, head dot.
+constexpr int kStoreBufBytes = BM * 128;                        // one 128-row x 128-byte output unit
+template <int BN, int CG, int EPI>
 struct Cfg {
   static constexpr int kABytes = BM * BK * 2;
   static constexpr int kBRows = BN / CG;                 // rows of the W tile this CTA stages
   static constexpr int kBBytes = kBRows * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kEpiBytes = kEpiWarps * kEpiWarpBytes;
-  static constexpr int kStagesRaw = (kSmemLimit - 1024 - 256 - kEpiBytes) / kStageBytes;
+  // after the stage ring - EPI 0: two 1024-aligned store buffers, mbarriers (256 B), bias slice (BN floats);
+  //                        EPI 1: mbarriers (256 B), per-warp staging areas.
+  static constexpr int kBarOff = EPI == 0 ? 2 * kStoreBufBytes : 0;           // relative to the end of the ring
+  static constexpr int kPostBytes = EPI == 0 ? 2 * kStoreBufBytes + 256 + 1024 : 256 + kEpiWarps * kEpiWarpBytes;
+  static constexpr int kStagesRaw = (kSmemLimit - 1024 - kPostBytes) / kStageBytes;
   static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
   static constexpr int kTmemCols = (2 * BN) < 32 ? 32 : 2 * BN;
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/ + kEpiBytes;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + kPostBytes;
 };
 
 // erf by Abramowitz-Stegun 7.1.26 (|abs err| <= 1.5e-7, branch-free: one rcp + one ex2) - far below the
@@ -96,16 +103,18 @@ __device__ __noinline__ float4 apply_act4(float4 v, int act) {
 // CG = 1: one CTA per 128 x BN tile.  CG = 2: a CTA pair (cluster of 2, cta_group::2) per 256 x BN tile -
 // each CTA stages its own 128 A rows and HALF of the W tile, one tcgen05.mma (M=256) drives both SMs, so
 // the L2->smem operand traffic per FLOP drops by a third and the W tile is fetched once per pair.
-template <int BN, int CG>
+template <int BN, int CG, int EPI>
 __global__ void __launch_bounds__(kThreads, 1)
-gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
-  using C = Cfg<BN, CG>;
+gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+            const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
+  using C = Cfg<BN, CG, EPI>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
   uint8_t* sA = smem;
   uint8_t* sB = smem + C::kStages * C::kABytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+  uint8_t* post = smem + C::kStages * C::kStageBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(post + C::kBarOff);
   uint64_t* full = bars;
   uint64_t* empty = bars + C::kStages;
   uint64_t* tfull = bars + 2 * C::kStages;
@@ -239,8 +248,121 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         }
       }
     }
+  } else if (warp >= 4 && EPI == 0) {
+    // ------------------------------------------------------------- store epilogue (bias + activation)
+    // Two groups of four warps (one warp per TMEM lane quadrant) alternate over 128-byte-wide column units.
+    // Per unit: TMEM -> registers, +bias, activation, pack; once the group's smem buffer has been drained by
+    // the previous TMA store, the 128 rows are written with the 128B swizzle and one thread issues the store.
+    const int q = warp & 3;
+    const int grp = (warp - 4) >> 2;
+    const int gtid = q * 32 + lane;                            // thread index inside the group == tile row
+    const int bar_id = 1 + grp;
+    const bool f32out = p.out_dtype == DE_DTYPE_F32;
+    const int ucols = f32out ? 32 : 64;                        // columns per 128-byte unit
+    const int units = BN / ucols;
+    uint8_t* sbuf = post + grp * kStoreBufBytes;
+    float* s_bias = reinterpret_cast<float*>(post + C::kBarOff + 256);
+    const int bias_mod = p.bias_mod > 0 ? p.bias_mod : p.N;
+    int as = 0;
+    uint32_t aphase = 0;
+    bool pending = false;                                      // this group has a store in flight on sbuf
+    for (int tile = unit; tile < num_tiles; tile += num_units) {
+      const int m_tile = (tile / p.n_tiles) * CG + cta_rank, n_tile = tile % p.n_tiles;
+      // bias slice of this group's units, fetched while the main loop of the tile is still running
+      for (int u = grp; u < units; u += 2) {
+        if (gtid < ucols) {
+          const int n = n_tile * BN + u * ucols + gtid;
+          s_bias[u * ucols + gtid] = (p.bias && n < p.N) ? __ldg(p.bias + (n % bias_mod)) : 0.f;
+        }
+      }
+      int b = 0, y0 = 0, x0 = 0;
+      if (p.a_mode == 1) {
+        const int per_img = p.tiles_x * p.tiles_y;
+        b = m_tile / per_img;
+        const int t = m_tile % per_img;
+        y0 = (t / p.tiles_x) * p.bh;
+        x0 = (t % p.tiles_x) * p.bw;
+      }
+      mbar_wait(&tfull[as], aphase);
+      tc_fence_after();
+      named_bar_sync(bar_id, 128);                             // bias slice visible to the whole group
+      const int last_u = grp + ((units - 1 - grp) / 2) * 2;    // last unit this group handles (if any)
+      if (grp >= units) {                                      // idle group (narrow tiles): just hand TMEM back
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          if (CG == 2 && cta_rank != 0) mbar_arrive_cluster(mapa_u32(&tempty[as], 0));
+          else mbar_arrive(&tempty[as]);
+        }
+      }
+#pragma unroll 1
+      for (int u = grp; u < units; u += 2) {
+        uint32_t ov[32];
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN + u * ucols;
+        const float* bs = s_bias + u * ucols;
+        if (f32out) {
+          uint32_t acc[32];
+          tmem_ld_32x32(taddr, acc);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j4 = 0; j4 < 8; ++j4) {
+            const float4 bb = *reinterpret_cast<const float4*>(bs + j4 * 4);
+            float4 v = make_float4(__uint_as_float(acc[j4 * 4]) + bb.x, __uint_as_float(acc[j4 * 4 + 1]) + bb.y,
+                                   __uint_as_float(acc[j4 * 4 + 2]) + bb.z, __uint_as_float(acc[j4 * 4 + 3]) + bb.w);
+            if (p.act != DE_ACT_NONE) v = apply_act4(v, p.act);
+            ov[j4 * 4] = __float_as_uint(v.x); ov[j4 * 4 + 1] = __float_as_uint(v.y);
+            ov[j4 * 4 + 2] = __float_as_uint(v.z); ov[j4 * 4 + 3] = __float_as_uint(v.w);
+          }
+        } else {
+#pragma unroll
+          for (int hh = 0; hh < 2; ++hh) {
+            uint32_t acc[32];
+            tmem_ld_32x32(taddr + hh * 32, acc);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j4 = 0; j4 < 8; ++j4) {
+              const float4 bb = *reinterpret_cast<const float4*>(bs + hh * 32 + j4 * 4);
+              float4 v = make_float4(__uint_as_float(acc[j4 * 4]) + bb.x, __uint_as_float(acc[j4 * 4 + 1]) + bb.y,
+                                     __uint_as_float(acc[j4 * 4 + 2]) + bb.z, __uint_as_float(acc[j4 * 4 + 3]) + bb.w);
+              if (p.act != DE_ACT_NONE) v = apply_act4(v, p.act);
+              ov[hh * 16 + j4 * 2] = pack_bf16(v.x, v.y);
+              ov[hh * 16 + j4 * 2 + 1] = pack_bf16(v.z, v.w);
+            }
+          }
+        }
+        if (u == last_u) {                                     // accumulator drained: release it early
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) {
+            if (CG == 2 && cta_rank != 0) mbar_arrive_cluster(mapa_u32(&tempty[as], 0));
+            else mbar_arrive(&tempty[as]);
+          }
+        }
+        if (pending && gtid == 0) tma_store_wait_read<0>();    // previous store has finished reading sbuf
+        named_bar_sync(bar_id, 128);
+        uint8_t* rowp = sbuf + gtid * 128;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<uint4*>(rowp + ((j ^ (gtid & 7)) << 4)) =
+              make_uint4(ov[j * 4], ov[j * 4 + 1], ov[j * 4 + 2], ov[j * 4 + 3]);
+        fence_proxy_async_smem();
+        named_bar_sync(bar_id, 128);
+        if (gtid == 0 && m_tile < p.m_tiles && !(p.debug & 2)) {
+          const int col0 = n_tile * BN + u * ucols;
+          if (p.a_mode == 0) tma_store_2d(&tmC, sbuf, col0, m_tile * BM);
+          else tma_store_4d(&tmC, sbuf, col0, x0, y0, b);
+          tma_store_commit();
+        }
+        pending = true;
+      }
+      if (++as == 2) {
+        as = 0;
+        aphase ^= 1;
+      }
+    }
+    if (pending && gtid == 0) tma_store_wait_read<0>();        // smem must outlive the last store's read
   } else if (warp >= 4) {
-    // ------------------------------------------------------------- epilogue
+    // ------------------------------------------------------------- general epilogue
     // TMEM -> registers (thread = accumulator row) -> per-warp smem staging tile -> re-read so that 8
     // lanes cover 32 consecutive columns of one row: every global access (residual read, output write)
     // is a fully used 64/128-byte row segment instead of 32 scattered 16-byte pieces.
@@ -252,7 +374,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const int c_end = kChunks >= 2 ? c_begin + kChunksPerHalf : (half == 0 ? 1 : 0);
     const int r = q * 32 + lane;
     const int bias_mod = p.bias_mod > 0 ? p.bias_mod : p.N;
-    uint8_t* epi = smem + C::kStages * C::kStageBytes + 256 + (warp - 4) * kEpiWarpBytes;
+    uint8_t* epi = post + 256 + (warp - 4) * kEpiWarpBytes;
     float* stg = reinterpret_cast<float*>(epi);                               // [32][36] fp32
     long long* s_ro = reinterpret_cast<long long*>(epi + 32 * kStgStride * 4);  // out row offset (elements) or -1
     long long* s_ar = s_ro + 32;                                              // add1 row offset (elements)
@@ -422,11 +544,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 // host side
 // ------------------------------------------------------------------------------------------------
 static bool make_map(CUtensorMap* map, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
-                     const uint32_t* box) {
+                     const uint32_t* box, CUtensorMapDataType dtype = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16) {
   auto fn = get_tensor_map_encoder();
   if (!fn) return false;
   uint32_t estr[5] = {1, 1, 1, 1, 1};
-  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), dims, strides_bytes, box, estr,
+  CUresult r = fn(map, dtype, rank, const_cast<void*>(base), dims, strides_bytes, box, estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -457,12 +579,15 @@ static void pick_conv_box(int H, int W, int* bw_out, int* bh_out) {
   *bh_out = bbh;
 }
 
-template <int BN, int CG>
-static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
-  using C = Cfg<BN, CG>;
+template <int BN, int CG, int EPI>
+static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const GemmParams& p,
+                  cudaStream_t st) {
+  using C = Cfg<BN, CG, EPI>;
+  static_assert(C::kStages >= 2, "smem budget leaves too few pipeline stages");
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_kernel<BN, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(gemm_kernel<BN, CG, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         C::kSmemBytes);
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(gemm)");
     attr_set = true;
   }
@@ -481,7 +606,7 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_kernel<BN, CG>, ta, tb, p);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_kernel<BN, CG, EPI>, ta, tb, tc, p);
   count_launch();
   if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(gemm_kernel)");
   return cuda_check_launch("gemm_kernel");
@@ -565,11 +690,34 @@ extern "C" int de_gemm(const DeGemm* g, void* stream) {
   p.head_b = g->head_b;
   p.debug = g->debug;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  // epilogue flavour: the TMA-store epilogue covers "bias + activation -> dense output"
+  const int es = g->out_dtype == DE_DTYPE_F32 ? 4 : 2;
+  bool store_epi = !g->add1 && !g->add2 && !g->out_relu && !g->head_w && g->out_rowmode == 0 && bn >= 64 &&
+                   (g->ldo * es) % 16 == 0 && (reinterpret_cast<uintptr_t>(g->out) & 15) == 0 &&
+                   (g->a_mode == 0 || g->ldo == g->N) && !(g->debug & 4);
+  CUtensorMap tc = tb;
+  if (store_epi) {
+    const CUtensorMapDataType dt = es == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    const uint32_t ucols = 128 / es;
+    if (g->a_mode == 0) {
+      const uint64_t dims[2] = {(uint64_t)g->N, (uint64_t)g->M};
+      const uint64_t strides[1] = {(uint64_t)g->ldo * es};
+      const uint32_t box[2] = {ucols, BM};
+      if (!make_map(&tc, g->out, 2, dims, strides, box, dt)) return DE_ERR_CUDA;
+    } else {
+      const uint64_t dims[4] = {(uint64_t)g->N, (uint64_t)g->W, (uint64_t)g->H, (uint64_t)g->B};
+      const uint64_t strides[3] = {(uint64_t)g->N * es, (uint64_t)g->W * g->N * es, (uint64_t)g->H * g->W * g->N * es};
+      const uint32_t box[4] = {ucols, (uint32_t)p.bw, (uint32_t)p.bh, 1};
+      if (!make_map(&tc, g->out, 4, dims, strides, box, dt)) return DE_ERR_CUDA;
+    }
+  }
   switch (bn) {
-    case 256: return cg == 2 ? launch<256, 2>(ta, tb, p, st) : launch<256, 1>(ta, tb, p, st);
-    case 128: return launch<128, 1>(ta, tb, p, st);
-    case 64: return launch<64, 1>(ta, tb, p, st);
-    case 32: return launch<32, 1>(ta, tb, p, st);
+    case 256:
+      if (cg == 2) return store_epi ? launch<256, 2, 0>(ta, tb, tc, p, st) : launch<256, 2, 1>(ta, tb, tc, p, st);
+      return store_epi ? launch<256, 1, 0>(ta, tb, tc, p, st) : launch<256, 1, 1>(ta, tb, tc, p, st);
+    case 128: return store_epi ? launch<128, 1, 0>(ta, tb, tc, p, st) : launch<128, 1, 1>(ta, tb, tc, p, st);
+    case 64: return store_epi ? launch<64, 1, 0>(ta, tb, tc, p, st) : launch<64, 1, 1>(ta, tb, tc, p, st);
+    case 32: return launch<32, 1, 1>(ta, tb, tc, p, st);
   }
   return fail(DE_ERR_INVALID, "de_gemm: block_n %d not in {32,64,128,256}", bn);
 }

@@ -7,23 +7,35 @@
 
 namespace deb {
 
-// ---------------------------------------------------------------- LayerNorm (one warp per row)
+// ---------------------------------------------------------------- (residual add +) LayerNorm, one warp per row
+// x (fp32 token stream) is optionally updated in place with x += y (the branch output a GEMM just wrote),
+// then normalised to bf16.  Folding the residual add here keeps the GEMM epilogues load-free (TMA-store
+// path) and hides the extra read behind the massive parallelism of a bandwidth kernel.
 template <int VEC>  // VEC float4 per lane: dim = 128*VEC
-__global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict__ x, long long ldx,
-                                                        const float* __restrict__ gamma,
+__global__ void __launch_bounds__(256) layernorm_kernel(float* __restrict__ x, long long ldx, const float* __restrict__ y,
+                                                        long long ldy, const float* __restrict__ gamma,
                                                         const float* __restrict__ beta, int rows, float eps,
                                                         __nv_bfloat16* __restrict__ out, long long ldo) {
   const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (row >= rows) return;
-  const float4* xr = reinterpret_cast<const float4*>(x + (long long)row * ldx);
+  float4* xr = reinterpret_cast<float4*>(x + (long long)row * ldx);
   float4 v[VEC];
   float sum = 0.f;
 #pragma unroll
-  for (int i = 0; i < VEC; ++i) {
-    v[i] = xr[lane + i * 32];
-    sum += v[i].x + v[i].y + v[i].z + v[i].w;
+  for (int i = 0; i < VEC; ++i) v[i] = xr[lane + i * 32];
+  if (y) {
+    const float4* yr = reinterpret_cast<const float4*>(y + (long long)row * ldy);
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) {
+      const float4 t = yr[lane + i * 32];
+      v[i].x += t.x; v[i].y += t.y; v[i].z += t.z; v[i].w += t.w;
+      xr[lane + i * 32] = v[i];
+    }
   }
+  if (!out) return;
+#pragma unroll
+  for (int i = 0; i < VEC; ++i) sum += v[i].x + v[i].y + v[i].z + v[i].w;
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
   const float mean = sum / (128.f * VEC);
@@ -269,16 +281,17 @@ __global__ void groupnorm_apply_kernel(const __nv_bfloat16* __restrict__ x, cons
 
 using namespace deb;
 
-extern "C" int de_layernorm(const float* x, int64_t ldx, const float* gamma, const float* beta, int rows, int dim,
-                            float eps, void* out_bf16, int64_t ldo, void* stream) {
-  if (!x || !gamma || !beta || !out_bf16 || rows <= 0) return fail(DE_ERR_INVALID, "de_layernorm: bad args");
-  if (dim % 128 != 0 || dim > 1024 || ldx % 4 != 0 || ldo % 4 != 0)
+extern "C" int de_layernorm(float* x, int64_t ldx, const float* y, int64_t ldy, const float* gamma, const float* beta,
+                            int rows, int dim, float eps, void* out_bf16, int64_t ldo, void* stream) {
+  if (!x || rows <= 0 || (out_bf16 && (!gamma || !beta)) || (!out_bf16 && !y))
+    return fail(DE_ERR_INVALID, "de_layernorm: bad args");
+  if (dim % 128 != 0 || dim > 1024 || ldx % 4 != 0 || ldo % 4 != 0 || (y && ldy % 4 != 0))
     return fail(DE_ERR_UNSUPPORTED, "de_layernorm: dim %d must be a multiple of 128, <= 1024", dim);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out_bf16);
   const int grid = (rows + 7) / 8;
   switch (dim / 128) {
-#define LN_CASE(V) case V: layernorm_kernel<V><<<grid, 256, 0, st>>>(x, ldx, gamma, beta, rows, eps, o, ldo); break;
+#define LN_CASE(V) case V: layernorm_kernel<V><<<grid, 256, 0, st>>>(x, ldx, y, ldy, gamma, beta, rows, eps, o, ldo); break;
     LN_CASE(1) LN_CASE(2) LN_CASE(3) LN_CASE(4) LN_CASE(5) LN_CASE(6) LN_CASE(7) LN_CASE(8)
 #undef LN_CASE
   }

@@ -116,9 +116,11 @@ typedef struct DeGemm {
 } DeGemm;
 int de_gemm(const DeGemm* g, void* stream);
 
-/* ---- LayerNorm over the last dim (eps given), fp32 in -> bf16 out (timm ViT norm1/norm2). */
-int de_layernorm(const float* x, int64_t ldx, const float* gamma, const float* beta, int rows, int dim,
-                 float eps, void* out_bf16, int64_t ldo, void* stream);
+/* ---- (residual add +) LayerNorm over the last dim (timm ViT norm1/norm2, eps 1e-6).
+ * if y != NULL: x += y in place (fp32 residual stream; y = the branch output a GEMM wrote);
+ * if out_bf16 != NULL: out = LN(x) * gamma + beta in bf16.  At least one of y / out_bf16 is required. */
+int de_layernorm(float* x, int64_t ldx, const float* y, int64_t ldy, const float* gamma, const float* beta, int rows,
+                 int dim, float eps, void* out_bf16, int64_t ldo, void* stream);
 
 /* ---- multi-head self-attention on a packed qkv buffer (timm Attention.forward):
  * qkv: bf16 [B*T, 3*heads*64] (q | k | v, each heads x 64), out: bf16 [B*T, heads*64].

@@ -139,6 +139,50 @@ def test_conv3x3_cta_pair(B, H, W, Cin):
     assert _relerr(out, ref) < 2e-5
 
 
+@pytest.mark.parametrize("M,N,K,cg,bn", [(577, 1024, 1024, 0, 0), (18464, 3072, 1024, 2, 256), (1000, 512, 320, 2, 256),
+                                         (700, 128, 192, 1, 128), (333, 72, 136, 0, 0), (4617, 256, 256, 1, 256)])
+@pytest.mark.parametrize("act", [0, 2])
+@pytest.mark.parametrize("f32", [False, True])
+def test_gemm_store_epilogue(M, N, K, cg, bn, act, f32):
+    """TMA-store epilogue (bias + activation, dense output): bf16 / fp32, single CTA and CTA pair, N tails."""
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    a = _rand((M, K), dev, seed=80).bfloat16()
+    w = _rand((N, K), dev, 0.05, seed=81).bfloat16()
+    bias = _rand((N,), dev, seed=82)
+    out = torch.full((M, N), float("nan"), dtype=torch.float32 if f32 else torch.bfloat16, device=dev)
+    ops.gemm(a, w, out, bias=bias, act=act, block_n=bn, cta_group=cg)
+    ref = a.float() @ w.float().t() + bias
+    if act == 2:
+        ref = F.gelu(ref)
+    torch.cuda.synchronize()
+    assert torch.isfinite(out.float()).all()
+    assert _relerr(out, ref) < (2e-5 if f32 else 6e-3), _relerr(out, ref)
+    # the general epilogue (debug bit 2 forces it) must agree with the store epilogue
+    out2 = torch.empty_like(out)
+    ops.gemm(a, w, out2, bias=bias, act=act, block_n=bn, cta_group=cg, debug=4)
+    torch.cuda.synchronize()
+    assert torch.equal(out, out2)
+
+
+@pytest.mark.parametrize("B,H,W,Cin,Cout,cg", [(3, 24, 24, 256, 256, 2), (1, 96, 96, 256, 256, 2), (2, 21, 12, 64, 128, 0),
+                                               (2, 32, 40, 48, 64, 0), (1, 24, 42, 256, 256, 1)])
+def test_conv3x3_store_epilogue(B, H, W, Cin, Cout, cg):
+    from depth_estimation_b200 import ops
+    from depth_estimation_b200.weights import pack_conv3x3
+    dev = _dev()
+    x = _rand((B, Cin, H, W), dev, seed=83).bfloat16()
+    wt = _rand((Cout, Cin, 3, 3), dev, 0.05, seed=84).bfloat16()
+    bias = _rand((Cout,), dev, seed=85)
+    out = torch.full((B, H, W, Cout), float("nan"), dtype=torch.bfloat16, device=dev)
+    ops.gemm(x.permute(0, 2, 3, 1).contiguous(), pack_conv3x3(wt), out.view(-1, Cout), conv=(B, H, W, Cin), N=Cout,
+             bias=bias, act=1, cta_group=cg, block_n=256 if cg == 2 else 0)
+    ref = F.relu(F.conv2d(x.float(), wt.float(), bias, padding=1)).permute(0, 2, 3, 1)
+    torch.cuda.synchronize()
+    assert torch.isfinite(out.float()).all()
+    assert _relerr(out, ref) < 6e-3
+
+
 CONV_CASES = [
     # B, H, W, Cin, Cout
     (2, 12, 12, 256, 256),
@@ -239,6 +283,16 @@ def test_layernorm(dim):
     ref = F.layer_norm(x, (dim,), g, b, 1e-6)
     torch.cuda.synchronize()
     assert _relerr(out, ref) < 5e-3
+    # fused residual add: x += y in place, out = LN(x + y); and the add-only form
+    y = _rand((1155, dim), dev, seed=39)
+    x0 = x.clone()
+    ops.layernorm(x, g, b, 1e-6, out, y=y)
+    torch.cuda.synchronize()
+    assert torch.equal(x, x0 + y)
+    assert _relerr(out, F.layer_norm(x0 + y, (dim,), g, b, 1e-6)) < 5e-3
+    ops.layernorm(x, None, None, 1e-6, None, y=y)
+    torch.cuda.synchronize()
+    assert torch.equal(x, (x0 + y) + y)
 
 
 @pytest.mark.parametrize("B,T,heads", [(2, 577, 16), (1, 1009, 12), (3, 64, 4), (1, 65, 2)])
