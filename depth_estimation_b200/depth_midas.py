@@ -199,3 +199,65 @@ def _build_net(model_type, sd, device):
         from .midas_small import MidasSmallNet
         return MidasSmallNet(sd, device)
     raise ValueError(f"unknown model_type {model_type!r}; expected one of {MODEL_TYPES}")
+
+
+class VidStream(object):
+    """Headless counterpart of the reference wrapper (`depth_midas.py:38-85`): same constructor and method
+    names, no HighGUI (`waitKey`/`destroyAllWindows` have no meaning on a compute box).  `src` is a video path
+    (opened with cv2.VideoCapture when OpenCV is present) or any iterable of uint8 BGR frames; `output` is a
+    path for an MJPG file (needs OpenCV) or None, in which case the 3-channel uint8 frames are kept in
+    `self.outputs`."""
+
+    def __init__(self, estimator, src=None, output=None):
+        self.estimator = estimator
+        self.FPS = 1 / 30
+        self.FPS_MS = int(self.FPS * 1000)
+        self.video = None
+        self._frames = None
+        self.w = self.h = 0
+        if isinstance(src, str):
+            import cv2
+            self.video = cv2.VideoCapture(src)
+            self.video.set(cv2.CAP_PROP_BUFFERSIZE, 2)
+            self.w, self.h = int(self.video.get(3)), int(self.video.get(4))
+        elif src is not None:
+            self._frames = iter(src)
+        self.output = output
+        self.writer = None
+        self.outputs = []
+        self.status = None
+        self.frame = None
+        self.cnt = 0
+
+    def _read(self):
+        if self.video is not None:
+            return self.video.read()
+        try:
+            return True, next(self._frames)
+        except (StopIteration, TypeError):
+            return False, None
+
+    def update(self):
+        while True:
+            self.status, self.frame = self._read()
+            if not self.status:
+                break
+            self.cnt += 1
+            self.write_output()
+        if self.video is not None:
+            self.video.release()
+        if self.writer is not None:
+            self.writer.release()
+
+    def write_output(self):
+        prediction = self.estimator.predict(self.frame)
+        output = prediction.astype(np.uint8)                    # wraps, exactly like depth_midas.py:83
+        three_c = np.stack([output, output, output], axis=-1)   # cv2.merge([o, o, o])
+        if self.output is not None:
+            import cv2
+            if self.writer is None:
+                h, w = output.shape
+                self.writer = cv2.VideoWriter(str(self.output), cv2.VideoWriter_fourcc(*'MJPG'), 20, (w, h))
+            self.writer.write(three_c)
+        else:
+            self.outputs.append(three_c)

@@ -1,0 +1,2 @@
+"""Drop-in module name of the reference (`from midas import DepthEstimator`)."""
+from depth_estimation_b200.depth_midas import DepthEstimator, VidStream  # noqa: F401
