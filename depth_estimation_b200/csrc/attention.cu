@@ -181,9 +181,9 @@ __global__ void __launch_bounds__(AT_THREADS) attention_kernel(const __nv_bfloat
 
 }  // namespace deb
 
-extern "C" int de_attention(const void* qkv, void* out, int B, int T, int heads, float scale, void* stream) {
+extern "C" int de_attention_mma(const void* qkv, void* out, int B, int T, int heads, float scale, void* stream) {
   using namespace deb;
-  if (!qkv || !out || B <= 0 || T <= 0 || heads <= 0) return fail(DE_ERR_INVALID, "de_attention: bad args");
+  if (!qkv || !out || B <= 0 || T <= 0 || heads <= 0) return fail(DE_ERR_INVALID, "de_attention_mma: bad args");
   dim3 grid((T + AT_BM - 1) / AT_BM, heads, B);
   attention_kernel<<<grid, AT_THREADS, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const __nv_bfloat16*>(qkv), reinterpret_cast<__nv_bfloat16*>(out), T, heads,

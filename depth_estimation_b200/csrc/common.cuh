@@ -220,3 +220,25 @@ DEV float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 DEV float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xFFFF0000u); }
 
 }  // namespace deb
+
+namespace deb {
+// MN-major (the contiguous dimension is M/N, e.g. V[keys][d] used as the B operand with N = d), 128B swizzle:
+// rows of 128 bytes (64 bf16 along N) indexed by K, 8-row swizzle atoms 1024 B apart (SBO); one 64-wide
+// N block only, so LBO is unused.
+DEV uint64_t make_sw128_mnmajor_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFF) >> 4);
+  d |= static_cast<uint64_t>(1) << 16;
+  d |= static_cast<uint64_t>(1024 >> 4) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(2) << 61;
+  return d;
+}
+// instruction descriptor with an MN-major B operand (bit 16)
+__host__ __device__ constexpr uint32_t make_idesc_bf16_bmn(int M, int N) { return make_idesc_bf16(M, N) | (1u << 16); }
+DEV float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+}  // namespace deb

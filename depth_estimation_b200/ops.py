@@ -169,11 +169,11 @@ def layernorm(x: torch.Tensor, gamma, beta, eps: float, out, y: torch.Tensor | N
     return out
 
 
-def attention(qkv: torch.Tensor, out: torch.Tensor, B: int, T: int, heads: int, scale: float):
+def attention(qkv: torch.Tensor, out: torch.Tensor, B: int, T: int, heads: int, scale: float, legacy_mma: bool = False):
     _need_cuda(qkv, out)
     assert qkv.dtype == torch.bfloat16 and out.dtype == torch.bfloat16 and qkv.is_contiguous() and out.is_contiguous()
-    _lib.check(_lib.load().de_attention(qkv.data_ptr(), out.data_ptr(), B, T, heads, float(scale), _stream()),
-               "de_attention")
+    fn = _lib.load().de_attention_mma if legacy_mma else _lib.load().de_attention
+    _lib.check(fn(qkv.data_ptr(), out.data_ptr(), B, T, heads, float(scale), _stream()), "de_attention")
     return out
 
 

@@ -124,8 +124,11 @@ int de_layernorm(float* x, int64_t ldx, const float* y, int64_t ldy, const float
 
 /* ---- multi-head self-attention on a packed qkv buffer (timm Attention.forward):
  * qkv: bf16 [B*T, 3*heads*64] (q | k | v, each heads x 64), out: bf16 [B*T, heads*64].
- * softmax(q k^T * scale) v, non-causal, fp32 softmax. head_dim must be 64. */
+ * softmax(q k^T * scale) v, non-causal, fp32 softmax. head_dim must be 64.
+ * tcgen05/TMEM flash kernel: S and O tiles in tensor memory, Q/K/V by TMA, V consumed MN-major. */
 int de_attention(const void* qkv, void* out, int B, int T, int heads, float scale, void* stream);
+/* Same contract on the legacy mma.sync tensor path (flash-attention-2 style); kept as a cross-check. */
+int de_attention_mma(const void* qkv, void* out, int B, int T, int heads, float scale, void* stream);
 
 /* ---- small bandwidth kernels used between the GEMMs ---- */
 /* fp32 [rows, dim] (ldx) -> bf16 [rows', dim]: drops the first `skip` rows of every group of `grp`

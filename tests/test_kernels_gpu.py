@@ -295,14 +295,15 @@ def test_layernorm(dim):
     assert torch.equal(x, (x0 + y) + y)
 
 
-@pytest.mark.parametrize("B,T,heads", [(2, 577, 16), (1, 1009, 12), (3, 64, 4), (1, 65, 2)])
-def test_attention(B, T, heads):
+@pytest.mark.parametrize("B,T,heads", [(2, 577, 16), (1, 1009, 12), (3, 64, 4), (1, 65, 2), (2, 128, 1), (2, 129, 3), (5, 769, 16)])
+@pytest.mark.parametrize("legacy", [False, True])
+def test_attention(B, T, heads, legacy):
     from depth_estimation_b200 import ops
     dev = _dev()
     D = heads * 64
     qkv = _rand((B * T, 3 * D), dev, 1.0, seed=33).bfloat16()
     out = torch.full((B * T, D), float("nan"), dtype=torch.bfloat16, device=dev)
-    ops.attention(qkv, out, B, T, heads, 0.125)
+    ops.attention(qkv, out, B, T, heads, 0.125, legacy_mma=legacy)
     q, k, v = qkv.float().view(B, T, 3, heads, 64).permute(2, 0, 3, 1, 4)
     ref = F.scaled_dot_product_attention(q, k, v).transpose(1, 2).reshape(B * T, D)
     torch.cuda.synchronize()
