@@ -221,18 +221,11 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, __nv_bfloat16* __
 
 }  // namespace deb
 
-// defined in attention.cu (mma.sync flash kernel, kept as the cross-check implementation)
-extern "C" int de_attention_mma(const void* qkv, void* out, int B, int T, int heads, float scale, void* stream);
-
-extern "C" int de_attention(const void* qkv, void* out, int B, int T, int heads, float scale, void* stream) {
+// First tcgen05 attention kernel (two CTAs per SM, O folded in registers).  Superseded by attention_ws.cu; reachable
+// with DEB_ATTENTION=1 as a cross-check.
+extern "C" int de_attention_v1(const void* qkv, void* out, int B, int T, int heads, float scale, void* stream) {
   using namespace deb;
   if (!qkv || !out || B <= 0 || T <= 0 || heads <= 0) return fail(DE_ERR_INVALID, "de_attention: bad args");
-  static int impl = -1;
-  if (impl < 0) {
-    const char* e = getenv("DEB_ATTENTION");
-    impl = (e && e[0] == 'm') ? 1 : 0;
-  }
-  if (impl == 1) return de_attention_mma(qkv, out, B, T, heads, scale, stream);
   auto fn = get_tensor_map_encoder();
   if (!fn) return DE_ERR_CUDA;
   CUtensorMap tm;

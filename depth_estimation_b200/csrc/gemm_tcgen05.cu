@@ -68,31 +68,30 @@ struct Cfg {
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + kPostBytes;
 };
 
-// erf by Abramowitz-Stegun 7.1.26 (|abs err| <= 1.5e-7, branch-free: one rcp + one ex2) - far below the
-// bf16 rounding of the GELU output, and ~4x smaller than libdevice erff, which matters because the
-// epilogue's code footprint has to stay inside the instruction cache.
-DEV float fast_erf(float x) {
-  const float ax = fabsf(x);
-  float t;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, ax, 1.0f)));
-  float poly = fmaf(1.061405429f, t, -1.453152027f);
-  poly = fmaf(poly, t, 1.421413741f);
-  poly = fmaf(poly, t, -0.284496736f);
-  poly = fmaf(poly, t, 0.254829592f);
+// Exact-erf GELU (timm nn.GELU) without erf: with a = |x|, Phi(-a) = 0.5*erfc(a/sqrt2) = 2^-q(a), and
+//   GELU(x) = x*Phi(x) = relu(x) - a*Phi(-a)        (x>0: x - x*Phi(-x);  x<0: x*Phi(x) = -a*Phi(-a)).
+// q(a) - 1 is fitted by a degree-6 polynomial without constant term (weighted minimax on [0,6]; beyond that
+// 2^-q underflows smoothly).  fp32 evaluation: max abs error 1.9e-6, max relative error 1.3e-4 wherever
+// |GELU| > 1e-6 - two orders below the bf16 rounding of the stored value - in 6 FFMA + 1 MUFU.EX2 + FMNMX +
+// FFMA, half the instructions (and half the MUFU traffic) of an Abramowitz-Stegun erf.  The epilogue warps are
+// issue-bound on this code when K is short (fc1: K=1024), so the count is what matters.
+DEV float gelu_fast(float x) {
+  const float a = fabsf(x);
+  float p = fmaf(-2.771519575617276e-05f, a, 0.0006936242571100593f);
+  p = fmaf(p, a, -0.007728741969913244f);
+  p = fmaf(p, a, 0.052738506346940994f);
+  p = fmaf(p, a, 0.45929643511772156f);
+  p = fmaf(p, a, 1.1510614156723022f);
   float e;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-1.4426950408889634f * ax * ax));
-  const float r = 1.0f - poly * t * e;
-  return copysignf(r, x);
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(fmaf(-p, a, -1.0f)));
+  return fmaf(-a, e, fmaxf(x, 0.f));
 }
 // Kept out of line on purpose: one copy of the activation code per kernel instead of one per use.
 __device__ __noinline__ float4 apply_act4(float4 v, int act) {
   if (act == DE_ACT_RELU) {
     v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f);
   } else if (act == DE_ACT_GELU) {
-    v.x = 0.5f * v.x * (1.0f + fast_erf(v.x * 0.70710678f));
-    v.y = 0.5f * v.y * (1.0f + fast_erf(v.y * 0.70710678f));
-    v.z = 0.5f * v.z * (1.0f + fast_erf(v.z * 0.70710678f));
-    v.w = 0.5f * v.w * (1.0f + fast_erf(v.w * 0.70710678f));
+    v.x = gelu_fast(v.x); v.y = gelu_fast(v.y); v.z = gelu_fast(v.z); v.w = gelu_fast(v.w);
   } else if (act == DE_ACT_RELU6) {
     v.x = fminf(fmaxf(v.x, 0.f), 6.f); v.y = fminf(fmaxf(v.y, 0.f), 6.f);
     v.z = fminf(fmaxf(v.z, 0.f), 6.f); v.w = fminf(fmaxf(v.w, 0.f), 6.f);
@@ -220,9 +219,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
-          if (lane == 0) {
-            const uint64_t adesc = make_sw128_kmajor_desc(smem_u32(sA + stage * C::kABytes));
-            const uint64_t bdesc = make_sw128_kmajor_desc(smem_u32(sB + stage * C::kBBytes));
+          // elect_one in a converged warp (not `lane == 0`): ptxas then knows the operands are warp-uniform and
+          // emits the UTCHMMAs back to back; under a lane test it wraps every one in an ELECT / BRA.U.ANY
+          // uniformisation loop (~50-100 cycles per instruction - measured with scripts/umma_probe.cu).
+          const uint64_t adesc = make_sw128_kmajor_desc(smem_u32(sA + stage * C::kABytes));
+          const uint64_t bdesc = make_sw128_kmajor_desc(smem_u32(sB + stage * C::kBBytes));
+          if (elect_one()) {
 #pragma unroll
             for (int k = 0; k < BK / 16; ++k) {
               if (CG == 2) umma_bf16_cg2(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
@@ -314,19 +316,34 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             ov[j4 * 4 + 2] = __float_as_uint(v.z); ov[j4 * 4 + 3] = __float_as_uint(v.w);
           }
         } else {
+          uint32_t acc2[2][32];                              // both halves in flight: one TMEM round trip per unit
+          tmem_ld_32x32(taddr, acc2[0]);
+          tmem_ld_32x32(taddr + 32, acc2[1]);
+          tmem_ld_wait();
 #pragma unroll
           for (int hh = 0; hh < 2; ++hh) {
-            uint32_t acc[32];
-            tmem_ld_32x32(taddr + hh * 32, acc);
-            tmem_ld_wait();
+            const uint32_t* acc = acc2[hh];
+            if (p.act == DE_ACT_GELU) {                        // hot (ViT fc1): GELU inlined, no per-float4 call
 #pragma unroll
-            for (int j4 = 0; j4 < 8; ++j4) {
-              const float4 bb = *reinterpret_cast<const float4*>(bs + hh * 32 + j4 * 4);
-              float4 v = make_float4(__uint_as_float(acc[j4 * 4]) + bb.x, __uint_as_float(acc[j4 * 4 + 1]) + bb.y,
-                                     __uint_as_float(acc[j4 * 4 + 2]) + bb.z, __uint_as_float(acc[j4 * 4 + 3]) + bb.w);
-              if (p.act != DE_ACT_NONE) v = apply_act4(v, p.act);
-              ov[hh * 16 + j4 * 2] = pack_bf16(v.x, v.y);
-              ov[hh * 16 + j4 * 2 + 1] = pack_bf16(v.z, v.w);
+              for (int j4 = 0; j4 < 8; ++j4) {
+                const float4 bb = *reinterpret_cast<const float4*>(bs + hh * 32 + j4 * 4);
+                const float v0 = gelu_fast(__uint_as_float(acc[j4 * 4]) + bb.x);
+                const float v1 = gelu_fast(__uint_as_float(acc[j4 * 4 + 1]) + bb.y);
+                const float v2 = gelu_fast(__uint_as_float(acc[j4 * 4 + 2]) + bb.z);
+                const float v3 = gelu_fast(__uint_as_float(acc[j4 * 4 + 3]) + bb.w);
+                ov[hh * 16 + j4 * 2] = pack_bf16(v0, v1);
+                ov[hh * 16 + j4 * 2 + 1] = pack_bf16(v2, v3);
+              }
+            } else {
+#pragma unroll
+              for (int j4 = 0; j4 < 8; ++j4) {
+                const float4 bb = *reinterpret_cast<const float4*>(bs + hh * 32 + j4 * 4);
+                float4 v = make_float4(__uint_as_float(acc[j4 * 4]) + bb.x, __uint_as_float(acc[j4 * 4 + 1]) + bb.y,
+                                       __uint_as_float(acc[j4 * 4 + 2]) + bb.z, __uint_as_float(acc[j4 * 4 + 3]) + bb.w);
+                if (p.act != DE_ACT_NONE) v = apply_act4(v, p.act);
+                ov[hh * 16 + j4 * 2] = pack_bf16(v.x, v.y);
+                ov[hh * 16 + j4 * 2 + 1] = pack_bf16(v.z, v.w);
+              }
             }
           }
         }

@@ -58,6 +58,7 @@ class DepthEstimator(object):
             self._norm = _IMAGENET_NORM
         self.use_cuda_graph = use_cuda_graph
         self._plans = {}
+        self._pipes = {}
 
     # ------------------------------------------------------------------ reference surface
     def predict(self, img):
@@ -96,6 +97,39 @@ class DepthEstimator(object):
         B, H, W, _ = frames_u8.shape
         plan = self._plan(B, H, W, 0, False)
         return plan.run_device(frames_u8)
+
+    def predict_stream(self, batches, depth=2):
+        """Pipelined form of predict_batch for a stream of equally-shaped uint8 [B,H,W,3] BGR host batches
+        (the headless `VidStream.stream` loop of midas_mediapipe.py:32-129 feeds this): a generator that yields
+        one np.float32 [B,H,W] result per input batch, in order, keeping up to `depth` batches in flight.
+
+        Per slot: pinned staging buffers + a captured graph of K1 -> net -> K8.  H2D copies run on their own
+        stream, compute on a second, D2H on a third, chained by events, so the host-side memcpys and the PCIe
+        transfers of batch i+1 / i-1 overlap the kernels of batch i.  Every frame still crosses the host
+        boundary in both directions; only the serialisation point of depth_midas.py:23,34 is gone."""
+        depth = max(1, int(depth))
+        pending = []                                  # (slot, event_out)
+        pipe = None
+        idx = 0
+        with torch.cuda.device(self.device):
+            for frames in batches:
+                frames = np.ascontiguousarray(frames)
+                if frames.ndim != 4 or frames.shape[3] != 3 or frames.dtype != np.uint8:
+                    raise TypeError("predict_stream expects uint8 [B,H,W,3] BGR batches")
+                if pipe is None or pipe.shape != frames.shape or pipe.depth != depth:
+                    while pending:                    # geometry change: drain, then rebuild the slots
+                        yield pipe.collect(*pending.pop(0))
+                    pipe = self._pipes.get((frames.shape, depth))
+                    if pipe is None:
+                        pipe = _Pipeline(self, frames.shape, depth)
+                        self._pipes[(frames.shape, depth)] = pipe
+                if len(pending) == depth:
+                    yield pipe.collect(*pending.pop(0))
+                slot = idx % depth
+                pending.append((slot, pipe.submit(slot, frames)))
+                idx += 1
+            while pending:
+                yield pipe.collect(*pending.pop(0))
 
     # ------------------------------------------------------------------ internals
     def _transform_rgb(self, rgb, mt):
@@ -186,6 +220,61 @@ class _Plan:
     def run_device(self, frames_u8):
         self._compute(frames_u8)
         return self.d_map
+
+
+class _Pipeline:
+    """`depth` in-flight slots for predict_stream: per slot a pinned input / output pair, device input / output
+    buffers and a CUDA graph of the compute; three streams (H2D, compute, D2H) chained by events.  The network's
+    work buffers are shared between slots - safe because all compute is ordered on the one compute stream."""
+
+    def __init__(self, est: DepthEstimator, shape, depth):
+        self.est, self.shape, self.depth = est, tuple(shape), depth
+        B, H, W, _ = shape
+        dev = est.device
+        self.plans = [_Plan(est, B, H, W, 0, False) for _ in range(depth)]
+        self.s_in, self.s_compute, self.s_out = (torch.cuda.Stream(dev) for _ in range(3))
+        self.ev_in = [torch.cuda.Event() for _ in range(depth)]
+        self.ev_done = [torch.cuda.Event() for _ in range(depth)]
+        self.ev_out = [torch.cuda.Event() for _ in range(depth)]
+        self.graphs = [None] * depth
+        cur = torch.cuda.current_stream(dev)
+        self.s_compute.wait_stream(cur)
+        with torch.cuda.stream(self.s_compute):
+            self.plans[0]._compute(self.plans[0].d_in)          # allocate work buffers / tap tables
+        self.s_compute.synchronize()
+        if est.use_cuda_graph:
+            for i, p in enumerate(self.plans):
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=self.s_compute):
+                    p._compute(p.d_in)
+                self.graphs[i] = g
+        for e in self.ev_done + self.ev_out:                    # so the first waits are no-ops
+            e.record(self.s_compute)
+
+    def submit(self, slot, frames):
+        p = self.plans[slot]
+        p.h_in.numpy()[...] = frames                            # slot is free: its previous result was collected
+        self.s_in.wait_event(self.ev_done[slot])                # previous compute on this slot has consumed d_in
+        with torch.cuda.stream(self.s_in):
+            p.d_in.copy_(p.h_in, non_blocking=True)
+            self.ev_in[slot].record()
+        self.s_compute.wait_event(self.ev_in[slot])
+        self.s_compute.wait_event(self.ev_out[slot])            # previous D2H of this slot has drained d_map
+        with torch.cuda.stream(self.s_compute):
+            if self.graphs[slot] is not None:
+                self.graphs[slot].replay()
+            else:
+                p._compute(p.d_in)
+            self.ev_done[slot].record()
+        self.s_out.wait_event(self.ev_done[slot])
+        with torch.cuda.stream(self.s_out):
+            p.h_map.copy_(p.d_map, non_blocking=True)
+            self.ev_out[slot].record()
+        return self.ev_out[slot]
+
+    def collect(self, slot, ev):
+        ev.synchronize()
+        return self.plans[slot].h_map.numpy().copy()
 
 
 def _build_net(model_type, sd, device):

@@ -7,7 +7,7 @@ timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smok
 BENCH_DETAIL=1 timeout 900 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench exit $?"
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref exit $?"
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file gpurun_out/launches.csv \
-  python bench.py --steps 1 --warmup 3 --no-e2e --no-cpu-baseline > gpurun_out/ncu_list.log 2>&1; echo "ncu list exit $?"
+  python bench.py --steps 1 --warmup 3 --no-e2e --no-cpu-baseline --no-latency > gpurun_out/ncu_list.log 2>&1; echo "ncu list exit $?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:gemm_kernel --launch-skip 40 -c 12 -f -o gpurun_out/gemm_full \
-  python bench.py --steps 1 --warmup 3 --no-e2e --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1; echo "ncu full exit $?"
+  python bench.py --steps 1 --warmup 3 --no-e2e --no-cpu-baseline --no-latency > gpurun_out/ncu_full.log 2>&1; echo "ncu full exit $?"
 tail -3 gpurun_out/pytest_gpu.log; cat gpurun_out/bench.json

@@ -52,3 +52,23 @@ def test_predict_matches_oracle(mt, W, H, kind):
     assert np.array_equal(maps[0], out)
     assert samples[0, 0] == out[H // 2, W // 3] and samples[0, 1] == out[H - 1, W - 1]
     assert np.abs(metric[0] - ref / 2.54).max() / np.abs(ref / 2.54).max() < 1e-2
+
+
+def test_predict_stream_matches_predict_batch():
+    """The pipelined generator returns, in order, exactly what the blocking call returns - across slot reuse
+    (5 batches through 2 slots), a geometry change mid-stream and depth 1/3."""
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    from depth_estimation_b200.depth_midas import DepthEstimator
+    est = DepthEstimator("MiDaS_small", seed=0)
+    rng = np.random.default_rng(5)
+    a = [rng.integers(0, 256, (3, 240, 320, 3), dtype=np.uint8) for _ in range(5)]
+    b = [rng.integers(0, 256, (2, 96, 128, 3), dtype=np.uint8) for _ in range(3)]
+    want = [est.predict_batch(f) for f in a + b]
+    for depth in (2, 1, 3):
+        got = list(est.predict_stream(iter(a + b), depth=depth))
+        assert len(got) == len(want)
+        for g, w in zip(got, want):
+            assert g.shape == w.shape and np.array_equal(g, w)
+    with pytest.raises(TypeError):
+        list(est.predict_stream([np.zeros((2, 8, 8), np.uint8)]))
