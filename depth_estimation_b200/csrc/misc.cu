@@ -12,8 +12,8 @@ namespace deb {
 // then normalised to bf16.  Folding the residual add here keeps the GEMM epilogues load-free (TMA-store
 // path) and hides the extra read behind the massive parallelism of a bandwidth kernel.
 template <int VEC>  // VEC float4 per lane: dim = 128*VEC
-__global__ void __launch_bounds__(256) layernorm_kernel(float* __restrict__ x, long long ldx, const float* __restrict__ y,
-                                                        long long ldy, const float* __restrict__ gamma,
+__global__ void __launch_bounds__(256) layernorm_kernel(float* __restrict__ x, long long ldx, const void* __restrict__ y,
+                                                        int y_bf16, long long ldy, const float* __restrict__ gamma,
                                                         const float* __restrict__ beta, int rows, float eps,
                                                         __nv_bfloat16* __restrict__ out, long long ldo) {
   const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
@@ -24,8 +24,16 @@ __global__ void __launch_bounds__(256) layernorm_kernel(float* __restrict__ x, l
   float sum = 0.f;
 #pragma unroll
   for (int i = 0; i < VEC; ++i) v[i] = xr[lane + i * 32];
-  if (y) {
-    const float4* yr = reinterpret_cast<const float4*>(y + (long long)row * ldy);
+  if (y && y_bf16) {                               // branch output stored as bf16 by the GEMM epilogue
+    const uint2* yr = reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(y) + (long long)row * ldy);
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) {
+      const uint2 t = yr[lane + i * 32];
+      v[i].x += bf16_lo(t.x); v[i].y += bf16_hi(t.x); v[i].z += bf16_lo(t.y); v[i].w += bf16_hi(t.y);
+      xr[lane + i * 32] = v[i];
+    }
+  } else if (y) {
+    const float4* yr = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(y) + (long long)row * ldy);
 #pragma unroll
     for (int i = 0; i < VEC; ++i) {
       const float4 t = yr[lane + i * 32];
@@ -281,8 +289,8 @@ __global__ void groupnorm_apply_kernel(const __nv_bfloat16* __restrict__ x, cons
 
 using namespace deb;
 
-extern "C" int de_layernorm(float* x, int64_t ldx, const float* y, int64_t ldy, const float* gamma, const float* beta,
-                            int rows, int dim, float eps, void* out_bf16, int64_t ldo, void* stream) {
+extern "C" int de_layernorm(float* x, int64_t ldx, const void* y, int y_dtype, int64_t ldy, const float* gamma,
+                            const float* beta, int rows, int dim, float eps, void* out_bf16, int64_t ldo, void* stream) {
   if (!x || rows <= 0 || (out_bf16 && (!gamma || !beta)) || (!out_bf16 && !y))
     return fail(DE_ERR_INVALID, "de_layernorm: bad args");
   if (dim % 128 != 0 || dim > 1024 || ldx % 4 != 0 || ldo % 4 != 0 || (y && ldy % 4 != 0))
@@ -291,7 +299,7 @@ extern "C" int de_layernorm(float* x, int64_t ldx, const float* y, int64_t ldy, 
   __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out_bf16);
   const int grid = (rows + 7) / 8;
   switch (dim / 128) {
-#define LN_CASE(V) case V: layernorm_kernel<V><<<grid, 256, 0, st>>>(x, ldx, y, ldy, gamma, beta, rows, eps, o, ldo); break;
+#define LN_CASE(V) case V: layernorm_kernel<V><<<grid, 256, 0, st>>>(x, ldx, y, y_dtype == DE_DTYPE_BF16 ? 1 : 0, ldy, gamma, beta, rows, eps, o, ldo); break;
     LN_CASE(1) LN_CASE(2) LN_CASE(3) LN_CASE(4) LN_CASE(5) LN_CASE(6) LN_CASE(7) LN_CASE(8)
 #undef LN_CASE
   }

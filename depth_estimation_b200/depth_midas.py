@@ -59,6 +59,7 @@ class DepthEstimator(object):
         self.use_cuda_graph = use_cuda_graph
         self._plans = {}
         self._pipes = {}
+        self._replayed_launches = 0
 
     # ------------------------------------------------------------------ reference surface
     def predict(self, img):
@@ -91,12 +92,18 @@ class DepthEstimator(object):
             res.append(plan.h_metric.float().numpy().copy())
         return res[0] if len(res) == 1 else tuple(res)
 
-    def predict_device(self, frames_u8: torch.Tensor) -> torch.Tensor:
+    def predict_device(self, frames_u8: torch.Tensor, eager: bool = False) -> torch.Tensor:
         """Device-resident path: uint8 [B,H,W,3] BGR CUDA tensor -> fp32 [B,H,W] CUDA tensor (a buffer
-        owned by the estimator, overwritten by the next call).  No host copies, no sync."""
+        owned by the estimator, overwritten by the next call).  No host copies, no sync.  eager=True launches
+        the kernels one by one instead of replaying the captured graph (profiling / per-kernel timing)."""
         B, H, W, _ = frames_u8.shape
         plan = self._plan(B, H, W, 0, False)
-        return plan.run_device(frames_u8)
+        return plan.run_device(frames_u8, eager)
+
+    def kernel_launches(self) -> int:
+        """Kernels of libdepthb200.so this process has put on the GPU so far: direct launches (counted by the
+        library) plus, for every CUDA-graph replay, the launches that graph captured."""
+        return int(ops._lib.launch_count()) + self._replayed_launches
 
     def predict_stream(self, batches, depth=2):
         """Pipelined form of predict_batch for a stream of equally-shaped uint8 [B,H,W,3] BGR host batches
@@ -212,13 +219,38 @@ class _Plan:
             torch.cuda.current_stream().wait_stream(s)
             torch.cuda.synchronize()
             g = torch.cuda.CUDAGraph()
+            n0 = ops._lib.launch_count()
             with torch.cuda.graph(g):
                 self._body()
+            self._graph_launches = int(ops._lib.launch_count() - n0)
             self.graph = g
         self.graph.replay()
+        self.est._replayed_launches += self._graph_launches
 
-    def run_device(self, frames_u8):
-        self._compute(frames_u8)
+    def run_device(self, frames_u8, eager=False):
+        """Device-resident step.  With CUDA graphs on, the frames are copied (device to device, ~2 us per MB) into
+        the plan's static input buffer and the captured K1 -> net -> K8 graph is replayed: ~230 launches become
+        one, which removes the inter-kernel launch gaps (measured 0.4 ms of a 21 ms DPT_Large batch-32 step)."""
+        if eager or not self.est.use_cuda_graph:
+            self._compute(frames_u8)
+            return self.d_map
+        if self._dev_graph is None:
+            s = torch.cuda.Stream()
+            s.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s):
+                self._compute(self.d_in)                        # allocates work buffers / tap tables
+            torch.cuda.current_stream().wait_stream(s)
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            n0 = ops._lib.launch_count()
+            with torch.cuda.graph(g):
+                self._compute(self.d_in)
+            self._dev_graph_launches = int(ops._lib.launch_count() - n0)
+            self._dev_graph = g
+        if frames_u8.data_ptr() != self.d_in.data_ptr():
+            self.d_in.copy_(frames_u8, non_blocking=True)
+        self._dev_graph.replay()
+        self.est._replayed_launches += self._dev_graph_launches
         return self.d_map
 
 
@@ -245,8 +277,10 @@ class _Pipeline:
         if est.use_cuda_graph:
             for i, p in enumerate(self.plans):
                 g = torch.cuda.CUDAGraph()
+                n0 = ops._lib.launch_count()
                 with torch.cuda.graph(g, stream=self.s_compute):
                     p._compute(p.d_in)
+                self.graph_launches = int(ops._lib.launch_count() - n0)
                 self.graphs[i] = g
         for e in self.ev_done + self.ev_out:                    # so the first waits are no-ops
             e.record(self.s_compute)
@@ -263,6 +297,7 @@ class _Pipeline:
         with torch.cuda.stream(self.s_compute):
             if self.graphs[slot] is not None:
                 self.graphs[slot].replay()
+                self.est._replayed_launches += self.graph_launches
             else:
                 p._compute(p.d_in)
             self.ev_done[slot].record()

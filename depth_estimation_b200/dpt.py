@@ -9,6 +9,8 @@ fp32 softmax; decoder activations bf16 NHWC.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.nn.functional as F
 
@@ -72,7 +74,9 @@ class ViTEncoder:
         qkv = self._buf(("qkv", M), (M, 3 * D), torch.bfloat16)
         att = self._buf(("att", M), (M, D), torch.bfloat16)
         hid = self._buf(("hid", M), (M, 4 * D), torch.bfloat16)
-        ybuf = self._buf(("y", M), (M, D), torch.float32)
+        # branch outputs (attention proj / fc2) go to the LayerNorm-with-residual kernel as bf16: the fp32 stream x
+        # itself is never rounded, and the GEMM writes / the LN reads half the bytes (DEB_Y_F32=1 restores fp32)
+        ybuf = self._buf(("y", M), (M, D), torch.float32 if os.environ.get("DEB_Y_F32") else torch.bfloat16)
         scale = (D // self.heads) ** -0.5
         y = None                                    # pending branch output, folded into the next LayerNorm
         for i, w in enumerate(self.blocks):

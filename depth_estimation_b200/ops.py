@@ -162,8 +162,9 @@ def layernorm(x: torch.Tensor, gamma, beta, eps: float, out, y: torch.Tensor | N
     """out = LN(x [+ y]) in bf16; with y the fp32 stream x is updated in place (x += y).  out may be None."""
     _need_cuda(x, gamma, beta, out, y)
     assert x.dtype == torch.float32 and x.dim() == 2 and (out is None or out.dtype == torch.bfloat16)
-    assert y is None or (y.dtype == torch.float32 and y.shape == x.shape)
-    _lib.check(_lib.load().de_layernorm(x.data_ptr(), x.stride(0), _ptr(y), y.stride(0) if y is not None else 0,
+    assert y is None or (y.dtype in (torch.float32, torch.bfloat16) and y.shape == x.shape)
+    _lib.check(_lib.load().de_layernorm(x.data_ptr(), x.stride(0), _ptr(y), _dt(y) if y is not None else 0,
+                                        y.stride(0) if y is not None else 0,
                                         _ptr(gamma), _ptr(beta), x.shape[0], x.shape[1], float(eps), _ptr(out),
                                         out.stride(0) if out is not None else 0, _stream()), "de_layernorm")
     return out

@@ -117,10 +117,10 @@ typedef struct DeGemm {
 int de_gemm(const DeGemm* g, void* stream);
 
 /* ---- (residual add +) LayerNorm over the last dim (timm ViT norm1/norm2, eps 1e-6).
- * if y != NULL: x += y in place (fp32 residual stream; y = the branch output a GEMM wrote);
+ * if y != NULL: x += y in place (fp32 residual stream; y = the branch output a GEMM wrote, y_dtype f32 or bf16);
  * if out_bf16 != NULL: out = LN(x) * gamma + beta in bf16.  At least one of y / out_bf16 is required. */
-int de_layernorm(float* x, int64_t ldx, const float* y, int64_t ldy, const float* gamma, const float* beta, int rows,
-                 int dim, float eps, void* out_bf16, int64_t ldo, void* stream);
+int de_layernorm(float* x, int64_t ldx, const void* y, int y_dtype, int64_t ldy, const float* gamma, const float* beta,
+                 int rows, int dim, float eps, void* out_bf16, int64_t ldo, void* stream);
 
 /* ---- multi-head self-attention on a packed qkv buffer (timm Attention.forward):
  * qkv: bf16 [B*T, 3*heads*64] (q | k | v, each heads x 64), out: bf16 [B*T, heads*64].

@@ -324,6 +324,13 @@ def test_layernorm(dim):
     ops.layernorm(x, None, None, 1e-6, None, y=y)
     torch.cuda.synchronize()
     assert torch.equal(x, (x0 + y) + y)
+    # bf16 branch output (what the ViT GEMM epilogues write): the fp32 stream adds the exact bf16 value
+    yb = y.bfloat16()
+    x1 = x.clone()
+    ops.layernorm(x, g, b, 1e-6, out, y=yb)
+    torch.cuda.synchronize()
+    assert torch.equal(x, x1 + yb.float())
+    assert _relerr(out, F.layer_norm(x1 + yb.float(), (dim,), g, b, 1e-6)) < 5e-3
 
 
 @pytest.mark.parametrize("B,T,heads", [(2, 577, 16), (1, 1009, 12), (3, 64, 4), (1, 65, 2), (2, 128, 1), (2, 129, 3), (5, 769, 16)])
