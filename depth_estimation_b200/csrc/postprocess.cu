@@ -3,7 +3,7 @@
 //   prediction [B,h,w] -> bicubic (Keys A=-0.75, align_corners=False, ATen fp32 coordinate rule) to the
 //   source resolution [B,H,W] fp32, optionally also the bf16 "metric" map D*metric_scale (=D/2.54) and
 //   the interpolated values at a few (row,col) sample points (the iris centres).
-// One CTA per output tile: source window staged in smem, horizontal pass, vertical pass, 16-byte stores.
+// One CTA per output tile: horizontal pass from global into smem, vertical pass, 16-byte streaming stores.
 #include "common.cuh"
 #include "depth_b200.h"
 #include "host_util.h"
@@ -40,55 +40,71 @@ DEV float dot4(float a, float b, float c, float d, float4 w) {
   return acc;
 }
 
+// Tile = 128 output columns x TH output rows, 256 threads.
+//  phase A (horizontal): thread column c = tid & 127 is FIXED, so its 4 tap indices / weights live in registers for
+//    the whole tile; the 4 taps of every needed source row come straight from global memory (the prediction is small
+//    and L2/L1 resident - no staging copy), result into s_h[row][c].
+//  phase B (vertical): a warp owns one output row at a time (row taps are warp-uniform -> broadcast loads), each
+//    lane 4 adjacent columns: 4 conflict-free LDS.128, 16 FMA, one 16-byte streaming store (the warp writes 512
+//    contiguous bytes).  The output is written once and never re-read: st.global.cs keeps it from evicting the taps.
+// No integer division anywhere; the arithmetic order (dot4 horizontally, then dot4 vertically) is unchanged, so the
+// map is bit-identical to the sample kernel below.
+constexpr int kPostTW = 128;
+
 __global__ void __launch_bounds__(kPostThreads) postprocess_kernel(const PostParams p) {
   extern __shared__ __align__(16) uint8_t smem[];
-  float* s_src = reinterpret_cast<float*>(smem);        // [max_rows][max_cols]
-  float* s_h = s_src + p.max_rows * p.max_cols;         // [max_rows][TW]
+  float* s_h = reinterpret_cast<float*>(smem);          // [max_rows][128]
   const int tid = threadIdx.x;
   const int b = blockIdx.z;
-  const int ox0 = blockIdx.x * p.TW, oy0 = blockIdx.y * p.TH;
-  const int ncols = min(p.TW, p.W - ox0), nrows = min(p.TH, p.H - oy0);
-  const int xs = __ldg(p.xidx + ox0 * 4), xe = __ldg(p.xidx + (ox0 + ncols - 1) * 4 + 3);
+  const int ox0 = blockIdx.x * kPostTW, oy0 = blockIdx.y * p.TH;
+  const int ncols = min(kPostTW, p.W - ox0), nrows = min(p.TH, p.H - oy0);
   const int ys = __ldg(p.yidx + oy0 * 4), ye = __ldg(p.yidx + (oy0 + nrows - 1) * 4 + 3);
-  const int nr = ye - ys + 1, nc = xe - xs + 1;
+  const int nr = ye - ys + 1;
   const long long fbase = (long long)b * p.h * p.w;
 
-  for (int i = tid; i < nr * nc; i += kPostThreads) {
-    const int rr = i / nc, cc = i % nc;
-    s_src[rr * p.max_cols + cc] = load_pred(p.src, p.in_dtype, fbase + (long long)(ys + rr) * p.w + xs + cc);
+  {
+    const int c = tid & (kPostTW - 1);
+    const int cx = min(ox0 + c, p.W - 1);               // columns past the edge recompute the last one (never stored)
+    const int4 xi = __ldg(reinterpret_cast<const int4*>(p.xidx) + cx);
+    const float4 w = __ldg(reinterpret_cast<const float4*>(p.xw) + cx);
+    if (p.in_dtype == DE_DTYPE_F32) {
+      const float* src = reinterpret_cast<const float*>(p.src) + fbase + (long long)ys * p.w;
+      for (int rr = tid >> 7; rr < nr; rr += kPostThreads / kPostTW) {
+        const float* row = src + (long long)rr * p.w;
+        s_h[rr * kPostTW + c] = dot4(__ldg(row + xi.x), __ldg(row + xi.y), __ldg(row + xi.z), __ldg(row + xi.w), w);
+      }
+    } else {
+      const __nv_bfloat16* src = reinterpret_cast<const __nv_bfloat16*>(p.src) + fbase + (long long)ys * p.w;
+      for (int rr = tid >> 7; rr < nr; rr += kPostThreads / kPostTW) {
+        const __nv_bfloat16* row = src + (long long)rr * p.w;
+        s_h[rr * kPostTW + c] = dot4(__bfloat162float(row[xi.x]), __bfloat162float(row[xi.y]),
+                                     __bfloat162float(row[xi.z]), __bfloat162float(row[xi.w]), w);
+      }
+    }
   }
   __syncthreads();
-  for (int i = tid; i < nr * ncols; i += kPostThreads) {
-    const int rr = i / ncols, c = i % ncols;
-    const int4 xi = __ldg(reinterpret_cast<const int4*>(p.xidx) + ox0 + c);
-    const float4 w = __ldg(reinterpret_cast<const float4*>(p.xw) + ox0 + c);
-    const float* row = s_src + rr * p.max_cols - xs;
-    s_h[rr * p.TW + c] = dot4(row[xi.x], row[xi.y], row[xi.z], row[xi.w], w);
-  }
-  __syncthreads();
-  // vertical pass: 4 adjacent columns per thread when the tile is 4-aligned
-  const int quads = (ncols + 3) >> 2;
-  for (int i = tid; i < nrows * quads; i += kPostThreads) {
-    const int cq = i % quads, ry = i / quads;
+
+  const int cq = tid & 31, c0 = cq * 4;
+  if (c0 >= ncols) return;
+  const bool quad_in = c0 + 4 <= ncols;
+  for (int ry = tid >> 5; ry < nrows; ry += kPostThreads / 32) {
     const int oy = oy0 + ry;
     const int4 yi = __ldg(reinterpret_cast<const int4*>(p.yidx) + oy);
     const float4 w = __ldg(reinterpret_cast<const float4*>(p.yw) + oy);
-    const float* r0 = s_h + (yi.x - ys) * p.TW;
-    const float* r1 = s_h + (yi.y - ys) * p.TW;
-    const float* r2 = s_h + (yi.z - ys) * p.TW;
-    const float* r3 = s_h + (yi.w - ys) * p.TW;
+    const float4 a0 = *reinterpret_cast<const float4*>(s_h + (yi.x - ys) * kPostTW + c0);
+    const float4 a1 = *reinterpret_cast<const float4*>(s_h + (yi.y - ys) * kPostTW + c0);
+    const float4 a2 = *reinterpret_cast<const float4*>(s_h + (yi.z - ys) * kPostTW + c0);
+    const float4 a3 = *reinterpret_cast<const float4*>(s_h + (yi.w - ys) * kPostTW + c0);
     float v[4];
-    const int c0 = cq * 4;
-#pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const int c = min(c0 + e, ncols - 1);
-      v[e] = dot4(r0[c], r1[c], r2[c], r3[c], w);
-    }
+    v[0] = dot4(a0.x, a1.x, a2.x, a3.x, w);
+    v[1] = dot4(a0.y, a1.y, a2.y, a3.y, w);
+    v[2] = dot4(a0.z, a1.z, a2.z, a3.z, w);
+    v[3] = dot4(a0.w, a1.w, a2.w, a3.w, w);
     const long long o = ((long long)b * p.H + oy) * p.W + ox0 + c0;
-    const bool full = (c0 + 4 <= ncols) && ((o & 3) == 0);
+    const bool full = quad_in && ((o & 3) == 0);
     if (p.out_map) {
       if (full) {
-        *reinterpret_cast<float4*>(p.out_map + o) = make_float4(v[0], v[1], v[2], v[3]);
+        __stcs(reinterpret_cast<float4*>(p.out_map + o), make_float4(v[0], v[1], v[2], v[3]));
       } else {
         for (int e = 0; e < 4 && c0 + e < ncols; ++e) p.out_map[o + e] = v[e];
       }
@@ -98,7 +114,7 @@ __global__ void __launch_bounds__(kPostThreads) postprocess_kernel(const PostPar
         uint2 m;
         m.x = pack_bf16(v[0] * p.metric_scale, v[1] * p.metric_scale);
         m.y = pack_bf16(v[2] * p.metric_scale, v[3] * p.metric_scale);
-        *reinterpret_cast<uint2*>(p.out_metric + o) = m;
+        __stcs(reinterpret_cast<uint2*>(p.out_metric + o), m);
       } else {
         for (int e = 0; e < 4 && c0 + e < ncols; ++e) p.out_metric[o + e] = __float2bfloat16(v[e] * p.metric_scale);
       }
@@ -150,29 +166,21 @@ extern "C" int de_postprocess(const void* pred, int in_dtype, int B, int h, int 
   p.metric_scale = metric_scale;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (out_map || out_metric) {
-    static const int cand[][2] = {{128, 16}, {128, 8}, {64, 8}, {32, 8}, {32, 4}, {16, 2}, {4, 1}};
+    static const int cand[] = {32, 16, 8, 4, 2, 1};           // output rows per tile; 128 columns always
     size_t smem = 0;
     bool ok = false;
-    for (auto& c : cand) {
-      p.TW = c[0];
-      p.TH = c[1];
-      p.max_cols = tx->max_extent(p.TW);
+    for (int th : cand) {
+      p.TW = kPostTW;
+      p.TH = th;
+      p.max_cols = 0;
       p.max_rows = ty->max_extent(p.TH);
-      smem = sizeof(float) * ((size_t)p.max_rows * p.max_cols + (size_t)p.max_rows * p.TW);
-      if (smem <= 200 * 1024) {
+      smem = sizeof(float) * (size_t)p.max_rows * kPostTW;
+      if (smem <= 40 * 1024) {                                  // several CTAs per SM: the kernel lives on occupancy
         ok = true;
         break;
       }
     }
     if (!ok) return fail(DE_ERR_UNSUPPORTED, "de_postprocess: resampling window too large");
-    if (smem > 48 * 1024) {
-      static bool configured = false;
-      if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(postprocess_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(postprocess)");
-        configured = true;
-      }
-    }
     dim3 grid((W + p.TW - 1) / p.TW, (H + p.TH - 1) / p.TH, B);
     postprocess_kernel<<<grid, kPostThreads, smem, st>>>(p);
     count_launch();
