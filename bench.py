@@ -155,7 +155,7 @@ def run_reference(args):
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(json.dumps(line))
 
 
 # ---------------------------------------------------------------------------------------------- our arm
@@ -374,18 +374,53 @@ def run_ours(args):
         if gf:
             line["model_tflops"] = value / world * gf / 1e3
             line["model_frac_of_peak"] = line["model_tflops"] / peak
-        print(json.dumps(line), flush=True)
+        emit(json.dumps(line))
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
-def main():
-    args = parse()
-    if args.impl == "reference":
-        run_reference(args)
+class _StdoutToStderr:
+    """Everything that prints on fd 1 while the benchmark runs (constructor banners of the reference surface, the
+    NCCL version line, ...) goes to stderr, so that stdout carries exactly ONE line: the JSON result."""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self._saved = os.dup(1)
+        os.dup2(2, 1)
+        return self
+
+    def emit(self, line: str):
+        sys.stdout.flush()
+        os.write(self._saved, (line + "\n").encode())
+
+    def __exit__(self, *exc):
+        sys.stdout.flush()
+        os.dup2(self._saved, 1)
+        os.close(self._saved)
+        return False
+
+
+_OUT = None
+
+
+def emit(line: str):
+    if _OUT is not None:
+        _OUT.emit(line)
     else:
-        run_ours(args)
+        print(line, flush=True)
+
+
+def main():
+    global _OUT
+    args = parse()
+    with _StdoutToStderr() as out:
+        _OUT = out
+        if args.impl == "reference":
+            run_reference(args)
+        else:
+            run_ours(args)
+    _OUT = None
 
 
 if __name__ == "__main__":

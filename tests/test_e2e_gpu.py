@@ -43,7 +43,9 @@ def test_predict_matches_oracle(mt, W, H, kind):
     assert (ref > 0).mean() > 0.9
     rel, dyn = _errs(out, ref)
     print(f"{mt} {W}x{H} {kind}: rel={rel:.3e} dyn={dyn:.3e}")
-    assert rel < 1e-2, (rel, dyn)                  # bf16 metric-depth budget (1 %)
+    # north_star: relative inverse depth within 1e-3 (fp32 accumulate); DPT_Hybrid's ResNetV2 stem (GroupNorm on
+    # bf16 activations) currently sits at ~6e-3 under random init - inside the 1 % bf16 metric-depth budget only
+    assert rel < (1e-2 if mt == "DPT_Hybrid" else 1e-3), (rel, dyn)
     # graph replay gives the same answer, and the batched / metric / sample outputs agree
     out2 = est.predict(frame)
     assert np.array_equal(out, out2)
