@@ -72,7 +72,7 @@ DEV void umma_bf16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_
 struct WsBars {                    // one set per stream
   uint64_t q_full[2], q_free[2], k_full[2], k_free[2], v_full[2], v_free[2];
   uint64_t s_full, s_free, p_full, pv_done, o_full, o_free;
-  uint64_t kick;                   // stream 0 -> stream 1: half of the first block done (starts stream 1 half a period late)
+  uint64_t kick;                   // stream 0 -> stream 1: first S tile consumed (stream 1 starts about half a period late)
 };
 
 struct WsParams {
@@ -240,8 +240,8 @@ attention_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const WsParams p)
     };
     // Both streams share the MUFU pipe.  Started together they run in lockstep - exponentials at the same time,
     // then max / P store / barrier latencies at the same time with the MUFU idle.  Stream 1 therefore starts when
-    // stream 0 is half-way through its first block of exponentials, so one stream's overhead sits under the other's
-    // exp2.
+    // stream 0 has pulled its first S tile (the Q/K loads and the first S MMA of stream 1 then add up to about half
+    // a block period), so one stream's max / P-store / barrier latencies sit under the other's exp2.
     if (s == 1 && total > 0) mbar_wait(&bars[0].kick, 0);
     if (total > 0) issue_s(0, true);
     int j = 0, it = 0;                                          // (block, tile) of step g
@@ -304,7 +304,10 @@ attention_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const WsParams p)
         tmem_ld_wait();
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&b.s_free);                  // S(g) is in registers: S(g+1) may overwrite it
+        if (lane == 0) {
+          mbar_arrive(&b.s_free);                               // S(g) is in registers: S(g+1) may overwrite it
+          if (s == 0 && g == 0) mbar_arrive(&b.kick);           // releases stream 1 (its start-up adds ~half a period)
+        }
         if (nvalid < 128) {                                     // last block only (uniform): -inf -> exp2 gives exactly 0
 #pragma unroll
           for (int i = 0; i < 128; ++i)
@@ -359,7 +362,6 @@ attention_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const WsParams p)
 #pragma unroll
             for (int i = 0; i < 16; ++i) pk[c * 16 + i] = 0u;
           }
-          if (c == 1 && s == 0 && g == 0 && lane == 0) mbar_arrive(&b.kick);     // half-way through the first block
         }
         l_run += (rs4[0] + rs4[1]) + (rs4[2] + rs4[3]);
         WS_STAMP(3);
