@@ -21,6 +21,7 @@ struct PostParams {
   const float* yw;
   float* out_map;
   __nv_bfloat16* out_metric;
+  uint8_t* out_vis;
   float metric_scale;
   int TW, TH, max_rows, max_cols;
 };
@@ -30,6 +31,15 @@ constexpr int kPostThreads = 256;
 DEV float load_pred(const void* src, int in_dtype, long long i) {
   if (in_dtype == DE_DTYPE_F32) return __ldg(reinterpret_cast<const float*>(src) + i);
   return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(src)[i]);
+}
+// The reference's to_video_frame (midas_mediapipe.py:141-150 / depth_midas.py:83): img.astype(np.uint8), then the
+// in-place uint8 `*= 5`, `+= 10` - both wrap modulo 256.  numpy's float32 -> uint8 cast on x86-64 truncates toward
+// zero to int32 and keeps the low byte (NaN / out-of-int32-range give 0x80000000 -> 0).
+DEV uint32_t vis_byte(float v) {
+  int t;
+  asm("cvt.rzi.s32.f32 %0, %1;" : "=r"(t) : "f"(v));
+  if (!(fabsf(v) < 2147483648.f)) t = static_cast<int>(0x80000000u);   // cvttss2si's "integer indefinite"
+  return (static_cast<uint32_t>(t) * 5u + 10u) & 0xffu;
 }
 // fixed evaluation order so the tile kernel and the sample kernel agree bit for bit
 DEV float dot4(float a, float b, float c, float d, float4 w) {
@@ -109,6 +119,14 @@ __global__ void __launch_bounds__(kPostThreads) postprocess_kernel(const PostPar
         for (int e = 0; e < 4 && c0 + e < ncols; ++e) p.out_map[o + e] = v[e];
       }
     }
+    if (p.out_vis) {
+      if (full) {
+        *reinterpret_cast<uint32_t*>(p.out_vis + o) =
+            vis_byte(v[0]) | (vis_byte(v[1]) << 8) | (vis_byte(v[2]) << 16) | (vis_byte(v[3]) << 24);
+      } else {
+        for (int e = 0; e < 4 && c0 + e < ncols; ++e) p.out_vis[o + e] = static_cast<uint8_t>(vis_byte(v[e]));
+      }
+    }
     if (p.out_metric) {
       if (full) {
         uint2 m;
@@ -149,8 +167,8 @@ __global__ void sample_kernel(const PostParams p, int B, const int32_t* sample_r
 }  // namespace deb
 
 extern "C" int de_postprocess(const void* pred, int in_dtype, int B, int h, int w, int H, int W, float* out_map,
-                              void* out_metric, float metric_scale, const int32_t* sample_rc, int n_samples,
-                              float* out_samples, void* stream) {
+                              void* out_metric, float metric_scale, uint8_t* out_vis, const int32_t* sample_rc,
+                              int n_samples, float* out_samples, void* stream) {
   using namespace deb;
   if (!pred || B <= 0 || h <= 0 || w <= 0 || H <= 0 || W <= 0) return fail(DE_ERR_INVALID, "de_postprocess: bad args");
   if (in_dtype != DE_DTYPE_F32 && in_dtype != DE_DTYPE_BF16) return fail(DE_ERR_INVALID, "de_postprocess: in_dtype");
@@ -164,8 +182,9 @@ extern "C" int de_postprocess(const void* pred, int in_dtype, int B, int h, int 
   p.out_map = out_map;
   p.out_metric = reinterpret_cast<__nv_bfloat16*>(out_metric);
   p.metric_scale = metric_scale;
+  p.out_vis = out_vis;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  if (out_map || out_metric) {
+  if (out_map || out_metric || out_vis) {
     static const int cand[] = {32, 16, 8, 4, 2, 1};           // output rows per tile; 128 columns always
     size_t smem = 0;
     bool ok = false;

@@ -71,13 +71,15 @@ class DepthEstimator(object):
         return out[0]
 
     # ------------------------------------------------------------------ supersets
-    def predict_batch(self, frames, samples_rc=None, want_metric=False):
+    def predict_batch(self, frames, samples_rc=None, want_metric=False, want_vis=False):
         """frames: np.uint8 [B,H,W,3] BGR (host).  Returns np.float32 [B,H,W]; with samples_rc
         (int [B,S,2] (row,col)) returns (maps, samples[B,S]); with want_metric adds the bf16 metric map
-        (face.py:137, D/2.54) as a float32 array."""
+        (face.py:137, D/2.54) as a float32 array; with want_vis adds the uint8 grey level of the reference's
+        to_video_frame (midas_mediapipe.py:141-150: uint8(map)*5+10, wrapping) - all from the same K8 launch."""
         frames = np.ascontiguousarray(frames)
         B, H, W, _ = frames.shape
-        plan = self._plan(B, H, W, 0 if samples_rc is None else int(np.asarray(samples_rc).shape[1]), want_metric)
+        plan = self._plan(B, H, W, 0 if samples_rc is None else int(np.asarray(samples_rc).shape[1]), want_metric,
+                          want_vis)
         plan.h_in.numpy()[...] = frames
         if samples_rc is not None:
             plan.h_rc.numpy()[...] = np.asarray(samples_rc, dtype=np.int32)
@@ -90,6 +92,8 @@ class DepthEstimator(object):
             res.append(plan.h_samples.numpy().copy())
         if want_metric:
             res.append(plan.h_metric.float().numpy().copy())
+        if want_vis:
+            res.append(plan.h_vis.numpy().copy())
         return res[0] if len(res) == 1 else tuple(res)
 
     def predict_device(self, frames_u8: torch.Tensor, eager: bool = False) -> torch.Tensor:
@@ -149,12 +153,12 @@ class DepthEstimator(object):
             d = torch.from_numpy(bgr[None]).to(self.device)
             return ops.preprocess(d, nh, nw, mean, std, ops.LAYOUT_NCHW_BF16)
 
-    def _plan(self, B, H, W, n_samples, want_metric):
-        key = (B, H, W, n_samples, want_metric)
+    def _plan(self, B, H, W, n_samples, want_metric, want_vis=False):
+        key = (B, H, W, n_samples, want_metric, want_vis)
         p = self._plans.get(key)
         if p is None:
             with torch.cuda.device(self.device):
-                p = _Plan(self, B, H, W, n_samples, want_metric)
+                p = _Plan(self, B, H, W, n_samples, want_metric, want_vis)
             self._plans[key] = p
         return p
 
@@ -163,7 +167,7 @@ class _Plan:
     """Static buffers + (optionally) a captured CUDA graph for one (B,H,W) geometry:
     pinned host frame -> H2D -> K1 -> net -> K8 -> D2H pinned."""
 
-    def __init__(self, est: DepthEstimator, B, H, W, n_samples, want_metric):
+    def __init__(self, est: DepthEstimator, B, H, W, n_samples, want_metric, want_vis=False):
         self.est = est
         dev = est.device
         self.B, self.H, self.W = B, H, W
@@ -175,6 +179,9 @@ class _Plan:
         self.want_metric = want_metric
         self.d_metric = torch.empty((B, H, W), dtype=torch.bfloat16, device=dev) if want_metric else None
         self.h_metric = torch.empty((B, H, W), dtype=torch.bfloat16).pin_memory() if want_metric else None
+        self.want_vis = want_vis
+        self.d_vis = torch.empty((B, H, W), dtype=torch.uint8, device=dev) if want_vis else None
+        self.h_vis = torch.empty((B, H, W), dtype=torch.uint8).pin_memory() if want_vis else None
         self.n_samples = n_samples
         if n_samples:
             self.h_rc = torch.zeros((B, n_samples, 2), dtype=torch.int32).pin_memory()
@@ -192,7 +199,7 @@ class _Plan:
         pred = net.forward(x, self.B, self.net_h, self.net_w)
         rc = self.d_rc if self.n_samples else None
         _, _, samples = ops.postprocess(pred, self.H, self.W, want_map=True, want_metric=self.want_metric,
-                                        sample_rc=rc, out_map=self.d_map, out_metric=self.d_metric)
+                                        sample_rc=rc, out_map=self.d_map, out_metric=self.d_metric, out_vis=self.d_vis)
         return samples
 
     def _body(self):
@@ -203,6 +210,8 @@ class _Plan:
         self.h_map.copy_(self.d_map, non_blocking=True)
         if self.want_metric:
             self.h_metric.copy_(self.d_metric, non_blocking=True)
+        if self.want_vis:
+            self.h_vis.copy_(self.d_vis, non_blocking=True)
         if self.n_samples:
             self.h_samples.copy_(samples, non_blocking=True)
 
@@ -375,7 +384,8 @@ class VidStream(object):
 
     def write_output(self):
         prediction = self.estimator.predict(self.frame)
-        output = prediction.astype(np.uint8)                    # wraps, exactly like depth_midas.py:83
+        with np.errstate(invalid="ignore"):
+            output = prediction.astype(np.uint8)                # wraps, exactly like depth_midas.py:83
         three_c = np.stack([output, output, output], axis=-1)   # cv2.merge([o, o, o])
         if self.output is not None:
             import cv2

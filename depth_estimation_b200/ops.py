@@ -78,8 +78,10 @@ def preprocess(frames_u8: torch.Tensor, net_h: int, net_w: int, mean, std, layou
 
 def postprocess(pred: torch.Tensor, H: int, W: int, want_map: bool = True, want_metric: bool = False,
                 metric_scale: float = 1.0 / 2.54, sample_rc: torch.Tensor | None = None,
-                out_map: torch.Tensor | None = None, out_metric: torch.Tensor | None = None):
-    """pred: [B,h,w] f32/bf16.  Returns (map f32 [B,H,W] | None, metric bf16 | None, samples f32 [B,S] | None)."""
+                out_map: torch.Tensor | None = None, out_metric: torch.Tensor | None = None,
+                out_vis: torch.Tensor | None = None):
+    """pred: [B,h,w] f32/bf16.  Returns (map f32 [B,H,W] | None, metric bf16 | None, samples f32 [B,S] | None).
+    out_vis: optional uint8 [B,H,W] receiving the reference's to_video_frame grey level (uint8(map)*5+10, wrapping)."""
     _need_cuda(pred, sample_rc)
     assert pred.dim() == 3 and pred.is_contiguous()
     B, h, w = pred.shape
@@ -93,7 +95,7 @@ def postprocess(pred: torch.Tensor, H: int, W: int, want_map: bool = True, want_
         ns = sample_rc.shape[1]
         samples = torch.empty((B, ns), dtype=torch.float32, device=pred.device)
     _lib.check(_lib.load().de_postprocess(pred.data_ptr(), _dt(pred), B, h, w, H, W, _ptr(out_map), _ptr(out_metric),
-                                          float(metric_scale), _ptr(sample_rc), ns, _ptr(samples), _stream()),
+                                          float(metric_scale), _ptr(out_vis), _ptr(sample_rc), ns, _ptr(samples), _stream()),
                "de_postprocess")
     return out_map, out_metric, samples
 

@@ -65,10 +65,12 @@ int de_preprocess(const uint8_t* bgr, int B, int H, int W, int64_t row_stride, i
  * resolution) fused with the metric tail of face.py:106-108,137 (ri_depth sampling, /2.54).
  * pred: [B,h,w] (in_dtype bf16 or f32).  Tap tables (mode 1) cached inside the library.
  * out_map: [B,H,W] f32 (may be NULL).  out_metric: [B,H,W] bf16 = map*metric_scale (may be NULL).
+ * out_vis: [B,H,W] uint8 (may be NULL) = the reference's to_video_frame grey level (midas_mediapipe.py:141-150,
+ * depth_midas.py:83): uint8(map) * 5 + 10 with numpy's wrapping uint8 arithmetic.
  * sample_rc: int32 [B,n_samples,2] (row, col) device indices into the OUTPUT map (may be NULL);
  * out_samples: float [B,n_samples] receives the interpolated value at those points. */
 int de_postprocess(const void* pred, int in_dtype, int B, int h, int w, int H, int W, float* out_map,
-                   void* out_metric, float metric_scale, const int32_t* sample_rc, int n_samples,
+                   void* out_metric, float metric_scale, uint8_t* out_vis, const int32_t* sample_rc, int n_samples,
                    float* out_samples, void* stream);
 
 /* ---- tcgen05 GEMM / implicit-GEMM convolution.  D = epilogue(A * Wt^T):

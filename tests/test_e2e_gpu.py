@@ -74,3 +74,29 @@ def test_predict_stream_matches_predict_batch():
             assert g.shape == w.shape and np.array_equal(g, w)
     with pytest.raises(TypeError):
         list(est.predict_stream([np.zeros((2, 8, 8), np.uint8)]))
+
+
+def test_stream_loop_and_fused_video_frame():
+    """SURVEY 8f N1/N2 on the real estimator: the headless midas_mediapipe.VidStream gives identical FaceDet
+    bookkeeping and identical output frames serial vs pipelined, and the uint8 grey level K8 emits equals the
+    reference's to_video_frame of the map."""
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    import midas_mediapipe
+    from depth_estimation_b200.depth_midas import DepthEstimator
+    from depth_estimation_b200.face import FaceDet
+    from tests.test_surface import _FakeDetector, _stream_frames
+    est = DepthEstimator("MiDaS_small", seed=0)
+    frames = _stream_frames(6, 96, 128)
+    runs = []
+    for pipelined in (False, True):
+        face = FaceDet(20, [505, 504, 675, 501])
+        vs = midas_mediapipe.VidStream(est, _FakeDetector(face), face, frames, None)
+        vs.stream(pipelined=pipelined)
+        runs.append((face, vs))
+    (fa, va), (fb, vb) = runs
+    assert fa.ri_depths == fb.ri_depths and fa.abs_depths == fb.abs_depths and fa.head_measurements == fb.head_measurements
+    assert all(np.array_equal(x, y) for x, y in zip(va.outputs, vb.outputs))
+    maps, vis = est.predict_batch(np.stack(frames[:2]), want_vis=True)
+    want = va.to_video_frame(maps * 37.0)[..., 0] if False else va.to_video_frame(maps)[..., 0]
+    assert vis.dtype == np.uint8 and np.array_equal(vis, want)

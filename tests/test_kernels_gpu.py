@@ -439,6 +439,20 @@ def test_postprocess_vs_torch(h, w, H, W):
         for s in range(3):
             r, c = rc[b, s].tolist()
             assert samples[b, s].item() == omap[b, r, c].item()
+    # video grey level (midas_mediapipe.py:141-150): uint8(map)*5+10 with numpy's wrapping casts, incl. values
+    # above 255, negative overshoot and a NaN
+    pred_w = pred * 40.0 - 30.0
+    pred_w[0, 0, 0] = float("nan")
+    vis = torch.empty((2, H, W), dtype=torch.uint8, device=dev)
+    omap_w, _, _ = ops.postprocess(pred_w, H, W, out_vis=vis)
+    torch.cuda.synchronize()
+    host = omap_w.cpu().numpy()
+    with np.errstate(invalid="ignore"):
+        want = host.astype(np.uint8)
+    want *= 5
+    want += 10
+    assert (host > 255).any() and (host < 0).any()
+    assert np.array_equal(vis.cpu().numpy(), want)
     # bf16 input path
     omap2, _, _ = ops.postprocess(pred.bfloat16(), H, W)
     ref2 = F.interpolate(pred.bfloat16().float().cpu().unsqueeze(1), size=(H, W), mode="bicubic", align_corners=False).squeeze(1).to(dev)
