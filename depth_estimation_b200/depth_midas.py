@@ -44,8 +44,9 @@ class DepthEstimator(object):
         ops._lib.load()
         if weights is None:
             weights = random_state_dict(model_type, seed)
-        elif isinstance(weights, str):
-            weights = torch.load(weights, map_location="cpu")
+        else:
+            from .weights import load_checkpoint
+            weights = load_checkpoint(weights, model_type)      # path or mapping in upstream naming, validated
         with torch.cuda.device(self.device):
             self.estimator = _build_net(model_type, weights, self.device)
         print('Loading transforms...')

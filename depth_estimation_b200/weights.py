@@ -54,3 +54,62 @@ def standardize_weight(w: torch.Tensor, eps: float = 1e-8) -> torch.Tensor:
     mean = flat.mean(dim=1, keepdim=True)
     var = flat.var(dim=1, unbiased=False, keepdim=True)
     return ((flat - mean) / torch.sqrt(var + eps)).reshape_as(w).float()
+
+
+# ------------------------------------------------------------------------------------------------ checkpoints
+# Upstream release files the reference's torch.hub call downloads (depth_midas.py:10) - names only, for messages.
+UPSTREAM_CHECKPOINTS = {"DPT_Large": "dpt_large-midas-2f21e586.pt", "DPT_Hybrid": "dpt_hybrid-midas-501f0c75.pt",
+                        "MiDaS_small": "midas_v21_small-70d6b9c8.pt"}
+# keys real checkpoints carry that the forward pass never reads (SURVEY.md 8a footer)
+_IGNORABLE = ("num_batches_tracked",)
+
+
+def state_dict_checksum(sd: dict) -> str:
+    """sha256 over (key, dtype, shape, raw bytes) in sorted key order - identifies a weight set independent of the
+    container format it was stored in."""
+    import hashlib
+    h = hashlib.sha256()
+    for k in sorted(sd):
+        t = sd[k].detach().cpu().contiguous()
+        h.update(k.encode())
+        h.update(str(t.dtype).encode())
+        h.update(str(tuple(t.shape)).encode())
+        h.update(t.view(torch.uint8).numpy().tobytes() if t.numel() else b"")
+    return h.hexdigest()
+
+
+def load_checkpoint(src, model_type: str, strict: bool = True) -> dict:
+    """Checkpoint ingestion: `src` is a path (torch.load, tensors only) or an already loaded
+    mapping in upstream naming - a bare state_dict, or one wrapped as {"state_dict": ...} / {"model": ...}, with or
+    without a "module." prefix.  Every key of the architecture's inventory (init.param_shapes) must be present with
+    the right shape; unknown keys are an error under `strict` (BatchNorm's num_batches_tracked is dropped).
+    Returns fp32 CPU tensors ready for the net constructors, which fold BN / weight standardisation and repack to
+    bf16 (functions above)."""
+    from .init import param_shapes
+    if isinstance(src, (str, bytes)) or hasattr(src, "__fspath__"):
+        obj = torch.load(src, map_location="cpu", weights_only=True)
+    else:
+        obj = src
+    for wrap in ("state_dict", "model"):
+        if isinstance(obj, dict) and wrap in obj and isinstance(obj[wrap], dict):
+            obj = obj[wrap]
+    if not isinstance(obj, dict):
+        raise TypeError(f"checkpoint for {model_type} is not a state_dict mapping")
+    sd = {}
+    for k, v in obj.items():
+        if not torch.is_tensor(v):
+            raise TypeError(f"checkpoint entry {k!r} is not a tensor")
+        k = k[len("module."):] if k.startswith("module.") else k
+        if k.endswith(_IGNORABLE):
+            continue
+        sd[k] = v.detach().to("cpu", torch.float32)
+    want = param_shapes(model_type)
+    missing = [k for k in want if k not in sd]
+    wrong = [f"{k}: {tuple(sd[k].shape)} != {tuple(want[k])}" for k in want if k in sd and tuple(sd[k].shape) != tuple(want[k])]
+    extra = [k for k in sd if k not in want]
+    if missing or wrong or (strict and extra):
+        hint = UPSTREAM_CHECKPOINTS.get(model_type, "?")
+        raise ValueError(f"checkpoint does not match {model_type} (upstream file {hint}): "
+                         f"{len(missing)} missing {missing[:3]}, {len(wrong)} mis-shaped {wrong[:3]}, "
+                         f"{len(extra)} unexpected {extra[:3]}")
+    return {k: sd[k] for k in want}

@@ -231,3 +231,32 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, re.M), f
+
+
+def test_checkpoint_ingestion_roundtrip_and_validation(tmp_path):
+    """a checkpoint written in upstream naming (here: the oracle module's own state_dict, wrapped and
+    prefixed the way training scripts leave them) loads, validates and hashes identically; damaged ones fail loudly."""
+    from depth_estimation_b200.weights import load_checkpoint, state_dict_checksum
+    from oracle.predict import build_model
+    model = build_model("MiDaS_small", seed=3)
+    sd = model.state_dict()
+    path = tmp_path / "midas_small.pt"
+    torch.save({"state_dict": {"module." + k: v for k, v in sd.items()}}, path)
+    got = load_checkpoint(str(path), "MiDaS_small")
+    ref = load_checkpoint(sd, "MiDaS_small")
+    assert list(got) == list(ref) and state_dict_checksum(got) == state_dict_checksum(ref)
+    assert all(v.dtype == torch.float32 and v.device.type == "cpu" for v in got.values())
+    assert not any(k.endswith("num_batches_tracked") for k in got)
+    k0 = next(iter(ref))
+    broken = dict(sd)
+    del broken[k0]
+    with pytest.raises(ValueError, match="missing"):
+        load_checkpoint(broken, "MiDaS_small")
+    with pytest.raises(ValueError, match="mis-shaped"):
+        load_checkpoint({**sd, k0: sd[k0][..., :1]}, "MiDaS_small")
+    with pytest.raises(ValueError, match="unexpected"):
+        load_checkpoint({**sd, "pretrained.bogus": torch.zeros(1)}, "MiDaS_small")
+    assert load_checkpoint({**sd, "pretrained.bogus": torch.zeros(1)}, "MiDaS_small", strict=False).keys() == ref.keys()
+    with pytest.raises(ValueError):
+        load_checkpoint(sd, "DPT_Hybrid")
+    assert state_dict_checksum(ref) != state_dict_checksum({**ref, k0: ref[k0] + 1})
