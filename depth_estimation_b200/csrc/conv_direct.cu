@@ -23,9 +23,9 @@ __host__ __device__ inline int same_pad_before(int in, int k, int s) {
 // ---------------------------------------------------------------- stem: NCHW bf16 (3 ch) -> NHWC bf16
 constexpr int kStemCo = 16;  // output channels per thread
 
-__global__ void __launch_bounds__(128) stem_conv_kernel(const __nv_bfloat16* __restrict__ x,
+__global__ void __launch_bounds__(128) stem_conv_kernel(const void* __restrict__ x, int x_f32,
                                                         const float* __restrict__ w,  // [Cout][k*k*3] (kh,kw,c)
-                                                        const float* __restrict__ bias, __nv_bfloat16* __restrict__ out,
+                                                        const float* __restrict__ bias, void* __restrict__ out, int out_f32,
                                                         int B, int H, int W, int Cout, int k, int stride, int Ho, int Wo,
                                                         int pad_y, int pad_x, int act) {
   extern __shared__ float s_w[];  // [k*k*3][Cout] transposed for broadcast float4 reads
@@ -48,7 +48,8 @@ __global__ void __launch_bounds__(128) stem_conv_kernel(const __nv_bfloat16* __r
   float acc[kStemCo];
 #pragma unroll
   for (int j = 0; j < kStemCo; ++j) acc[j] = bias ? bias[cg * kStemCo + j] : 0.f;
-  const __nv_bfloat16* xb = x + (long long)b * 3 * H * W;
+  const __nv_bfloat16* xb = reinterpret_cast<const __nv_bfloat16*>(x) + (long long)b * 3 * H * W;
+  const float* xf = reinterpret_cast<const float*>(x) + (long long)b * 3 * H * W;
   for (int ky = 0; ky < k; ++ky) {
     const int iy = oy * stride + ky - pad_y;
     if (iy < 0 || iy >= H) continue;
@@ -57,7 +58,8 @@ __global__ void __launch_bounds__(128) stem_conv_kernel(const __nv_bfloat16* __r
       if (ix < 0 || ix >= W) continue;
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
-        const float v = __bfloat162float(xb[((long long)c * H + iy) * W + ix]);
+        const long long e = ((long long)c * H + iy) * W + ix;
+        const float v = x_f32 ? __ldg(xf + e) : __bfloat162float(xb[e]);
         const float4* wp = reinterpret_cast<const float4*>(s_w + ((ky * k + kx) * 3 + c) * Cout + cg * kStemCo);
 #pragma unroll
         for (int j4 = 0; j4 < kStemCo / 4; ++j4) {
@@ -76,11 +78,20 @@ __global__ void __launch_bounds__(128) stem_conv_kernel(const __nv_bfloat16* __r
     float a = acc[2 * j], c = acc[2 * j + 1];
     if (act == DE_ACT_RELU6) { a = fminf(fmaxf(a, 0.f), 6.f); c = fminf(fmaxf(c, 0.f), 6.f); }
     else if (act == DE_ACT_RELU) { a = fmaxf(a, 0.f); c = fmaxf(c, 0.f); }
+    acc[2 * j] = a;
+    acc[2 * j + 1] = c;
     o[j] = pack_bf16(a, c);
   }
-  uint4* op = reinterpret_cast<uint4*>(out + (((long long)b * Ho + oy) * Wo + ox) * Cout + cg * kStemCo);
-  op[0] = make_uint4(o[0], o[1], o[2], o[3]);
-  op[1] = make_uint4(o[4], o[5], o[6], o[7]);
+  const long long e = (((long long)b * Ho + oy) * Wo + ox) * Cout + cg * kStemCo;
+  if (out_f32) {
+    float4* op = reinterpret_cast<float4*>(reinterpret_cast<float*>(out) + e);
+#pragma unroll
+    for (int j4 = 0; j4 < kStemCo / 4; ++j4) op[j4] = make_float4(acc[j4 * 4], acc[j4 * 4 + 1], acc[j4 * 4 + 2], acc[j4 * 4 + 3]);
+  } else {
+    uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(out) + e);
+    op[0] = make_uint4(o[0], o[1], o[2], o[3]);
+    op[1] = make_uint4(o[4], o[5], o[6], o[7]);
+  }
 }
 
 // ---------------------------------------------------------------- depthwise, NHWC bf16
@@ -135,8 +146,9 @@ __global__ void __launch_bounds__(256) depthwise_kernel(const __nv_bfloat16* __r
 }
 
 // ---------------------------------------------------------------- maxpool 3x3 s2 TF-same, NHWC bf16
-__global__ void maxpool3x3s2_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, int B, int H,
-                                    int W, int C, int Ho, int Wo, int pad_y, int pad_x) {
+// in: bf16 or fp32 NHWC.  out_mode 0: bf16 NHWC; 1: the [hi | hi | lo] split3 operand layout (misc.cu store_split3).
+__global__ void maxpool3x3s2_kernel(const void* __restrict__ x, int x_f32, __nv_bfloat16* __restrict__ out, int out_mode,
+                                    int B, int H, int W, int C, int Ho, int Wo, int pad_y, int pad_x) {
   const int cgs = C >> 3;
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (long long)B * Ho * Wo * cgs) return;
@@ -155,31 +167,51 @@ __global__ void maxpool3x3s2_kernel(const __nv_bfloat16* __restrict__ x, __nv_bf
     for (int kx = 0; kx < 3; ++kx) {
       const int ix = ox * 2 + kx - pad_x;
       if (ix < 0 || ix >= W) continue;
-      const uint4 v = *reinterpret_cast<const uint4*>(x + (((long long)b * H + iy) * W + ix) * C + c);
-      m[0] = fmaxf(m[0], bf16_lo(v.x)); m[1] = fmaxf(m[1], bf16_hi(v.x));
-      m[2] = fmaxf(m[2], bf16_lo(v.y)); m[3] = fmaxf(m[3], bf16_hi(v.y));
-      m[4] = fmaxf(m[4], bf16_lo(v.z)); m[5] = fmaxf(m[5], bf16_hi(v.z));
-      m[6] = fmaxf(m[6], bf16_lo(v.w)); m[7] = fmaxf(m[7], bf16_hi(v.w));
+      const long long e = (((long long)b * H + iy) * W + ix) * C + c;
+      if (x_f32) {
+        const float4 u0 = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(x) + e);
+        const float4 u1 = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(x) + e + 4);
+        m[0] = fmaxf(m[0], u0.x); m[1] = fmaxf(m[1], u0.y); m[2] = fmaxf(m[2], u0.z); m[3] = fmaxf(m[3], u0.w);
+        m[4] = fmaxf(m[4], u1.x); m[5] = fmaxf(m[5], u1.y); m[6] = fmaxf(m[6], u1.z); m[7] = fmaxf(m[7], u1.w);
+      } else {
+        const uint4 v = *reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(x) + e);
+        m[0] = fmaxf(m[0], bf16_lo(v.x)); m[1] = fmaxf(m[1], bf16_hi(v.x));
+        m[2] = fmaxf(m[2], bf16_lo(v.y)); m[3] = fmaxf(m[3], bf16_hi(v.y));
+        m[4] = fmaxf(m[4], bf16_lo(v.z)); m[5] = fmaxf(m[5], bf16_hi(v.z));
+        m[6] = fmaxf(m[6], bf16_lo(v.w)); m[7] = fmaxf(m[7], bf16_hi(v.w));
+      }
     }
   }
-  *reinterpret_cast<uint4*>(out + (((long long)b * Ho + oy) * Wo + ox) * C + c) =
-      make_uint4(pack_bf16(m[0], m[1]), pack_bf16(m[2], m[3]), pack_bf16(m[4], m[5]), pack_bf16(m[6], m[7]));
+  const long long row = ((long long)b * Ho + oy) * Wo + ox;
+  uint32_t hi[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) hi[k] = pack_bf16(m[2 * k], m[2 * k + 1]);
+  if (out_mode == 0) {
+    *reinterpret_cast<uint4*>(out + row * C + c) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+  } else {
+    uint32_t lo[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) lo[k] = pack_bf16(m[2 * k] - bf16_lo(hi[k]), m[2 * k + 1] - bf16_hi(hi[k]));
+    __nv_bfloat16* o = out + row * 3 * C + c;
+    *reinterpret_cast<uint4*>(o) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+    *reinterpret_cast<uint4*>(o + C) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+    *reinterpret_cast<uint4*>(o + 2 * C) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+  }
 }
 
 }  // namespace deb
 
 using namespace deb;
 
-extern "C" int de_stem_conv(const void* x_nchw, const float* w, const float* bias, void* out_nhwc, int B, int H, int W,
-                            int Cout, int k, int stride, int act, void* stream) {
+extern "C" int de_stem_conv(const void* x_nchw, int x_dtype, const float* w, const float* bias, void* out_nhwc, int out_dtype,
+                            int B, int H, int W, int Cout, int k, int stride, int act, void* stream) {
   if (!x_nchw || !w || !out_nhwc || Cout % kStemCo != 0 || k < 1 || k > 7)
     return fail(DE_ERR_INVALID, "de_stem_conv: bad args (Cout %% 16, k <= 7)");
   const int Ho = (H + stride - 1) / stride, Wo = (W + stride - 1) / stride;
   const long long n = (long long)B * Ho * Wo * (Cout / kStemCo);
   const size_t smem = sizeof(float) * k * k * 3 * Cout;
   stem_conv_kernel<<<(unsigned)((n + 127) / 128), 128, smem, reinterpret_cast<cudaStream_t>(stream)>>>(
-      reinterpret_cast<const __nv_bfloat16*>(x_nchw), w, bias, reinterpret_cast<__nv_bfloat16*>(out_nhwc), B, H, W, Cout,
-      k, stride, Ho, Wo, same_pad_before(H, k, stride), same_pad_before(W, k, stride), act);
+      x_nchw, x_dtype == DE_DTYPE_F32, w, bias, out_nhwc, out_dtype == DE_DTYPE_F32, B, H, W, Cout, k, stride, Ho, Wo, same_pad_before(H, k, stride), same_pad_before(W, k, stride), act);
   count_launch();
   return cuda_check_launch("stem_conv_kernel");
 }
@@ -202,12 +234,13 @@ extern "C" int de_depthwise(const void* x, const void* w_tapmajor, const float* 
   return cuda_check_launch("depthwise_kernel");
 }
 
-extern "C" int de_maxpool3x3s2(const void* x, void* out, int B, int H, int W, int C, void* stream) {
+extern "C" int de_maxpool3x3s2(const void* x, int x_dtype, void* out, int out_mode, int B, int H, int W, int C,
+                               void* stream) {
   if (!x || !out || C % 8 != 0) return fail(DE_ERR_INVALID, "de_maxpool3x3s2: bad args");
   const int Ho = (H + 1) / 2, Wo = (W + 1) / 2;
   const long long n = (long long)B * Ho * Wo * (C / 8);
   maxpool3x3s2_kernel<<<(unsigned)((n + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(out), B, H, W, C, Ho, Wo,
+      x, x_dtype == DE_DTYPE_F32, reinterpret_cast<__nv_bfloat16*>(out), out_mode, B, H, W, C, Ho, Wo,
       same_pad_before(H, 3, 2), same_pad_before(W, 3, 2));
   count_launch();
   return cuda_check_launch("maxpool3x3s2_kernel");

@@ -182,7 +182,35 @@ __global__ void subsample_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloa
 //         last-bit noise visible as rounding flips, so the statistics must be bit-reproducible)
 // pass 2: fixed-order sum over blocks -> (mean, rstd)
 // pass 3: y = act((x-mean)*rstd*gamma + beta [+ add]) -> bf16 (and optionally an fp32 copy)
-__global__ void __launch_bounds__(256) groupnorm_partial_kernel(const __nv_bfloat16* __restrict__ x, int HW, int C,
+// 8 consecutive channels of a bf16 or fp32 NHWC tensor as floats
+DEV void load8(const void* x, int x_f32, long long elem, float* f) {
+  if (x_f32) {
+    const float4 u0 = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(x) + elem);
+    const float4 u1 = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(x) + elem + 4);
+    f[0] = u0.x; f[1] = u0.y; f[2] = u0.z; f[3] = u0.w; f[4] = u1.x; f[5] = u1.y; f[6] = u1.z; f[7] = u1.w;
+  } else {
+    const uint4 t = *reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(x) + elem);
+    f[0] = bf16_lo(t.x); f[1] = bf16_hi(t.x); f[2] = bf16_lo(t.y); f[3] = bf16_hi(t.y);
+    f[4] = bf16_lo(t.z); f[5] = bf16_hi(t.z); f[6] = bf16_lo(t.w); f[7] = bf16_hi(t.w);
+  }
+}
+// "split3" operand layout of the precise (bf16x3) convolutions: a row of C fp32 values becomes 3C bf16 values
+// [hi | hi | lo], hi = bf16(v), lo = bf16(v - hi).  Against weights packed [Wh | Wl | Wh] along K, one ordinary bf16
+// GEMM then accumulates Ah*Wh + Ah*Wl + Al*Wh in fp32 - ~16 mantissa bits instead of 8 (weights.split3_*).
+DEV void store_split3(__nv_bfloat16* out, long long row, int C, int c0, const float* f) {
+  uint32_t hi[4], lo[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    hi[k] = pack_bf16(f[2 * k], f[2 * k + 1]);
+    lo[k] = pack_bf16(f[2 * k] - bf16_lo(hi[k]), f[2 * k + 1] - bf16_hi(hi[k]));
+  }
+  __nv_bfloat16* o = out + row * 3 * C + c0;
+  *reinterpret_cast<uint4*>(o) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+  *reinterpret_cast<uint4*>(o + C) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+  *reinterpret_cast<uint4*>(o + 2 * C) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+}
+
+__global__ void __launch_bounds__(256) groupnorm_partial_kernel(const void* __restrict__ x, int x_f32, int HW, int C,
                                                                 int groups, int px_per_block,
                                                                 double* __restrict__ partial) {
   __shared__ float s_su[256 * 8], s_sq[256 * 8];
@@ -196,9 +224,8 @@ __global__ void __launch_bounds__(256) groupnorm_partial_kernel(const __nv_bfloa
 #pragma unroll
   for (int j = 0; j < 8; ++j) su[j] = sq[j] = 0.f;
   for (int p = p0 + pl; p < p1; p += lanes) {
-    const uint4 t = *reinterpret_cast<const uint4*>(x + ((long long)b * HW + p) * C + v * 8);
-    const float f[8] = {bf16_lo(t.x), bf16_hi(t.x), bf16_lo(t.y), bf16_hi(t.y),
-                        bf16_lo(t.z), bf16_hi(t.z), bf16_lo(t.w), bf16_hi(t.w)};
+    float f[8];
+    load8(x, x_f32, ((long long)b * HW + p) * C + v * 8, f);
 #pragma unroll
     for (int j = 0; j < 8; ++j) { su[j] += f[j]; sq[j] = fmaf(f[j], f[j], sq[j]); }
   }
@@ -240,18 +267,19 @@ __global__ void groupnorm_finalize_kernel(const double* __restrict__ partial, in
   stats[i] = make_float2((float)m, (float)(1.0 / sqrt(var + (double)eps)));
 }
 
-__global__ void groupnorm_apply_kernel(const __nv_bfloat16* __restrict__ x, const float2* __restrict__ stats,
+__global__ void groupnorm_apply_kernel(const void* __restrict__ x, int x_f32, const float2* __restrict__ stats,
                                        const float* __restrict__ gamma, const float* __restrict__ beta,
                                        const void* __restrict__ add, int add_dtype, __nv_bfloat16* __restrict__ out,
-                                       float* __restrict__ out_f32, int B, int HW, int C, int groups, int act) {
+                                       int out_mode, float* __restrict__ out_f32, __nv_bfloat16* __restrict__ out_plain,
+                                       int B, int HW, int C, int groups, int act) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const int vec = C >> 3;
   if (i >= (long long)B * HW * vec) return;
   const int c0 = static_cast<int>(i % vec) * 8;
   const int b = static_cast<int>(i / ((long long)HW * vec));
   const int cpg = C / groups;
-  const uint4 t = *reinterpret_cast<const uint4*>(x + i * 8);
-  float f[8] = {bf16_lo(t.x), bf16_hi(t.x), bf16_lo(t.y), bf16_hi(t.y), bf16_lo(t.z), bf16_hi(t.z), bf16_lo(t.w), bf16_hi(t.w)};
+  float f[8];
+  load8(x, x_f32, i * 8, f);
   float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (add) {
     if (add_dtype == DE_DTYPE_F32) {
@@ -277,8 +305,12 @@ __global__ void groupnorm_apply_kernel(const __nv_bfloat16* __restrict__ x, cons
     if (act == DE_ACT_RELU) y = fmaxf(y, 0.f);
     f[j] = y;
   }
-  *reinterpret_cast<uint4*>(out + i * 8) =
-      make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+  const uint4 plain = make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+  if (out) {
+    if (out_mode == 1) store_split3(out, i / vec, C, c0, f);
+    else *reinterpret_cast<uint4*>(out + i * 8) = plain;
+  }
+  if (out_plain) *reinterpret_cast<uint4*>(out_plain + i * 8) = plain;
   if (out_f32) {
     *reinterpret_cast<float4*>(out_f32 + i * 8) = make_float4(f[0], f[1], f[2], f[3]);
     *reinterpret_cast<float4*>(out_f32 + i * 8 + 4) = make_float4(f[4], f[5], f[6], f[7]);
@@ -365,12 +397,15 @@ extern "C" int de_subsample(const void* x, void* out, int B, int H, int W, int C
   return cuda_check_launch("subsample_kernel");
 }
 
-extern "C" int de_groupnorm(const void* x, const float* gamma, const float* beta, const void* add, int add_dtype,
-                            void* out, float* out_f32, int B, int HW, int C, int groups, float eps, int act,
-                            void* ws, int64_t ws_bytes, void* stream) {
-  if (!x || !gamma || !beta || !out || !ws) return fail(DE_ERR_INVALID, "de_groupnorm: null pointer");
+extern "C" int de_groupnorm(const void* x, int x_dtype, const float* gamma, const float* beta, const void* add,
+                            int add_dtype, void* out, int out_mode, float* out_f32, void* out_plain, int B, int HW, int C,
+                            int groups, float eps, int act, void* ws, int64_t ws_bytes, void* stream) {
+  if (!x || !gamma || !beta || !ws || (!out && !out_f32 && !out_plain)) return fail(DE_ERR_INVALID, "de_groupnorm: null pointer");
   if (C % 8 != 0 || C > 2048 || groups > 64 || groups < 1 || C % groups != 0 || 256 % (C / 8) != 0)
     return fail(DE_ERR_UNSUPPORTED, "de_groupnorm: C=%d groups=%d unsupported", C, groups);
+  if ((x_dtype != DE_DTYPE_BF16 && x_dtype != DE_DTYPE_F32) || out_mode < 0 || out_mode > 1)
+    return fail(DE_ERR_INVALID, "de_groupnorm: x_dtype %d / out_mode %d", x_dtype, out_mode);
+  const int x_f32 = x_dtype == DE_DTYPE_F32;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   int px_per_block = (HW + 147) / 148;      // enough blocks to fill the GPU even at B=1
   const int lanes = 256 / (C / 8);
@@ -382,16 +417,15 @@ extern "C" int de_groupnorm(const void* x, const float* gamma, const float* beta
   float2* stats = reinterpret_cast<float2*>(ws);
   double* partial = reinterpret_cast<double*>(reinterpret_cast<char*>(ws) + ((stats_bytes + 15) / 16) * 16);
   dim3 grid(nblocks, B);
-  groupnorm_partial_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(x), HW, C, groups, px_per_block,
-                                                partial);
+  groupnorm_partial_kernel<<<grid, 256, 0, st>>>(x, x_f32, HW, C, groups, px_per_block, partial);
   count_launch();
   groupnorm_finalize_kernel<<<(B * groups + 127) / 128, 128, 0, st>>>(partial, nblocks, groups,
                                                                      (double)HW * (C / groups), eps, stats, B * groups);
   count_launch();
   const long long n = (long long)B * HW * (C / 8);
   groupnorm_apply_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(
-      reinterpret_cast<const __nv_bfloat16*>(x), stats, gamma, beta, add, add_dtype,
-      reinterpret_cast<__nv_bfloat16*>(out), out_f32, B, HW, C, groups, act);
+      x, x_f32, stats, gamma, beta, add, add_dtype, reinterpret_cast<__nv_bfloat16*>(out), out_mode, out_f32,
+      reinterpret_cast<__nv_bfloat16*>(out_plain), B, HW, C, groups, act);
   count_launch();
   return cuda_check_launch("groupnorm kernels");
 }

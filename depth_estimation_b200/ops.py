@@ -224,27 +224,30 @@ def subsample(x: torch.Tensor, out: torch.Tensor, stride: int):
     return out
 
 
-def groupnorm(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, out: torch.Tensor, ws: torch.Tensor,
+def groupnorm(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, out: torch.Tensor | None, ws: torch.Tensor,
               act: int = ACT_RELU, add: torch.Tensor | None = None, out_f32: torch.Tensor | None = None,
-              groups: int = 32, eps: float = 1e-5):
-    """x: bf16 NHWC [B,H,W,C]; ws: byte scratch (torch.uint8) - see include/depth_b200.h for the size."""
-    _need_cuda(x, gamma, beta, out, ws, add, out_f32)
+              groups: int = 32, eps: float = 1e-5, split: bool = False, out_plain: torch.Tensor | None = None):
+    """x: bf16 or f32 NHWC [B,H,W,C]; out: bf16 [B,H,W,C], or the split3 operand [B,H,W,3C] when `split`;
+    ws: byte scratch (torch.uint8) - see include/depth_b200.h for the size."""
+    _need_cuda(x, gamma, beta, out, ws, add, out_f32, out_plain)
     B, H, W, Cc = x.shape
-    assert x.dtype == torch.bfloat16 and x.is_contiguous() and ws.dtype == torch.uint8
-    _lib.check(_lib.load().de_groupnorm(x.data_ptr(), gamma.data_ptr(), beta.data_ptr(), _ptr(add),
-                                        _dt(add) if add is not None else 0, out.data_ptr(), _ptr(out_f32), B, H * W,
-                                        Cc, groups, float(eps), act, ws.data_ptr(), ws.numel(), _stream()),
+    assert x.dtype in (torch.bfloat16, torch.float32) and x.is_contiguous() and ws.dtype == torch.uint8
+    assert out is None or (out.dtype == torch.bfloat16 and out.shape[-1] == (3 * Cc if split else Cc))
+    _lib.check(_lib.load().de_groupnorm(x.data_ptr(), _dt(x), gamma.data_ptr(), beta.data_ptr(), _ptr(add),
+                                        _dt(add) if add is not None else 0, _ptr(out), 1 if split else 0, _ptr(out_f32),
+                                        _ptr(out_plain), B, H * W, Cc, groups, float(eps), act, ws.data_ptr(),
+                                        ws.numel(), _stream()),
                "de_groupnorm")
     return out
 
 
 def stem_conv(x_nchw: torch.Tensor, w: torch.Tensor, bias, out: torch.Tensor, k: int, stride: int, act: int):
-    """x: bf16 NCHW [B,3,H,W]; w: f32 [Cout, k*k*3]; out: bf16 NHWC."""
+    """x: bf16 or f32 NCHW [B,3,H,W]; w: f32 [Cout, k*k*3]; out: bf16 or f32 NHWC."""
     _need_cuda(x_nchw, w, bias, out)
     B, _, H, W = x_nchw.shape
-    assert x_nchw.dtype == torch.bfloat16 and x_nchw.is_contiguous() and w.dtype == torch.float32
-    _lib.check(_lib.load().de_stem_conv(x_nchw.data_ptr(), w.data_ptr(), _ptr(bias), out.data_ptr(), B, H, W,
-                                        w.shape[0], k, stride, act, _stream()), "de_stem_conv")
+    assert x_nchw.dtype in (torch.bfloat16, torch.float32) and x_nchw.is_contiguous() and w.dtype == torch.float32
+    _lib.check(_lib.load().de_stem_conv(x_nchw.data_ptr(), _dt(x_nchw), w.data_ptr(), _ptr(bias), out.data_ptr(), _dt(out),
+                                        B, H, W, w.shape[0], k, stride, act, _stream()), "de_stem_conv")
     return out
 
 
@@ -258,8 +261,11 @@ def depthwise(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, out: torch.T
     return out
 
 
-def maxpool3x3s2(x: torch.Tensor, out: torch.Tensor):
+def maxpool3x3s2(x: torch.Tensor, out: torch.Tensor, split: bool = False):
+    """x: bf16 or f32 NHWC; out: bf16 [B,Ho,Wo,C], or the split3 operand [B,Ho,Wo,3C] when `split`."""
     _need_cuda(x, out)
     B, H, W, Cc = x.shape
-    _lib.check(_lib.load().de_maxpool3x3s2(x.data_ptr(), out.data_ptr(), B, H, W, Cc, _stream()), "de_maxpool3x3s2")
+    assert out.dtype == torch.bfloat16 and out.shape[-1] == (3 * Cc if split else Cc)
+    _lib.check(_lib.load().de_maxpool3x3s2(x.data_ptr(), _dt(x), out.data_ptr(), 1 if split else 0, B, H, W, Cc,
+                                           _stream()), "de_maxpool3x3s2")
     return out

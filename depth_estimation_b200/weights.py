@@ -42,6 +42,30 @@ def pack_conv1x1(w: torch.Tensor) -> torch.Tensor:
     return w.reshape(w.shape[0], w.shape[1]).to(torch.bfloat16).contiguous()
 
 
+def _hi_lo(w: torch.Tensor):
+    hi = w.to(torch.bfloat16)
+    lo = (w.float() - hi.float()).to(torch.bfloat16)
+    return hi, lo
+
+
+def split3_conv1x1(w: torch.Tensor) -> torch.Tensor:
+    """fp32 [Cout,Cin(,1,1)] -> bf16 [Cout, 3*Cin] = [Wh | Wl | Wh] (hi = bf16(w), lo = bf16(w - hi)).  Against an
+    activation row laid out [Ah | Ah | Al] (the kernels' split3 output mode) the ordinary bf16 GEMM accumulates
+    Ah*Wh + Ah*Wl + Al*Wh in fp32: a bf16x3 product with ~16 mantissa bits, used where bf16's 8 bits are not enough
+    (DPT_Hybrid's weight-standardised ResNetV2 - see dpt_hybrid.py)."""
+    hi, lo = _hi_lo(w.reshape(w.shape[0], w.shape[1]))
+    return torch.cat([hi, lo, hi], dim=1).contiguous()
+
+
+def split3_conv3x3(w: torch.Tensor) -> torch.Tensor:
+    """fp32 [Cout,Cin,3,3] -> bf16 [Cout, 9*3*Cin], k = tap*(3*Cin) + {Wh | Wl | Wh}: the tap-major layout of both the
+    implicit-GEMM conv (Cin' = 3*Cin must be a multiple of 64) and de_im2col3x3 + GEMM, on split3 activations."""
+    cout, cin = w.shape[:2]
+    assert (3 * cin) % 64 == 0
+    hi, lo = _hi_lo(w.permute(0, 2, 3, 1).reshape(cout, 9, cin))
+    return torch.cat([hi, lo, hi], dim=2).reshape(cout, 27 * cin).contiguous()
+
+
 def fold_bn(w: torch.Tensor, bn_w, bn_b, bn_mean, bn_var, eps: float):
     """conv (no bias) followed by BatchNorm(eval) -> (w', b') in fp32."""
     scale = bn_w / torch.sqrt(bn_var + eps)

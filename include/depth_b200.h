@@ -149,26 +149,30 @@ int de_im2col3x3(const void* x, void* out, int B, int H, int W, int C, int strid
                  int Wo, void* stream);
 /* out[b,y,x,:] = x[b,y*s,x*s,:] (input gather of a 1x1 stride-s conv), NHWC bf16. */
 int de_subsample(const void* x, void* out, int B, int H, int W, int C, int stride, void* stream);
-/* GroupNorm over (HW, C/groups) per sample, NHWC bf16: out = act((x-mean)*rstd*gamma+beta [+ add]).
- * add: bf16 or f32 (add_dtype), same shape, may be NULL.  out_f32: optional fp32 copy of the result (the
- * ResNetV2 residual stream).  Deterministic (fixed-order reductions).  ws: device scratch of at least
+/* GroupNorm over (HW, C/groups) per sample, NHWC: y = act((x-mean)*rstd*gamma+beta [+ add]).
+ * x: bf16 or f32 (x_dtype).  add: bf16 or f32 (add_dtype), same shape, may be NULL.  Outputs (each may be NULL, at
+ * least one required): out - bf16, out_mode 0: [.., C]; out_mode 1: the "split3" operand layout [.., 3C] =
+ * [hi | hi | lo] with hi = bf16(y), lo = bf16(y - hi), which against weights packed [Wh | Wl | Wh] along K gives a
+ * bf16x3 (~16 mantissa bit) product on the ordinary bf16 GEMM (DPT_Hybrid's ResNetV2 stages); out_f32 - fp32 copy
+ * (the ResNetV2 residual stream); out_plain - bf16 [.., C] copy (decoder input).  Deterministic (fixed-order
+ * reductions).  ws: device scratch of at least
  * 8*B*groups + 16*B*groups*ceil(HW/max(ceil(HW/148), 4*256/(C/8))) + 32 bytes.
  * (timm GroupNormAct, eps 1e-5, 32 groups.) */
-int de_groupnorm(const void* x, const float* gamma, const float* beta, const void* add, int add_dtype, void* out,
-                 float* out_f32, int B, int HW, int C, int groups, float eps, int act, void* ws, int64_t ws_bytes,
-                 void* stream);
+int de_groupnorm(const void* x, int x_dtype, const float* gamma, const float* beta, const void* add, int add_dtype,
+                 void* out, int out_mode, float* out_f32, void* out_plain, int B, int HW, int C, int groups, float eps,
+                 int act, void* ws, int64_t ws_bytes, void* stream);
 
 /* ---- direct (CUDA-core) convolutions for non-GEMM shapes; TF-"same" padding (geffnet Conv2dSame /
  * timm StdConv2dSame, MaxPool2dSame): pad_total = max((ceil(i/s)-1)*s+k-i, 0), extra pixel bottom/right. */
-/* 3-channel stem: x NCHW bf16 [B,3,H,W] (K1 layout 0), w float [Cout][k*k*3] ((kh,kw,c) order, BN
- * folded), bias float[Cout] or NULL -> NHWC bf16 [B,ceil(H/s),ceil(W/s),Cout]. Cout % 16 == 0. */
-int de_stem_conv(const void* x_nchw, const float* w, const float* bias, void* out_nhwc, int B, int H, int W,
-                 int Cout, int k, int stride, int act, void* stream);
+/* 3-channel stem: x NCHW bf16 or f32 [B,3,H,W] (K1 layout 0 / 2), w float [Cout][k*k*3] ((kh,kw,c) order, BN
+ * folded), bias float[Cout] or NULL -> NHWC bf16 or f32 [B,ceil(H/s),ceil(W/s),Cout]. Cout % 16 == 0. */
+int de_stem_conv(const void* x_nchw, int x_dtype, const float* w, const float* bias, void* out_nhwc, int out_dtype,
+                 int B, int H, int W, int Cout, int k, int stride, int act, void* stream);
 /* depthwise k in {3,5}: x NHWC bf16, w bf16 [k*k][C] (tap-major, BN folded), bias float[C]. */
 int de_depthwise(const void* x, const void* w_tapmajor, const float* bias, void* out, int B, int H, int W, int C,
                  int k, int stride, int act, void* stream);
-/* MaxPool 3x3 stride 2 TF-same, NHWC bf16. */
-int de_maxpool3x3s2(const void* x, void* out, int B, int H, int W, int C, void* stream);
+/* MaxPool 3x3 stride 2 TF-same, NHWC bf16 or f32 in; out bf16 [.., C] (out_mode 0) or split3 [.., 3C] (1). */
+int de_maxpool3x3s2(const void* x, int x_dtype, void* out, int out_mode, int B, int H, int W, int C, void* stream);
 
 #ifdef __cplusplus
 }

@@ -43,9 +43,11 @@ def test_predict_matches_oracle(mt, W, H, kind):
     assert (ref > 0).mean() > 0.9
     rel, dyn = _errs(out, ref)
     print(f"{mt} {W}x{H} {kind}: rel={rel:.3e} dyn={dyn:.3e}")
-    # north_star: relative inverse depth within 1e-3 (fp32 accumulate); DPT_Hybrid's ResNetV2 stem (GroupNorm on
-    # bf16 activations) currently sits at ~6e-3 under random init - inside the 1 % bf16 metric-depth budget only
-    assert rel < (1e-2 if mt == "DPT_Hybrid" else 1e-3), (rel, dyn)
+    # north_star: relative inverse depth within 1e-3 (fp32 accumulate).  DPT_Hybrid: its ResNetV2 stages run as bf16x3
+    # (plain bf16 operands drift 25 % at the stage-3 output under random init - the oracle with bf16 rounding injected
+    # reproduces that - and gave 5.8e-3 here); what is left (1.3e-3) is the shared bf16 decoder on an output whose
+    # maximum is small against its own dynamic range: in `dyn` terms the hybrid (4e-3) is 3x tighter than DPT_Large.
+    assert rel < (2e-3 if mt == "DPT_Hybrid" else 1e-3), (rel, dyn)
     # graph replay gives the same answer, and the batched / metric / sample outputs agree
     out2 = est.predict(frame)
     assert np.array_equal(out, out2)

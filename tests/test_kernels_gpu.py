@@ -551,3 +551,89 @@ def test_subsample_and_same_im2col():
     ref = F.unfold(xp, 3, stride=2).view(2, 32, 9, 35).permute(0, 3, 2, 1).reshape(70, 288)
     torch.cuda.synchronize()
     assert torch.equal(col.float(), ref)
+
+
+# ------------------------------------------------------------------ split3 (bf16x3) operand path of DPT_Hybrid's ResNetV2
+def _unsplit(t, Cc):
+    """[.., 3C] = [hi | hi | lo] -> fp32 hi + lo (and check the two hi copies agree)."""
+    hi, hi2, lo = t[..., :Cc].float(), t[..., Cc:2 * Cc].float(), t[..., 2 * Cc:].float()
+    assert torch.equal(hi, hi2)
+    return hi + lo
+
+
+def test_groupnorm_f32_in_split_out():
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    B, H, W, Cc = 2, 24, 40, 128
+    x = _rand((B, H, W, Cc), dev, 2.0, seed=64) + 0.7
+    g, b = _rand((Cc,), dev, seed=65), _rand((Cc,), dev, seed=66)
+    add = _rand((B, H, W, Cc), dev, seed=67)
+    ws = torch.zeros(1 << 20, dtype=torch.uint8, device=dev)
+    out = torch.empty((B, H, W, 3 * Cc), dtype=torch.bfloat16, device=dev)
+    o32 = torch.empty_like(x)
+    opl = torch.empty((B, H, W, Cc), dtype=torch.bfloat16, device=dev)
+    ops.groupnorm(x, g, b, out, ws, act=ops.ACT_RELU, add=add, out_f32=o32, split=True, out_plain=opl)
+    ref = F.relu(F.group_norm(x.double().permute(0, 3, 1, 2), 32, g.double(), b.double(), 1e-5).permute(0, 2, 3, 1) + add.double())
+    torch.cuda.synchronize()
+    assert _relerr(o32, ref) < 2e-6
+    assert torch.equal(opl, o32.bfloat16())
+    assert torch.equal(out[..., :Cc], opl)
+    assert (_unsplit(out, Cc) - o32).abs().max() <= o32.abs().max() * 2.0 ** -16      # hi + lo carries ~16 bits
+    # fp32-only output (the stem's norm and the downsample shortcut)
+    only = torch.empty_like(x)
+    ops.groupnorm(x, g, b, None, ws, act=ops.ACT_RELU, add=add, out_f32=only)
+    torch.cuda.synchronize()
+    assert torch.equal(only, o32)
+
+
+def test_maxpool_f32_in_split_out():
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    x = _rand((2, 64, 35, 22), dev, seed=68)
+    out = torch.empty((2, 18, 11, 192), dtype=torch.bfloat16, device=dev)
+    ops.maxpool3x3s2(x.permute(0, 2, 3, 1).contiguous(), out, split=True)
+    ref = F.max_pool2d(_tf_same_pad(x, 3, 2, float("-inf")), 3, 2).permute(0, 2, 3, 1)
+    torch.cuda.synchronize()
+    assert (_unsplit(out, 64) - ref).abs().max() <= ref.abs().max() * 2.0 ** -16
+
+
+def test_stem_conv_f32():
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    k, s, Cout, H, W = 7, 2, 64, 96, 130
+    x = _rand((2, 3, H, W), dev, seed=69)
+    w = _rand((Cout, 3, k, k), dev, 0.1, seed=70)
+    out = torch.empty((2, H // 2, W // 2, Cout), dtype=torch.float32, device=dev)
+    ops.stem_conv(x, w.permute(0, 2, 3, 1).reshape(Cout, -1).contiguous(), None, out, k, s, ops.ACT_NONE)
+    ref = F.conv2d(_tf_same_pad(x.double(), k, s), w.double(), None, stride=s).permute(0, 2, 3, 1)
+    torch.cuda.synchronize()
+    assert _relerr(out, ref) < 1e-5
+
+
+@pytest.mark.parametrize("conv", [False, True])
+def test_split3_gemm_precision(conv):
+    """Activations [Ah | Ah | Al] x weights [Wh | Wl | Wh] on the unchanged bf16 GEMM / implicit 3x3 conv: the result
+    must be ~2^-16-accurate against fp64, where plain bf16 operands give ~2^-8."""
+    from depth_estimation_b200 import ops
+    from depth_estimation_b200.weights import split3_conv1x1, split3_conv3x3
+    dev = _dev()
+    B, H, W, Cin, Cout = 2, 24, 24, 64, 64
+    a = F.relu(_rand((B, H, W, Cin), dev, seed=71) + 0.5)
+    hi = a.bfloat16()
+    lo = (a - hi.float()).bfloat16()
+    a3 = torch.cat([hi, hi, lo], dim=-1).contiguous()
+    out = torch.empty((B, H, W, Cout), dtype=torch.float32, device=dev)
+    if conv:
+        w = _rand((Cout, Cin, 3, 3), dev, 0.1, seed=72)
+        ops.gemm(a3, split3_conv3x3(w), out.view(-1, Cout), conv=(B, H, W, 3 * Cin), N=Cout)
+        ref = F.conv2d(a.double().permute(0, 3, 1, 2), w.double(), padding=1).permute(0, 2, 3, 1)
+        plain = F.conv2d(hi.double().permute(0, 3, 1, 2), w.bfloat16().double(), padding=1).permute(0, 2, 3, 1)
+    else:
+        w = _rand((Cout, Cin), dev, 0.1, seed=72)
+        ops.gemm(a3.view(-1, 3 * Cin), split3_conv1x1(w), out.view(-1, Cout))
+        ref = a.double() @ w.double().t()
+        plain = hi.double() @ w.bfloat16().double().t()
+    torch.cuda.synchronize()
+    e3, e1 = _relerr(out, ref), _relerr(plain, ref)
+    print(f"split3 {'conv' if conv else 'gemm'}: rel err {e3:.2e} (plain bf16 operands {e1:.2e})")
+    assert e3 < 3e-5 and e3 < e1 / 30
