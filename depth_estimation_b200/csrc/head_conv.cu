@@ -1,0 +1,260 @@
+// Fused DPT head tail for sm_100a: conv3x3(Cin -> 32, pad 1) + bias + ReLU + conv1x1(32 -> 1) + bias + ReLU on an
+// NHWC bf16 activation, fp32 [B,H,W] out  ([UPSTREAM] midas/dpt_depth.py head: output_conv[2..5]).
+//
+// Why not the general implicit-GEMM kernel: with N = 32 the MMAs are short (128x32x16) and the general kernel
+// re-fetches the A tile from L2 for each of the 9 filter taps - 85 B/clk/SM of L2->smem traffic, which is what bounds
+// it (1.59 ms per 32-frame DPT_Large step, 219 TFLOP/s).  Here
+//   * the whole filter bank (9*Cin x 32 bf16 = 72 KB at Cin = 128) is loaded into shared memory once per CTA;
+//   * the activation is staged as HALO tiles: for an 8 x 16 pixel output tile, three TMA boxes per 64-channel block,
+//     one per horizontal tap dx, each (8+2) rows x 16 pixels x 64 channels.  The three vertical taps of a box are the
+//     same shared memory viewed 16 rows (2048 B = two swizzle atoms) further down, so a box feeds 3 taps x 4 K-steps
+//     = 12 MMAs and the L2->smem traffic per tile drops from 9 to 3.75 tile-equivalents;
+//   * accumulators live in 4 TMEM stages of 32 columns; four epilogue warps apply bias/ReLU, the 32->1 dot and the
+//     final ReLU straight from TMEM and write one fp32 per pixel.
+// Roles: warp 0 TMA producer, warp 1 MMA issuer, warp 2 TMEM allocator, warps 4..7 epilogue.  Persistent CTAs, one
+// per SM, tiles handed out round-robin (x fastest, so concurrently running CTAs share halo rows in L2).
+#include <cuda.h>
+
+#include "common.cuh"
+#include "depth_b200.h"
+#include "host_util.h"
+
+namespace deb {
+
+constexpr int kHcBW = 16, kHcBH = 8;                        // output tile: 8 rows x 16 pixels = 128 accumulator rows
+constexpr int kHcBoxRows = kHcBH + 2;
+constexpr int kHcStageBytes = kHcBoxRows * kHcBW * 128;     // 20480: (10 x 16) pixels x 64 channels bf16
+constexpr int kHcN = 32;
+constexpr int kHcWChunk = kHcN * 128;                       // 4096: 32 filters x 64 K bf16
+constexpr int kHcAcc = 4;                                   // TMEM accumulator stages
+constexpr int kHcThreads = 256;
+constexpr int kHcMaxStages = 8;
+
+struct HeadConvParams {
+  int B, H, W, cin_blocks, tiles_x, tiles_y, num_tiles, stages;
+  const float* bias;
+  const float* head_w;
+  float head_b;
+  float* out;
+};
+
+__global__ void __launch_bounds__(kHcThreads, 1)
+head_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, const HeadConvParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+  const int w_chunks = 9 * p.cin_blocks;
+  uint8_t* sW = smem;                                        // [tap][cb] chunks of 4096 B
+  uint8_t* sA = smem + w_chunks * kHcWChunk;                 // stage ring
+  uint8_t* post = sA + p.stages * kHcStageBytes;
+  uint64_t* full = reinterpret_cast<uint64_t*>(post);
+  uint64_t* empty = full + kHcMaxStages;
+  uint64_t* tfull = empty + kHcMaxStages;
+  uint64_t* tempty = tfull + kHcAcc;
+  uint64_t* wfull = tempty + kHcAcc;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wfull + 1);
+  float* s_bias = reinterpret_cast<float*>(post + 256);      // 32 bias + 32 head weights
+  float* s_hw = s_bias + kHcN;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmW);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < p.stages; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < kHcAcc; ++i) {
+      mbar_init(&tfull[i], 1);
+      mbar_init(&tempty[i], 4);
+    }
+    mbar_init(wfull, 1);
+    mbar_fence_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, kHcAcc * kHcN);
+    tmem_relinquish();
+  }
+  if (warp == 3) {
+    s_bias[lane] = p.bias ? __ldg(p.bias + lane) : 0.f;
+    s_hw[lane] = __ldg(p.head_w + lane);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int per_img = p.tiles_x * p.tiles_y;
+  const int stages_per_tile = 3 * p.cin_blocks;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      mbar_arrive_expect_tx(wfull, w_chunks * kHcWChunk);
+      for (int c = 0; c < w_chunks; ++c) tma_load_2d(sW + c * kHcWChunk, &tmW, wfull, c * 64, 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        const int b = tile / per_img, t = tile % per_img;
+        const int y0 = (t / p.tiles_x) * kHcBH, x0 = (t % p.tiles_x) * kHcBW;
+        for (int s = 0; s < stages_per_tile; ++s) {
+          const int cb = s / 3, dx = s % 3;
+          mbar_wait(&empty[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&full[stage], kHcStageBytes);
+          tma_load_4d(sA + stage * kHcStageBytes, &tmA, &full[stage], cb * 64, x0 + dx - 1, y0 - 1, b);
+          if (++stage == p.stages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    constexpr uint32_t idesc = make_idesc_bf16(128, kHcN);
+    mbar_wait(wfull, 0);
+    tc_fence_after();
+    int stage = 0;
+    uint32_t phase = 0;
+    int as = 0;
+    uint32_t aphase = 0;
+    const uint32_t w_base = smem_u32(sW);
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      mbar_wait(&tempty[as], aphase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + as * kHcN;
+      for (int s = 0; s < stages_per_tile; ++s) {
+        const int cb = s / 3, dx = s % 3;
+        mbar_wait(&full[stage], phase);
+        tc_fence_after();
+        // warp-uniform descriptors + elect_one: back-to-back UTCHMMA issue (see gemm_tcgen05.cu)
+        const uint64_t adesc = make_sw128_kmajor_desc(smem_u32(sA + stage * kHcStageBytes));
+        const uint64_t bdesc = make_sw128_kmajor_desc(w_base + (dx * p.cin_blocks + cb) * kHcWChunk);
+        const uint64_t b_dy = static_cast<uint64_t>((3 * p.cin_blocks * kHcWChunk) >> 4);   // next filter row (dy+1)
+        if (elect_one()) {
+#pragma unroll
+          for (int dy = 0; dy < 3; ++dy) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              umma_bf16(d_tmem, adesc + dy * ((kHcBW * 128) >> 4) + 2 * k, bdesc + dy * b_dy + 2 * k, idesc,
+                        (s | dy | k) != 0);
+          }
+          umma_commit(&empty[stage]);
+          if (s == stages_per_tile - 1) umma_commit(&tfull[as]);
+        }
+        __syncwarp();
+        if (++stage == p.stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      if (++as == kHcAcc) {
+        as = 0;
+        aphase ^= 1;
+      }
+    }
+  } else if (warp >= 4) {
+    // ------------------------------------------------------------------ epilogue: one accumulator row per thread
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
+    int as = 0;
+    uint32_t aphase = 0;
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      const int b = tile / per_img, t = tile % per_img;
+      const int y = (t / p.tiles_x) * kHcBH + r / kHcBW, x = (t % p.tiles_x) * kHcBW + r % kHcBW;
+      mbar_wait(&tfull[as], aphase);
+      tc_fence_after();
+      uint32_t acc[32];
+      tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * kHcN, acc);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[as]);
+      float s0 = p.head_b, s1 = 0.f;
+#pragma unroll
+      for (int n = 0; n < kHcN; n += 2) {
+        s0 = fmaf(fmaxf(__uint_as_float(acc[n]) + s_bias[n], 0.f), s_hw[n], s0);
+        s1 = fmaf(fmaxf(__uint_as_float(acc[n + 1]) + s_bias[n + 1], 0.f), s_hw[n + 1], s1);
+      }
+      if (y < p.H && x < p.W) p.out[((long long)b * p.H + y) * p.W + x] = fmaxf(s0 + s1, 0.f);
+      if (++as == kHcAcc) {
+        as = 0;
+        aphase ^= 1;
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kHcAcc * kHcN);
+  }
+}
+
+static bool hc_make_map(CUtensorMap* map, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                        const uint32_t* box) {
+  auto fn = get_tensor_map_encoder();
+  if (!fn) return false;
+  uint32_t estr[5] = {1, 1, 1, 1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), dims, strides_bytes, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed with CUresult %d (head conv, rank %d)", (int)r, rank);
+    return false;
+  }
+  return true;
+}
+
+}  // namespace deb
+
+extern "C" int de_head_conv(const void* x, const void* w, int64_t ldw, const float* bias, const float* head_w,
+                            float head_b, float* out, int B, int H, int W, int Cin, void* stream) {
+  using namespace deb;
+  if (!x || !w || !head_w || !out) return fail(DE_ERR_INVALID, "de_head_conv: null pointer");
+  if (B < 1 || H < 1 || W < 1 || Cin < 64 || Cin % 64 != 0) return fail(DE_ERR_UNSUPPORTED, "de_head_conv: Cin=%d must be a multiple of 64", Cin);
+  if (ldw < 9LL * Cin || ldw % 8 != 0) return fail(DE_ERR_INVALID, "de_head_conv: ldw=%lld too small / unaligned", (long long)ldw);
+  HeadConvParams p{};
+  p.B = B; p.H = H; p.W = W;
+  p.cin_blocks = Cin / 64;
+  p.tiles_x = (W + kHcBW - 1) / kHcBW;
+  p.tiles_y = (H + kHcBH - 1) / kHcBH;
+  const long long tiles = (long long)B * p.tiles_x * p.tiles_y;
+  if (tiles > 0x7fffffffLL) return fail(DE_ERR_UNSUPPORTED, "de_head_conv: too many tiles");
+  p.num_tiles = (int)tiles;
+  p.bias = bias; p.head_w = head_w; p.head_b = head_b; p.out = out;
+  const int w_bytes = 9 * p.cin_blocks * kHcWChunk;
+  const int post_bytes = 256 + 2 * kHcN * 4;
+  int stages = (232448 - 1024 - post_bytes - w_bytes) / kHcStageBytes;
+  if (stages > kHcMaxStages) stages = kHcMaxStages;
+  if (stages < 3) return fail(DE_ERR_UNSUPPORTED, "de_head_conv: Cin=%d leaves no room for the activation ring", Cin);
+  p.stages = stages;
+  const int smem_bytes = 1024 + w_bytes + stages * kHcStageBytes + post_bytes;
+  CUtensorMap ta, tw;
+  {
+    const uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)B};
+    const uint64_t strides[3] = {(uint64_t)Cin * 2, (uint64_t)W * Cin * 2, (uint64_t)H * W * Cin * 2};
+    const uint32_t box[4] = {64, kHcBW, kHcBoxRows, 1};
+    if (!hc_make_map(&ta, x, 4, dims, strides, box)) return DE_ERR_CUDA;
+  }
+  {
+    const uint64_t dims[2] = {(uint64_t)9 * Cin, (uint64_t)kHcN};
+    const uint64_t strides[1] = {(uint64_t)ldw * 2};
+    const uint32_t box[2] = {64, kHcN};
+    if (!hc_make_map(&tw, w, 2, dims, strides, box)) return DE_ERR_CUDA;
+  }
+  static int attr_smem = 0;
+  if (attr_smem < smem_bytes) {
+    cudaError_t e = cudaFuncSetAttribute(head_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(head_conv)");
+    attr_smem = smem_bytes;
+  }
+  int grid = num_sms();
+  if (p.num_tiles < grid) grid = p.num_tiles;
+  head_conv_kernel<<<grid, kHcThreads, smem_bytes, reinterpret_cast<cudaStream_t>(stream)>>>(ta, tw, p);
+  count_launch();
+  return cuda_check_launch("head_conv_kernel");
+}

@@ -251,6 +251,19 @@ def stem_conv(x_nchw: torch.Tensor, w: torch.Tensor, bias, out: torch.Tensor, k:
     return out
 
 
+def head_conv(x: torch.Tensor, w: torch.Tensor, bias, head_w: torch.Tensor, head_b: float, out: torch.Tensor):
+    """relu(head_b + head_w . relu(conv3x3(x, w) + bias)): x bf16 NHWC [B,H,W,Cin] (Cin % 64 == 0), w bf16 [32, 9*Cin]
+    tap-major, out fp32 [B,H,W]."""
+    _need_cuda(x, w, bias, head_w, out)
+    B, H, W, Cin = x.shape
+    assert x.dtype == torch.bfloat16 and x.is_contiguous() and w.dtype == torch.bfloat16 and w.shape[0] == 32
+    assert out.dtype == torch.float32 and out.is_contiguous() and tuple(out.shape) == (B, H, W)
+    assert head_w.dtype == torch.float32 and head_w.numel() == 32 and (bias is None or bias.dtype == torch.float32)
+    _lib.check(_lib.load().de_head_conv(x.data_ptr(), w.data_ptr(), w.stride(0), _ptr(bias), head_w.data_ptr(),
+                                        float(head_b), out.data_ptr(), B, H, W, Cin, _stream()), "de_head_conv")
+    return out
+
+
 def depthwise(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, out: torch.Tensor, k: int, stride: int, act: int):
     """x: bf16 NHWC; w: bf16 [k*k, C]; bias f32 [C]."""
     _need_cuda(x, w, bias, out)

@@ -162,6 +162,14 @@ int de_groupnorm(const void* x, int x_dtype, const float* gamma, const float* be
                  void* out, int out_mode, float* out_f32, void* out_plain, int B, int HW, int C, int groups, float eps,
                  int act, void* ws, int64_t ws_bytes, void* stream);
 
+/* Fused DPT head tail ([UPSTREAM] midas/dpt_depth.py head, output_conv[2..5]):
+ * out[b,y,x] = relu(head_b + sum_n head_w[n] * relu(bias[n] + conv3x3(x, w)[b,y,x,n])), n < 32.
+ * x: NHWC bf16 [B,H,W,Cin], Cin % 64 == 0 (filter bank must fit shared memory: Cin <= 192); w: bf16 [32, ldw >= 9*Cin],
+ * k = (kh*3+kw)*Cin + ci (weights.pack_conv3x3); bias / head_w: float[32]; out: float [B,H,W].  Halo-tiled tcgen05
+ * kernel with the filter bank resident in shared memory (csrc/head_conv.cu). */
+int de_head_conv(const void* x, const void* w, int64_t ldw, const float* bias, const float* head_w, float head_b,
+                 float* out, int B, int H, int W, int Cin, void* stream);
+
 /* ---- direct (CUDA-core) convolutions for non-GEMM shapes; TF-"same" padding (geffnet Conv2dSame /
  * timm StdConv2dSame, MaxPool2dSame): pad_total = max((ceil(i/s)-1)*s+k-i, 0), extra pixel bottom/right. */
 /* 3-channel stem: x NCHW bf16 or f32 [B,3,H,W] (K1 layout 0 / 2), w float [Cout][k*k*3] ((kh,kw,c) order, BN

@@ -302,6 +302,30 @@ def test_head_dot():
     assert _relerr(out, ref) < 2e-5
 
 
+@pytest.mark.parametrize("B,H,W,Cin", [(1, 64, 96, 128), (2, 20, 40, 128), (3, 8, 16, 64), (1, 37, 53, 128), (2, 96, 96, 192)])
+def test_head_conv(B, H, W, Cin):
+    """Halo-tiled head kernel (csrc/head_conv.cu) vs torch fp32 and vs the general kernel's head-dot epilogue, on
+    tile-aligned and ragged sizes (partial tiles on both edges, TMA zero-filled halo)."""
+    from depth_estimation_b200 import ops
+    from depth_estimation_b200.weights import pack_conv3x3
+    dev = _dev()
+    x = _rand((B, H, W, Cin), dev, seed=27).bfloat16()
+    wt = _rand((32, Cin, 3, 3), dev, 0.05, seed=28).bfloat16()
+    bias = _rand((32,), dev, seed=29)
+    w2 = _rand((32,), dev, seed=26)
+    out = torch.full((B, H, W), -7.0, dtype=torch.float32, device=dev)
+    ops.head_conv(x, pack_conv3x3(wt), bias, w2, 0.7, out)
+    t = F.relu(F.conv2d(x.float().permute(0, 3, 1, 2), wt.float(), bias, padding=1))
+    ref = F.relu((t * w2.view(1, 32, 1, 1)).sum(1) + 0.7)
+    torch.cuda.synchronize()
+    assert _relerr(out, ref) < 2e-5
+    if Cin % 64 == 0:
+        gen = torch.empty_like(out)
+        ops.gemm(x, pack_conv3x3(wt), gen, conv=(B, H, W, Cin), bias=bias, act=1, head=(w2, 0.7), N=32)
+        torch.cuda.synchronize()
+        assert _relerr(out, gen) < 2e-6
+
+
 # ------------------------------------------------------------------------------------ others
 @pytest.mark.parametrize("dim", [768, 1024])
 def test_layernorm(dim):
