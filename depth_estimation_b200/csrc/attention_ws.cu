@@ -48,6 +48,11 @@ DEV void tmem_st_32x32(uint32_t taddr, const uint32_t* r) {
       : "memory");
 }
 DEV void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+DEV float fmax3(float a, float b, float c) {
+  float d;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
 // tcgen05.mma, both operands from shared-memory descriptors, accumulate flag known at compile time
 template <bool kAcc>
 DEV void umma_bf16_c(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc) {
@@ -315,11 +320,11 @@ attention_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const WsParams p)
         }
         float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-        for (int i = 0; i < 128; i += 4) {
-          mx4[0] = fmaxf(mx4[0], __uint_as_float(sv[i]));
-          mx4[1] = fmaxf(mx4[1], __uint_as_float(sv[i + 1]));
-          mx4[2] = fmaxf(mx4[2], __uint_as_float(sv[i + 2]));
-          mx4[3] = fmaxf(mx4[3], __uint_as_float(sv[i + 3]));
+        for (int i = 0; i < 128; i += 8) {                      // 3-input max (FMNMX3): 64 instructions, not 128
+          mx4[0] = fmax3(mx4[0], __uint_as_float(sv[i]), __uint_as_float(sv[i + 1]));
+          mx4[1] = fmax3(mx4[1], __uint_as_float(sv[i + 2]), __uint_as_float(sv[i + 3]));
+          mx4[2] = fmax3(mx4[2], __uint_as_float(sv[i + 4]), __uint_as_float(sv[i + 5]));
+          mx4[3] = fmax3(mx4[3], __uint_as_float(sv[i + 6]), __uint_as_float(sv[i + 7]));
         }
         WS_STAMP(2);
         const float m_new = fmaxf(m_run, fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])));
@@ -362,14 +367,16 @@ attention_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const WsParams p)
 #pragma unroll
             for (int i = 0; i < 16; ++i) pk[c * 16 + i] = 0u;
           }
+          if (c == 1) {                                         // first half of P leaves while the second is computed
+            if (g > 0 && !pv_waited) {                          // PV(g-1) must be done reading P(g-1)
+              mbar_wait(&b.pv_done, (g - 1) & 1);
+              tc_fence_after();
+            }
+            tmem_st_32x32(tP, pk);
+          }
         }
         l_run += (rs4[0] + rs4[1]) + (rs4[2] + rs4[3]);
         WS_STAMP(3);
-        if (g > 0 && !pv_waited) {                              // PV(g-1) must be done reading P(g-1)
-          mbar_wait(&b.pv_done, (g - 1) & 1);
-          tc_fence_after();
-        }
-        tmem_st_32x32(tP, pk);
         if (nch > 2) tmem_st_32x32(tP + 32, pk + 32);
         tmem_st_wait();
         tc_fence_before();
