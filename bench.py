@@ -199,7 +199,11 @@ def instrumented_step(est, frames_dev, B, H, W):
     def attn_flops(qkv, out, B_, T, heads, *a, **k):
         return 4.0 * B_ * heads * T * T * 64
 
+    def head_up_flops(x, *a, **k):
+        return 2.0 * x.shape[0] * 4 * x.shape[1] * x.shape[2] * 32 * 9 * x.shape[3]
+
     wrap("head_conv", head_flops)
+    wrap("head_up_conv", head_up_flops)
     wrap("attention", attn_flops)
     for n in ("preprocess", "postprocess", "layernorm", "cast_tokens", "fill_cls", "upsample2x",
               "im2col3x3", "stem_conv", "depthwise", "maxpool3x3s2", "groupnorm"):
@@ -360,7 +364,7 @@ def run_ours(args):
                     "launches_per_step": g["launches"], "share_of_step": g["ms"] / tot_ms,
                     "kernel_ms_per_step": {k: round(v["ms"], 3) for k, v in sorted(agg.items())},
                     "other_tensor_kernels_tflops": {k: round(agg[k]["flops"] / (agg[k]["ms"] * 1e-3) / 1e12, 1)
-                                                    for k in ("attention", "head_conv") if k in agg and agg[k]["ms"] > 0}}
+                                                    for k in ("attention", "head_conv", "head_up_conv") if k in agg and agg[k]["ms"] > 0}}
         gf = GFLOP_PER_FRAME.get((args.model, W, H))
         cpu = None
         if not args.no_cpu_baseline:

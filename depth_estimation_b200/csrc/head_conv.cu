@@ -194,13 +194,318 @@ head_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   }
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Same head tail with the bilinear x2 upsample in front of it fused in ([UPSTREAM] output_conv[1..5]): the kernel
+// reads the LOW-resolution activation and never materialises the upsampled one (1.2 GB written + read back per
+// 32-frame DPT_Large step; the upsample kernel and the L2->smem feed of the kernel above were the two costs left).
+// Eight producer warps replace the TMA producer: per (tile, 64-channel block) they interpolate the 10 x 18 pixel halo
+// once (fp32 lerps, rounded to bf16 exactly like de_upsample2x) and write it to shared memory three times - one copy
+// per horizontal tap dx, in the 128B-swizzled K-major layout the UMMA descriptors expect - then publish the unit
+// with fence.proxy.async + an mbarrier arrive per warp.  MMA issue, TMEM stages and epilogue are as above.
+constexpr int kHuProdWarps = 10;                            // two groups of 5 warps (upper / lower 5 halo rows), each 18 halo
+constexpr int kHuThreads = 256 + 32 * kHuProdWarps;        // columns x 8 channel groups = 144 of 160 threads busy
+constexpr int kHuUnitBytes = 3 * kHcStageBytes;             // three dx copies of one 64-channel block
+constexpr int kHuUnits = 2;
+// low-resolution source window of one (tile, 64-channel block): the 10 x 18 halo spans <= 4.5 x 8.5 source pixels, i.e.
+// <= 7 x 11 taps with the +1 neighbours; staged by TMA (no swizzle, 128 B per pixel) two units ahead of the producers
+constexpr int kHuSrcRows = 7, kHuSrcCols = 12;
+constexpr int kHuSrcBytes = kHuSrcRows * kHuSrcCols * 128;  // 10752
+constexpr int kHuSrcSlotBytes = 11264;                      // 11 KB slots keep everything 1024-aligned
+constexpr int kHuSrcSlots = 2;
+
+struct HeadUpParams {
+  const __nv_bfloat16* x;     // [B, Hs, Ws, Cin]
+  int B, Hs, Ws, H, W, Cin, cin_blocks, tiles_x, tiles_y, num_tiles, align_corners;
+  float rh, rw;
+  const float* bias;
+  const float* head_w;
+  float head_b;
+  float* out;
+};
+
+// first source row / column the halo of a tile touches (same expression in the TMA warp and in the producers)
+DEV int hu_src_base(int o0, float r, int align_corners) {
+  const int o = o0 < 0 ? 0 : o0;
+  const float s = align_corners ? r * o : fmaxf(0.5f * (o + 0.5f) - 0.5f, 0.f);
+  return static_cast<int>(s);
+}
+
+__global__ void __launch_bounds__(kHuThreads, 1)
+head_up_conv_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX, const HeadUpParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+  const int w_chunks = 9 * p.cin_blocks;
+  uint8_t* sW = smem;
+  uint8_t* sA = smem + w_chunks * kHcWChunk;                 // kHuUnits units of three 20 KB copies
+  uint8_t* sX = sA + kHuUnits * kHuUnitBytes;                // source windows
+  uint8_t* post = sX + kHuSrcSlots * kHuSrcSlotBytes;
+  uint64_t* full = reinterpret_cast<uint64_t*>(post);
+  uint64_t* empty = full + kHuUnits;
+  uint64_t* tfull = empty + kHuUnits;
+  uint64_t* tempty = tfull + kHcAcc;
+  uint64_t* wfull = tempty + kHcAcc;
+  uint64_t* xfull = wfull + 1;
+  uint64_t* xempty = xfull + kHuSrcSlots;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(xempty + kHuSrcSlots);
+  float* s_bias = reinterpret_cast<float*>(post + 256);
+  float* s_hw = s_bias + kHcN;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmW);
+    tma_prefetch_desc(&tmX);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < kHuUnits; ++i) {
+      mbar_init(&full[i], kHuProdWarps);
+      mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < kHuSrcSlots; ++i) {
+      mbar_init(&xfull[i], 1);
+      mbar_init(&xempty[i], kHuProdWarps);
+    }
+    for (int i = 0; i < kHcAcc; ++i) {
+      mbar_init(&tfull[i], 1);
+      mbar_init(&tempty[i], 4);
+    }
+    mbar_init(wfull, 1);
+    mbar_fence_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, kHcAcc * kHcN);
+    tmem_relinquish();
+  }
+  if (warp == 3) {
+    s_bias[lane] = p.bias ? __ldg(p.bias + lane) : 0.f;
+    s_hw[lane] = __ldg(p.head_w + lane);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int per_img = p.tiles_x * p.tiles_y;
+  const int units_per_tile = p.cin_blocks;
+
+  if (warp == 0) {
+    if (lane == 0) {                                         // filter bank once, then the source windows
+      mbar_arrive_expect_tx(wfull, w_chunks * kHcWChunk);
+      for (int c = 0; c < w_chunks; ++c) tma_load_2d(sW + c * kHcWChunk, &tmW, wfull, c * 64, 0);
+      int xs = 0;
+      uint32_t xphase = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        const int b = tile / per_img, t = tile % per_img;
+        const int ysb = hu_src_base((t / p.tiles_x) * kHcBH - 1, p.rh, p.align_corners);
+        const int xsb = hu_src_base((t % p.tiles_x) * kHcBW - 1, p.rw, p.align_corners);
+        for (int cb = 0; cb < units_per_tile; ++cb) {
+          mbar_wait(&xempty[xs], xphase ^ 1);
+          mbar_arrive_expect_tx(&xfull[xs], kHuSrcBytes);
+          tma_load_4d(sX + xs * kHuSrcSlotBytes, &tmX, &xfull[xs], cb * 64, xsb, ysb, b);
+          if (++xs == kHuSrcSlots) {
+            xs = 0;
+            xphase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    constexpr uint32_t idesc = make_idesc_bf16(128, kHcN);
+    mbar_wait(wfull, 0);
+    tc_fence_after();
+    int u = 0;
+    uint32_t phase = 0;
+    int as = 0;
+    uint32_t aphase = 0;
+    const uint32_t w_base = smem_u32(sW);
+    const uint64_t b_dy = static_cast<uint64_t>((3 * p.cin_blocks * kHcWChunk) >> 4);
+    const uint64_t b_dx = static_cast<uint64_t>((p.cin_blocks * kHcWChunk) >> 4);
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      mbar_wait(&tempty[as], aphase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + as * kHcN;
+      for (int cb = 0; cb < units_per_tile; ++cb) {
+        mbar_wait(&full[u], phase);
+        tc_fence_after();
+        const uint64_t adesc = make_sw128_kmajor_desc(smem_u32(sA + u * kHuUnitBytes));
+        const uint64_t bdesc = make_sw128_kmajor_desc(w_base + cb * kHcWChunk);
+        if (elect_one()) {
+#pragma unroll
+          for (int dx = 0; dx < 3; ++dx) {
+#pragma unroll
+            for (int dy = 0; dy < 3; ++dy) {
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                umma_bf16(d_tmem, adesc + dx * (kHcStageBytes >> 4) + dy * ((kHcBW * 128) >> 4) + 2 * k,
+                          bdesc + dx * b_dx + dy * b_dy + 2 * k, idesc, (cb | dx | dy | k) != 0);
+            }
+          }
+          umma_commit(&empty[u]);
+          if (cb == units_per_tile - 1) umma_commit(&tfull[as]);
+        }
+        __syncwarp();
+        if (++u == kHuUnits) {
+          u = 0;
+          phase ^= 1;
+        }
+      }
+      if (++as == kHcAcc) {
+        as = 0;
+        aphase ^= 1;
+      }
+    }
+  } else if (warp >= 4 && warp < 8) {
+    // ------------------------------------------------------------------ epilogue: one accumulator row per thread
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
+    int as = 0;
+    uint32_t aphase = 0;
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      const int b = tile / per_img, t = tile % per_img;
+      const int y = (t / p.tiles_x) * kHcBH + r / kHcBW, x = (t % p.tiles_x) * kHcBW + r % kHcBW;
+      mbar_wait(&tfull[as], aphase);
+      tc_fence_after();
+      uint32_t acc[32];
+      tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * kHcN, acc);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[as]);
+      float s0 = p.head_b, s1 = 0.f;
+#pragma unroll
+      for (int n = 0; n < kHcN; n += 2) {
+        s0 = fmaf(fmaxf(__uint_as_float(acc[n]) + s_bias[n], 0.f), s_hw[n], s0);
+        s1 = fmaf(fmaxf(__uint_as_float(acc[n + 1]) + s_bias[n + 1], 0.f), s_hw[n + 1], s1);
+      }
+      if (y < p.H && x < p.W) p.out[((long long)b * p.H + y) * p.W + x] = fmaxf(s0 + s1, 0.f);
+      if (++as == kHcAcc) {
+        as = 0;
+        aphase ^= 1;
+      }
+    }
+  } else if (warp >= 8) {
+    // ------------------------------------------------------------------ producers: interpolate + swizzled smem writes
+    // Thread = (halo column hx, 8-channel group q, upper / lower half of the 10 halo rows).  The column's horizontal
+    // taps and weights are fixed for the whole tile; walking down its 5 rows, the horizontally interpolated source row
+    // (8 fp32) is kept and reused while the source row index repeats (x2 upsampling: every other step), so a thread
+    // reads ~8 instead of 20 16-byte vectors per unit.  Shared-memory bandwidth is what bounds this kernel (the
+    // N = 32 MMAs alone read 5 KB each), so every avoided LDS / STS counts.
+    const int ptid = threadIdx.x - 256;
+    const int half = ptid / 160, pin = ptid - half * 160;    // warp-uniform row half: no divergence in the row walk
+    const int q = pin & 7;
+    const int hx = pin >> 3;                                 // 0..19, columns >= 18 idle
+    const bool active = hx < kHcBW + 2;
+    const int hy0 = half * (kHcBoxRows / 2);
+    // byte offsets of this thread's 16-byte chunk inside the three dx copies (row = hy*16 + j and 16 % 8 == 0, so the
+    // swizzle phase row & 7 is j & 7 for every halo row); -1: this column does not exist in that copy
+    int soff[3];
+#pragma unroll
+    for (int dx = 0; dx < 3; ++dx) {
+      const int j = hx - dx;
+      soff[dx] = (active && j >= 0 && j < kHcBW) ? dx * kHcStageBytes + j * 128 + ((q ^ (j & 7)) << 4) : -1;
+    }
+    int u = 0, xs = 0;
+    uint32_t phase = 0, xphase = 0;
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      const int t = tile % per_img;
+      const int y0 = (t / p.tiles_x) * kHcBH - 1, x0 = (t % p.tiles_x) * kHcBW - 1;
+      const int ysb = hu_src_base(y0, p.rh, p.align_corners), xsb = hu_src_base(x0, p.rw, p.align_corners);
+      const int ox = x0 + hx;
+      const bool col_ok = active && ox >= 0 && ox < p.W;
+      const float sx = p.align_corners ? p.rw * ox : fmaxf(0.5f * (ox + 0.5f) - 0.5f, 0.f);
+      const int xs0 = min(static_cast<int>(sx), p.Ws - 1), xs1 = min(xs0 + 1, p.Ws - 1);
+      const float lx = sx - xs0, hxw = 1.f - lx;
+      const int c0 = (xs0 - xsb) * 128 + q * 16, c1 = (xs1 - xsb) * 128 + q * 16;
+      for (int cb = 0; cb < units_per_tile; ++cb) {
+        mbar_wait(&xfull[xs], xphase);                       // source window landed (TMA)
+        mbar_wait(&empty[u], phase ^ 1);                     // the MMAs are done with this unit's three copies
+        uint8_t* ubase = sA + u * kHuUnitBytes;
+        const uint8_t* src = sX + xs * kHuSrcSlotBytes;
+        float h0[8], h1[8];
+        int cy0 = -1, cy1 = -1;                                // source rows held in h0 / h1
+        auto hrow = [&](int ys, float* h) {
+          const uint8_t* rp = src + (ys - ysb) * (kHuSrcCols * 128);
+          const uint4 a = *reinterpret_cast<const uint4*>(rp + c0);
+          const uint4 bq = *reinterpret_cast<const uint4*>(rp + c1);
+          const uint32_t* pa = &a.x;
+          const uint32_t* pb = &bq.x;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            h[2 * k] = hxw * bf16_lo(pa[k]) + lx * bf16_lo(pb[k]);
+            h[2 * k + 1] = hxw * bf16_hi(pa[k]) + lx * bf16_hi(pb[k]);
+          }
+        };
+#pragma unroll
+        for (int i = 0; i < kHcBoxRows / 2; ++i) {
+          const int hy = hy0 + i;
+          const int oy = y0 + hy;
+          uint4 val = make_uint4(0u, 0u, 0u, 0u);
+          if (col_ok && oy >= 0 && oy < p.H) {
+            const float sy = p.align_corners ? p.rh * oy : fmaxf(0.5f * (oy + 0.5f) - 0.5f, 0.f);
+            const int ys0 = min(static_cast<int>(sy), p.Hs - 1), ys1 = min(ys0 + 1, p.Hs - 1);
+            const float ly = sy - ys0, hyw = 1.f - ly;
+            if (ys0 != cy0) {
+              if (ys0 == cy1) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) h0[k] = h1[k];
+              } else {
+                hrow(ys0, h0);
+              }
+              cy0 = ys0;
+            }
+            if (ys1 != cy1) {
+              if (ys1 == cy0) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) h1[k] = h0[k];
+              } else {
+                hrow(ys1, h1);
+              }
+              cy1 = ys1;
+            }
+            uint32_t o[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k)                        // same expression tree as upsample2x_kernel (misc.cu)
+              o[k] = pack_bf16(hyw * h0[2 * k] + ly * h1[2 * k], hyw * h0[2 * k + 1] + ly * h1[2 * k + 1]);
+            val = make_uint4(o[0], o[1], o[2], o[3]);
+          }
+#pragma unroll
+          for (int dx = 0; dx < 3; ++dx)
+            if (soff[dx] >= 0) *reinterpret_cast<uint4*>(ubase + soff[dx] + hy * (kHcBW * 128)) = val;
+        }
+        fence_proxy_async_smem();                              // generic-proxy writes -> visible to the UMMA (async proxy)
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive(&full[u]);
+          mbar_arrive(&xempty[xs]);
+        }
+        if (++u == kHuUnits) {
+          u = 0;
+          phase ^= 1;
+        }
+        if (++xs == kHuSrcSlots) {
+          xs = 0;
+          xphase ^= 1;
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kHcAcc * kHcN);
+  }
+}
+
 static bool hc_make_map(CUtensorMap* map, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
-                        const uint32_t* box) {
+                        const uint32_t* box, CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
   auto fn = get_tensor_map_encoder();
   if (!fn) return false;
   uint32_t estr[5] = {1, 1, 1, 1, 1};
   CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), dims, strides_bytes, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled failed with CUresult %d (head conv, rank %d)", (int)r, rank);
@@ -257,4 +562,54 @@ extern "C" int de_head_conv(const void* x, const void* w, int64_t ldw, const flo
   head_conv_kernel<<<grid, kHcThreads, smem_bytes, reinterpret_cast<cudaStream_t>(stream)>>>(ta, tw, p);
   count_launch();
   return cuda_check_launch("head_conv_kernel");
+}
+
+extern "C" int de_head_up_conv(const void* x, const void* w, int64_t ldw, const float* bias, const float* head_w,
+                               float head_b, float* out, int B, int Hs, int Ws, int Cin, int align_corners, void* stream) {
+  using namespace deb;
+  if (!x || !w || !head_w || !out) return fail(DE_ERR_INVALID, "de_head_up_conv: null pointer");
+  if (B < 1 || Hs < 1 || Ws < 1 || Cin < 64 || Cin % 64 != 0) return fail(DE_ERR_UNSUPPORTED, "de_head_up_conv: Cin=%d must be a multiple of 64", Cin);
+  if (ldw < 9LL * Cin || ldw % 8 != 0) return fail(DE_ERR_INVALID, "de_head_up_conv: ldw=%lld too small / unaligned", (long long)ldw);
+  HeadUpParams p{};
+  p.x = reinterpret_cast<const __nv_bfloat16*>(x);
+  p.B = B; p.Hs = Hs; p.Ws = Ws; p.H = 2 * Hs; p.W = 2 * Ws; p.Cin = Cin;
+  p.cin_blocks = Cin / 64;
+  p.tiles_x = (p.W + kHcBW - 1) / kHcBW;
+  p.tiles_y = (p.H + kHcBH - 1) / kHcBH;
+  const long long tiles = (long long)B * p.tiles_x * p.tiles_y;
+  if (tiles > 0x7fffffffLL) return fail(DE_ERR_UNSUPPORTED, "de_head_up_conv: too many tiles");
+  p.num_tiles = (int)tiles;
+  p.align_corners = align_corners;
+  // ATen area_pixel_compute_scale (align_corners): (in - 1) / (out - 1) in float
+  p.rh = p.H > 1 ? (float)(Hs - 1) / (float)(p.H - 1) : 0.f;
+  p.rw = p.W > 1 ? (float)(Ws - 1) / (float)(p.W - 1) : 0.f;
+  p.bias = bias; p.head_w = head_w; p.head_b = head_b; p.out = out;
+  const int w_bytes = 9 * p.cin_blocks * kHcWChunk;
+  const int post_bytes = 256 + 2 * kHcN * 4;
+  const int smem_bytes = 1024 + w_bytes + kHuUnits * kHuUnitBytes + kHuSrcSlots * kHuSrcSlotBytes + post_bytes;
+  if (smem_bytes > 232448) return fail(DE_ERR_UNSUPPORTED, "de_head_up_conv: Cin=%d does not fit shared memory", Cin);
+  CUtensorMap tw, tx;
+  {
+    const uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)Ws, (uint64_t)Hs, (uint64_t)B};
+    const uint64_t strides[3] = {(uint64_t)Cin * 2, (uint64_t)Ws * Cin * 2, (uint64_t)Hs * Ws * Cin * 2};
+    const uint32_t box[4] = {64, kHuSrcCols, kHuSrcRows, 1};
+    if (!hc_make_map(&tx, x, 4, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_NONE)) return DE_ERR_CUDA;
+  }
+  {
+    const uint64_t dims[2] = {(uint64_t)9 * Cin, (uint64_t)kHcN};
+    const uint64_t strides[1] = {(uint64_t)ldw * 2};
+    const uint32_t box[2] = {64, kHcN};
+    if (!hc_make_map(&tw, w, 2, dims, strides, box)) return DE_ERR_CUDA;
+  }
+  static int attr_smem = 0;
+  if (attr_smem < smem_bytes) {
+    cudaError_t e = cudaFuncSetAttribute(head_up_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(head_up_conv)");
+    attr_smem = smem_bytes;
+  }
+  int grid = num_sms();
+  if (p.num_tiles < grid) grid = p.num_tiles;
+  head_up_conv_kernel<<<grid, kHuThreads, smem_bytes, reinterpret_cast<cudaStream_t>(stream)>>>(tw, tx, p);
+  count_launch();
+  return cuda_check_launch("head_up_conv_kernel");
 }

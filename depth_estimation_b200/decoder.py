@@ -12,8 +12,9 @@ Layout: NHWC bf16 activations, fp32 accumulation.  Fusions (all parity-checked a
   * `path + RCU1(l)` is folded into RCU1.conv2's epilogue (two addends);
   * the 1x1 out_conv is applied BEFORE the bilinear x2 (linear ops commute; interpolation weights sum to
     one, so the bias commutes as well) - 4x fewer FLOPs;
-  * the head's conv3x3(->32)+ReLU+conv1x1(32->1)+ReLU is a single launch (csrc/head_conv.cu for DPT's 128
-    channels, the GEMM kernel's head-dot epilogue for MiDaS_small's 32).
+  * the head's upsample x2 + conv3x3(->32)+ReLU+conv1x1(32->1)+ReLU is a single launch for DPT's 128 channels
+    (csrc/head_conv.cu: the upsampled activation only ever exists in shared memory); MiDaS_small's 32 channels
+    use de_upsample2x + the GEMM kernel's head-dot epilogue.
 """
 from __future__ import annotations
 
@@ -106,12 +107,12 @@ class ScratchDecoder:
         _, H, W, Cc = path.shape
         h0 = self._buf(("h0", B, H, W), (B, H, W, self.h0_c))
         self._conv(path, self.h0_w, h0, B, H, W, Cc, bias=self.h0_b)
-        h1 = self._buf(("h1", B, H, W), (B, 2 * H, 2 * W, self.h0_c))
-        ops.upsample2x(h0, h1, self.head_ac)
         pred = self._buf(("pred", B, H, W), (B, 2 * H, 2 * W), torch.float32)
-        if self.h0_c % 64 == 0 and self.h0_c <= 192:        # DPT: halo-tiled kernel, filter bank resident in smem
-            ops.head_conv(h1, self.h2_w, self.h2_b, self.h4_w, self.h4_b, pred)
+        if self.h0_c % 64 == 0 and self.h0_c <= 128:        # DPT: upsample + head tail in one halo-tiled kernel
+            ops.head_up_conv(h0, self.h2_w, self.h2_b, self.h4_w, self.h4_b, pred, self.head_ac)
         else:                                               # MiDaS_small (32 channels): general implicit-GEMM kernel
+            h1 = self._buf(("h1", B, H, W), (B, 2 * H, 2 * W, self.h0_c))
+            ops.upsample2x(h0, h1, self.head_ac)
             ops.gemm(h1, self.h2_w, pred, conv=(B, 2 * H, 2 * W, self.h0_c), bias=self.h2_b, act=ops.ACT_RELU,
                      head=(self.h4_w, self.h4_b), N=32)
         return pred

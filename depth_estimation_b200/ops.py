@@ -264,6 +264,21 @@ def head_conv(x: torch.Tensor, w: torch.Tensor, bias, head_w: torch.Tensor, head
     return out
 
 
+def head_up_conv(x: torch.Tensor, w: torch.Tensor, bias, head_w: torch.Tensor, head_b: float, out: torch.Tensor,
+                 align_corners: bool):
+    """head_conv(upsample2x(x)) without materialising the upsampled tensor: x bf16 NHWC [B,Hs,Ws,Cin], out fp32
+    [B,2Hs,2Ws]."""
+    _need_cuda(x, w, bias, head_w, out)
+    B, Hs, Ws, Cin = x.shape
+    assert x.dtype == torch.bfloat16 and x.is_contiguous() and w.dtype == torch.bfloat16 and w.shape[0] == 32
+    assert out.dtype == torch.float32 and out.is_contiguous() and tuple(out.shape) == (B, 2 * Hs, 2 * Ws)
+    assert head_w.dtype == torch.float32 and head_w.numel() == 32 and (bias is None or bias.dtype == torch.float32)
+    _lib.check(_lib.load().de_head_up_conv(x.data_ptr(), w.data_ptr(), w.stride(0), _ptr(bias), head_w.data_ptr(),
+                                           float(head_b), out.data_ptr(), B, Hs, Ws, Cin, 1 if align_corners else 0,
+                                           _stream()), "de_head_up_conv")
+    return out
+
+
 def depthwise(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, out: torch.Tensor, k: int, stride: int, act: int):
     """x: bf16 NHWC; w: bf16 [k*k, C]; bias f32 [C]."""
     _need_cuda(x, w, bias, out)

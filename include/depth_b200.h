@@ -170,6 +170,12 @@ int de_groupnorm(const void* x, int x_dtype, const float* gamma, const float* be
 int de_head_conv(const void* x, const void* w, int64_t ldw, const float* bias, const float* head_w, float head_b,
                  float* out, int B, int H, int W, int Cin, void* stream);
 
+/* The same head tail with the bilinear x2 upsample in front of it fused in (output_conv[1..5]): x is the LOW-resolution
+ * NHWC bf16 activation [B,Hs,Ws,Cin]; out: float [B,2*Hs,2*Ws].  The upsampled activation is interpolated into shared
+ * memory (rounded to bf16 exactly as de_upsample2x does) and never written to HBM. */
+int de_head_up_conv(const void* x, const void* w, int64_t ldw, const float* bias, const float* head_w, float head_b,
+                    float* out, int B, int Hs, int Ws, int Cin, int align_corners, void* stream);
+
 /* ---- direct (CUDA-core) convolutions for non-GEMM shapes; TF-"same" padding (geffnet Conv2dSame /
  * timm StdConv2dSame, MaxPool2dSame): pad_total = max((ceil(i/s)-1)*s+k-i, 0), extra pixel bottom/right. */
 /* 3-channel stem: x NCHW bf16 or f32 [B,3,H,W] (K1 layout 0 / 2), w float [Cout][k*k*3] ((kh,kw,c) order, BN

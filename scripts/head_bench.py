@@ -36,6 +36,10 @@ print(f"head_conv (halo, resident filters): {t:.3f} ms  {fl / t / 1e9:.0f} TFLOP
 t = timeit(lambda: ops.gemm(x, w, out, conv=(B, H, W, Cin), bias=bias, act=1, head=(w2, 0.7), N=32))
 print(f"gemm head-dot epilogue            : {t:.3f} ms  {fl / t / 1e9:.0f} TFLOP/s")
 
+lo = torch.randn((B, H // 2, W // 2, Cin), device=dev).bfloat16()
+t = timeit(lambda: ops.head_up_conv(lo, w, bias, w2, 0.7, out, True))
+print(f"head_up_conv (fused x2 upsample)  : {t:.3f} ms  {fl / t / 1e9:.0f} TFLOP/s")
+
 # x2 bilinear upsample at the two big decoder shapes
 for (h, w, c) in ((192, 192, 128), (96, 96, 256)):
     src = torch.randn((B, h, w, c), device=dev).bfloat16()

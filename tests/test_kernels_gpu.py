@@ -326,6 +326,31 @@ def test_head_conv(B, H, W, Cin):
         assert _relerr(out, gen) < 2e-6
 
 
+@pytest.mark.parametrize("B,Hs,Ws,Cin,ac", [(1, 32, 48, 128, True), (2, 10, 20, 128, True), (1, 19, 27, 64, True),
+                                             (2, 12, 8, 128, False), (1, 48, 48, 128, True)])
+def test_head_up_conv(B, Hs, Ws, Cin, ac):
+    """Fused bilinear x2 + head tail vs the two-kernel path (bit-identical interpolation, same MMAs) and vs torch."""
+    from depth_estimation_b200 import ops
+    from depth_estimation_b200.weights import pack_conv3x3
+    dev = _dev()
+    x = _rand((B, Hs, Ws, Cin), dev, seed=81).bfloat16()
+    wt = _rand((32, Cin, 3, 3), dev, 0.05, seed=82).bfloat16()
+    bias = _rand((32,), dev, seed=83)
+    w2 = _rand((32,), dev, seed=84)
+    out = torch.full((B, 2 * Hs, 2 * Ws), -7.0, dtype=torch.float32, device=dev)
+    ops.head_up_conv(x, pack_conv3x3(wt), bias, w2, 0.3, out, ac)
+    up = torch.empty((B, 2 * Hs, 2 * Ws, Cin), dtype=torch.bfloat16, device=dev)
+    ops.upsample2x(x, up, ac)
+    two = torch.empty_like(out)
+    ops.head_conv(up, pack_conv3x3(wt), bias, w2, 0.3, two)
+    t = F.interpolate(x.float().permute(0, 3, 1, 2), scale_factor=2, mode="bilinear", align_corners=ac)
+    t = F.relu(F.conv2d(t.bfloat16().float(), wt.float(), bias, padding=1))
+    ref = F.relu((t * w2.view(1, 32, 1, 1)).sum(1) + 0.3)
+    torch.cuda.synchronize()
+    assert _relerr(out, two) < 1e-6, _relerr(out, two)
+    assert _relerr(out, ref) < 5e-3
+
+
 # ------------------------------------------------------------------------------------ others
 @pytest.mark.parametrize("dim", [768, 1024])
 def test_layernorm(dim):
