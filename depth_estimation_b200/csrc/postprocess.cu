@@ -66,9 +66,10 @@ DEV float dot4(float a, float b, float c, float d, float4 w) {
 constexpr int kPostTW = 128;
 
 // one output row of the tile for this lane's 4 columns: vertical taps from s_h, then every requested view of the map
-template <bool kFull>
-DEV void post_store_row(const PostParams& p, const float* hcol, int4 yo, float4 w, long long o, int nleft) {
-  const float4 a0 = *reinterpret_cast<const float4*>(hcol + yo.x);
+// kOuts: bit 0 fp32 map, bit 1 uint8 grey level, bit 2 bf16 metric map (compile-time: no per-row pointer tests)
+template <bool kFull, int kOuts>
+DEV void post_store_row(const PostParams& p, const char* hcol, int4 yo, float4 w, long long o, int nleft) {
+  const float4 a0 = *reinterpret_cast<const float4*>(hcol + yo.x);     // yo: byte offsets into s_h
   const float4 a1 = *reinterpret_cast<const float4*>(hcol + yo.y);
   const float4 a2 = *reinterpret_cast<const float4*>(hcol + yo.z);
   const float4 a3 = *reinterpret_cast<const float4*>(hcol + yo.w);
@@ -78,11 +79,11 @@ DEV void post_store_row(const PostParams& p, const float* hcol, int4 yo, float4 
   v[2] = dot4(a0.z, a1.z, a2.z, a3.z, w);
   v[3] = dot4(a0.w, a1.w, a2.w, a3.w, w);
   if (kFull) {
-    if (p.out_map) __stcs(reinterpret_cast<float4*>(p.out_map + o), make_float4(v[0], v[1], v[2], v[3]));
-    if (p.out_vis)
+    if (kOuts & 1) __stcs(reinterpret_cast<float4*>(p.out_map + o), make_float4(v[0], v[1], v[2], v[3]));
+    if (kOuts & 2)
       *reinterpret_cast<uint32_t*>(p.out_vis + o) =
           vis_byte(v[0]) | (vis_byte(v[1]) << 8) | (vis_byte(v[2]) << 16) | (vis_byte(v[3]) << 24);
-    if (p.out_metric) {
+    if (kOuts & 4) {
       uint2 m;
       m.x = pack_bf16(v[0] * p.metric_scale, v[1] * p.metric_scale);
       m.y = pack_bf16(v[2] * p.metric_scale, v[3] * p.metric_scale);
@@ -90,14 +91,15 @@ DEV void post_store_row(const PostParams& p, const float* hcol, int4 yo, float4 
     }
   } else {
     for (int e = 0; e < 4 && e < nleft; ++e) {
-      if (p.out_map) p.out_map[o + e] = v[e];
-      if (p.out_vis) p.out_vis[o + e] = static_cast<uint8_t>(vis_byte(v[e]));
-      if (p.out_metric) p.out_metric[o + e] = __float2bfloat16(v[e] * p.metric_scale);
+      if (kOuts & 1) p.out_map[o + e] = v[e];
+      if (kOuts & 2) p.out_vis[o + e] = static_cast<uint8_t>(vis_byte(v[e]));
+      if (kOuts & 4) p.out_metric[o + e] = __float2bfloat16(v[e] * p.metric_scale);
     }
   }
 }
 
-__global__ void __launch_bounds__(kPostThreads) postprocess_kernel(const PostParams p) {
+template <int kOuts>
+__global__ void __launch_bounds__(kPostThreads, 6) postprocess_kernel(const PostParams p) {   // <= 40 registers: 6 CTAs/SM
   extern __shared__ __align__(16) uint8_t smem[];
   float* s_h = reinterpret_cast<float*>(smem);                        // [max_rows][128]
   int4* s_yo = reinterpret_cast<int4*>(s_h + p.max_rows * kPostTW);   // [TH] s_h offsets of the 4 row taps
@@ -130,7 +132,8 @@ __global__ void __launch_bounds__(kPostThreads) postprocess_kernel(const PostPar
     }
     if (tid < nrows) {
       int4 yi = __ldg(reinterpret_cast<const int4*>(p.yidx) + oy0 + tid);
-      yi.x = (yi.x - ys) * kPostTW; yi.y = (yi.y - ys) * kPostTW; yi.z = (yi.z - ys) * kPostTW; yi.w = (yi.w - ys) * kPostTW;
+      yi.x = (yi.x - ys) * (kPostTW * 4); yi.y = (yi.y - ys) * (kPostTW * 4);      // byte offsets into s_h
+      yi.z = (yi.z - ys) * (kPostTW * 4); yi.w = (yi.w - ys) * (kPostTW * 4);
       s_yo[tid] = yi;
       s_yw[tid] = __ldg(reinterpret_cast<const float4*>(p.yw) + oy0 + tid);
     }
@@ -158,16 +161,16 @@ __global__ void __launch_bounds__(kPostThreads) postprocess_kernel(const PostPar
   // ---- phase B: vertical taps, stores
   const int c0 = (tid & 31) * 4;
   if (c0 >= ncols) return;
-  const float* hcol = s_h + c0;
+  const char* hcol = reinterpret_cast<const char*>(s_h + c0);
   long long o = ((long long)b * p.H + oy0 + (tid >> 5)) * p.W + ox0 + c0;
   const int ostep = (kPostThreads / 32) * p.W;
   // 16-byte stores need the quad inside the tile and 4-element alignment of every row start: W % 4 == 0
   if (c0 + 4 <= ncols && (p.W & 3) == 0) {
     for (int ry = tid >> 5; ry < nrows; ry += kPostThreads / 32, o += ostep)
-      post_store_row<true>(p, hcol, s_yo[ry], s_yw[ry], o, 4);
+      post_store_row<true, kOuts>(p, hcol, s_yo[ry], s_yw[ry], o, 4);
   } else {
     for (int ry = tid >> 5; ry < nrows; ry += kPostThreads / 32, o += ostep)
-      post_store_row<false>(p, hcol, s_yo[ry], s_yw[ry], o, ncols - c0);
+      post_store_row<false, kOuts>(p, hcol, s_yo[ry], s_yw[ry], o, ncols - c0);
   }
 }
 
@@ -278,7 +281,16 @@ extern "C" int de_postprocess(const void* pred, int in_dtype, int B, int h, int 
     }
     if (!ok) return fail(DE_ERR_UNSUPPORTED, "de_postprocess: resampling window too large");
     dim3 grid((W + p.TW - 1) / p.TW, (H + p.TH - 1) / p.TH, B);
-    postprocess_kernel<<<grid, kPostThreads, smem, st>>>(p);
+    const int outs = (out_map ? 1 : 0) | (out_vis ? 2 : 0) | (out_metric ? 4 : 0);
+    switch (outs) {
+      case 1: postprocess_kernel<1><<<grid, kPostThreads, smem, st>>>(p); break;
+      case 2: postprocess_kernel<2><<<grid, kPostThreads, smem, st>>>(p); break;
+      case 3: postprocess_kernel<3><<<grid, kPostThreads, smem, st>>>(p); break;
+      case 4: postprocess_kernel<4><<<grid, kPostThreads, smem, st>>>(p); break;
+      case 5: postprocess_kernel<5><<<grid, kPostThreads, smem, st>>>(p); break;
+      case 6: postprocess_kernel<6><<<grid, kPostThreads, smem, st>>>(p); break;
+      default: postprocess_kernel<7><<<grid, kPostThreads, smem, st>>>(p); break;
+    }
     count_launch();
     int rc = cuda_check_launch("postprocess_kernel");
     if (rc != DE_OK) return rc;

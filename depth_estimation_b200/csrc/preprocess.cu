@@ -36,6 +36,13 @@ struct PreParams {
 };
 
 constexpr int kPreThreads = 256;
+#ifndef PRE_MINB
+#define PRE_MINB 5          // 48 registers -> 5 CTAs/SM; measured best of {4,5,6} x unroll {1,2} (+7-10 % over 4)
+#endif
+#ifndef PRE_UNROLL
+#define PRE_UNROLL 1
+#endif
+constexpr int kPreUnroll = PRE_UNROLL;
 constexpr int kPreTW = 64;                                  // output columns per CTA (2 per lane)
 
 // byte k of a little-endian word -> float, exactly: 0x4B0000bb is 2^23 + b
@@ -77,7 +84,7 @@ DEV float vdot(float a, float b, float c, float d, float4 w) {
   return acc;
 }
 
-__global__ void __launch_bounds__(kPreThreads) preprocess_kernel(const PreParams p) {
+__global__ void __launch_bounds__(kPreThreads, PRE_MINB) preprocess_kernel(const PreParams p) {
   extern __shared__ __align__(16) float s_line[];             // [8 warps][max_words * 4]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.z;
@@ -114,6 +121,7 @@ __global__ void __launch_bounds__(kPreThreads) preprocess_kernel(const PreParams
     const uint8_t* r2 = frame + (long long)yi.z * p.row_stride;
     const uint8_t* r3 = frame + (long long)yi.w * p.row_stride;
     // ---- V: four vertical taps on the raw bytes, one 32-bit word per lane and iteration
+#pragma unroll kPreUnroll
     for (int wi = lane; wi < nwords; wi += 32) {
       uint32_t u0, u1, u2, u3;
       if (fast) {                                               // whole tile aligned and inside the buffer (CTA-uniform)
