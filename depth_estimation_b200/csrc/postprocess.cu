@@ -22,7 +22,7 @@ struct PostParams {
   float* out_map;
   __nv_bfloat16* out_metric;
   uint8_t* out_vis;
-  float metric_scale;
+  float metric_scale, metric_shift;   // metric = map*scale + shift (rel2abs: 1/2.54, 0; rel2abs_2: m/30.48, b/30.48)
   int TW, TH, max_rows, max_cols;
 };
 
@@ -85,15 +85,15 @@ DEV void post_store_row(const PostParams& p, const char* hcol, int4 yo, float4 w
           vis_byte(v[0]) | (vis_byte(v[1]) << 8) | (vis_byte(v[2]) << 16) | (vis_byte(v[3]) << 24);
     if (kOuts & 4) {
       uint2 m;
-      m.x = pack_bf16(v[0] * p.metric_scale, v[1] * p.metric_scale);
-      m.y = pack_bf16(v[2] * p.metric_scale, v[3] * p.metric_scale);
+      m.x = pack_bf16(fmaf(v[0], p.metric_scale, p.metric_shift), fmaf(v[1], p.metric_scale, p.metric_shift));
+      m.y = pack_bf16(fmaf(v[2], p.metric_scale, p.metric_shift), fmaf(v[3], p.metric_scale, p.metric_shift));
       __stcs(reinterpret_cast<uint2*>(p.out_metric + o), m);
     }
   } else {
     for (int e = 0; e < 4 && e < nleft; ++e) {
       if (kOuts & 1) p.out_map[o + e] = v[e];
       if (kOuts & 2) p.out_vis[o + e] = static_cast<uint8_t>(vis_byte(v[e]));
-      if (kOuts & 4) p.out_metric[o + e] = __float2bfloat16(v[e] * p.metric_scale);
+      if (kOuts & 4) p.out_metric[o + e] = __float2bfloat16(fmaf(v[e], p.metric_scale, p.metric_shift));
     }
   }
 }
@@ -197,15 +197,15 @@ __global__ void __launch_bounds__(256) postprocess_copy_kernel(const PostParams 
           vis_byte(v[0]) | (vis_byte(v[1]) << 8) | (vis_byte(v[2]) << 16) | (vis_byte(v[3]) << 24);
     if (p.out_metric) {
       uint2 m;
-      m.x = pack_bf16(v[0] * p.metric_scale, v[1] * p.metric_scale);
-      m.y = pack_bf16(v[2] * p.metric_scale, v[3] * p.metric_scale);
+      m.x = pack_bf16(fmaf(v[0], p.metric_scale, p.metric_shift), fmaf(v[1], p.metric_scale, p.metric_shift));
+      m.y = pack_bf16(fmaf(v[2], p.metric_scale, p.metric_shift), fmaf(v[3], p.metric_scale, p.metric_shift));
       __stcs(reinterpret_cast<uint2*>(p.out_metric) + i, m);
     }
   } else {
     for (int k = 0; k < cnt; ++k) {
       if (p.out_map) p.out_map[e + k] = v[k];
       if (p.out_vis) p.out_vis[e + k] = static_cast<uint8_t>(vis_byte(v[k]));
-      if (p.out_metric) p.out_metric[e + k] = __float2bfloat16(v[k] * p.metric_scale);
+      if (p.out_metric) p.out_metric[e + k] = __float2bfloat16(fmaf(v[k], p.metric_scale, p.metric_shift));
     }
   }
 }
@@ -237,7 +237,7 @@ __global__ void sample_kernel(const PostParams p, int B, const int32_t* sample_r
 }  // namespace deb
 
 extern "C" int de_postprocess(const void* pred, int in_dtype, int B, int h, int w, int H, int W, float* out_map,
-                              void* out_metric, float metric_scale, uint8_t* out_vis, const int32_t* sample_rc,
+                              void* out_metric, float metric_scale, float metric_shift, uint8_t* out_vis, const int32_t* sample_rc,
                               int n_samples, float* out_samples, void* stream) {
   using namespace deb;
   if (!pred || B <= 0 || h <= 0 || w <= 0 || H <= 0 || W <= 0) return fail(DE_ERR_INVALID, "de_postprocess: bad args");
@@ -252,6 +252,7 @@ extern "C" int de_postprocess(const void* pred, int in_dtype, int B, int h, int 
   p.out_map = out_map;
   p.out_metric = reinterpret_cast<__nv_bfloat16*>(out_metric);
   p.metric_scale = metric_scale;
+  p.metric_shift = metric_shift;
   p.out_vis = out_vis;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const bool ptr16 = ((reinterpret_cast<uintptr_t>(pred) | reinterpret_cast<uintptr_t>(out_map) |

@@ -33,6 +33,11 @@ struct PreParams {
   int layout;
   void* out;
   int TH, max_words, aligned;
+  // format 1: NV12 source - src is the Y plane (row_stride / frame_stride describe it), uv the
+  // interleaved half-resolution U,V plane; the BGR bytes the kernels consume are produced on the fly
+  int format;
+  const uint8_t* uv;
+  long long uv_row_stride, uv_frame_stride;
 };
 
 constexpr int kPreThreads = 256;
@@ -76,6 +81,27 @@ DEV uint32_t load_word(const PreParams& p, const uint8_t* ptr) {
   return w;
 }
 
+// NV12 -> the 32-bit word of interleaved BGR bytes [byte_off, byte_off+4) of frame row `row`, bit-exact with
+// cv2.cvtColor(COLOR_YUV2BGR_NV12) (OpenCV color_yuv: ITU-R BT.601 limited range, 20-bit fixed point, saturating).
+DEV uint32_t nv12_pixel_bgr(const PreParams& p, int b, int row, int px) {
+  if (px >= p.W) return 0u;
+  const int yv = __ldg(p.src + (long long)b * p.frame_stride + (long long)row * p.row_stride + px);
+  const uint8_t* uvp = p.uv + (long long)b * p.uv_frame_stride + (long long)(row >> 1) * p.uv_row_stride + (px & ~1);
+  const int u = static_cast<int>(__ldg(uvp)) - 128, v = static_cast<int>(__ldg(uvp + 1)) - 128;
+  const int y = max(0, yv - 16) * 1220542 + (1 << 19);
+  const int r = min(max((y + 1673527 * v) >> 20, 0), 255);
+  const int g = min(max((y - 852492 * v - 409993 * u) >> 20, 0), 255);
+  const int bl = min(max((y + 2116026 * u) >> 20, 0), 255);
+  return static_cast<uint32_t>(bl) | (static_cast<uint32_t>(g) << 8) | (static_cast<uint32_t>(r) << 16);
+}
+DEV uint32_t nv12_word(const PreParams& p, int b, int row, int byte_off) {
+  const int px = byte_off / 3, c0 = byte_off - px * 3;
+  // 4 bytes starting at channel c0 of pixel px never reach past pixel px + 1
+  const unsigned long long two = static_cast<unsigned long long>(nv12_pixel_bgr(p, b, row, px)) |
+                                 (static_cast<unsigned long long>(nv12_pixel_bgr(p, b, row, px + 1)) << 24);
+  return static_cast<uint32_t>(two >> (8 * c0));
+}
+
 DEV float vdot(float a, float b, float c, float d, float4 w) {
   float acc = a * w.x;
   acc = fmaf(b, w.y, acc);
@@ -96,7 +122,7 @@ __global__ void __launch_bounds__(kPreThreads, PRE_MINB) preprocess_kernel(const
   float* line = s_line + warp * (p.max_words * 4);
   const uint8_t* frame = p.src + (long long)b * p.frame_stride + sb0;
   const int y_last = __ldg(p.yidx + (oy0 + nrows - 1) * 4 + 3);
-  const bool fast = p.aligned && (long long)b * p.frame_stride + sb0 + (long long)y_last * p.row_stride + 4LL * nwords <= p.total_bytes;
+  const bool fast = p.format == 0 && p.aligned && (long long)b * p.frame_stride + sb0 + (long long)y_last * p.row_stride + 4LL * nwords <= p.total_bytes;
 
   // this lane's two output columns: tap offsets into the fp32 line (R channel = byte 2 of the BGR pixel)
   const bool active = 2 * lane < ncols;
@@ -129,9 +155,12 @@ __global__ void __launch_bounds__(kPreThreads, PRE_MINB) preprocess_kernel(const
         u1 = __ldg(reinterpret_cast<const uint32_t*>(r1) + wi);
         u2 = __ldg(reinterpret_cast<const uint32_t*>(r2) + wi);
         u3 = __ldg(reinterpret_cast<const uint32_t*>(r3) + wi);
-      } else {
+      } else if (p.format == 0) {
         u0 = load_word(p, r0 + 4 * wi); u1 = load_word(p, r1 + 4 * wi);
         u2 = load_word(p, r2 + 4 * wi); u3 = load_word(p, r3 + 4 * wi);
+      } else {
+        u0 = nv12_word(p, b, yi.x, sb0 + 4 * wi); u1 = nv12_word(p, b, yi.y, sb0 + 4 * wi);
+        u2 = nv12_word(p, b, yi.z, sb0 + 4 * wi); u3 = nv12_word(p, b, yi.w, sb0 + 4 * wi);
       }
       float4 v;
       v.x = vdot(byte_to_float(u0, 0), byte_to_float(u1, 0), byte_to_float(u2, 0), byte_to_float(u3, 0), wy);
@@ -161,7 +190,12 @@ __global__ void __launch_bounds__(128) preprocess_copy_kernel(const PreParams p)
   if (x4 * 4 >= p.W) return;
   const int y = blockIdx.y, b = blockIdx.z;
   const uint8_t* ptr = p.src + (long long)b * p.frame_stride + (long long)y * p.row_stride + x4 * 12;
-  const uint32_t u0 = load_word(p, ptr), u1 = load_word(p, ptr + 4), u2 = load_word(p, ptr + 8);
+  uint32_t u0, u1, u2;
+  if (p.format == 0) {
+    u0 = load_word(p, ptr); u1 = load_word(p, ptr + 4); u2 = load_word(p, ptr + 8);
+  } else {
+    u0 = nv12_word(p, b, y, x4 * 12); u1 = nv12_word(p, b, y, x4 * 12 + 4); u2 = nv12_word(p, b, y, x4 * 12 + 8);
+  }
   // bytes: u0 = B0 G0 R0 B1 | u1 = G1 R1 B2 G2 | u2 = R2 B3 G3 R3
   const float r[4] = {byte_to_float(u0, 2), byte_to_float(u1, 1), byte_to_float(u2, 0), byte_to_float(u2, 3)};
   const float g[4] = {byte_to_float(u0, 1), byte_to_float(u1, 0), byte_to_float(u1, 3), byte_to_float(u2, 2)};
@@ -223,15 +257,19 @@ __global__ void __launch_bounds__(256) preprocess_copy16_kernel(const PreParams 
 
 }  // namespace deb
 
-extern "C" int de_preprocess(const uint8_t* bgr, int B, int H, int W, int64_t row_stride, int64_t frame_stride,
-                             int net_h, int net_w, const float* mean_host, const float* std_host, int layout,
-                             void* out, void* stream) {
+static int run_preprocess(const uint8_t* bgr, const uint8_t* uv, int64_t uv_row_stride, int64_t uv_frame_stride, int B,
+                          int H, int W, int64_t row_stride, int64_t frame_stride, int net_h, int net_w,
+                          const float* mean_host, const float* std_host, int layout, void* out, void* stream) {
   using namespace deb;
+  const int format = uv ? 1 : 0;
   if (!bgr || !out || B <= 0 || H <= 0 || W <= 0) return fail(DE_ERR_INVALID, "de_preprocess: bad args");
   if (net_h % 32 != 0 || net_w % 32 != 0 || net_h <= 0 || net_w <= 0)
     return fail(DE_ERR_INVALID, "de_preprocess: net size %dx%d is not a positive multiple of 32", net_h, net_w);
   if (layout < 0 || layout > 2) return fail(DE_ERR_INVALID, "de_preprocess: layout %d", layout);
-  if (row_stride < (int64_t)W * 3 || frame_stride < row_stride * H) return fail(DE_ERR_INVALID, "de_preprocess: strides");
+  if (format == 0 && (row_stride < (int64_t)W * 3 || frame_stride < row_stride * H)) return fail(DE_ERR_INVALID, "de_preprocess: strides");
+  if (format == 1 && (row_stride < W || frame_stride < row_stride * H || (W & 1) || (H & 1) || uv_row_stride < W ||
+                      uv_frame_stride < uv_row_stride * (H / 2)))
+    return fail(DE_ERR_INVALID, "de_preprocess_nv12: strides / odd frame size");
   const AxisTaps* tx = get_axis_taps(W, net_w, 0);
   const AxisTaps* ty = get_axis_taps(H, net_h, 0);
   if (!tx || !ty) return DE_ERR_CUDA;
@@ -248,10 +286,14 @@ extern "C" int de_preprocess(const uint8_t* bgr, int B, int H, int W, int64_t ro
   }
   p.layout = layout;
   p.out = out;
+  p.format = format;
+  p.uv = uv;
+  p.uv_row_stride = uv_row_stride;
+  p.uv_frame_stride = uv_frame_stride;
   p.aligned = ((reinterpret_cast<uintptr_t>(bgr) | (uintptr_t)row_stride | (uintptr_t)frame_stride) & 3) == 0;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (H == net_h && W == net_w) {                             // cv2.resize is a copy for equal sizes
-    const bool wide = layout != 2 && W % 16 == 0 &&
+    const bool wide = format == 0 && layout != 2 && W % 16 == 0 &&
                       ((reinterpret_cast<uintptr_t>(bgr) | (uintptr_t)row_stride | (uintptr_t)frame_stride |
                         reinterpret_cast<uintptr_t>(out)) & 15) == 0;
     if (wide) {
@@ -280,4 +322,20 @@ extern "C" int de_preprocess(const uint8_t* bgr, int B, int H, int W, int64_t ro
   preprocess_kernel<<<grid, kPreThreads, smem, st>>>(p);
   count_launch();
   return cuda_check_launch("preprocess_kernel");
+}
+
+extern "C" int de_preprocess(const uint8_t* bgr, int B, int H, int W, int64_t row_stride, int64_t frame_stride,
+                             int net_h, int net_w, const float* mean_host, const float* std_host, int layout,
+                             void* out, void* stream) {
+  return run_preprocess(bgr, nullptr, 0, 0, B, H, W, row_stride, frame_stride, net_h, net_w, mean_host, std_host, layout,
+                        out, stream);
+}
+
+extern "C" int de_preprocess_nv12(const uint8_t* y_plane, const uint8_t* uv_plane, int B, int H, int W, int64_t y_row_stride,
+                                  int64_t y_frame_stride, int64_t uv_row_stride, int64_t uv_frame_stride, int net_h,
+                                  int net_w, const float* mean_host, const float* std_host, int layout, void* out,
+                                  void* stream) {
+  if (!uv_plane) return deb::fail(DE_ERR_INVALID, "de_preprocess_nv12: null UV plane");
+  return run_preprocess(y_plane, uv_plane, uv_row_stride, uv_frame_stride, B, H, W, y_row_stride, y_frame_stride, net_h,
+                        net_w, mean_host, std_host, layout, out, stream);
 }

@@ -61,6 +61,7 @@ class DepthEstimator(object):
         self._plans = {}
         self._pipes = {}
         self._replayed_launches = 0
+        self.metric_affine = (1.0 / 2.54, 0.0)                  # K8's metric map = map*scale + shift (face.py:137)
 
     # ------------------------------------------------------------------ reference surface
     def predict(self, img):
@@ -96,6 +97,46 @@ class DepthEstimator(object):
         if want_vis:
             res.append(plan.h_vis.numpy().copy())
         return res[0] if len(res) == 1 else tuple(res)
+
+    # ------------------------------------------------------------------ SURVEY 8f N4
+    def set_metric_affine(self, scale: float = 1.0 / 2.54, shift: float = 0.0):
+        """Metric map K8 emits with want_metric: map*scale + shift.  (1/2.54, 0) is `FaceDet.rel2abs` (face.py:137)."""
+        if (float(scale), float(shift)) != self.metric_affine:
+            self.metric_affine = (float(scale), float(shift))
+            self._plans.clear()                                 # the scalars are baked into the captured graphs
+            self._pipes.clear()
+
+    def calibrate_metric(self, pred_depths, gt_depths_cm):
+        """Least-squares rel -> abs calibration of `FaceDet.rel2abs_2` (face.py:118-130): fits pred = m/gt + b, then has
+        K8 emit cm_to_ft(map*m + b) = map*(m/30.48) + b/30.48 as its metric map.  Returns (m, b)."""
+        gt = [1 / x for x in gt_depths_cm]
+        A = np.vstack([gt, np.ones(len(gt))]).T
+        m, b = np.linalg.lstsq(A, np.asarray(pred_depths, dtype=np.float64), rcond=None)[0]
+        self.set_metric_affine(m / 30.48, b / 30.48)
+        return float(m), float(b)
+
+    def predict_nv12(self, nv12):
+        """Frames as a hardware decoder delivers them: uint8 [H*3/2, W] (or [B, H*3/2, W]) NV12 - Y plane followed by
+        the interleaved half-resolution UV plane, the array cv2.cvtColor(.., COLOR_YUV2BGR_NV12) takes.  The colour
+        conversion is fused into K1; the result equals predict(cv2.cvtColor(nv12, COLOR_YUV2BGR_NV12)) bit for bit."""
+        a = np.ascontiguousarray(nv12)
+        single = a.ndim == 2
+        if single:
+            a = a[None]
+        if a.dtype != np.uint8 or a.ndim != 3 or a.shape[1] % 3 != 0 or a.shape[2] % 2 != 0:
+            raise TypeError("predict_nv12 expects uint8 [H*3/2, W] NV12 frames with even H and W")
+        B, H, W = a.shape[0], a.shape[1] * 2 // 3, a.shape[2]
+        with torch.cuda.device(self.device):
+            t = torch.from_numpy(a).to(self.device)
+            y = t[:, :H]
+            uv = t[:, H:].reshape(B, H // 2, W // 2, 2)
+            net_w, net_h = ops.get_size(W, H, self.model_type)
+            mean, std = self._norm
+            x = ops.preprocess_nv12(y, uv, net_h, net_w, mean, std, self.estimator.preprocess_layout)
+            pred = self.estimator.forward(x, B, net_h, net_w)
+            out, _, _ = ops.postprocess(pred, H, W)
+            res = out.cpu().numpy()
+        return res[0] if single else res
 
     def predict_device(self, frames_u8: torch.Tensor, eager: bool = False) -> torch.Tensor:
         """Device-resident path: uint8 [B,H,W,3] BGR CUDA tensor -> fp32 [B,H,W] CUDA tensor (a buffer
@@ -200,7 +241,7 @@ class _Plan:
         pred = net.forward(x, self.B, self.net_h, self.net_w)
         rc = self.d_rc if self.n_samples else None
         _, _, samples = ops.postprocess(pred, self.H, self.W, want_map=True, want_metric=self.want_metric,
-                                        sample_rc=rc, out_map=self.d_map, out_metric=self.d_metric, out_vis=self.d_vis)
+                                        metric_scale=est.metric_affine[0], metric_shift=est.metric_affine[1], sample_rc=rc, out_map=self.d_map, out_metric=self.d_metric, out_vis=self.d_vis)
         return samples
 
     def _body(self):

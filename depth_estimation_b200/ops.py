@@ -76,8 +76,35 @@ def preprocess(frames_u8: torch.Tensor, net_h: int, net_w: int, mean, std, layou
     return out
 
 
+def _alloc_net_input(B, net_h, net_w, layout, device):
+    if layout == LAYOUT_NCHW_BF16:
+        return torch.empty((B, 3, net_h, net_w), dtype=torch.bfloat16, device=device)
+    if layout == LAYOUT_PATCH16_BF16:
+        return torch.empty((B * (net_h // 16) * (net_w // 16), 768), dtype=torch.bfloat16, device=device)
+    return torch.empty((B, 3, net_h, net_w), dtype=torch.float32, device=device)
+
+
+def preprocess_nv12(y: torch.Tensor, uv: torch.Tensor, net_h: int, net_w: int, mean, std,
+                    layout: int = LAYOUT_NCHW_BF16, out: torch.Tensor | None = None) -> torch.Tensor:
+    """K1 on NV12 frames: y uint8 [B,H,W], uv uint8 [B,H/2,W/2,2] (interleaved U,V), both on the GPU.  Bit-exact with
+    cv2.cvtColor(COLOR_YUV2BGR_NV12) followed by `preprocess`."""
+    _need_cuda(y, uv)
+    assert y.dtype == torch.uint8 and uv.dtype == torch.uint8 and y.dim() == 3 and uv.dim() == 4 and uv.shape[3] == 2
+    B, H, W = y.shape
+    assert tuple(uv.shape) == (B, H // 2, W // 2, 2) and y.stride(2) == 1 and uv.stride(3) == 1 and uv.stride(2) == 2
+    if out is None:
+        out = _alloc_net_input(B, net_h, net_w, layout, y.device)
+    m = (C.c_float * 3)(*[float(v) for v in mean])
+    s = (C.c_float * 3)(*[float(v) for v in std])
+    _lib.check(_lib.load().de_preprocess_nv12(y.data_ptr(), uv.data_ptr(), B, H, W, y.stride(1),
+                                              y.stride(0) if B > 1 else y.stride(1) * H, uv.stride(1),
+                                              uv.stride(0) if B > 1 else uv.stride(1) * (H // 2), net_h, net_w, m, s,
+                                              layout, out.data_ptr(), _stream()), "de_preprocess_nv12")
+    return out
+
+
 def postprocess(pred: torch.Tensor, H: int, W: int, want_map: bool = True, want_metric: bool = False,
-                metric_scale: float = 1.0 / 2.54, sample_rc: torch.Tensor | None = None,
+                metric_scale: float = 1.0 / 2.54, metric_shift: float = 0.0, sample_rc: torch.Tensor | None = None,
                 out_map: torch.Tensor | None = None, out_metric: torch.Tensor | None = None,
                 out_vis: torch.Tensor | None = None):
     """pred: [B,h,w] f32/bf16.  Returns (map f32 [B,H,W] | None, metric bf16 | None, samples f32 [B,S] | None).
@@ -95,7 +122,7 @@ def postprocess(pred: torch.Tensor, H: int, W: int, want_map: bool = True, want_
         ns = sample_rc.shape[1]
         samples = torch.empty((B, ns), dtype=torch.float32, device=pred.device)
     _lib.check(_lib.load().de_postprocess(pred.data_ptr(), _dt(pred), B, h, w, H, W, _ptr(out_map), _ptr(out_metric),
-                                          float(metric_scale), _ptr(out_vis), _ptr(sample_rc), ns, _ptr(samples), _stream()),
+                                          float(metric_scale), float(metric_shift), _ptr(out_vis), _ptr(sample_rc), ns, _ptr(samples), _stream()),
                "de_postprocess")
     return out_map, out_metric, samples
 

@@ -61,17 +61,26 @@ int de_preprocess(const uint8_t* bgr, int B, int H, int W, int64_t row_stride, i
                   int net_h, int net_w, const float* mean_host, const float* std_host, int layout, void* out,
                   void* stream);
 
+/* K1 on an NV12 frame as a hardware decoder delivers it (replaces the host BGR hop in front of
+ * depth_midas.py:22): y_plane uint8 [B,H,W] (strides in bytes), uv_plane uint8 [B,H/2,W/2,2] interleaved U,V.  The
+ * colour conversion is fused into the resampling kernel and is bit-exact with
+ * cv2.cvtColor(nv12, COLOR_YUV2BGR_NV12) followed by de_preprocess.  H and W even. */
+int de_preprocess_nv12(const uint8_t* y_plane, const uint8_t* uv_plane, int B, int H, int W, int64_t y_row_stride,
+                       int64_t y_frame_stride, int64_t uv_row_stride, int64_t uv_frame_stride, int net_h, int net_w,
+                       const float* mean_host, const float* std_host, int layout, void* out, void* stream);
+
 /* ---- K8: replaces depth_midas.py:28-33 (F.interpolate bicubic, align_corners=False, to the source
  * resolution) fused with the metric tail of face.py:106-108,137 (ri_depth sampling, /2.54).
  * pred: [B,h,w] (in_dtype bf16 or f32).  Tap tables (mode 1) cached inside the library.
- * out_map: [B,H,W] f32 (may be NULL).  out_metric: [B,H,W] bf16 = map*metric_scale (may be NULL).
+ * out_map: [B,H,W] f32 (may be NULL).  out_metric: [B,H,W] bf16 = map*metric_scale + metric_shift (may be NULL):
+ * (1/2.54, 0) is face.py:137 rel2abs; (m/30.48, b/30.48) the calibrated rel2abs_2 of face.py:118-130 in feet.
  * out_vis: [B,H,W] uint8 (may be NULL) = the reference's to_video_frame grey level (midas_mediapipe.py:141-150,
  * depth_midas.py:83): uint8(map) * 5 + 10 with numpy's wrapping uint8 arithmetic.
  * sample_rc: int32 [B,n_samples,2] (row, col) device indices into the OUTPUT map (may be NULL);
  * out_samples: float [B,n_samples] receives the interpolated value at those points. */
 int de_postprocess(const void* pred, int in_dtype, int B, int h, int w, int H, int W, float* out_map,
-                   void* out_metric, float metric_scale, uint8_t* out_vis, const int32_t* sample_rc, int n_samples,
-                   float* out_samples, void* stream);
+                   void* out_metric, float metric_scale, float metric_shift, uint8_t* out_vis, const int32_t* sample_rc,
+                   int n_samples, float* out_samples, void* stream);
 
 /* ---- tcgen05 GEMM / implicit-GEMM convolution.  D = epilogue(A * Wt^T):
  *   a_mode 0: A is a bf16 row-major matrix [M,K] (lda elements); K % 8 == 0.

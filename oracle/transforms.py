@@ -146,3 +146,20 @@ def midas_transform_bgr(img_bgr_u8: np.ndarray, model_type: str) -> np.ndarray:
     """depth_midas.py:22-23: cvtColor(BGR2RGB) then self.transform(img)."""
     rgb = np.ascontiguousarray(img_bgr_u8[:, :, ::-1])
     return midas_transform(rgb, transform_name_for(model_type))
+
+
+def nv12_to_bgr(nv12: np.ndarray) -> np.ndarray:
+    """NV12 [H*3/2, W] uint8 -> BGR [H, W, 3] uint8, restating OpenCV's cvtColor(COLOR_YUV2BGR_NV12) (ITU-R BT.601
+    limited range, 20-bit fixed point, saturating) - the host conversion K1's NV12 path fuses.
+    Pinned bit-exact against the installed cv2 in tests/test_oracle_cpu.py."""
+    H = nv12.shape[0] * 2 // 3
+    W = nv12.shape[1]
+    Y = nv12[:H].astype(np.int64)
+    UV = nv12[H:].reshape(H // 2, W // 2, 2).astype(np.int64)
+    U = np.repeat(np.repeat(UV[..., 0], 2, 0), 2, 1) - 128
+    V = np.repeat(np.repeat(UV[..., 1], 2, 0), 2, 1) - 128
+    y = np.maximum(0, Y - 16) * 1220542 + (1 << 19)
+    r = (y + 1673527 * V) >> 20
+    g = (y - 852492 * V - 409993 * U) >> 20
+    b = (y + 2116026 * U) >> 20
+    return np.stack([b, g, r], -1).clip(0, 255).astype(np.uint8)

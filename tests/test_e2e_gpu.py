@@ -102,3 +102,33 @@ def test_stream_loop_and_fused_video_frame():
     maps, vis = est.predict_batch(np.stack(frames[:2]), want_vis=True)
     want = va.to_video_frame(maps * 37.0)[..., 0] if False else va.to_video_frame(maps)[..., 0]
     assert vis.dtype == np.uint8 and np.array_equal(vis, want)
+
+
+def test_nv12_predict_and_calibrated_metric():
+    """N4: predict_nv12 == predict(cv2 NV12->BGR) bit for bit; calibrate_metric reproduces FaceDet.rel2abs_2."""
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    import cv2
+    from depth_estimation_b200.depth_midas import DepthEstimator
+    from depth_estimation_b200.face import FaceDet
+    est = DepthEstimator("MiDaS_small", seed=0)
+    rng = np.random.default_rng(11)
+    nv12 = rng.integers(0, 256, (480 * 3 // 2, 640), dtype=np.uint8)
+    want = est.predict(cv2.cvtColor(nv12, cv2.COLOR_YUV2BGR_NV12))
+    got = est.predict_nv12(nv12)
+    assert got.shape == want.shape and np.array_equal(got, want)
+    # least-squares calibration (face.py:118-130): pred = m/gt + b
+    gt_cm = [40.0, 55.0, 70.0, 90.0, 120.0]
+    pred = [2.1 / g * 100 + 0.3 + 0.01 * i for i, g in enumerate(gt_cm)]
+    m, b = est.calibrate_metric(pred, gt_cm)
+    face = FaceDet(20, (100, 100, 300, 100))
+    face.ri_depth = 1.0
+    face.rel2abs_2(pred, gt_cm)
+    assert abs(face.m - m) < 1e-9 * max(1, abs(m)) and abs(face.b - b) < 1e-9 * max(1, abs(b))
+    frame = cv2.cvtColor(nv12, cv2.COLOR_YUV2BGR_NV12)
+    maps, metric = est.predict_batch(frame[None], want_metric=True)
+    ref = (maps[0] * m + b) / 30.48
+    assert np.abs(metric[0] - ref).max() <= 1e-2 * np.abs(ref).max()
+    est.set_metric_affine()                                    # back to face.py:137
+    maps2, metric2 = est.predict_batch(frame[None], want_metric=True)
+    assert np.array_equal(maps2, maps) and np.abs(metric2[0] - maps[0] / 2.54).max() <= 1e-2 * np.abs(maps[0] / 2.54).max()

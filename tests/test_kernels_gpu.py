@@ -686,3 +686,34 @@ def test_split3_gemm_precision(conv):
     e3, e1 = _relerr(out, ref), _relerr(plain, ref)
     print(f"split3 {'conv' if conv else 'gemm'}: rel err {e3:.2e} (plain bf16 operands {e1:.2e})")
     assert e3 < 3e-5 and e3 < e1 / 30
+
+
+# ------------------------------------------------------------------ NV12 ingest, calibrated metric scale
+@pytest.mark.parametrize("H,W,mt,layout", [(480, 640, "MiDaS_small", 0), (360, 642, "DPT_Large", 1), (384, 384, "DPT_Large", 1),
+                                           (256, 256, "MiDaS_small", 2)])
+def test_preprocess_nv12_matches_bgr_path(H, W, mt, layout):
+    """K1 with the NV12 -> BGR conversion fused == cv2.cvtColor(COLOR_YUV2BGR_NV12) followed by K1, bit for bit
+    (resampling path, ragged width, and the identity-size copy path)."""
+    import cv2
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    rng = np.random.default_rng(7)
+    nv12 = rng.integers(0, 256, (2, H * 3 // 2, W), dtype=np.uint8)
+    bgr = np.stack([cv2.cvtColor(f, cv2.COLOR_YUV2BGR_NV12) for f in nv12])
+    nw, nh = ops.get_size(W, H, mt)
+    mean, std = ((0.5,) * 3, (0.5,) * 3) if mt != "MiDaS_small" else ((0.485, 0.456, 0.406), (0.229, 0.224, 0.225))
+    t = torch.from_numpy(nv12).to(dev)
+    y, uv = t[:, :H], t[:, H:].reshape(2, H // 2, W // 2, 2)
+    a = ops.preprocess_nv12(y, uv, nh, nw, mean, std, layout)
+    b = ops.preprocess(torch.from_numpy(bgr).to(dev), nh, nw, mean, std, layout)
+    torch.cuda.synchronize()
+    assert a.shape == b.shape and torch.equal(a, b)
+
+
+def test_postprocess_metric_affine():
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    pred = _rand((2, 96, 128), dev, seed=90).abs() * 10
+    omap, ometric, _ = ops.postprocess(pred, 240, 320, want_metric=True, metric_scale=0.37, metric_shift=-1.25)
+    torch.cuda.synchronize()
+    assert _relerr(ometric, omap * 0.37 - 1.25) < 8e-3          # bf16 rounding of fmaf(map, scale, shift)

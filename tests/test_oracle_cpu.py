@@ -260,3 +260,17 @@ def test_checkpoint_ingestion_roundtrip_and_validation(tmp_path):
     with pytest.raises(ValueError):
         load_checkpoint(sd, "DPT_Hybrid")
     assert state_dict_checksum(ref) != state_dict_checksum({**ref, k0: ref[k0] + 1})
+
+
+def test_nv12_restatement_matches_opencv():
+    """N4: the fixed-point NV12 -> BGR rule K1 fuses is the installed OpenCV's, bit for bit (incl. saturation)."""
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.default_rng(3)
+    for H, W in ((16, 32), (270, 482), (2, 2)):
+        nv12 = rng.integers(0, 256, (H * 3 // 2, W), dtype=np.uint8)
+        assert np.array_equal(T.nv12_to_bgr(nv12), cv2.cvtColor(nv12, cv2.COLOR_YUV2BGR_NV12))
+    ext = np.zeros((3, 2), dtype=np.uint8)
+    for yv, u, v in ((0, 0, 0), (255, 255, 255), (255, 0, 255), (16, 255, 0), (235, 128, 128)):
+        ext[:2] = yv
+        ext[2] = (u, v)
+        assert np.array_equal(T.nv12_to_bgr(ext), cv2.cvtColor(ext, cv2.COLOR_YUV2BGR_NV12))
