@@ -16,6 +16,8 @@ CASES = [
     ("MiDaS_small", 640, 480, "S"),
     ("MiDaS_small", 1280, 720, "U"),
     ("DPT_Hybrid", 384, 384, "S"),
+    ("DPT_Large", 1920, 1080, "S"),            # BASELINE config #5: net 384x672 (1009 tokens), full-res bicubic out
+    ("DPT_Hybrid", 640, 480, "U"),
 ]
 
 
@@ -132,3 +134,22 @@ def test_nv12_predict_and_calibrated_metric():
     est.set_metric_affine()                                    # back to face.py:137
     maps2, metric2 = est.predict_batch(frame[None], want_metric=True)
     assert np.array_equal(maps2, maps) and np.abs(metric2[0] - maps[0] / 2.54).max() <= 1e-2 * np.abs(maps[0] / 2.54).max()
+
+
+@pytest.mark.parametrize("mt,W,H,B", [("DPT_Large", 384, 384, 8), ("MiDaS_small", 1280, 720, 6), ("DPT_Hybrid", 384, 384, 3)])
+def test_batch_is_independent_frames(mt, W, H, B):
+    """Size-independent property at BASELINE batch shapes: frames never interact - a batch equals the per-frame
+    results, and permuting the batch permutes the maps (the data-parallel sharding of SURVEY 8e rests on this)."""
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    from depth_estimation_b200.depth_midas import DepthEstimator
+    est = DepthEstimator(mt, seed=1)
+    rng = np.random.default_rng(21)
+    frames = rng.integers(0, 256, (B, H, W, 3), dtype=np.uint8)
+    maps = est.predict_batch(frames)
+    perm = rng.permutation(B)
+    maps_p = est.predict_batch(frames[perm])
+    assert np.array_equal(maps_p, maps[perm])
+    for i in (0, B - 1):
+        single = est.predict(frames[i])
+        assert np.abs(single - maps[i]).max() <= 1e-5 * np.abs(maps[i]).max()
