@@ -1,4 +1,5 @@
 // Host-side plumbing of the C ABI: error strings, launch counter, get_size and the cubic tap tables.
+#include <stdlib.h>
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
@@ -46,6 +47,15 @@ int num_sms() {
     if (n <= 0) n = 148;
   }
   return n;
+}
+
+bool pdl_enabled(int cls) {
+  static int mask = -1;
+  if (mask < 0) {
+    const char* e = getenv("DEB_PDL");
+    mask = e ? atoi(e) : 3;   // LayerNorm off: early-scheduled GEMM CTAs squat on the SMs and cost it occupancy (measured)
+  }
+  return (mask & cls) != 0;
 }
 
 TensorMapEncodeTiledFn get_tensor_map_encoder() {

@@ -133,10 +133,12 @@ attention_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const WsParams p)
     tmem_alloc(tmem_slot, 512);
     tmem_relinquish();
   }
+  pdl_launch();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
 
   // tile index -> (row of the first query, row of the first key of the image, head column)
   auto tile_of = [&](int s, int it, int& q_row, int& kv_row, int& hcol) {
@@ -478,7 +480,8 @@ extern "C" int de_attention(const void* qkv, void* out, int B, int T, int heads,
   p.scale_log2e = scale * 1.4426950408889634f;
   const int sms = num_sms();
   const int grid = p.ntiles < sms ? p.ntiles : sms;
-  attention_ws_kernel<<<grid, kWsThreads, kWsSmem, reinterpret_cast<cudaStream_t>(stream)>>>(tm, p);
+  cudaError_t le = launch_pdl(2, attention_ws_kernel, dim3(grid), dim3(kWsThreads), kWsSmem, reinterpret_cast<cudaStream_t>(stream), tm, p);
   count_launch();
+  if (le != cudaSuccess) return cuda_fail(le, "cudaLaunchKernelEx(attention_ws_kernel)");
   return cuda_check_launch("attention_ws_kernel");
 }

@@ -201,6 +201,14 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N) {
          (static_cast<uint32_t>(M >> 4) << 24);
 }
 
+// ------------------------------------------------------------------ programmatic dependent launch
+// A kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may start while its predecessor in the
+// stream is still draining: everything up to pdl_wait() (barrier init, TMEM allocation, descriptor prefetch, smem
+// carve-up) overlaps the predecessor's tail; pdl_wait() returns once the predecessor has completed and its writes
+// are visible.  pdl_launch() lets the successor's CTAs be scheduled as soon as SMs free up.
+DEV void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+DEV void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ------------------------------------------------------------------ misc
 DEV bool elect_one() {
   uint32_t pred;

@@ -150,10 +150,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       tmem_relinquish();
     }
   }
+  pdl_launch();                       // the next kernel's prologue may overlap this kernel
   tc_fence_before();
   if (CG == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                         // predecessor complete: its outputs may be read, its inputs overwritten
 
   if (warp == 0) {
     // ------------------------------------------------------------- TMA producer (one per CTA)
@@ -616,13 +618,15 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMa
   cfg.blockDim = dim3(kThreads);
   cfg.dynamicSmemBytes = C::kSmemBytes;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = CG;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = pdl_enabled(1) ? 2 : 1;
   cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_kernel<BN, CG, EPI>, ta, tb, tc, p);
   count_launch();
   if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(gemm_kernel)");
@@ -679,8 +683,9 @@ extern "C" int de_gemm(const DeGemm* g, void* stream) {
     const uint64_t dims[2] = {(uint64_t)ktot, (uint64_t)g->N};
     const uint64_t strides[1] = {(uint64_t)g->ldw * 2};
     // pair mode: N a multiple of 256 and enough 256-row tile pairs to occupy the 74 SM pairs
-    if (cg == 0) cg = (bn == 256 && g->N % 256 == 0 && ((p.m_tiles + 1) / 2) * (g->N / 256) >= 64) ? 2 : 1;
-    if (cg == 2 && (bn != 256 || g->N % 256 != 0)) return fail(DE_ERR_INVALID, "de_gemm: cta_group 2 needs block_n 256 and N %% 256 == 0");
+    if (cg == 0) cg = ((bn == 256 || bn == 128) && g->N % bn == 0 && ((p.m_tiles + 1) / 2) * (g->N / bn) >= 64) ? 2 : 1;
+    if (cg == 2 && ((bn != 256 && bn != 128) || g->N % bn != 0))
+      return fail(DE_ERR_INVALID, "de_gemm: cta_group 2 needs block_n 128 / 256 and N %% block_n == 0");
     const uint32_t box[2] = {BK, (uint32_t)(bn / cg)};
     if (!make_map(&tb, g->w, 2, dims, strides, box)) return DE_ERR_CUDA;
   }
@@ -732,7 +737,9 @@ extern "C" int de_gemm(const DeGemm* g, void* stream) {
     case 256:
       if (cg == 2) return store_epi ? launch<256, 2, 0>(ta, tb, tc, p, st) : launch<256, 2, 1>(ta, tb, tc, p, st);
       return store_epi ? launch<256, 1, 0>(ta, tb, tc, p, st) : launch<256, 1, 1>(ta, tb, tc, p, st);
-    case 128: return store_epi ? launch<128, 1, 0>(ta, tb, tc, p, st) : launch<128, 1, 1>(ta, tb, tc, p, st);
+    case 128:
+      if (cg == 2) return store_epi ? launch<128, 2, 0>(ta, tb, tc, p, st) : launch<128, 2, 1>(ta, tb, tc, p, st);
+      return store_epi ? launch<128, 1, 0>(ta, tb, tc, p, st) : launch<128, 1, 1>(ta, tb, tc, p, st);
     case 64: return store_epi ? launch<64, 1, 0>(ta, tb, tc, p, st) : launch<64, 1, 1>(ta, tb, tc, p, st);
     case 32: return launch<32, 1, 1>(ta, tb, tc, p, st);
   }

@@ -282,12 +282,14 @@ head_up_conv_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_consta
     s_bias[lane] = p.bias ? __ldg(p.bias + lane) : 0.f;
     s_hw[lane] = __ldg(p.head_w + lane);
   }
+  pdl_launch();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const int per_img = p.tiles_x * p.tiles_y;
   const int units_per_tile = p.cin_blocks;
+  pdl_wait();
 
   if (warp == 0) {
     if (lane == 0) {                                         // filter bank once, then the source windows
@@ -609,7 +611,9 @@ extern "C" int de_head_up_conv(const void* x, const void* w, int64_t ldw, const 
   }
   int grid = num_sms();
   if (p.num_tiles < grid) grid = p.num_tiles;
-  head_up_conv_kernel<<<grid, kHuThreads, smem_bytes, reinterpret_cast<cudaStream_t>(stream)>>>(tw, tx, p);
+  cudaError_t le = launch_pdl(2, head_up_conv_kernel, dim3(grid), dim3(kHuThreads), (size_t)smem_bytes,
+                              reinterpret_cast<cudaStream_t>(stream), tw, tx, p);
   count_launch();
+  if (le != cudaSuccess) return cuda_fail(le, "cudaLaunchKernelEx(head_up_conv_kernel)");
   return cuda_check_launch("head_up_conv_kernel");
 }

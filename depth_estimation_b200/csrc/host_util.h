@@ -13,11 +13,31 @@ int cuda_fail(cudaError_t e, const char* what);
 int cuda_check_launch(const char* what);
 void count_launch();
 int num_sms();
+// programmatic dependent launch per kernel class (1 GEMM, 2 attention / head, 4 LayerNorm); DEB_PDL=<mask>, default 3
+bool pdl_enabled(int cls);
 
 typedef CUresult (*TensorMapEncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                            const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
                                            CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
                                            CUtensorMapFloatOOBfill);
 TensorMapEncodeTiledFn get_tensor_map_encoder();
+
+// Launch with programmatic stream serialization (see common.cuh pdl_wait / pdl_launch).  Only for kernels that call
+// pdl_wait() before their first global-memory access.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(int cls, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                              Args... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled(cls) ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 
 }  // namespace deb

@@ -18,6 +18,8 @@ __global__ void __launch_bounds__(256) layernorm_kernel(float* __restrict__ x, l
                                                         __nv_bfloat16* __restrict__ out, long long ldo) {
   const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
+  pdl_launch();
+  pdl_wait();
   if (row >= rows) return;
   float4* xr = reinterpret_cast<float4*>(x + (long long)row * ldx);
   float4 v[VEC];
@@ -357,7 +359,7 @@ extern "C" int de_layernorm(float* x, int64_t ldx, const void* y, int y_dtype, i
   __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out_bf16);
   const int grid = (rows + 7) / 8;
   switch (dim / 128) {
-#define LN_CASE(V) case V: layernorm_kernel<V><<<grid, 256, 0, st>>>(x, ldx, y, y_dtype == DE_DTYPE_BF16 ? 1 : 0, ldy, gamma, beta, rows, eps, o, ldo); break;
+#define LN_CASE(V) case V: launch_pdl(4, layernorm_kernel<V>, dim3(grid), dim3(256), 0, st, x, (long long)ldx, y, y_dtype == DE_DTYPE_BF16 ? 1 : 0, (long long)ldy, gamma, beta, rows, eps, o, (long long)ldo); break;
     LN_CASE(1) LN_CASE(2) LN_CASE(3) LN_CASE(4) LN_CASE(5) LN_CASE(6) LN_CASE(7) LN_CASE(8)
 #undef LN_CASE
   }
