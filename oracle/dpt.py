@@ -2,7 +2,9 @@
 ``DPTDepthModel`` (midas/dpt_depth.py, midas/vit.py, midas/blocks.py) as loaded by
 ``/root/reference/depth_midas.py:10`` for model_type "DPT_Large" and "DPT_Hybrid".  Upstream source is
 not vendored - published algorithm restated, upstream ``state_dict`` key names kept.
-PARITY UNPINNED by the reference (it has no tests); decoder cross-checked against HF transformers DPT.
+PARITY UNPINNED by the reference (it has no tests); the whole model (ViT-L / ResNetV2+ViT-B, reassemble, fusion,
+head) is cross-checked against the independently written HF transformers ``DPTForDepthEstimation`` with
+identical weights in tests/test_oracle_hf_crosscheck.py (agreement 1e-6 .. 4e-6 of the dynamic range).
 """
 from __future__ import annotations
 
