@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libdepthb200.so")
+# DEPTH_B200_LIB points at another build of the same library (kernel tuning variants); there is still no fallback
+LIB_PATH = os.environ.get("DEPTH_B200_LIB") or os.path.join(_HERE, "libdepthb200.so")
 
 DE_DTYPE_BF16, DE_DTYPE_F32 = 0, 1
 ACT_NONE, ACT_RELU, ACT_GELU, ACT_RELU6 = 0, 1, 2, 3

@@ -35,6 +35,10 @@ constexpr int kWsTile = 128 * 128;                       // [128 rows x 64 bf16]
 constexpr int kWsStreamBytes = 6 * kWsTile;              // Q0 Q1 | K0 K1 | V0 V1
 constexpr int kWsSmem = 2 * kWsStreamBytes + 1024 /*align slack*/ + 512 /*barriers*/;
 constexpr float kRescaleThreshold = 8.0f;                // log2 units
+#ifndef WS_POLY_MASK
+#define WS_POLY_MASK 0x24                                // pairs 2 and 5 of every 8: a quarter of the exponentials
+#endif
+constexpr unsigned kWsPolyMask = WS_POLY_MASK;
 
 DEV void tmem_st_32x32(uint32_t taddr, const uint32_t* r) {
   asm volatile(
@@ -353,17 +357,22 @@ attention_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const WsParams p)
           m_ref = m_new;
         }
         const float msc = m_ref * sl2e;
-        float rs4[4] = {0.f, 0.f, 0.f, 0.f};
+        const float2 sl2 = make_float2(sl2e, sl2e), nmsc2 = make_float2(-msc, -msc);
+        float2 rs2[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
         uint32_t pk[64];
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           if (c < nch) {
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
-              const float p0 = ex2_approx(fmaf(__uint_as_float(sv[c * 32 + 2 * i]), sl2e, -msc));
-              const float p1 = ex2_approx(fmaf(__uint_as_float(sv[c * 32 + 2 * i + 1]), sl2e, -msc));
-              rs4[i & 3] += p0 + p1;
-              pk[c * 16 + i] = pack_bf16(p0, p1);
+              // packed scale / subtract and row sums (FFMA2 / FADD2); kWsPolyMask selects the pairs of every 8 whose
+              // exponentials run as a polynomial on the FMA pipe instead of MUFU.EX2 (the softmax bottleneck)
+              const float2 x = ffma2(make_float2(__uint_as_float(sv[c * 32 + 2 * i]), __uint_as_float(sv[c * 32 + 2 * i + 1])), sl2, nmsc2);
+              float2 pp;
+              if ((kWsPolyMask >> (i & 7)) & 1) pp = ex2_poly2(x);
+              else pp = make_float2(ex2_approx(x.x), ex2_approx(x.y));
+              rs2[i & 1] = fadd2(rs2[i & 1], pp);
+              pk[c * 16 + i] = pack_bf16(pp.x, pp.y);
             }
           } else {
 #pragma unroll
@@ -377,7 +386,7 @@ attention_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const WsParams p)
             tmem_st_32x32(tP, pk);
           }
         }
-        l_run += (rs4[0] + rs4[1]) + (rs4[2] + rs4[3]);
+        l_run += (rs2[0].x + rs2[0].y) + (rs2[1].x + rs2[1].y);
         WS_STAMP(3);
         if (nch > 2) tmem_st_32x32(tP + 32, pk + 32);
         tmem_st_wait();

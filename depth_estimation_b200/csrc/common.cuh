@@ -244,9 +244,42 @@ DEV uint64_t make_sw128_mnmajor_desc(uint32_t smem_addr) {
 }
 // instruction descriptor with an MN-major B operand (bit 16)
 __host__ __device__ constexpr uint32_t make_idesc_bf16_bmn(int M, int N) { return make_idesc_bf16(M, N) | (1u << 16); }
+// packed fp32 pairs (sm_100 FFMA2 / FMUL2 / FADD2): two IEEE fp32 operations per issue slot, same rounding as scalar
+DEV float2 fmul2(float2 a, float2 b) {
+  float2 d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(reinterpret_cast<unsigned long long&>(d)) : "l"(reinterpret_cast<unsigned long long&>(a)), "l"(reinterpret_cast<unsigned long long&>(b)));
+  return d;
+}
+DEV float2 ffma2(float2 a, float2 b, float2 c) {
+  float2 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(reinterpret_cast<unsigned long long&>(d)) : "l"(reinterpret_cast<unsigned long long&>(a)), "l"(reinterpret_cast<unsigned long long&>(b)), "l"(reinterpret_cast<unsigned long long&>(c)));
+  return d;
+}
+DEV float2 fadd2(float2 a, float2 b) {
+  float2 d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(reinterpret_cast<unsigned long long&>(d)) : "l"(reinterpret_cast<unsigned long long&>(a)), "l"(reinterpret_cast<unsigned long long&>(b)));
+  return d;
+}
 DEV float ex2_approx(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+}
+// exp2 on the FMA pipe for a pair of arguments (Cody-Waite split + degree-3 minimax polynomial of 2^f on
+// [-0.5, 0.5], max relative error 7.5e-5 - far below the bf16 rounding of the probabilities it feeds): the softmax
+// kernels send a fraction of their exponentials here because MUFU.EX2 (16 lanes / clk / SM) is their bottleneck.
+// x is clamped to >= -126 (2^-126 instead of 0 for masked entries); x <= 127 is the caller's business.
+DEV float2 ex2_poly2(float2 x) {
+  x.x = fmaxf(x.x, -126.f);
+  x.y = fmaxf(x.y, -126.f);
+  const float2 t = fadd2(x, make_float2(12582912.f, 12582912.f));          // 1.5 * 2^23: round(x) in the low mantissa bits
+  const float2 r = fadd2(t, make_float2(-12582912.f, -12582912.f));
+  const float2 f = ffma2(r, make_float2(-1.f, -1.f), x);                    // x - round(x), exact
+  float2 p = ffma2(make_float2(0.055171433836221695f, 0.055171433836221695f), f, make_float2(0.24261081218719482f, 0.24261081218719482f));
+  p = ffma2(p, f, make_float2(0.6932609677314758f, 0.6932609677314758f));
+  p = ffma2(p, f, make_float2(0.9999281167984009f, 0.9999281167984009f));
+  p.x = __uint_as_float(__float_as_uint(p.x) + (__float_as_uint(t.x) << 23));
+  p.y = __uint_as_float(__float_as_uint(p.y) + (__float_as_uint(t.y) << 23));
+  return p;
 }
 }  // namespace deb

@@ -678,6 +678,12 @@ extern "C" int de_gemm(const DeGemm* g, void* stream) {
   } else {
     return fail(DE_ERR_INVALID, "de_gemm: bad a_mode %d", g->a_mode);
   }
+  // small problems (the batch-1 latency path: 5 row tiles at T=577): halve the tile width until the grid covers at
+  // least half of the SMs - a 45-CTA launch of 256-wide tiles leaves 100 SMs idle and every CTA streams 2x the weights
+  if (g->block_n == 0 && !g->head_w) {
+    const int half_sms = num_sms() / 2;
+    while (bn > 64 && g->N % (bn / 2) == 0 && p.m_tiles * ((g->N + bn - 1) / bn) < half_sms) bn >>= 1;
+  }
   if (g->ldw % 8 != 0 || g->ldw < ktot) return fail(DE_ERR_INVALID, "de_gemm: ldw=%lld too small / unaligned for K=%lld", (long long)g->ldw, (long long)ktot);
   {
     const uint64_t dims[2] = {(uint64_t)ktot, (uint64_t)g->N};

@@ -238,10 +238,16 @@ DEV void store_split3(__nv_bfloat16* out, long long row, int C, int c0, const fl
   *reinterpret_cast<uint4*>(o + 2 * C) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
 }
 
+// Pass 1 of 2: per-CTA partial sums; the LAST CTA of a sample to finish (arrival counter in the workspace, left at
+// zero again) reduces that sample's partials in a fixed order - one warp per group, lane-strided double sums and a
+// shuffle tree - and writes (mean, rstd).  Deterministic, and no separate finalize launch: at batch 1 the old
+// single-thread-per-group finalize kernel cost 18 us per GroupNorm, a quarter of DPT_Hybrid's frame latency.
 __global__ void __launch_bounds__(256) groupnorm_partial_kernel(const void* __restrict__ x, int x_f32, int HW, int C,
                                                                 int groups, int px_per_block,
-                                                                double* __restrict__ partial) {
+                                                                double* __restrict__ partial, unsigned* __restrict__ counters,
+                                                                float2* __restrict__ stats, double n, float eps) {
   __shared__ float s_su[256 * 8], s_sq[256 * 8];
+  __shared__ bool s_last;
   const int b = blockIdx.y;
   const int vec = C >> 3;                    // 8-channel vectors per pixel
   const int lanes = 256 / vec;               // pixels processed concurrently
@@ -275,24 +281,38 @@ __global__ void __launch_bounds__(256) groupnorm_partial_kernel(const void* __re
     double* o = partial + (((long long)b * gridDim.x + blockIdx.x) * groups + g) * 2;
     o[0] = a;
     o[1] = q;
+    __threadfence();
   }
-}
-
-__global__ void groupnorm_finalize_kernel(const double* __restrict__ partial, int nblocks, int groups, double n,
-                                          float eps, float2* __restrict__ stats, int total) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;   // (b, g)
-  if (i >= total) return;
-  const int b = i / groups, g = i % groups;
-  double a = 0.0, q = 0.0;
-  for (int k = 0; k < nblocks; ++k) {
-    const double* o = partial + (((long long)b * nblocks + k) * groups + g) * 2;
-    a += o[0];
-    q += o[1];
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned prev = atomicAdd(counters + b, 1u);
+    s_last = prev == gridDim.x - 1;
+    if (s_last) counters[b] = 0;                 // every CTA of this sample has arrived: ready for the next call
   }
-  const double m = a / n;
-  double var = q / n - m * m;
-  if (var < 0) var = 0;
-  stats[i] = make_float2((float)m, (float)(1.0 / sqrt(var + (double)eps)));
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nblocks = gridDim.x;
+  for (int g = warp; g < groups; g += 8) {
+    double a = 0.0, q = 0.0;
+    for (int k = lane; k < nblocks; k += 32) {
+      const double2 v = __ldcg(reinterpret_cast<const double2*>(partial + (((long long)b * nblocks + k) * groups + g) * 2));
+      a += v.x;
+      q += v.y;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      a += __shfl_xor_sync(0xffffffffu, a, o);
+      q += __shfl_xor_sync(0xffffffffu, q, o);
+    }
+    if (lane == 0) {
+      const double m = a / n;
+      double var = q / n - m * m;
+      if (var < 0) var = 0;
+      stats[b * groups + g] = make_float2((float)m, (float)(1.0 / sqrt(var + (double)eps)));
+    }
+  }
 }
 
 __global__ void groupnorm_apply_kernel(const void* __restrict__ x, int x_f32, const float2* __restrict__ stats,
@@ -440,15 +460,16 @@ extern "C" int de_groupnorm(const void* x, int x_dtype, const float* gamma, cons
   if (px_per_block < lanes * 4) px_per_block = lanes * 4;
   const int nblocks = (HW + px_per_block - 1) / px_per_block;
   const int64_t stats_bytes = (int64_t)sizeof(float2) * B * groups;
-  const int64_t need = stats_bytes + (int64_t)sizeof(double) * 2 * B * nblocks * groups + 16;
+  const int64_t partial_bytes = (int64_t)sizeof(double) * 2 * B * nblocks * groups;
+  const int64_t need = stats_bytes + partial_bytes + 16 + (int64_t)sizeof(unsigned) * B;
   if (ws_bytes < need) return fail(DE_ERR_INVALID, "de_groupnorm: workspace %lld < %lld bytes", (long long)ws_bytes, (long long)need);
   float2* stats = reinterpret_cast<float2*>(ws);
   double* partial = reinterpret_cast<double*>(reinterpret_cast<char*>(ws) + ((stats_bytes + 15) / 16) * 16);
+  // arrival counters live in the LAST 4*B bytes of the workspace (zero before the first call, zero after every call)
+  unsigned* counters = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(ws) + ((ws_bytes - (int64_t)sizeof(unsigned) * B) & ~3LL));
   dim3 grid(nblocks, B);
-  groupnorm_partial_kernel<<<grid, 256, 0, st>>>(x, x_f32, HW, C, groups, px_per_block, partial);
-  count_launch();
-  groupnorm_finalize_kernel<<<(B * groups + 127) / 128, 128, 0, st>>>(partial, nblocks, groups,
-                                                                     (double)HW * (C / groups), eps, stats, B * groups);
+  groupnorm_partial_kernel<<<grid, 256, 0, st>>>(x, x_f32, HW, C, groups, px_per_block, partial, counters, stats,
+                                                 (double)HW * (C / groups), eps);
   count_launch();
   const long long n = (long long)B * HW * (C / 8);
   groupnorm_apply_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(

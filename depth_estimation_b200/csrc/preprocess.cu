@@ -1,17 +1,28 @@
 // K1 - fused MiDaS input transform (replaces /root/reference/depth_midas.py:22-23):
 //   uint8 BGR HWC frame -> (BGR->RGB) -> /255 -> cv2.INTER_CUBIC resize to (net_h, net_w) ->
 //   (x-mean)/std -> bf16 NCHW (or the ViT patch matrix, or fp32 NCHW for parity checks).
-// The frame is read once and the tensor written once.  Two kernels:
-//   * preprocess_copy_kernel - source size == net size (BASELINE configs #2/#3: 384x384 frames).  cv2.resize
-//     degenerates to a copy there (and the cubic taps to [0,1,0,0]), so this is a pure streaming kernel:
-//     12 input bytes -> 4 pixels x 3 channels per thread, 8-byte stores.
-//   * preprocess_kernel - general resample.  A CTA owns 64 output columns x TH output rows; each of its 8 warps
-//     takes whole output rows: (V) the 4 vertical taps are applied to the interleaved source BYTES of the row
-//     strip, one aligned 32-bit word (4 bytes) per lane and iteration -> fp32 row in the warp's private smem
-//     line; (H) the lane's two output columns (tap tables in registers) gather 4 taps x 3 channels from that
-//     line, normalise and store.  Rows never leave their warp, so there is no block-wide barrier, and no integer
-//     division anywhere.  The vertical pass does 16 byte->float conversions + 16 FMAs per input word; at 2.8x
-//     down-scaling (1080p -> 384x672) that FMA-pipe work, not HBM, bounds the kernel.
+// The frame is read once and the tensor written once.  Kernels:
+//   * preprocess_copy16_kernel - source size == net size (BASELINE configs #2/#3: 384x384 frames).  cv2.resize
+//     degenerates to a copy there (and the cubic taps to [0,1,0,0]), so this is a pure streaming kernel: two items of
+//     16 pixels per thread (six 16-byte loads issued up front), per channel one 32-byte run written with a single
+//     256-bit store (sm_100 STG.256) - a full sector, and a full patch row of the patch-matrix layout.  The
+//     128-bit-store version reached 0.62 of the HBM copy figure, this one 0.96 (profiles/r01_prepost_v2.md).
+//     preprocess_copy_kernel is the generic-alignment fallback (4 pixels per thread).
+//   * preprocess_kernel - general resample, horizontal pass first (the order cv2's resize uses: it is also the
+//     cheap order when down-scaling, because the byte -> float conversions and the first four taps are spent on
+//     net_w instead of W columns per source row).  A CTA owns 64 output columns x TH output rows.
+//     (H) thread = (output column, two source rows): the column's 4 taps x 3 channels are 12 contiguous source bytes;
+//     four aligned 32-bit loads + three funnel shifts bring them into three registers, 12 exact byte -> float
+//     conversions and the taps run as packed fp32 pairs (FADD2 / FFMA2: B,G of a row share a tap weight, so do the R
+//     values of the two rows), and the three channel values go to shared memory as fp32 [source row][RGB][64].
+//     Border columns (clamped, non-contiguous taps), unaligned buffers and NV12 sources fetch per tap instead.
+//     (V) thread = (output row, channel, 4 columns): four float4 reads from the staged rows, vertical taps,
+//     normalise, one 8/16-byte store.  TH is chosen on the host so that the staged rows (TH * scale + 3) fit the
+//     shared-memory budget; the vertical halo re-reads 3 source rows per tile (L2 hits).
+//     Tried and dropped (round 1, numbers in DESIGN.md): vertical-first on raw bytes (2.7x the conversions), and a
+//     persistent variant that stages the raw strip with per-row bulk async copies two tiles ahead (producer warp,
+//     mbarriers) - 0.26-0.37 of the copy figure against 0.38-0.40 for this kernel: per-tile overhead and the
+//     H -> V barrier, not bytes in flight, are what is left.
 #include <algorithm>
 
 #include "common.cuh"
@@ -32,7 +43,7 @@ struct PreParams {
   float scale[3], shift[3];  // RGB order: out = v*scale - shift
   int layout;
   void* out;
-  int TH, max_words, aligned;
+  int TH, max_rows, aligned;
   // format 1: NV12 source - src is the Y plane (row_stride / frame_stride describe it), uv the
   // interleaved half-resolution U,V plane; the BGR bytes the kernels consume are produced on the fly
   int format;
@@ -42,13 +53,12 @@ struct PreParams {
 
 constexpr int kPreThreads = 256;
 #ifndef PRE_MINB
-#define PRE_MINB 5          // 48 registers -> 5 CTAs/SM; measured best of {4,5,6} x unroll {1,2} (+7-10 % over 4)
+#define PRE_MINB 5
 #endif
-#ifndef PRE_UNROLL
-#define PRE_UNROLL 1
+#ifndef PRE_SMEM_KB
+#define PRE_SMEM_KB 40      // staged fp32 rows per CTA (768 B each): 5 CTAs / SM (measured best of 3..6)
 #endif
-constexpr int kPreUnroll = PRE_UNROLL;
-constexpr int kPreTW = 64;                                  // output columns per CTA (2 per lane)
+constexpr int kPreTW = 64;                                  // output columns per CTA
 
 // byte k of a little-endian word -> float, exactly: 0x4B0000bb is 2^23 + b
 DEV float byte_to_float(uint32_t word, int k) {
@@ -102,86 +112,154 @@ DEV uint32_t nv12_word(const PreParams& p, int b, int row, int byte_off) {
   return static_cast<uint32_t>(two >> (8 * c0));
 }
 
-DEV float vdot(float a, float b, float c, float d, float4 w) {
-  float acc = a * w.x;
-  acc = fmaf(b, w.y, acc);
-  acc = fmaf(c, w.z, acc);
-  acc = fmaf(d, w.w, acc);
-  return acc;
+// one source pixel as 0x00RRGGBB-style word (B in byte 0), any alignment / either source format
+DEV uint32_t pixel_bgr(const PreParams& p, int b, int row, int px) {
+  if (p.format == 1) return nv12_pixel_bgr(p, b, row, px);
+  const uint8_t* q = p.src + (long long)b * p.frame_stride + (long long)row * p.row_stride + (long long)px * 3;
+  return static_cast<uint32_t>(__ldg(q)) | (static_cast<uint32_t>(__ldg(q + 1)) << 8) | (static_cast<uint32_t>(__ldg(q + 2)) << 16);
+}
+
+// horizontal taps of one output column on one source row: a0..a2 hold the 12 bytes B0 G0 R0 B1 ... R3
+// (tap t, BGR channel c at byte 3t+c); result in RGB order
+DEV void htaps(uint32_t a0, uint32_t a1, uint32_t a2, const float4 w, float& r, float& g, float& bl) {
+  bl = byte_to_float(a0, 0) * w.x;
+  g = byte_to_float(a0, 1) * w.x;
+  r = byte_to_float(a0, 2) * w.x;
+  bl = fmaf(byte_to_float(a0, 3), w.y, bl);
+  g = fmaf(byte_to_float(a1, 0), w.y, g);
+  r = fmaf(byte_to_float(a1, 1), w.y, r);
+  bl = fmaf(byte_to_float(a1, 2), w.z, bl);
+  g = fmaf(byte_to_float(a1, 3), w.z, g);
+  r = fmaf(byte_to_float(a2, 0), w.z, r);
+  bl = fmaf(byte_to_float(a2, 1), w.w, bl);
+  g = fmaf(byte_to_float(a2, 2), w.w, g);
+  r = fmaf(byte_to_float(a2, 3), w.w, r);
+}
+
+// {byte kx of x, byte ky of y} -> float2, exactly
+DEV float2 bytes_to_float2(uint32_t x, int kx, uint32_t y, int ky) {
+  const float2 m = make_float2(__uint_as_float(__byte_perm(x, 0x4B000000u, 0x7540u | kx)),
+                               __uint_as_float(__byte_perm(y, 0x4B000000u, 0x7540u | ky)));
+  return fadd2(m, make_float2(-8388608.0f, -8388608.0f));
+}
+// htaps() for two source rows at once (a*: row A, b*: row B), same per-channel operation order, half the FMA-pipe
+// instructions: (B,G) of a row share a tap weight, the two rows' R values share it too
+DEV void htaps2(uint32_t a0, uint32_t a1, uint32_t a2, uint32_t b0, uint32_t b1, uint32_t b2, const float4 w,
+                float2& bgA, float2& bgB, float2& rr) {
+  const float2 w0 = make_float2(w.x, w.x), w1 = make_float2(w.y, w.y), w2 = make_float2(w.z, w.z), w3 = make_float2(w.w, w.w);
+  bgA = fmul2(bytes_to_float2(a0, 0, a0, 1), w0);
+  bgB = fmul2(bytes_to_float2(b0, 0, b0, 1), w0);
+  rr = fmul2(bytes_to_float2(a0, 2, b0, 2), w0);
+  bgA = ffma2(bytes_to_float2(a0, 3, a1, 0), w1, bgA);
+  bgB = ffma2(bytes_to_float2(b0, 3, b1, 0), w1, bgB);
+  rr = ffma2(bytes_to_float2(a1, 1, b1, 1), w1, rr);
+  bgA = ffma2(bytes_to_float2(a1, 2, a1, 3), w2, bgA);
+  bgB = ffma2(bytes_to_float2(b1, 2, b1, 3), w2, bgB);
+  rr = ffma2(bytes_to_float2(a2, 0, b2, 0), w2, rr);
+  bgA = ffma2(bytes_to_float2(a2, 1, a2, 2), w3, bgA);
+  bgB = ffma2(bytes_to_float2(b2, 1, b2, 2), w3, bgB);
+  rr = ffma2(bytes_to_float2(a2, 3, b2, 3), w3, rr);
+}
+
+DEV void store_px4(const PreParams& p, int b, int ch, int oy, int ox, float4 v) {
+  if (p.layout == 0) {
+    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + (((long long)b * 3 + ch) * p.net_h + oy) * p.net_w + ox;
+    *reinterpret_cast<uint2*>(o) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
+  } else if (p.layout == 1) {
+    const int gw = p.net_w >> 4, gh = p.net_h >> 4;
+    const long long prow = ((long long)b * gh + (oy >> 4)) * gw + (ox >> 4);
+    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + prow * 768 + ch * 256 + (oy & 15) * 16 + (ox & 15);
+    *reinterpret_cast<uint2*>(o) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
+  } else {
+    float* o = reinterpret_cast<float*>(p.out) + (((long long)b * 3 + ch) * p.net_h + oy) * p.net_w + ox;
+    *reinterpret_cast<float4*>(o) = v;
+  }
+}
+
+// (V) item = (output row, RGB channel, group of 4 columns): vertical taps on the staged fp32 rows, normalise, store
+template <int kThreads>
+DEV void vertical_phase(const PreParams& p, const float* s_h, int b, int ox0, int oy0, int ncols, int nrows, int ys) {
+  const int nitems = nrows * 48;
+  for (int item = threadIdx.x; item < nitems; item += kThreads) {
+    const int ry = item / 48, rem = item - ry * 48;
+    const int ch = rem >> 4, cg = rem & 15;
+    if (cg * 4 >= ncols) continue;
+    const int oy = oy0 + ry;
+    const int4 yi = __ldg(reinterpret_cast<const int4*>(p.yidx) + oy);
+    const float4 wy = __ldg(reinterpret_cast<const float4*>(p.yw) + oy);
+    const float* src = s_h + ch * kPreTW + cg * 4;
+    const float4 t0 = *reinterpret_cast<const float4*>(src + (yi.x - ys) * (3 * kPreTW));
+    const float4 t1 = *reinterpret_cast<const float4*>(src + (yi.y - ys) * (3 * kPreTW));
+    const float4 t2 = *reinterpret_cast<const float4*>(src + (yi.z - ys) * (3 * kPreTW));
+    const float4 t3 = *reinterpret_cast<const float4*>(src + (yi.w - ys) * (3 * kPreTW));
+    const float2 sc = make_float2(p.scale[ch], p.scale[ch]), sf = make_float2(-p.shift[ch], -p.shift[ch]);
+    const float2 w0 = make_float2(wy.x, wy.x), w1 = make_float2(wy.y, wy.y), w2 = make_float2(wy.z, wy.z), w3 = make_float2(wy.w, wy.w);
+    float2 lo = fmul2(make_float2(t0.x, t0.y), w0), hi = fmul2(make_float2(t0.z, t0.w), w0);
+    lo = ffma2(make_float2(t1.x, t1.y), w1, lo); hi = ffma2(make_float2(t1.z, t1.w), w1, hi);
+    lo = ffma2(make_float2(t2.x, t2.y), w2, lo); hi = ffma2(make_float2(t2.z, t2.w), w2, hi);
+    lo = ffma2(make_float2(t3.x, t3.y), w3, lo); hi = ffma2(make_float2(t3.z, t3.w), w3, hi);
+    lo = ffma2(lo, sc, sf); hi = ffma2(hi, sc, sf);
+    store_px4(p, b, ch, oy, ox0 + cg * 4, make_float4(lo.x, lo.y, hi.x, hi.y));
+  }
 }
 
 __global__ void __launch_bounds__(kPreThreads, PRE_MINB) preprocess_kernel(const PreParams p) {
-  extern __shared__ __align__(16) float s_line[];             // [8 warps][max_words * 4]
+  extern __shared__ __align__(16) float s_h[];                // [max_rows][3 (RGB)][64]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.z;
   const int ox0 = blockIdx.x * kPreTW, oy0 = blockIdx.y * p.TH;
   const int ncols = min(kPreTW, p.net_w - ox0), nrows = min(p.TH, p.net_h - oy0);
-  const int xs = __ldg(p.xidx + ox0 * 4), xe = __ldg(p.xidx + (ox0 + ncols - 1) * 4 + 3);
-  const int sb0 = (xs * 3) & ~3;                               // first staged byte of the row strip (word aligned)
-  const int nwords = (xe * 3 + 3 - sb0 + 3) >> 2;
-  float* line = s_line + warp * (p.max_words * 4);
-  const uint8_t* frame = p.src + (long long)b * p.frame_stride + sb0;
-  const int y_last = __ldg(p.yidx + (oy0 + nrows - 1) * 4 + 3);
-  const bool fast = p.format == 0 && p.aligned && (long long)b * p.frame_stride + sb0 + (long long)y_last * p.row_stride + 4LL * nwords <= p.total_bytes;
+  const int ys = __ldg(p.yidx + oy0 * 4), ye = __ldg(p.yidx + (oy0 + nrows - 1) * 4 + 3);
+  const int nsrc = ye - ys + 1;
 
-  // this lane's two output columns: tap offsets into the fp32 line (R channel = byte 2 of the BGR pixel)
-  const bool active = 2 * lane < ncols;
-  const int c0 = ox0 + 2 * lane;
-  int4 o0 = make_int4(0, 0, 0, 0), o1 = o0;
-  float4 w0 = make_float4(0.f, 0.f, 0.f, 0.f), w1 = w0;
-  if (active) {
-    o0 = __ldg(reinterpret_cast<const int4*>(p.xidx) + c0);
-    o1 = __ldg(reinterpret_cast<const int4*>(p.xidx) + c0 + 1);
-    w0 = __ldg(reinterpret_cast<const float4*>(p.xw) + c0);
-    w1 = __ldg(reinterpret_cast<const float4*>(p.xw) + c0 + 1);
-    o0.x = o0.x * 3 - sb0; o0.y = o0.y * 3 - sb0; o0.z = o0.z * 3 - sb0; o0.w = o0.w * 3 - sb0;
-    o1.x = o1.x * 3 - sb0; o1.y = o1.y * 3 - sb0; o1.z = o1.z * 3 - sb0; o1.w = o1.w * 3 - sb0;
-  }
-
-  for (int ry = warp; ry < nrows; ry += kPreThreads / 32) {
-    const int oy = oy0 + ry;
-    const int4 yi = __ldg(reinterpret_cast<const int4*>(p.yidx) + oy);
-    const float4 wy = __ldg(reinterpret_cast<const float4*>(p.yw) + oy);
-    const uint8_t* r0 = frame + (long long)yi.x * p.row_stride;
-    const uint8_t* r1 = frame + (long long)yi.y * p.row_stride;
-    const uint8_t* r2 = frame + (long long)yi.z * p.row_stride;
-    const uint8_t* r3 = frame + (long long)yi.w * p.row_stride;
-    // ---- V: four vertical taps on the raw bytes, one 32-bit word per lane and iteration
-#pragma unroll kPreUnroll
-    for (int wi = lane; wi < nwords; wi += 32) {
-      uint32_t u0, u1, u2, u3;
-      if (fast) {                                               // whole tile aligned and inside the buffer (CTA-uniform)
-        u0 = __ldg(reinterpret_cast<const uint32_t*>(r0) + wi);
-        u1 = __ldg(reinterpret_cast<const uint32_t*>(r1) + wi);
-        u2 = __ldg(reinterpret_cast<const uint32_t*>(r2) + wi);
-        u3 = __ldg(reinterpret_cast<const uint32_t*>(r3) + wi);
-      } else if (p.format == 0) {
-        u0 = load_word(p, r0 + 4 * wi); u1 = load_word(p, r1 + 4 * wi);
-        u2 = load_word(p, r2 + 4 * wi); u3 = load_word(p, r3 + 4 * wi);
-      } else {
-        u0 = nv12_word(p, b, yi.x, sb0 + 4 * wi); u1 = nv12_word(p, b, yi.y, sb0 + 4 * wi);
-        u2 = nv12_word(p, b, yi.z, sb0 + 4 * wi); u3 = nv12_word(p, b, yi.w, sb0 + 4 * wi);
+  // ---- H: this thread's output column; warps (2k, 2k+1) share source rows k, k+4, ...
+  const int col = (warp & 1) * 32 + lane;
+  if ((warp & 1) * 32 < ncols) {                              // warp-uniform (net_w is a multiple of 32)
+    const int4 xi = __ldg(reinterpret_cast<const int4*>(p.xidx) + ox0 + col);
+    const float4 xw = __ldg(reinterpret_cast<const float4*>(p.xw) + ox0 + col);
+    const int o = xi.x * 3;
+    // aligned fast path: taps contiguous, word loads legal, and the 16 bytes read stay inside the buffer
+    const bool lane_fast = p.format == 0 && p.aligned && xi.y == xi.x + 1 && xi.z == xi.x + 2 && xi.w == xi.x + 3 &&
+                           (long long)b * p.frame_stride + (long long)ye * p.row_stride + (o & ~3) + 16 <= p.total_bytes;
+    float* dst = s_h + col;
+    if (__all_sync(0xffffffffu, lane_fast)) {
+      const uint32_t* base = reinterpret_cast<const uint32_t*>(p.src + (long long)b * p.frame_stride + (long long)ys * p.row_stride) + (o >> 2);
+      const long long rs = p.row_stride >> 2;
+      const int sh = (o & 3) * 8;
+      // two source rows per iteration (rows sr and sr + 4): eight independent loads in flight, packed fp32 taps
+      constexpr int kStep = kPreThreads / 64;
+      for (int sr = warp >> 1; sr < nsrc; sr += 2 * kStep) {
+        const uint32_t* rp = base + sr * rs;
+        const bool two = sr + kStep < nsrc;                        // warp-uniform
+        const uint32_t* rq = two ? rp + kStep * rs : rp;
+        const uint32_t u0 = __ldg(rp), u1 = __ldg(rp + 1), u2 = __ldg(rp + 2), u3 = __ldg(rp + 3);
+        const uint32_t v0 = __ldg(rq), v1 = __ldg(rq + 1), v2 = __ldg(rq + 2), v3 = __ldg(rq + 3);
+        float2 bgA, bgB, rr;
+        htaps2(__funnelshift_r(u0, u1, sh), __funnelshift_r(u1, u2, sh), __funnelshift_r(u2, u3, sh),
+               __funnelshift_r(v0, v1, sh), __funnelshift_r(v1, v2, sh), __funnelshift_r(v2, v3, sh), xw, bgA, bgB, rr);
+        float* d = dst + sr * (3 * kPreTW);
+        d[0] = rr.x; d[kPreTW] = bgA.y; d[2 * kPreTW] = bgA.x;
+        if (two) {
+          d += kStep * 3 * kPreTW;
+          d[0] = rr.y; d[kPreTW] = bgB.y; d[2 * kPreTW] = bgB.x;
+        }
       }
-      float4 v;
-      v.x = vdot(byte_to_float(u0, 0), byte_to_float(u1, 0), byte_to_float(u2, 0), byte_to_float(u3, 0), wy);
-      v.y = vdot(byte_to_float(u0, 1), byte_to_float(u1, 1), byte_to_float(u2, 1), byte_to_float(u3, 1), wy);
-      v.z = vdot(byte_to_float(u0, 2), byte_to_float(u1, 2), byte_to_float(u2, 2), byte_to_float(u3, 2), wy);
-      v.w = vdot(byte_to_float(u0, 3), byte_to_float(u1, 3), byte_to_float(u2, 3), byte_to_float(u3, 3), wy);
-      reinterpret_cast<float4*>(line)[wi] = v;
-    }
-    __syncwarp();
-    // ---- H: four horizontal taps per channel for the lane's two columns, normalise, store (BGR -> RGB)
-    if (active) {
-#pragma unroll
-      for (int ch = 0; ch < 3; ++ch) {
-        const float* l = line + (2 - ch);
-        const float a = vdot(l[o0.x], l[o0.y], l[o0.z], l[o0.w], w0);
-        const float c = vdot(l[o1.x], l[o1.y], l[o1.z], l[o1.w], w1);
-        store_px2(p, b, ch, oy, c0, fmaf(a, p.scale[ch], -p.shift[ch]), fmaf(c, p.scale[ch], -p.shift[ch]));
+    } else {
+      for (int sr = warp >> 1; sr < nsrc; sr += kPreThreads / 64) {
+        const int row = ys + sr;
+        const uint32_t p0 = pixel_bgr(p, b, row, xi.x), p1 = pixel_bgr(p, b, row, xi.y);
+        const uint32_t p2 = pixel_bgr(p, b, row, xi.z), p3 = pixel_bgr(p, b, row, xi.w);
+        float r, g, bl;
+        htaps(p0 | (p1 << 24), (p1 >> 8) | (p2 << 16), (p2 >> 16) | (p3 << 8), xw, r, g, bl);
+        dst[(sr * 3 + 0) * kPreTW] = r;
+        dst[(sr * 3 + 1) * kPreTW] = g;
+        dst[(sr * 3 + 2) * kPreTW] = bl;
       }
     }
-    __syncwarp();
   }
+  __syncthreads();
+
+  vertical_phase<kPreThreads>(p, s_h, b, ox0, oy0, ncols, nrows, ys);
 }
 
 // source size == net size, generic alignment: 4 pixels (12 bytes, 3 words) per thread
@@ -224,35 +302,53 @@ DEV void copy16_channel(const uint32_t (&u)[12], float scale, float shift, uint4
   hi = make_uint4(pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]), pack_bf16(v[12], v[13]), pack_bf16(v[14], v[15]));
 }
 
+// one 32-byte (sector-sized) streaming store: sm_100 has 256-bit global accesses
+DEV void st_stream_256(void* ptr, const uint4& lo, const uint4& hi) {
+  asm volatile("st.global.cs.v8.u32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(ptr), "r"(lo.x), "r"(lo.y), "r"(lo.z), "r"(lo.w),
+               "r"(hi.x), "r"(hi.y), "r"(hi.z), "r"(hi.w)
+               : "memory");
+}
+
+#ifndef PRE_COPY_ILP
+#define PRE_COPY_ILP 2
+#endif
+constexpr int kCopyIlp = PRE_COPY_ILP;
+
 __global__ void __launch_bounds__(256) preprocess_copy16_kernel(const PreParams p) {
   const int nx = p.W >> 4;
-  const long long item = (long long)blockIdx.x * 256 + threadIdx.x;     // (frame row, 16-pixel group), flattened
-  const long long rowi = item / nx;
-  if (rowi >= (long long)p.B * p.H) return;
-  const int x16 = static_cast<int>(item - rowi * nx);
-  const int b = static_cast<int>(rowi / p.H), y = static_cast<int>(rowi - (long long)b * p.H);
-  const uint4* ptr = reinterpret_cast<const uint4*>(p.src + (long long)b * p.frame_stride + (long long)y * p.row_stride) + x16 * 3;
-  const uint4 q0 = __ldg(ptr), q1 = __ldg(ptr + 1), q2 = __ldg(ptr + 2);
-  const uint32_t u[12] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w};
-  __nv_bfloat16* base = reinterpret_cast<__nv_bfloat16*>(p.out);
-  long long o, cstride;                                         // element offset of (b, ch 0, y, x16*16); channel stride
-  if (p.layout == 0) {
-    cstride = (long long)p.net_h * p.net_w;
-    o = ((long long)b * 3 * p.net_h + y) * p.net_w + x16 * 16;
-  } else {
-    cstride = 256;
-    o = (((long long)b * (p.net_h >> 4) + (y >> 4)) * nx + x16) * 768 + (y & 15) * 16;
+  const long long nitems = (long long)p.B * p.H * nx;
+  uint4 q[kCopyIlp][3];
+  long long o[kCopyIlp];
+  bool ok[kCopyIlp];
+  const long long cstride = p.layout == 0 ? (long long)p.net_h * p.net_w : 256;   // channel stride in elements
+  // all loads of the thread's items first (48 bytes each), then convert and store
+#pragma unroll
+  for (int k = 0; k < kCopyIlp; ++k) {
+    const long long item = ((long long)blockIdx.x * kCopyIlp + k) * 256 + threadIdx.x;   // (frame row, 16-pixel group)
+    ok[k] = item < nitems;
+    if (!ok[k]) continue;
+    const long long rowi = item / nx;
+    const int x16 = static_cast<int>(item - rowi * nx);
+    const int b = static_cast<int>(rowi / p.H), y = static_cast<int>(rowi - (long long)b * p.H);
+    const uint4* ptr = reinterpret_cast<const uint4*>(p.src + (long long)b * p.frame_stride + (long long)y * p.row_stride) + x16 * 3;
+    q[k][0] = __ldg(ptr); q[k][1] = __ldg(ptr + 1); q[k][2] = __ldg(ptr + 2);
+    o[k] = p.layout == 0 ? ((long long)b * 3 * p.net_h + y) * p.net_w + x16 * 16
+                         : (((long long)b * (p.net_h >> 4) + (y >> 4)) * nx + x16) * 768 + (y & 15) * 16;
   }
-  uint4 lo, hi;
-  copy16_channel<0>(u, p.scale[0], p.shift[0], lo, hi);
-  __stcs(reinterpret_cast<uint4*>(base + o), lo);
-  __stcs(reinterpret_cast<uint4*>(base + o) + 1, hi);
-  copy16_channel<1>(u, p.scale[1], p.shift[1], lo, hi);
-  __stcs(reinterpret_cast<uint4*>(base + o + cstride), lo);
-  __stcs(reinterpret_cast<uint4*>(base + o + cstride) + 1, hi);
-  copy16_channel<2>(u, p.scale[2], p.shift[2], lo, hi);
-  __stcs(reinterpret_cast<uint4*>(base + o + 2 * cstride), lo);
-  __stcs(reinterpret_cast<uint4*>(base + o + 2 * cstride) + 1, hi);
+  __nv_bfloat16* base = reinterpret_cast<__nv_bfloat16*>(p.out);
+#pragma unroll
+  for (int k = 0; k < kCopyIlp; ++k) {
+    if (!ok[k]) continue;
+    const uint32_t u[12] = {q[k][0].x, q[k][0].y, q[k][0].z, q[k][0].w, q[k][1].x, q[k][1].y,
+                            q[k][1].z, q[k][1].w, q[k][2].x, q[k][2].y, q[k][2].z, q[k][2].w};
+    uint4 lo, hi;
+    copy16_channel<0>(u, p.scale[0], p.shift[0], lo, hi);
+    st_stream_256(base + o[k], lo, hi);
+    copy16_channel<1>(u, p.scale[1], p.shift[1], lo, hi);
+    st_stream_256(base + o[k] + cstride, lo, hi);
+    copy16_channel<2>(u, p.scale[2], p.shift[2], lo, hi);
+    st_stream_256(base + o[k] + 2 * cstride, lo, hi);
+  }
 }
 
 }  // namespace deb
@@ -295,10 +391,10 @@ static int run_preprocess(const uint8_t* bgr, const uint8_t* uv, int64_t uv_row_
   if (H == net_h && W == net_w) {                             // cv2.resize is a copy for equal sizes
     const bool wide = format == 0 && layout != 2 && W % 16 == 0 &&
                       ((reinterpret_cast<uintptr_t>(bgr) | (uintptr_t)row_stride | (uintptr_t)frame_stride |
-                        reinterpret_cast<uintptr_t>(out)) & 15) == 0;
+                        reinterpret_cast<uintptr_t>(out)) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 31) == 0;
     if (wide) {
       const long long items = (long long)B * H * (W / 16);
-      preprocess_copy16_kernel<<<(unsigned)((items + 255) / 256), 256, 0, st>>>(p);
+      preprocess_copy16_kernel<<<(unsigned)((items + 256 * kCopyIlp - 1) / (256 * kCopyIlp)), 256, 0, st>>>(p);
     } else {
       dim3 grid((W / 4 + 127) / 128, H, B);
       preprocess_copy_kernel<<<grid, 128, 0, st>>>(p);
@@ -306,14 +402,15 @@ static int run_preprocess(const uint8_t* bgr, const uint8_t* uv, int64_t uv_row_
     count_launch();
     return cuda_check_launch("preprocess_copy_kernel");
   }
+  // largest power-of-two tile height whose staged source rows fit the shared-memory budget (TH = 1 needs 4 rows)
   p.TH = 32;
-  p.max_words = (tx->max_extent(kPreTW) * 3 + 6) / 4 + 1;
-  const size_t smem = (size_t)(kPreThreads / 32) * p.max_words * 16;
-  if (smem > 200 * 1024) return fail(DE_ERR_UNSUPPORTED, "de_preprocess: downscale factor too large for the staged row strip");
-  if (smem > 48 * 1024) {
+  while (p.TH > 1 && (size_t)ty->max_extent(p.TH) * 3 * kPreTW * sizeof(float) > (size_t)PRE_SMEM_KB * 1024) p.TH >>= 1;
+  p.max_rows = ty->max_extent(p.TH);
+  const size_t smem = (size_t)p.max_rows * 3 * kPreTW * sizeof(float);
+  {
     static bool configured = false;
     if (!configured) {
-      cudaError_t e = cudaFuncSetAttribute(preprocess_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+      cudaError_t e = cudaFuncSetAttribute(preprocess_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PRE_SMEM_KB * 1024);
       if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(preprocess)");
       configured = true;
     }

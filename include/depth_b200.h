@@ -165,7 +165,9 @@ int de_subsample(const void* x, void* out, int B, int H, int W, int C, int strid
  * bf16x3 (~16 mantissa bit) product on the ordinary bf16 GEMM (DPT_Hybrid's ResNetV2 stages); out_f32 - fp32 copy
  * (the ResNetV2 residual stream); out_plain - bf16 [.., C] copy (decoder input).  Deterministic (fixed-order
  * reductions).  ws: device scratch of at least
- * 8*B*groups + 16*B*groups*ceil(HW/max(ceil(HW/148), 4*256/(C/8))) + 32 bytes.
+ * 8*B*groups + 16*B*groups*ceil(HW/max(ceil(HW/148), 4*256/(C/8))) + 32 + 4*B bytes.  Its last 4*B bytes are
+ * arrival counters: they must be ZERO before the first call (cudaMemset the buffer once) and every call leaves them
+ * zero; calls sharing a workspace must be ordered on one stream.
  * (timm GroupNormAct, eps 1e-5, 32 groups.) */
 int de_groupnorm(const void* x, int x_dtype, const float* gamma, const float* beta, const void* add, int add_dtype,
                  void* out, int out_mode, float* out_f32, void* out_plain, int B, int HW, int C, int groups, float eps,

@@ -40,23 +40,68 @@ def hf_hybrid_config(**over):
 
 
 def randomize_(model, seed=0, positive_head_bias=True):
-    """Every parameter gets a non-trivial seeded value (HF leaves cls/pos-embed/biases at zero), scaled so the
-    activations stay O(1); the head biases follow SURVEY 8d D2's degeneracy guard (final ReLU must not zero the map)."""
+    """Every parameter gets a non-trivial seeded value (HF leaves cls/pos-embed/biases at zero), drawn from the same
+    distribution as ``depth_estimation_b200.init.random_state_dict`` - the init every other parity case runs on:
+    Linear 0.02, conv 1/sqrt(fan_in), norm gains 1 +- 0.1, biases / pos-embed 0.02 - with the head biases of SURVEY 8d
+    D2's degeneracy guard (the final ReLU must not zero the map).  An attenuating init (all gains 0.7/sqrt(fan_in),
+    the first version of this file) shrinks the signal by 0.7 per decoder conv until the map is bias-dominated
+    (max / dynamic range = 6); bf16 activation rounding (2^-9 of the MAGNITUDE) then reads as 2e-3 of the maximum and
+    1.3e-2 of the range, for the fp32-accumulating CUDA path and for the oracle with bf16 rounding injected alike - a
+    property of that init, not of either implementation."""
     g = torch.Generator().manual_seed(seed)
     with torch.no_grad():
         for name, p in model.named_parameters():
-            if p.ndim >= 2 and "embeddings.position" not in name and "cls_token" not in name:
+            if "embeddings.position" in name or "cls_token" in name:
+                p.copy_(0.02 * torch.randn(p.shape, generator=g))
+            elif p.ndim == 2:
+                p.copy_(0.02 * torch.randn(p.shape, generator=g))
+            elif p.ndim > 2:
                 fan_in = p[0].numel()
-                p.copy_(torch.randn(p.shape, generator=g) * (0.7 / fan_in ** 0.5))
+                p.copy_(torch.randn(p.shape, generator=g) * (1.0 / fan_in ** 0.5))
             elif name.endswith("weight"):                                  # norm gains
                 p.copy_(1.0 + 0.1 * torch.randn(p.shape, generator=g))
-            else:                                                          # biases, cls token, pos-embed
-                p.copy_(0.05 * torch.randn(p.shape, generator=g))
+            else:                                                          # biases
+                p.copy_(0.02 * torch.randn(p.shape, generator=g))
         if positive_head_bias:
             sd = dict(model.named_parameters())
             sd["head.head.4.bias"].fill_(1.0)
-            sd["head.head.2.bias"].add_(0.5)
+            sd["head.head.2.bias"].fill_(0.5)
+            sd["head.head.4.weight"].abs_()          # 32 post-ReLU inputs x positive weights: the map cannot clip to 0
     return model
+
+
+class bf16_operands:
+    """Context manager: ``model`` computes with bf16-rounded operands (inputs and weights of every Linear / Conv /
+    ConvTranspose, both sides of every explicit matmul) and fp32 accumulation - the arithmetic contract of the CUDA
+    path (north_star: "bf16 ... fp32 accumulate") applied to an independent implementation.  Its distance from the
+    fp32 run of the same model is the precision floor of that contract for the given weights and input."""
+
+    def __init__(self, model):
+        self.model, self.hooks, self.saved = model, [], {}
+
+    @staticmethod
+    def _rb(t):
+        return t.bfloat16().float() if torch.is_floating_point(t) else t
+
+    def __enter__(self):
+        rb = self._rb
+        for name, m in self.model.named_modules():
+            if isinstance(m, (torch.nn.Linear, torch.nn.Conv2d, torch.nn.ConvTranspose2d)):
+                self.saved[name] = m.weight.data
+                m.weight.data = rb(m.weight.data)
+                self.hooks.append(m.register_forward_pre_hook(lambda mod, inp: (rb(inp[0]),) + tuple(inp[1:])))
+        self._matmul = torch.matmul
+        torch.matmul = lambda a, b, *k, **kw: self._matmul(rb(a), rb(b), *k, **kw)
+        return self.model
+
+    def __exit__(self, *exc):
+        torch.matmul = self._matmul
+        for h in self.hooks:
+            h.remove()
+        mods = dict(self.model.named_modules())
+        for name, w in self.saved.items():
+            mods[name].weight.data = w
+        return False
 
 
 _BLOCK = {
