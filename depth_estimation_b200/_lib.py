@@ -31,7 +31,7 @@ class DeGemm(C.Structure):
         ("out_rowmode", C.c_int), ("grp", C.c_int), ("pad", C.c_int), ("off", C.c_int),
         ("ps_gh", C.c_int), ("ps_gw", C.c_int), ("ps_s", C.c_int), ("ps_cout", C.c_int),
         ("head_w", C.c_void_p), ("head_b", C.c_float),
-        ("block_n", C.c_int), ("debug", C.c_int), ("cta_group", C.c_int),
+        ("block_n", C.c_int), ("debug", C.c_int), ("cta_group", C.c_int), ("accumulate", C.c_int),
     ]
 
 

@@ -71,6 +71,12 @@ DEV void tma_store_4d(const void* desc, const void* smem_src, int c0, int c1, in
                ::"l"(reinterpret_cast<uint64_t>(desc)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
                : "memory");
 }
+// same box, added into global memory (element type of the tensor map: fp32 here) - a read-modify-write at L2
+DEV void tma_reduce_add_2d(const void* desc, const void* smem_src, int c0, int c1) {
+  asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(desc)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
+               : "memory");
+}
 DEV void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 // wait until the smem sources of all but the newest N committed store groups have been read
 template <int N>
@@ -260,6 +266,13 @@ DEV float2 fadd2(float2 a, float2 b) {
   asm("add.rn.f32x2 %0, %1, %2;" : "=l"(reinterpret_cast<unsigned long long&>(d)) : "l"(reinterpret_cast<unsigned long long&>(a)), "l"(reinterpret_cast<unsigned long long&>(b)));
   return d;
 }
+// one 32-byte (sector-sized) streaming store: sm_100 has 256-bit global accesses
+DEV void st_stream_256(void* ptr, const uint4& lo, const uint4& hi) {
+  asm volatile("st.global.cs.v8.u32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(ptr), "r"(lo.x), "r"(lo.y), "r"(lo.z), "r"(lo.w),
+               "r"(hi.x), "r"(hi.y), "r"(hi.z), "r"(hi.w)
+               : "memory");
+}
+
 DEV float ex2_approx(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));

@@ -46,6 +46,7 @@ struct GemmParams {
   const float* head_w;
   float head_b;
   int debug;  // bit0: skip epilogue body (perf experiments only), bit1: skip global stores
+  int accumulate;  // store epilogue only: TMA reduce-add instead of store
 };
 
 // EPI 0: "store" epilogue - bias + activation only, output tile staged in 128B-swizzled smem and written
@@ -368,7 +369,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         named_bar_sync(bar_id, 128);
         if (gtid == 0 && m_tile < p.m_tiles && !(p.debug & 2)) {
           const int col0 = n_tile * BN + u * ucols;
-          if (p.a_mode == 0) tma_store_2d(&tmC, sbuf, col0, m_tile * BM);
+          if (p.accumulate) tma_reduce_add_2d(&tmC, sbuf, col0, m_tile * BM);
+          else if (p.a_mode == 0) tma_store_2d(&tmC, sbuf, col0, m_tile * BM);
           else tma_store_4d(&tmC, sbuf, col0, x0, y0, b);
           tma_store_commit();
         }
@@ -717,12 +719,15 @@ extern "C" int de_gemm(const DeGemm* g, void* stream) {
   p.head_w = g->head_w;
   p.head_b = g->head_b;
   p.debug = g->debug;
+  p.accumulate = g->accumulate;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   // epilogue flavour: the TMA-store epilogue covers "bias + activation -> dense output"
   const int es = g->out_dtype == DE_DTYPE_F32 ? 4 : 2;
   bool store_epi = !g->add1 && !g->add2 && !g->out_relu && !g->head_w && g->out_rowmode == 0 && bn >= 64 &&
                    (g->ldo * es) % 16 == 0 && (reinterpret_cast<uintptr_t>(g->out) & 15) == 0 &&
                    (g->a_mode == 0 || g->ldo == g->N) && !(g->debug & 4);
+  if (g->accumulate && (!store_epi || g->a_mode != 0 || g->out_dtype != DE_DTYPE_F32))
+    return fail(DE_ERR_INVALID, "de_gemm: accumulate needs the dense fp32 store epilogue (a_mode 0, no add1/add2/out_relu/row maps)");
   CUtensorMap tc = tb;
   if (store_epi) {
     const CUtensorMapDataType dt = es == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;

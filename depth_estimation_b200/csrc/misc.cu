@@ -104,25 +104,33 @@ __global__ void fill_cls_kernel(float* __restrict__ x, long long ldx, int B, int
 // upsampling needs at most kUpRows/2 + 2 source rows for kUpRows output rows - so a thread issues ~6 16-byte loads
 // and 4 16-byte streaming stores instead of 4 loads per store, with a quarter of the index arithmetic.
 constexpr int kUpRows = 4;
+// kV = 16-byte vectors (8 channels each) per thread.  kV = 2 (C % 16 == 0): 32 bytes per output pixel and thread,
+// written with one 256-bit streaming store (a full sector) - the write side is 4/5 of this kernel's traffic.
+template <int kV>
 DEV void up_hrow(const __nv_bfloat16* rowp, int x0off, int x1off, float hx, float lx, float* h) {
-  const uint4 a = *reinterpret_cast<const uint4*>(rowp + x0off);
-  const uint4 b = *reinterpret_cast<const uint4*>(rowp + x1off);
-  const uint32_t* pa = &a.x;
-  const uint32_t* pb = &b.x;
 #pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    h[2 * k] = hx * bf16_lo(pa[k]) + lx * bf16_lo(pb[k]);
-    h[2 * k + 1] = hx * bf16_hi(pa[k]) + lx * bf16_hi(pb[k]);
+  for (int v = 0; v < kV; ++v) {
+    const uint4 a = *reinterpret_cast<const uint4*>(rowp + x0off + 8 * v);
+    const uint4 b = *reinterpret_cast<const uint4*>(rowp + x1off + 8 * v);
+    const uint32_t* pa = &a.x;
+    const uint32_t* pb = &b.x;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      h[8 * v + 2 * k] = hx * bf16_lo(pa[k]) + lx * bf16_lo(pb[k]);
+      h[8 * v + 2 * k + 1] = hx * bf16_hi(pa[k]) + lx * bf16_hi(pb[k]);
+    }
   }
 }
+template <int kV>
 __global__ void __launch_bounds__(256) upsample2x_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out,
                                                          int B, int H, int W, int C, int align_corners, int cg_shift) {
-  const int cg = C >> 3;
+  constexpr int kCh = 8 * kV;
+  const int cg = C / kCh;
   const int OH = 2 * H, OW = 2 * W;
-  const unsigned idx = blockIdx.x * 256u + threadIdx.x;          // (ox, 8-channel group) inside the row
+  const unsigned idx = blockIdx.x * 256u + threadIdx.x;          // (ox, channel group) inside the row
   const int ox = cg_shift >= 0 ? static_cast<int>(idx >> cg_shift) : static_cast<int>(idx / (unsigned)cg);
   if (ox >= OW) return;
-  const int c = static_cast<int>(idx - (unsigned)ox * (unsigned)cg) * 8;
+  const int c = static_cast<int>(idx - (unsigned)ox * (unsigned)cg) * kCh;
   const int oy0 = blockIdx.y * kUpRows, b = blockIdx.z;
   // ATen area_pixel_compute_scale: (in-1)/(out-1) in float, src = scale*dst (align_corners); else 0.5*(dst+0.5)-0.5 >= 0
   const float rh = OH > 1 ? (float)(H - 1) / (float)(OH - 1) : 0.f;
@@ -132,7 +140,7 @@ __global__ void __launch_bounds__(256) upsample2x_kernel(const __nv_bfloat16* __
   const float lx = sx - x0, hx = 1.f - lx;
   const __nv_bfloat16* base = x + (long long)b * H * W * C + c;
   const int x0off = x0 * C, x1off = x1 * C;
-  float h0[8], h1[8];
+  float h0[kCh], h1[kCh];
   int cy0 = -1, cy1 = -1;                                        // source rows currently held in h0 / h1
   __nv_bfloat16* op = out + (((long long)b * OH + oy0) * OW + ox) * C + c;
 #pragma unroll
@@ -145,26 +153,28 @@ __global__ void __launch_bounds__(256) upsample2x_kernel(const __nv_bfloat16* __
     if (y0 != cy0) {                                             // block-uniform branches (oy is per block)
       if (y0 == cy1) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) h0[j] = h1[j];
+        for (int j = 0; j < kCh; ++j) h0[j] = h1[j];
       } else {
-        up_hrow(base + (long long)y0 * W * C, x0off, x1off, hx, lx, h0);
+        up_hrow<kV>(base + (long long)y0 * W * C, x0off, x1off, hx, lx, h0);
       }
       cy0 = y0;
     }
     if (y1 != cy1) {
       if (y1 == cy0) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) h1[j] = h0[j];
+        for (int j = 0; j < kCh; ++j) h1[j] = h0[j];
       } else {
-        up_hrow(base + (long long)y1 * W * C, x0off, x1off, hx, lx, h1);
+        up_hrow<kV>(base + (long long)y1 * W * C, x0off, x1off, hx, lx, h1);
       }
       cy1 = y1;
     }
-    uint32_t o[4];
+    uint32_t o[4 * kV];
 #pragma unroll
-    for (int k = 0; k < 4; ++k)
+    for (int k = 0; k < 4 * kV; ++k)
       o[k] = pack_bf16(hy * h0[2 * k] + ly * h1[2 * k], hy * h0[2 * k + 1] + ly * h1[2 * k + 1]);
-    __stcs(reinterpret_cast<uint4*>(op + (long long)r * OW * C), make_uint4(o[0], o[1], o[2], o[3]));
+    __nv_bfloat16* dst = op + (long long)r * OW * C;
+    if constexpr (kV == 2) st_stream_256(dst, make_uint4(o[0], o[1], o[2], o[3]), make_uint4(o[4], o[5], o[6], o[7]));
+    else __stcs(reinterpret_cast<uint4*>(dst), make_uint4(o[0], o[1], o[2], o[3]));
   }
 }
 
@@ -413,13 +423,18 @@ extern "C" int de_fill_cls(float* x, int64_t ldx, int B, int T, int dim, const f
 extern "C" int de_upsample2x(const void* x, void* out, int B, int H, int W, int C, int align_corners, void* stream) {
   if (!x || !out || C % 8 != 0) return fail(DE_ERR_INVALID, "de_upsample2x: bad args (C %% 8)");
   if (B > 65535 || 2 * H > 65535) return fail(DE_ERR_UNSUPPORTED, "de_upsample2x: B / 2H exceed the grid limits");
-  const int cg = C / 8;
+  const bool wide = C % 16 == 0 && ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out)) & 31) == 0;
+  const int cg = wide ? C / 16 : C / 8;
   int cg_shift = -1;
   for (int sft = 0; sft < 12; ++sft)
     if ((1 << sft) == cg) cg_shift = sft;
   dim3 grid((unsigned)((2LL * W * cg + 255) / 256), (2 * H + kUpRows - 1) / kUpRows, B);
-  upsample2x_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(out), B, H, W, C, align_corners, cg_shift);
+  if (wide)
+    upsample2x_kernel<2><<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(out), B, H, W, C, align_corners, cg_shift);
+  else
+    upsample2x_kernel<1><<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(out), B, H, W, C, align_corners, cg_shift);
   count_launch();
   return cuda_check_launch("upsample2x_kernel");
 }

@@ -302,13 +302,6 @@ DEV void copy16_channel(const uint32_t (&u)[12], float scale, float shift, uint4
   hi = make_uint4(pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]), pack_bf16(v[12], v[13]), pack_bf16(v[14], v[15]));
 }
 
-// one 32-byte (sector-sized) streaming store: sm_100 has 256-bit global accesses
-DEV void st_stream_256(void* ptr, const uint4& lo, const uint4& hi) {
-  asm volatile("st.global.cs.v8.u32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(ptr), "r"(lo.x), "r"(lo.y), "r"(lo.z), "r"(lo.w),
-               "r"(hi.x), "r"(hi.y), "r"(hi.z), "r"(hi.w)
-               : "memory");
-}
-
 #ifndef PRE_COPY_ILP
 #define PRE_COPY_ILP 2
 #endif

@@ -74,25 +74,38 @@ class ViTEncoder:
         qkv = self._buf(("qkv", M), (M, 3 * D), torch.bfloat16)
         att = self._buf(("att", M), (M, D), torch.bfloat16)
         hid = self._buf(("hid", M), (M, 4 * D), torch.bfloat16)
-        # branch outputs (attention proj / fc2) go to the LayerNorm-with-residual kernel as bf16: the fp32 stream x
-        # itself is never rounded, and the GEMM writes / the LN reads half the bytes (DEB_Y_F32=1 restores fp32)
-        ybuf = self._buf(("y", M), (M, D), torch.float32 if os.environ.get("DEB_Y_F32") else torch.bfloat16)
+        # branch outputs (attention proj / fc2) are ADDED into the fp32 stream by the GEMM itself (TMA reduce-add
+        # epilogue, accumulate=True): no bf16 branch buffer, no rounding of the branch, and LayerNorm only reads x
+        # (6 instead of 12 bytes per element).  DEB_Y_BUF=1 restores the bf16 branch buffer + add-in-LayerNorm path.
         scale = (D // self.heads) ** -0.5
-        y = None                                    # pending branch output, folded into the next LayerNorm
+        if os.environ.get("DEB_Y_BUF"):
+            ybuf = self._buf(("y", M), (M, D), torch.bfloat16)
+            y = None                                # pending branch output, folded into the next LayerNorm
+            for i, w in enumerate(self.blocks):
+                ops.layernorm(x, w["n1w"], w["n1b"], 1e-6, xn, y=y)
+                if (i - 1) in hooks:                # x now holds the output of block i-1
+                    on_hook(i - 1, x)
+                ops.gemm(xn, w["qkv_w"], qkv, bias=w["qkv_b"])
+                ops.attention(qkv, att, B, T, self.heads, scale)
+                ops.gemm(att, w["proj_w"], ybuf, bias=w["proj_b"])
+                ops.layernorm(x, w["n2w"], w["n2b"], 1e-6, xn, y=ybuf)
+                ops.gemm(xn, w["fc1_w"], hid, bias=w["fc1_b"], act=ops.ACT_GELU)
+                ops.gemm(hid, w["fc2_w"], ybuf, bias=w["fc2_b"])
+                y = ybuf
+            ops.layernorm(x, None, None, 1e-6, None, y=y)
+            if (self.depth - 1) in hooks:
+                on_hook(self.depth - 1, x)
+            return
         for i, w in enumerate(self.blocks):
-            ops.layernorm(x, w["n1w"], w["n1b"], 1e-6, xn, y=y)
-            if (i - 1) in hooks:                    # x now holds the output of block i-1
-                on_hook(i - 1, x)
+            ops.layernorm(x, w["n1w"], w["n1b"], 1e-6, xn)
             ops.gemm(xn, w["qkv_w"], qkv, bias=w["qkv_b"])
             ops.attention(qkv, att, B, T, self.heads, scale)
-            ops.gemm(att, w["proj_w"], ybuf, bias=w["proj_b"])
-            ops.layernorm(x, w["n2w"], w["n2b"], 1e-6, xn, y=ybuf)
+            ops.gemm(att, w["proj_w"], x, bias=w["proj_b"], accumulate=True)
+            ops.layernorm(x, w["n2w"], w["n2b"], 1e-6, xn)
             ops.gemm(xn, w["fc1_w"], hid, bias=w["fc1_b"], act=ops.ACT_GELU)
-            ops.gemm(hid, w["fc2_w"], ybuf, bias=w["fc2_b"])
-            y = ybuf
-        ops.layernorm(x, None, None, 1e-6, None, y=y)
-        if (self.depth - 1) in hooks:
-            on_hook(self.depth - 1, x)
+            ops.gemm(hid, w["fc2_w"], x, bias=w["fc2_b"], accumulate=True)
+            if i in hooks:
+                on_hook(i, x)
 
 
 class Reassemble:

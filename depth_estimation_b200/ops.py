@@ -130,8 +130,8 @@ def postprocess(pred: torch.Tensor, H: int, W: int, want_map: bool = True, want_
 # ------------------------------------------------------------------------------- GEMM / conv
 def gemm(a: torch.Tensor, w: torch.Tensor, out: torch.Tensor, *, M=None, N=None, K=None, bias=None, act=ACT_NONE,
          add1=None, add1_rowmode=0, add1_pre=False, ld_add1=None, add2=None, out_relu=None, out_rowmode=0, grp=0,
-         pad=0, off=0, ldo=None, conv=None, pixel_shuffle=None, bias_mod=0, head=None, block_n=0, cta_group=0, debug=0):
-    """out = epilogue(a @ w.T) through de_gemm.  a: bf16 [M,K] (or NHWC [B,H,W,Cin] with conv=(B,H,W,Cin));
+         pad=0, off=0, ldo=None, conv=None, pixel_shuffle=None, bias_mod=0, head=None, block_n=0, cta_group=0, debug=0, accumulate=False):
+    """out = epilogue(a @ w.T) through de_gemm (accumulate=True: out += ..., fp32 dense output only).  a: bf16 [M,K] (or NHWC [B,H,W,Cin] with conv=(B,H,W,Cin));
     w: bf16 [N,K].  See include/depth_b200.h for the epilogue contract."""
     _need_cuda(a, w, out, bias, add1, add2, out_relu)
     assert a.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and w.dim() == 2 and w.stride(1) == 1
@@ -183,6 +183,7 @@ def gemm(a: torch.Tensor, w: torch.Tensor, out: torch.Tensor, *, M=None, N=None,
     g.block_n = int(block_n)
     g.cta_group = int(cta_group)
     g.debug = int(debug)
+    g.accumulate = 1 if accumulate else 0
     _lib.check(_lib.load().de_gemm(C.byref(g), _stream()), "de_gemm")
     return out
 

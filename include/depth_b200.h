@@ -124,6 +124,10 @@ typedef struct DeGemm {
   int block_n; /* 0 = auto; else 32/64/128/256 */
   int debug;     /* 0 in production; perf experiments: bit0 skip epilogue body, bit1 skip global stores */
   int cta_group; /* 0 = auto; 1 = one CTA per 128-row tile; 2 = CTA pair per 256-row tile (block_n 256) */
+  int accumulate; /* 1: out += epilogue(A W^T) instead of out = ... (fp32 dense output, a_mode 0, bias + activation
+                   * only): the tile leaves through a TMA reduce-add, so the ViT residual stream x += proj(..) /
+                   * x += fc2(..) needs neither a bf16 branch buffer nor an add pass.  Each element receives exactly one
+                   * add per call - deterministic. */
 } DeGemm;
 int de_gemm(const DeGemm* g, void* stream);
 

@@ -165,6 +165,30 @@ def test_gemm_store_epilogue(M, N, K, cg, bn, act, f32):
     assert torch.equal(out, out2)
 
 
+@pytest.mark.parametrize("M,N,K,cg,bn", [(577, 1024, 1024, 0, 0), (18464, 1024, 1024, 2, 256), (1154, 768, 3072, 0, 0),
+                                         (333, 72, 136, 0, 0)])
+def test_gemm_accumulate(M, N, K, cg, bn):
+    """accumulate=True: x += A W^T + bias through the TMA reduce-add epilogue (the ViT residual stream update).  Exactly
+    one add per element: x0 + (store-epilogue result) bit for bit, twice in a row, and row tails stay untouched."""
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    a = _rand((M, K), dev, seed=90).bfloat16()
+    w = _rand((N, K), dev, 0.05, seed=91).bfloat16()
+    bias = _rand((N,), dev, seed=92)
+    x0 = _rand((M + 3, N), dev, seed=93)
+    y = torch.empty((M, N), dtype=torch.float32, device=dev)
+    ops.gemm(a, w, y, bias=bias, block_n=bn, cta_group=cg)
+    x = x0.clone()
+    ops.gemm(a, w, x[:M], bias=bias, block_n=bn, cta_group=cg, accumulate=True)
+    torch.cuda.synchronize()
+    assert torch.equal(x[:M], x0[:M] + y) and torch.equal(x[M:], x0[M:])
+    ops.gemm(a, w, x[:M], bias=bias, block_n=bn, cta_group=cg, accumulate=True)
+    torch.cuda.synchronize()
+    assert torch.equal(x[:M], (x0[:M] + y) + y)
+    with pytest.raises(RuntimeError):                      # bf16 output cannot accumulate
+        ops.gemm(a, w, torch.empty((M, N), dtype=torch.bfloat16, device=dev), bias=bias, accumulate=True)
+
+
 @pytest.mark.parametrize("f32", [True, False])
 def test_gemm_gelu_pointwise_accuracy(f32):
     """The epilogue's exp2-polynomial GELU against torch's erf GELU on every bf16 value in [-9, 9] (identity
