@@ -23,6 +23,10 @@ __host__ __device__ inline int same_pad_before(int in, int k, int s) {
 // ---------------------------------------------------------------- stem: NCHW bf16 (3 ch) -> NHWC bf16
 constexpr int kStemCo = 16;  // output channels per thread
 
+// Two adjacent output pixels x 16 output channels per thread: every weight float4 read from shared memory feeds
+// four packed FFMA2 (two channels each, both pixels) instead of four scalar FMAs of one pixel - half the shared-memory
+// reads and half the FMA-pipe instructions per MAC of the one-pixel version.
+// Accumulation order per output element is unchanged (bias, then taps in (ky, kx, c) order).
 __global__ void __launch_bounds__(128) stem_conv_kernel(const void* __restrict__ x, int x_f32,
                                                         const float* __restrict__ w,  // [Cout][k*k*3] (kh,kw,c)
                                                         const float* __restrict__ bias, void* __restrict__ out, int out_f32,
@@ -30,67 +34,89 @@ __global__ void __launch_bounds__(128) stem_conv_kernel(const void* __restrict__
                                                         int pad_y, int pad_x, int act) {
   extern __shared__ float s_w[];  // [k*k*3][Cout] transposed for broadcast float4 reads
   const int taps = k * k * 3;
+  // coalesced global reads (adjacent lanes -> adjacent taps of one filter), transposed on the way into smem.  Reading
+  // with adjacent lanes on adjacent FILTERS (588-byte stride: 32 lines per warp load, 73 dependent rounds) made this
+  // prologue ~20 us per CTA - most of the kernel's time at batch 1.
   for (int i = threadIdx.x; i < taps * Cout; i += blockDim.x) {
-    const int co = i % Cout, t = i / Cout;
-    s_w[i] = w[co * taps + t];
+    const int co = i / taps, t = i - co * taps;
+    s_w[t * Cout + co] = __ldg(w + i);
   }
   __syncthreads();
   const int cgs = Cout / kStemCo;
+  const int Wo2 = (Wo + 1) >> 1;
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= (long long)B * Ho * Wo * cgs) return;
-  // pixel-major thread order (adjacent threads -> adjacent ox) keeps the input reads coalesced
-  const int ox = static_cast<int>(idx % Wo);
-  long long t = idx / Wo;
+  if (idx >= (long long)B * Ho * Wo2 * cgs) return;
+  // pixel-major thread order (adjacent threads -> adjacent pixel pairs) keeps the input reads coalesced
+  const int ox0 = static_cast<int>(idx % Wo2) * 2;
+  long long t = idx / Wo2;
   const int oy = static_cast<int>(t % Ho);
   t /= Ho;
   const int cg = static_cast<int>(t % cgs);
   const int b = static_cast<int>(t / cgs);
-  float acc[kStemCo];
+  const bool two = ox0 + 1 < Wo;
+  float2 acc[2][kStemCo / 2];
 #pragma unroll
-  for (int j = 0; j < kStemCo; ++j) acc[j] = bias ? bias[cg * kStemCo + j] : 0.f;
+  for (int j = 0; j < kStemCo / 2; ++j) {
+    const float2 bv = bias ? make_float2(bias[cg * kStemCo + 2 * j], bias[cg * kStemCo + 2 * j + 1]) : make_float2(0.f, 0.f);
+    acc[0][j] = bv;
+    acc[1][j] = bv;
+  }
   const __nv_bfloat16* xb = reinterpret_cast<const __nv_bfloat16*>(x) + (long long)b * 3 * H * W;
   const float* xf = reinterpret_cast<const float*>(x) + (long long)b * 3 * H * W;
   for (int ky = 0; ky < k; ++ky) {
     const int iy = oy * stride + ky - pad_y;
     if (iy < 0 || iy >= H) continue;
     for (int kx = 0; kx < k; ++kx) {
-      const int ix = ox * stride + kx - pad_x;
-      if (ix < 0 || ix >= W) continue;
+      const int ix0 = ox0 * stride + kx - pad_x, ix1 = ix0 + stride;
+      const bool in0 = ix0 >= 0 && ix0 < W, in1 = two && ix1 >= 0 && ix1 < W;
+      if (!in0 && !in1) continue;
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
-        const long long e = ((long long)c * H + iy) * W + ix;
-        const float v = x_f32 ? __ldg(xf + e) : __bfloat162float(xb[e]);
+        const long long e = ((long long)c * H + iy) * W;
+        float v0 = 0.f, v1 = 0.f;
+        if (in0) v0 = x_f32 ? __ldg(xf + e + ix0) : __bfloat162float(xb[e + ix0]);
+        if (in1) v1 = x_f32 ? __ldg(xf + e + ix1) : __bfloat162float(xb[e + ix1]);
         const float4* wp = reinterpret_cast<const float4*>(s_w + ((ky * k + kx) * 3 + c) * Cout + cg * kStemCo);
+        const float2 p0 = make_float2(v0, v0), p1 = make_float2(v1, v1);
+        // a pixel whose tap falls into the padding must skip the tap (x + 0*w would still be exact, but keeps -0 / NaN
+        // semantics identical to the one-pixel kernel only if skipped)
 #pragma unroll
         for (int j4 = 0; j4 < kStemCo / 4; ++j4) {
           const float4 ww = wp[j4];
-          acc[j4 * 4 + 0] = fmaf(v, ww.x, acc[j4 * 4 + 0]);
-          acc[j4 * 4 + 1] = fmaf(v, ww.y, acc[j4 * 4 + 1]);
-          acc[j4 * 4 + 2] = fmaf(v, ww.z, acc[j4 * 4 + 2]);
-          acc[j4 * 4 + 3] = fmaf(v, ww.w, acc[j4 * 4 + 3]);
+          if (in0) {
+            acc[0][2 * j4] = ffma2(p0, make_float2(ww.x, ww.y), acc[0][2 * j4]);
+            acc[0][2 * j4 + 1] = ffma2(p0, make_float2(ww.z, ww.w), acc[0][2 * j4 + 1]);
+          }
+          if (in1) {
+            acc[1][2 * j4] = ffma2(p1, make_float2(ww.x, ww.y), acc[1][2 * j4]);
+            acc[1][2 * j4 + 1] = ffma2(p1, make_float2(ww.z, ww.w), acc[1][2 * j4 + 1]);
+          }
         }
       }
     }
   }
-  uint32_t o[kStemCo / 2];
 #pragma unroll
-  for (int j = 0; j < kStemCo / 2; ++j) {
-    float a = acc[2 * j], c = acc[2 * j + 1];
-    if (act == DE_ACT_RELU6) { a = fminf(fmaxf(a, 0.f), 6.f); c = fminf(fmaxf(c, 0.f), 6.f); }
-    else if (act == DE_ACT_RELU) { a = fmaxf(a, 0.f); c = fmaxf(c, 0.f); }
-    acc[2 * j] = a;
-    acc[2 * j + 1] = c;
-    o[j] = pack_bf16(a, c);
-  }
-  const long long e = (((long long)b * Ho + oy) * Wo + ox) * Cout + cg * kStemCo;
-  if (out_f32) {
-    float4* op = reinterpret_cast<float4*>(reinterpret_cast<float*>(out) + e);
+  for (int px = 0; px < 2; ++px) {
+    if (px == 1 && !two) break;
+    float r[kStemCo];
 #pragma unroll
-    for (int j4 = 0; j4 < kStemCo / 4; ++j4) op[j4] = make_float4(acc[j4 * 4], acc[j4 * 4 + 1], acc[j4 * 4 + 2], acc[j4 * 4 + 3]);
-  } else {
-    uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(out) + e);
-    op[0] = make_uint4(o[0], o[1], o[2], o[3]);
-    op[1] = make_uint4(o[4], o[5], o[6], o[7]);
+    for (int j = 0; j < kStemCo / 2; ++j) {
+      float a = acc[px][j].x, c = acc[px][j].y;
+      if (act == DE_ACT_RELU6) { a = fminf(fmaxf(a, 0.f), 6.f); c = fminf(fmaxf(c, 0.f), 6.f); }
+      else if (act == DE_ACT_RELU) { a = fmaxf(a, 0.f); c = fmaxf(c, 0.f); }
+      r[2 * j] = a;
+      r[2 * j + 1] = c;
+    }
+    const long long e = (((long long)b * Ho + oy) * Wo + ox0 + px) * Cout + cg * kStemCo;
+    if (out_f32) {
+      float4* op = reinterpret_cast<float4*>(reinterpret_cast<float*>(out) + e);
+#pragma unroll
+      for (int j4 = 0; j4 < kStemCo / 4; ++j4) op[j4] = make_float4(r[j4 * 4], r[j4 * 4 + 1], r[j4 * 4 + 2], r[j4 * 4 + 3]);
+    } else {
+      uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(out) + e);
+      op[0] = make_uint4(pack_bf16(r[0], r[1]), pack_bf16(r[2], r[3]), pack_bf16(r[4], r[5]), pack_bf16(r[6], r[7]));
+      op[1] = make_uint4(pack_bf16(r[8], r[9]), pack_bf16(r[10], r[11]), pack_bf16(r[12], r[13]), pack_bf16(r[14], r[15]));
+    }
   }
 }
 
@@ -208,7 +234,7 @@ extern "C" int de_stem_conv(const void* x_nchw, int x_dtype, const float* w, con
   if (!x_nchw || !w || !out_nhwc || Cout % kStemCo != 0 || k < 1 || k > 7)
     return fail(DE_ERR_INVALID, "de_stem_conv: bad args (Cout %% 16, k <= 7)");
   const int Ho = (H + stride - 1) / stride, Wo = (W + stride - 1) / stride;
-  const long long n = (long long)B * Ho * Wo * (Cout / kStemCo);
+  const long long n = (long long)B * Ho * ((Wo + 1) / 2) * (Cout / kStemCo);
   const size_t smem = sizeof(float) * k * k * 3 * Cout;
   stem_conv_kernel<<<(unsigned)((n + 127) / 128), 128, smem, reinterpret_cast<cudaStream_t>(stream)>>>(
       x_nchw, x_dtype == DE_DTYPE_F32, w, bias, out_nhwc, out_dtype == DE_DTYPE_F32, B, H, W, Cout, k, stride, Ho, Wo, same_pad_before(H, k, stride), same_pad_before(W, k, stride), act);
