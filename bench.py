@@ -206,7 +206,7 @@ def instrumented_step(est, frames_dev, B, H, W):
     wrap("head_up_conv", head_up_flops)
     wrap("attention", attn_flops)
     for n in ("preprocess", "postprocess", "layernorm", "cast_tokens", "fill_cls", "upsample2x",
-              "im2col3x3", "stem_conv", "depthwise", "maxpool3x3s2", "groupnorm"):
+              "im2col3x3", "stem_conv", "stem_im2col_split3", "depthwise", "maxpool3x3s2", "groupnorm"):
         if hasattr(ops, n):
             wrap(n)
     wrap("gemm", gemm_flops)

@@ -20,6 +20,8 @@ of this stage (12 % of the model); the ViT-B blocks and the decoder stay plain b
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from . import ops
@@ -57,6 +59,11 @@ class DPTHybridNet:
         bp = "pretrained.model.patch_embed.backbone."
         w = standardize_weight(sd[bp + "stem.conv.weight"].detach().to(dev, torch.float32))
         self.stem_w = w.permute(0, 2, 3, 1).reshape(64, 147).contiguous()
+        # the stem runs on the tensor cores at the stages' bf16x3 precision: split3 im2col rows x [Wh | Wl | Wh]
+        self.stem_kp = 152                                   # 147 taps padded to a multiple of 8
+        wp = torch.zeros((64, self.stem_kp), dtype=torch.float32, device=dev)
+        wp[:, :147] = self.stem_w
+        self.stem_w3 = split3_conv1x1(wp)
         self.stem_n = (sd[bp + "stem.norm.weight"].detach().to(dev, torch.float32).contiguous(),
                        sd[bp + "stem.norm.bias"].detach().to(dev, torch.float32).contiguous())
         self.stages = []
@@ -131,7 +138,12 @@ class DPTHybridNet:
         """x_nchw: fp32 [B,3,net_h,net_w] from K1 (layout 2).  Returns fp32 [B, net_h, net_w] (>= 0)."""
         H, W = (net_h + 1) // 2, (net_w + 1) // 2
         s0 = self._buf(("stem", B, H, W), (B, H, W, 64), torch.float32)
-        ops.stem_conv(x_nchw, self.stem_w, None, s0, 7, 2, ops.ACT_NONE)
+        if os.environ.get("DEB_STEM_DIRECT"):                # CUDA-core direct conv in fp32 (cross-check)
+            ops.stem_conv(x_nchw, self.stem_w, None, s0, 7, 2, ops.ACT_NONE)
+        else:
+            col = self._buf(("stemcol", B, H, W), (B * H * W, 3 * self.stem_kp))
+            ops.stem_im2col_split3(x_nchw, col, 7, 2, self.stem_kp)
+            ops.gemm(col, self.stem_w3, s0.view(-1, 64))
         s1 = self._buf(("stemn", B, H, W), (B, H, W, 64), torch.float32)
         ops.groupnorm(s0, self.stem_n[0], self.stem_n[1], None, self._ws, act=ops.ACT_RELU, out_f32=s1)
         Hp, Wp = (H + 1) // 2, (W + 1) // 2

@@ -279,6 +279,18 @@ def stem_conv(x_nchw: torch.Tensor, w: torch.Tensor, bias, out: torch.Tensor, k:
     return out
 
 
+def stem_im2col_split3(x_nchw: torch.Tensor, out: torch.Tensor, k: int, stride: int, kp: int):
+    """x: f32 NCHW [B,3,H,W] -> out bf16 [B*Ho*Wo, 3*kp] = [hi | hi | lo] im2col rows (TF-same padding), see depth_b200.h."""
+    _need_cuda(x_nchw, out)
+    B, _, H, W = x_nchw.shape
+    Ho, Wo = (H + stride - 1) // stride, (W + stride - 1) // stride
+    assert x_nchw.dtype == torch.float32 and x_nchw.is_contiguous() and out.dtype == torch.bfloat16 and out.is_contiguous()
+    assert out.numel() == B * Ho * Wo * 3 * kp
+    _lib.check(_lib.load().de_stem_im2col_split3(x_nchw.data_ptr(), out.data_ptr(), B, H, W, k, stride, kp, _stream()),
+               "de_stem_im2col_split3")
+    return out
+
+
 def head_conv(x: torch.Tensor, w: torch.Tensor, bias, head_w: torch.Tensor, head_b: float, out: torch.Tensor):
     """relu(head_b + head_w . relu(conv3x3(x, w) + bias)): x bf16 NHWC [B,H,W,Cin] (Cin % 64 == 0), w bf16 [32, 9*Cin]
     tap-major, out fp32 [B,H,W]."""

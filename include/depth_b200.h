@@ -197,6 +197,12 @@ int de_head_up_conv(const void* x, const void* w, int64_t ldw, const float* bias
  * folded), bias float[Cout] or NULL -> NHWC bf16 or f32 [B,ceil(H/s),ceil(W/s),Cout]. Cout % 16 == 0. */
 int de_stem_conv(const void* x_nchw, int x_dtype, const float* w, const float* bias, void* out_nhwc, int out_dtype,
                  int B, int H, int W, int Cout, int k, int stride, int act, void* stream);
+/* The same stem as a tensor-core GEMM operand: x NCHW f32 [B,3,H,W] -> bf16 [B*ceil(H/s)*ceil(W/s), 3*kp], row =
+ * [hi(kp) | hi(kp) | lo(kp)] of the TF-"same"-padded k x k x 3 window in (kh,kw,c) order (zero for columns >= 3*k*k;
+ * kp % 8 == 0), hi = bf16(v), lo = bf16(v - hi).  de_gemm against the filter bank packed [Wh | Wl | Wh] (each kp wide)
+ * gives the stem convolution at bf16x3 precision (DPT_Hybrid's StdConv 7x7/2; replaces timm
+ * ResNetV2.stem.conv inside the hub model of /root/reference/depth_midas.py:10). */
+int de_stem_im2col_split3(const float* x_nchw, void* out_bf16, int B, int H, int W, int k, int stride, int kp, void* stream);
 /* depthwise k in {3,5}: x NHWC bf16, w bf16 [k*k][C] (tap-major, BN folded), bias float[C]. */
 int de_depthwise(const void* x, const void* w_tapmajor, const float* bias, void* out, int B, int H, int W, int C,
                  int k, int stride, int act, void* stream);

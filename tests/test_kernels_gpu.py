@@ -683,6 +683,35 @@ def test_stem_conv_f32():
     assert _relerr(out, ref) < 1e-5
 
 
+@pytest.mark.parametrize("B,H,W", [(2, 96, 130), (1, 384, 384), (3, 33, 47)])
+def test_stem_im2col_split3_gemm(B, H, W):
+    """DPT_Hybrid's 7x7/2 TF-same stem as split3 im2col rows x [Wh | Wl | Wh] on the bf16 GEMM: bf16x3 precision
+    against fp64, identical rows to a torch unfold of the padded input, zero padding columns."""
+    from depth_estimation_b200 import ops
+    from depth_estimation_b200.weights import split3_conv1x1
+    dev = _dev()
+    k, s, Cout, kp = 7, 2, 64, 152
+    x = _rand((B, 3, H, W), dev, seed=71)
+    w = _rand((Cout, 3, k, k), dev, 0.1, seed=72)
+    Ho, Wo = (H + 1) // 2, (W + 1) // 2
+    col = torch.full((B * Ho * Wo, 3 * kp), float("nan"), dtype=torch.bfloat16, device=dev)
+    ops.stem_im2col_split3(x, col, k, s, kp)
+    torch.cuda.synchronize()
+    # rows: (kh, kw, c) order of the padded window
+    unf = F.unfold(_tf_same_pad(x, k, s), k, stride=s).view(B, 3, k * k, Ho * Wo).permute(0, 3, 2, 1).reshape(B * Ho * Wo, 147)
+    hi = unf.bfloat16()
+    lo = (unf - hi.float()).bfloat16()
+    assert torch.equal(col[:, :147], hi) and torch.equal(col[:, kp:kp + 147], hi) and torch.equal(col[:, 2 * kp:2 * kp + 147], lo)
+    assert (col[:, 147:kp] == 0).all() and (col[:, kp + 147:2 * kp] == 0).all() and (col[:, 2 * kp + 147:] == 0).all()
+    wp = torch.zeros((Cout, kp), dtype=torch.float32, device=dev)
+    wp[:, :147] = w.permute(0, 2, 3, 1).reshape(Cout, -1)
+    out = torch.empty((B * Ho * Wo, Cout), dtype=torch.float32, device=dev)
+    ops.gemm(col, split3_conv1x1(wp), out)
+    ref = F.conv2d(_tf_same_pad(x.double(), k, s), w.double(), None, stride=s).permute(0, 2, 3, 1).reshape(-1, Cout)
+    torch.cuda.synchronize()
+    assert _relerr(out, ref) < 3e-5, _relerr(out, ref)
+
+
 @pytest.mark.parametrize("conv", [False, True])
 def test_split3_gemm_precision(conv):
     """Activations [Ah | Ah | Al] x weights [Wh | Wl | Wh] on the unchanged bf16 GEMM / implicit 3x3 conv: the result
