@@ -53,6 +53,11 @@ struct GemmParams {
 //        with TMA stores (no per-row address math, no LSU store traffic).
 // EPI 1: "general" epilogue - residual adds, row remaps, pixel shuffle, dual store, head dot.
 constexpr int kStoreBufBytes = BM * 128;                        // one 128-row x 128-byte output unit
+// staging buffers per epilogue group.  2 lets a group fill one unit while the TMA engine still reads the previous one,
+// but costs a pipeline stage (6 -> 5 at 256-wide tiles): measured 1753 against 1778 frames/s on the DPT_Large step, so 1.
+#ifndef STORE_BUFS_PER_GROUP
+#define STORE_BUFS_PER_GROUP 1
+#endif
 template <int BN, int CG, int EPI>
 struct Cfg {
   static constexpr int kABytes = BM * BK * 2;
@@ -61,8 +66,9 @@ struct Cfg {
   static constexpr int kStageBytes = kABytes + kBBytes;
   // after the stage ring - EPI 0: two 1024-aligned store buffers, mbarriers (256 B), bias slice (BN floats);
   //                        EPI 1: mbarriers (256 B), per-warp staging areas.
-  static constexpr int kBarOff = EPI == 0 ? 2 * kStoreBufBytes : 0;           // relative to the end of the ring
-  static constexpr int kPostBytes = EPI == 0 ? 2 * kStoreBufBytes + 256 + 1024 : 256 + kEpiWarps * kEpiWarpBytes;
+  static constexpr int kStoreBufs = EPI == 0 ? 2 * STORE_BUFS_PER_GROUP : 0;  // per epilogue group: STORE_BUFS_PER_GROUP
+  static constexpr int kBarOff = kStoreBufs * kStoreBufBytes;                 // relative to the end of the ring
+  static constexpr int kPostBytes = EPI == 0 ? kStoreBufs * kStoreBufBytes + 256 + 1024 : 256 + kEpiWarps * kEpiWarpBytes;
   static constexpr int kStagesRaw = (kSmemLimit - 1024 - kPostBytes) / kStageBytes;
   static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
   static constexpr int kTmemCols = (2 * BN) < 32 ? 32 : 2 * BN;
@@ -265,7 +271,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const bool f32out = p.out_dtype == DE_DTYPE_F32;
     const int ucols = f32out ? 32 : 64;                        // columns per 128-byte unit
     const int units = BN / ucols;
-    uint8_t* sbuf = post + grp * kStoreBufBytes;
+    uint8_t* const sbuf0 = post + grp * (STORE_BUFS_PER_GROUP * kStoreBufBytes);
+    int sb = 0;                                                // staging buffer of the next unit
     float* s_bias = reinterpret_cast<float*>(post + C::kBarOff + 256);
     const int bias_mod = p.bias_mod > 0 ? p.bias_mod : p.N;
     int as = 0;
@@ -358,7 +365,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             else mbar_arrive(&tempty[as]);
           }
         }
-        if (pending && gtid == 0) tma_store_wait_read<0>();    // previous store has finished reading sbuf
+        // the store that last used this buffer (STORE_BUFS_PER_GROUP units ago) has finished reading it
+        if (pending && gtid == 0) tma_store_wait_read<STORE_BUFS_PER_GROUP - 1>();
+        uint8_t* const sbuf = sbuf0 + sb * kStoreBufBytes;
+        sb = sb + 1 == STORE_BUFS_PER_GROUP ? 0 : sb + 1;
         named_bar_sync(bar_id, 128);
         uint8_t* rowp = sbuf + gtid * 128;
 #pragma unroll
@@ -367,12 +377,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               make_uint4(ov[j * 4], ov[j * 4 + 1], ov[j * 4 + 2], ov[j * 4 + 3]);
         fence_proxy_async_smem();
         named_bar_sync(bar_id, 128);
-        if (gtid == 0 && m_tile < p.m_tiles && !(p.debug & 2)) {
-          const int col0 = n_tile * BN + u * ucols;
-          if (p.accumulate) tma_reduce_add_2d(&tmC, sbuf, col0, m_tile * BM);
-          else if (p.a_mode == 0) tma_store_2d(&tmC, sbuf, col0, m_tile * BM);
-          else tma_store_4d(&tmC, sbuf, col0, x0, y0, b);
-          tma_store_commit();
+        if (gtid == 0) {
+          if (m_tile < p.m_tiles && !(p.debug & 2)) {
+            const int col0 = n_tile * BN + u * ucols;
+            if (p.accumulate) tma_reduce_add_2d(&tmC, sbuf, col0, m_tile * BM);
+            else if (p.a_mode == 0) tma_store_2d(&tmC, sbuf, col0, m_tile * BM);
+            else tma_store_4d(&tmC, sbuf, col0, x0, y0, b);
+          }
+          tma_store_commit();            // one (possibly empty) group per unit: wait_read<N> counts units, not stores
         }
         pending = true;
       }

@@ -9,6 +9,9 @@ is no CPU fallback: without a CUDA device or the built library the constructor r
 """
 from __future__ import annotations
 
+import os
+from concurrent.futures import ThreadPoolExecutor
+
 import numpy as np
 import torch
 
@@ -161,11 +164,19 @@ class DepthEstimator(object):
         transfers of batch i+1 / i-1 overlap the kernels of batch i.  Every frame still crosses the host
         boundary in both directions; only the serialisation point of depth_midas.py:23,34 is gone."""
         depth = max(1, int(depth))
-        pending = []                                  # (slot, event_out)
+        pending = []                                  # (slot, future -> the slot's D2H-done event)
         pipe = None
         idx = 0
+        last = None
+        it = iter(batches)
         with torch.cuda.device(self.device):
-            for frames in batches:
+            while True:
+                if last is not None:
+                    last.result()                     # previous batch staged and enqueued: its source array is free again
+                try:
+                    frames = next(it)
+                except StopIteration:
+                    break
                 frames = np.ascontiguousarray(frames)
                 if frames.ndim != 4 or frames.shape[3] != 3 or frames.dtype != np.uint8:
                     raise TypeError("predict_stream expects uint8 [B,H,W,3] BGR batches")
@@ -176,11 +187,15 @@ class DepthEstimator(object):
                     if pipe is None:
                         pipe = _Pipeline(self, frames.shape, depth)
                         self._pipes[(frames.shape, depth)] = pipe
-                if len(pending) == depth:
-                    yield pipe.collect(*pending.pop(0))
-                slot = idx % depth
-                pending.append((slot, pipe.submit(slot, frames)))
+                    idx = 0
+                # depth + 1 slots: the batch collected below (idx - depth) and the one being staged (idx) never share
+                # buffers, so the host copy into pinned memory (worker thread) overlaps the copy out of it (this thread)
+                slot = idx % pipe.nslots
+                last = pipe.submit_async(slot, frames)
+                pending.append((slot, last))
                 idx += 1
+                if len(pending) > depth:
+                    yield pipe.collect(*pending.pop(0))
             while pending:
                 yield pipe.collect(*pending.pop(0))
 
@@ -314,12 +329,16 @@ class _Pipeline:
         self.est, self.shape, self.depth = est, tuple(shape), depth
         B, H, W, _ = shape
         dev = est.device
-        self.plans = [_Plan(est, B, H, W, 0, False) for _ in range(depth)]
+        self.nslots = n = depth + 1
+        self.plans = [_Plan(est, B, H, W, 0, False) for _ in range(n)]
         self.s_in, self.s_compute, self.s_out = (torch.cuda.Stream(dev) for _ in range(3))
-        self.ev_in = [torch.cuda.Event() for _ in range(depth)]
-        self.ev_done = [torch.cuda.Event() for _ in range(depth)]
-        self.ev_out = [torch.cuda.Event() for _ in range(depth)]
-        self.graphs = [None] * depth
+        self.ev_in = [torch.cuda.Event() for _ in range(n)]
+        self.ev_done = [torch.cuda.Event() for _ in range(n)]
+        self.ev_out = [torch.cuda.Event() for _ in range(n)]
+        self.graphs = [None] * n
+        # one worker thread stages frames into pinned memory and enqueues the slot's work (numpy's memcpy releases the
+        # GIL); DEB_STAGE_THREAD=0 runs it inline
+        self._pool = None if os.environ.get("DEB_STAGE_THREAD") == "0" else ThreadPoolExecutor(1, "deb-stage")
         cur = torch.cuda.current_stream(dev)
         self.s_compute.wait_stream(cur)
         with torch.cuda.stream(self.s_compute):
@@ -335,6 +354,16 @@ class _Pipeline:
                 self.graphs[i] = g
         for e in self.ev_done + self.ev_out:                    # so the first waits are no-ops
             e.record(self.s_compute)
+
+    def submit_async(self, slot, frames):
+        """Future of submit(slot, frames) (already completed when the worker thread is disabled)."""
+        if self._pool is not None:
+            return self._pool.submit(self._submit_on_device, slot, frames)
+        return _Done(self.submit(slot, frames))
+
+    def _submit_on_device(self, slot, frames):
+        with torch.cuda.device(self.est.device):
+            return self.submit(slot, frames)
 
     def submit(self, slot, frames):
         p = self.plans[slot]
@@ -358,9 +387,19 @@ class _Pipeline:
             self.ev_out[slot].record()
         return self.ev_out[slot]
 
-    def collect(self, slot, ev):
-        ev.synchronize()
+    def collect(self, slot, fut):
+        fut.result().synchronize()                              # enqueued (worker exceptions surface here), then D2H done
         return self.plans[slot].h_map.numpy().copy()
+
+
+class _Done:
+    """A completed future (inline staging)."""
+
+    def __init__(self, value):
+        self._value = value
+
+    def result(self):
+        return self._value
 
 
 def _build_net(model_type, sd, device):
