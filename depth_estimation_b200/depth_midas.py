@@ -337,8 +337,12 @@ class _Pipeline:
         self.ev_out = [torch.cuda.Event() for _ in range(n)]
         self.graphs = [None] * n
         # one worker thread stages frames into pinned memory and enqueues the slot's work (numpy's memcpy releases the
-        # GIL); DEB_STAGE_THREAD=0 runs it inline
-        self._pool = None if os.environ.get("DEB_STAGE_THREAD") == "0" else ThreadPoolExecutor(1, "deb-stage")
+        # GIL).  Worth it when the copies are long: MiDaS_small at 720p (88 MB in, 118 MB out per 32 frames) goes from
+        # 990 to 1235 frames/s end to end; at 14 MB per batch (DPT_Large 384^2) the hand-off costs more than it hides,
+        # so small batches are staged inline.  DEB_STAGE_THREAD=0 / 1 forces either.
+        mode = os.environ.get("DEB_STAGE_THREAD")
+        threaded = mode == "1" or (mode != "0" and B * H * W * 3 >= (32 << 20))
+        self._pool = ThreadPoolExecutor(1, "deb-stage") if threaded else None
         cur = torch.cuda.current_stream(dev)
         self.s_compute.wait_stream(cur)
         with torch.cuda.stream(self.s_compute):
