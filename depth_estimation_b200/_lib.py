@@ -31,7 +31,7 @@ class DeGemm(C.Structure):
         ("out_rowmode", C.c_int), ("grp", C.c_int), ("pad", C.c_int), ("off", C.c_int),
         ("ps_gh", C.c_int), ("ps_gw", C.c_int), ("ps_s", C.c_int), ("ps_cout", C.c_int),
         ("head_w", C.c_void_p), ("head_b", C.c_float),
-        ("block_n", C.c_int), ("debug", C.c_int), ("cta_group", C.c_int), ("accumulate", C.c_int),
+        ("block_n", C.c_int), ("epilogue", C.c_int), ("cta_group", C.c_int), ("accumulate", C.c_int),
     ]
 
 
@@ -54,13 +54,13 @@ SIGNATURES = {
     "de_layernorm": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                C.c_float, C.c_void_p, C.c_int64, C.c_void_p]),
     "de_attention": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_void_p]),
-    "de_attention_mma": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_void_p]),
     "de_cast_tokens": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "de_fill_cls": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "de_upsample2x": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "de_im2col3x3": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                C.c_int, C.c_int, C.c_void_p]),
     "de_subsample": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "de_groupnorm_ws_bytes": (C.c_int64, [C.c_int, C.c_int, C.c_int, C.c_int]),
     "de_groupnorm": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int,
                                C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int,
                                C.c_void_p, C.c_int64, C.c_void_p]),

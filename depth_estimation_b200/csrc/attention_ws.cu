@@ -436,21 +436,10 @@ attention_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const WsParams p)
 
 }  // namespace deb
 
-// attention_tc.cu (first tcgen05 kernel, two CTAs per SM) and attention.cu (mma.sync) stay as cross-checks
-extern "C" int de_attention_v1(const void* qkv, void* out, int B, int T, int heads, float scale, void* stream);
-extern "C" int de_attention_mma(const void* qkv, void* out, int B, int T, int heads, float scale, void* stream);
-
 extern "C" int de_attention(const void* qkv, void* out, int B, int T, int heads, float scale, void* stream) {
   using namespace deb;
   if (!qkv || !out || B <= 0 || T <= 0 || heads <= 0) return fail(DE_ERR_INVALID, "de_attention: bad args");
   if (!(scale > 0.f)) return fail(DE_ERR_INVALID, "de_attention: scale must be positive");
-  static int impl = -1;
-  if (impl < 0) {
-    const char* e = getenv("DEB_ATTENTION");
-    impl = !e ? 0 : (e[0] == 'm' ? 2 : (e[0] == '1' ? 1 : 0));
-  }
-  if (impl == 2) return de_attention_mma(qkv, out, B, T, heads, scale, stream);
-  if (impl == 1) return de_attention_v1(qkv, out, B, T, heads, scale, stream);
   auto fn = get_tensor_map_encoder();
   if (!fn) return DE_ERR_CUDA;
   CUtensorMap tm;
@@ -462,11 +451,10 @@ extern "C" int de_attention(const void* qkv, void* out, int B, int T, int heads,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(DE_ERR_CUDA, "de_attention: cuTensorMapEncodeTiled failed (%d)", (int)r);
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(attention_ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWsSmem);
+  static SmemOptIn optin;
+  {
+    cudaError_t e = ensure_smem(optin, attention_ws_kernel, (int)kWsSmem);
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(attention_ws)");
-    attr_set = true;
   }
   WsParams p{};
   p.out = reinterpret_cast<__nv_bfloat16*>(out);

@@ -45,7 +45,6 @@ struct GemmParams {
   int ps_gh, ps_gw, ps_s, ps_cout;
   const float* head_w;
   float head_b;
-  int debug;  // bit0: skip epilogue body (perf experiments only), bit1: skip global stores
   int accumulate;  // store epilogue only: TMA reduce-add instead of store
 };
 
@@ -378,7 +377,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         fence_proxy_async_smem();
         named_bar_sync(bar_id, 128);
         if (gtid == 0) {
-          if (m_tile < p.m_tiles && !(p.debug & 2)) {
+          if (m_tile < p.m_tiles) {
             const int col0 = n_tile * BN + u * ucols;
             if (p.accumulate) tma_reduce_add_2d(&tmC, sbuf, col0, m_tile * BM);
             else if (p.a_mode == 0) tma_store_2d(&tmC, sbuf, col0, m_tile * BM);
@@ -483,7 +482,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                           __uint_as_float(acc[j4 * 4 + 2]), __uint_as_float(acc[j4 * 4 + 3]));
         __syncwarp();
         const int n0 = n_tile * BN + c * 32;
-        if (n0 >= p.N || (p.debug & 1)) continue;
+        if (n0 >= p.N) continue;
         const bool col_ok = cc < p.N - n0;       // N % 8 == 0 and cc % 4 == 0: whole float4 in or out
         long long colpart = n0 + cc;
         if (p.out_rowmode == 2) {
@@ -534,7 +533,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             if ((lane & 7) == 0 && hro >= 0) reinterpret_cast<float*>(p.out)[hro] = fmaxf(d + p.head_b, 0.f);
             continue;
           }
-          if (ro < 0 || (p.debug & 2)) continue;
+          if (ro < 0) continue;
           const long long o = ro + colpart;
           v.x += bf16_lo(a2_[i].x); v.y += bf16_hi(a2_[i].x); v.z += bf16_lo(a2_[i].y); v.w += bf16_hi(a2_[i].y);
           if (p.out_dtype == DE_DTYPE_F32) {
@@ -617,12 +616,10 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMa
                   cudaStream_t st) {
   using C = Cfg<BN, CG, EPI>;
   static_assert(C::kStages >= 2, "smem budget leaves too few pipeline stages");
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_kernel<BN, CG, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         C::kSmemBytes);
+  static SmemOptIn optin;
+  {
+    cudaError_t e = ensure_smem(optin, gemm_kernel<BN, CG, EPI>, (int)C::kSmemBytes);
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(gemm)");
-    attr_set = true;
   }
   const int tiles = ((p.m_tiles + CG - 1) / CG) * p.n_tiles;
   int units = num_sms() / CG;
@@ -730,14 +727,13 @@ extern "C" int de_gemm(const DeGemm* g, void* stream) {
   p.ps_gh = g->ps_gh; p.ps_gw = g->ps_gw; p.ps_s = g->ps_s; p.ps_cout = g->ps_cout > 0 ? g->ps_cout : 1;
   p.head_w = g->head_w;
   p.head_b = g->head_b;
-  p.debug = g->debug;
   p.accumulate = g->accumulate;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   // epilogue flavour: the TMA-store epilogue covers "bias + activation -> dense output"
   const int es = g->out_dtype == DE_DTYPE_F32 ? 4 : 2;
   bool store_epi = !g->add1 && !g->add2 && !g->out_relu && !g->head_w && g->out_rowmode == 0 && bn >= 64 &&
                    (g->ldo * es) % 16 == 0 && (reinterpret_cast<uintptr_t>(g->out) & 15) == 0 &&
-                   (g->a_mode == 0 || g->ldo == g->N) && !(g->debug & 4);
+                   (g->a_mode == 0 || g->ldo == g->N) && g->epilogue != 1;
   if (g->accumulate && (!store_epi || g->a_mode != 0 || g->out_dtype != DE_DTYPE_F32))
     return fail(DE_ERR_INVALID, "de_gemm: accumulate needs the dense fp32 store epilogue (a_mode 0, no add1/add2/out_relu/row maps)");
   CUtensorMap tc = tb;

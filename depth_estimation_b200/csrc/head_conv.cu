@@ -553,11 +553,10 @@ extern "C" int de_head_conv(const void* x, const void* w, int64_t ldw, const flo
     const uint32_t box[2] = {64, kHcN};
     if (!hc_make_map(&tw, w, 2, dims, strides, box)) return DE_ERR_CUDA;
   }
-  static int attr_smem = 0;
-  if (attr_smem < smem_bytes) {
-    cudaError_t e = cudaFuncSetAttribute(head_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+  static SmemOptIn optin;
+  {
+    cudaError_t e = ensure_smem(optin, head_conv_kernel, smem_bytes);
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(head_conv)");
-    attr_smem = smem_bytes;
   }
   int grid = num_sms();
   if (p.num_tiles < grid) grid = p.num_tiles;
@@ -603,11 +602,10 @@ extern "C" int de_head_up_conv(const void* x, const void* w, int64_t ldw, const 
     const uint32_t box[2] = {64, kHcN};
     if (!hc_make_map(&tw, w, 2, dims, strides, box)) return DE_ERR_CUDA;
   }
-  static int attr_smem = 0;
-  if (attr_smem < smem_bytes) {
-    cudaError_t e = cudaFuncSetAttribute(head_up_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+  static SmemOptIn optin;
+  {
+    cudaError_t e = ensure_smem(optin, head_up_conv_kernel, smem_bytes);
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(head_up_conv)");
-    attr_smem = smem_bytes;
   }
   int grid = num_sms();
   if (p.num_tiles < grid) grid = p.num_tiles;

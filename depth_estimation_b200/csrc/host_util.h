@@ -22,6 +22,22 @@ typedef CUresult (*TensorMapEncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cu
                                            CUtensorMapFloatOOBfill);
 TensorMapEncodeTiledFn get_tensor_map_encoder();
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is a PER-DEVICE setting: remember, per kernel and device, the largest
+// opt-in made so far (one static SmemOptIn per kernel instantiation).
+struct SmemOptIn {
+  int bytes[32] = {0};
+};
+template <typename K>
+inline cudaError_t ensure_smem(SmemOptIn& s, K kernel, int bytes) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const bool cached = dev >= 0 && dev < 32;
+  if (cached && s.bytes[dev] >= bytes) return cudaSuccess;
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess && cached) s.bytes[dev] = bytes;
+  return e;
+}
+
 // Launch with programmatic stream serialization (see common.cuh pdl_wait / pdl_launch).  Only for kernels that call
 // pdl_wait() before their first global-memory access.
 template <typename... KArgs, typename... Args>

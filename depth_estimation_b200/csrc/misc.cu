@@ -487,28 +487,46 @@ extern "C" int de_subsample(const void* x, void* out, int B, int H, int W, int C
   return cuda_check_launch("subsample_kernel");
 }
 
+// Workspace layout of de_groupnorm: [arrival counters: kGnCounterBytes | stats float2[B*groups] (16-aligned) | partials]
+static const int64_t kGnCounterBytes = 16384;          // 4096 samples per call
+struct GnLayout {
+  int px_per_block, nblocks;
+  int64_t stats_bytes, total;
+};
+static GnLayout gn_layout(int B, int HW, int C, int groups) {
+  GnLayout L;
+  L.px_per_block = (HW + 147) / 148;      // enough blocks to fill the GPU even at B=1
+  const int lanes = 256 / (C / 8);
+  if (L.px_per_block < lanes * 4) L.px_per_block = lanes * 4;
+  L.nblocks = (HW + L.px_per_block - 1) / L.px_per_block;
+  L.stats_bytes = (((int64_t)sizeof(float2) * B * groups + 15) / 16) * 16;
+  L.total = kGnCounterBytes + L.stats_bytes + (int64_t)sizeof(double) * 2 * B * L.nblocks * groups;
+  return L;
+}
+extern "C" int64_t de_groupnorm_ws_bytes(int B, int HW, int C, int groups) {
+  if (B <= 0 || HW <= 0 || C < 8 || C % 8 != 0 || groups < 1 || 256 % (C / 8) != 0) return 0;
+  return gn_layout(B, HW, C, groups).total;
+}
+
 extern "C" int de_groupnorm(const void* x, int x_dtype, const float* gamma, const float* beta, const void* add,
                             int add_dtype, void* out, int out_mode, float* out_f32, void* out_plain, int B, int HW, int C,
                             int groups, float eps, int act, void* ws, int64_t ws_bytes, void* stream) {
   if (!x || !gamma || !beta || !ws || (!out && !out_f32 && !out_plain)) return fail(DE_ERR_INVALID, "de_groupnorm: null pointer");
   if (C % 8 != 0 || C > 2048 || groups > 64 || groups < 1 || C % groups != 0 || 256 % (C / 8) != 0)
     return fail(DE_ERR_UNSUPPORTED, "de_groupnorm: C=%d groups=%d unsupported", C, groups);
+  if (B < 1 || (int64_t)B * 4 > kGnCounterBytes) return fail(DE_ERR_UNSUPPORTED, "de_groupnorm: B=%d (1..4096)", B);
   if ((x_dtype != DE_DTYPE_BF16 && x_dtype != DE_DTYPE_F32) || out_mode < 0 || out_mode > 1)
     return fail(DE_ERR_INVALID, "de_groupnorm: x_dtype %d / out_mode %d", x_dtype, out_mode);
   const int x_f32 = x_dtype == DE_DTYPE_F32;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  int px_per_block = (HW + 147) / 148;      // enough blocks to fill the GPU even at B=1
-  const int lanes = 256 / (C / 8);
-  if (px_per_block < lanes * 4) px_per_block = lanes * 4;
-  const int nblocks = (HW + px_per_block - 1) / px_per_block;
-  const int64_t stats_bytes = (int64_t)sizeof(float2) * B * groups;
-  const int64_t partial_bytes = (int64_t)sizeof(double) * 2 * B * nblocks * groups;
-  const int64_t need = stats_bytes + partial_bytes + 16 + (int64_t)sizeof(unsigned) * B;
-  if (ws_bytes < need) return fail(DE_ERR_INVALID, "de_groupnorm: workspace %lld < %lld bytes", (long long)ws_bytes, (long long)need);
-  float2* stats = reinterpret_cast<float2*>(ws);
-  double* partial = reinterpret_cast<double*>(reinterpret_cast<char*>(ws) + ((stats_bytes + 15) / 16) * 16);
-  // arrival counters live in the LAST 4*B bytes of the workspace (zero before the first call, zero after every call)
-  unsigned* counters = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(ws) + ((ws_bytes - (int64_t)sizeof(unsigned) * B) & ~3LL));
+  GnLayout L = gn_layout(B, HW, C, groups);
+  if (ws_bytes < L.total) return fail(DE_ERR_INVALID, "de_groupnorm: workspace %lld < %lld bytes (de_groupnorm_ws_bytes)", (long long)ws_bytes, (long long)L.total);
+  const int px_per_block = L.px_per_block, nblocks = L.nblocks;
+  // arrival counters at a FIXED offset (the first kGnCounterBytes of the workspace; zero before the first call, zero
+  // after every call), so calls with different B / HW can share a workspace without a counter ever aliasing a partial
+  unsigned* counters = reinterpret_cast<unsigned*>(ws);
+  float2* stats = reinterpret_cast<float2*>(reinterpret_cast<char*>(ws) + kGnCounterBytes);
+  double* partial = reinterpret_cast<double*>(reinterpret_cast<char*>(ws) + kGnCounterBytes + L.stats_bytes);
   dim3 grid(nblocks, B);
   groupnorm_partial_kernel<<<grid, 256, 0, st>>>(x, x_f32, HW, C, groups, px_per_block, partial, counters, stats,
                                                  (double)HW * (C / groups), eps);

@@ -401,12 +401,9 @@ static int run_preprocess(const uint8_t* bgr, const uint8_t* uv, int64_t uv_row_
   p.max_rows = ty->max_extent(p.TH);
   const size_t smem = (size_t)p.max_rows * 3 * kPreTW * sizeof(float);
   {
-    static bool configured = false;
-    if (!configured) {
-      cudaError_t e = cudaFuncSetAttribute(preprocess_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PRE_SMEM_KB * 1024);
-      if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(preprocess)");
-      configured = true;
-    }
+    static SmemOptIn optin;
+    cudaError_t e = ensure_smem(optin, preprocess_kernel, PRE_SMEM_KB * 1024);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(preprocess)");
   }
   dim3 grid((net_w + kPreTW - 1) / kPreTW, (net_h + p.TH - 1) / p.TH, B);
   preprocess_kernel<<<grid, kPreThreads, smem, st>>>(p);

@@ -58,8 +58,10 @@ class ScratchDecoder:
         self._bufs = {}
 
     def _buf(self, key, shape, dtype=torch.bfloat16):
+        # keyed on (name, shape, dtype): a buffer whose address is baked into a captured CUDA graph is never replaced
+        key = (key, tuple(shape), dtype)
         t = self._bufs.get(key)
-        if t is None or tuple(t.shape) != tuple(shape) or t.dtype != dtype:
+        if t is None:
             t = torch.empty(shape, dtype=dtype, device=self.dev)
             self._bufs[key] = t
         return t

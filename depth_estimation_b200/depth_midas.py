@@ -23,15 +23,21 @@ _DPT_NORM = ((0.5, 0.5, 0.5), (0.5, 0.5, 0.5))
 _IMAGENET_NORM = ((0.485, 0.456, 0.406), (0.229, 0.224, 0.225))
 
 
+# [UPSTREAM] hubconf.transforms(): name -> (target, Resize method for de_get_size, normalisation)
+_TRANSFORM_SPECS = {"default_transform": (384, 0, _IMAGENET_NORM), "small_transform": (256, 0, _IMAGENET_NORM),
+                    "dpt_transform": (384, 1, _DPT_NORM)}
+
+
 class _Transforms:
-    """Stand-in for the hub ``transforms`` namespace (depth_midas.py:12-16): the callables run K1 and
-    return the network input on the device (NCHW bf16 [1,3,h,w])."""
+    """Stand-in for the hub ``transforms`` namespace (depth_midas.py:12-16).  Each callable takes the RGB frame the
+    reference passes (:22-23), runs K1 and returns what the hub transform returns - a float32 [1,3,h,w] tensor - except
+    that it already lives on the estimator's device (the reference's `.to(self.device)` at :23 is then a no-op)."""
 
     def __init__(self, owner):
         self._o = owner
-        self.dpt_transform = lambda rgb: owner._transform_rgb(rgb, "DPT_Large")
-        self.small_transform = lambda rgb: owner._transform_rgb(rgb, "MiDaS_small")
-        self.default_transform = self.small_transform
+        self.dpt_transform = lambda rgb: owner._transform_rgb(rgb, "dpt_transform")
+        self.small_transform = lambda rgb: owner._transform_rgb(rgb, "small_transform")
+        self.default_transform = lambda rgb: owner._transform_rgb(rgb, "default_transform")
 
 
 class DepthEstimator(object):
@@ -147,7 +153,8 @@ class DepthEstimator(object):
         the kernels one by one instead of replaying the captured graph (profiling / per-kernel timing)."""
         B, H, W, _ = frames_u8.shape
         plan = self._plan(B, H, W, 0, False)
-        return plan.run_device(frames_u8, eager)
+        with torch.cuda.device(self.device):
+            return plan.run_device(frames_u8, eager)
 
     def kernel_launches(self) -> int:
         """Kernels of libdepthb200.so this process has put on the GPU so far: direct launches (counted by the
@@ -200,15 +207,15 @@ class DepthEstimator(object):
                 yield pipe.collect(*pending.pop(0))
 
     # ------------------------------------------------------------------ internals
-    def _transform_rgb(self, rgb, mt):
+    def _transform_rgb(self, rgb, name):
         """Reference-style transform(img): takes the RGB frame the reference passes (:22-23)."""
         bgr = np.ascontiguousarray(rgb[:, :, ::-1])
         H, W = bgr.shape[:2]
-        nw, nh = ops.get_size(W, H, mt)
-        mean, std = _DPT_NORM if mt in ("DPT_Large", "DPT_Hybrid") else _IMAGENET_NORM
+        target, method, (mean, std) = _TRANSFORM_SPECS[name]
+        nw, nh = ops.get_size_for(W, H, target, method)
         with torch.cuda.device(self.device):
             d = torch.from_numpy(bgr[None]).to(self.device)
-            return ops.preprocess(d, nh, nw, mean, std, ops.LAYOUT_NCHW_BF16)
+            return ops.preprocess(d, nh, nw, mean, std, ops.LAYOUT_NCHW_F32)
 
     def _plan(self, B, H, W, n_samples, want_metric, want_vis=False):
         key = (B, H, W, n_samples, want_metric, want_vis)

@@ -61,8 +61,10 @@ class ViTEncoder:
         return self._pos[key]
 
     def _buf(self, key, shape, dtype):
+        # keyed on (name, shape, dtype): a buffer whose address is baked into a captured CUDA graph is never replaced
+        key = (key, tuple(shape), dtype)
         t = self._bufs.get(key)
-        if t is None or tuple(t.shape) != tuple(shape):
+        if t is None:
             t = torch.empty(shape, dtype=dtype, device=self.dev)
             self._bufs[key] = t
         return t
@@ -135,8 +137,10 @@ class Reassemble:
         self._bufs = {}
 
     def _buf(self, key, shape, dtype=torch.bfloat16):
+        # keyed on (name, shape, dtype): a buffer whose address is baked into a captured CUDA graph is never replaced
+        key = (key, tuple(shape), dtype)
         t = self._bufs.get(key)
-        if t is None or tuple(t.shape) != tuple(shape):
+        if t is None:
             t = torch.empty(shape, dtype=dtype, device=self.dev)
             self._bufs[key] = t
         return t

@@ -82,14 +82,30 @@ class DPTHybridNet:
         self.dec = ScratchDecoder(sd, (256, 512, 768, 768), (256, 256, 256, 256), True, dev)
         self._bufs = {}
         self._x = {}
-        self._ws = torch.zeros(4 << 20, dtype=torch.uint8, device=dev)
+        self._ws_bufs = {}
+        self._ws = None                                      # GroupNorm workspace of the geometry being run
 
     def _buf(self, key, shape, dtype=torch.bfloat16):
+        # keyed on (name, shape, dtype): a buffer whose address is baked into a captured CUDA graph is never replaced
+        key = (key, tuple(shape), dtype)
         t = self._bufs.get(key)
-        if t is None or tuple(t.shape) != tuple(shape) or t.dtype != dtype:
+        if t is None:
             t = torch.empty(shape, dtype=dtype, device=self.dev)
             self._bufs[key] = t
         return t
+
+    def _workspace(self, B, H0, W0):
+        """GroupNorm workspace for one (B, stem H, stem W) geometry, sized for its largest call (the stem's: most pixels
+        per sample).  One buffer per geometry, zeroed once (arrival counters) and never replaced - its address is baked
+        into that geometry's captured graph."""
+        key = (B, H0, W0)
+        ws = self._ws_bufs.get(key)
+        if ws is None:
+            need = max(ops.groupnorm_ws_bytes(B, (H0 >> i) * (W0 >> i) if i else H0 * W0, c)
+                       for i, c in ((0, 64), (1, 256), (1, 64), (2, 512), (2, 128), (3, 1024), (3, 256)))
+            ws = torch.zeros(need + 4096, dtype=torch.uint8, device=self.dev)
+            self._ws_bufs[key] = ws
+        return ws
 
     def _gn(self, x, nrm, key, act=ops.ACT_RELU, add=None, want_f32=False, want_plain=False):
         """x: fp32 conv output [B,H,W,C] -> (split3 bf16 [B,H,W,3C], fp32 copy or None, plain bf16 copy or None)."""
@@ -137,6 +153,7 @@ class DPTHybridNet:
     def forward(self, x_nchw: torch.Tensor, B: int, net_h: int, net_w: int) -> torch.Tensor:
         """x_nchw: fp32 [B,3,net_h,net_w] from K1 (layout 2).  Returns fp32 [B, net_h, net_w] (>= 0)."""
         H, W = (net_h + 1) // 2, (net_w + 1) // 2
+        self._ws = self._workspace(B, H, W)
         s0 = self._buf(("stem", B, H, W), (B, H, W, 64), torch.float32)
         if os.environ.get("DEB_STEM_DIRECT"):                # CUDA-core direct conv in fp32 (cross-check)
             ops.stem_conv(x_nchw, self.stem_w, None, s0, 7, 2, ops.ACT_NONE)

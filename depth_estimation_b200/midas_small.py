@@ -75,8 +75,10 @@ class MidasSmallNet:
         self._bufs = {}
 
     def _buf(self, key, shape):
+        # keyed on (name, shape): a buffer whose address is baked into a captured CUDA graph is never replaced
+        key = (key, tuple(shape))
         t = self._bufs.get(key)
-        if t is None or tuple(t.shape) != tuple(shape):
+        if t is None:
             t = torch.empty(shape, dtype=torch.bfloat16, device=self.dev)
             self._bufs[key] = t
         return t

@@ -34,13 +34,17 @@ def _need_cuda(*ts):
 
 
 # ------------------------------------------------------------------------------- host helpers
+def get_size_for(width: int, height: int, target: int, method: int):
+    """[UPSTREAM] Resize.get_size: method 0 = "upper_bound", 1 = "minimal".  Returns (net_w, net_h)."""
+    w, h = C.c_int(), C.c_int()
+    _lib.check(_lib.load().de_get_size(width, height, target, method, C.byref(w), C.byref(h)), "de_get_size")
+    return w.value, h.value
+
+
 def get_size(width: int, height: int, model_type: str):
     """(net_w, net_h) the reference transform would resize to (depth_midas.py:13-16,23)."""
     dpt = model_type in ("DPT_Large", "DPT_Hybrid")
-    w, h = C.c_int(), C.c_int()
-    _lib.check(_lib.load().de_get_size(width, height, 384 if dpt else 256, 1 if dpt else 0, C.byref(w), C.byref(h)),
-               "de_get_size")
-    return w.value, h.value
+    return get_size_for(width, height, 384 if dpt else 256, 1 if dpt else 0)
 
 
 def cubic_taps(src: int, dst: int, mode: int):
@@ -130,7 +134,7 @@ def postprocess(pred: torch.Tensor, H: int, W: int, want_map: bool = True, want_
 # ------------------------------------------------------------------------------- GEMM / conv
 def gemm(a: torch.Tensor, w: torch.Tensor, out: torch.Tensor, *, M=None, N=None, K=None, bias=None, act=ACT_NONE,
          add1=None, add1_rowmode=0, add1_pre=False, ld_add1=None, add2=None, out_relu=None, out_rowmode=0, grp=0,
-         pad=0, off=0, ldo=None, conv=None, pixel_shuffle=None, bias_mod=0, head=None, block_n=0, cta_group=0, debug=0, accumulate=False):
+         pad=0, off=0, ldo=None, conv=None, pixel_shuffle=None, bias_mod=0, head=None, block_n=0, cta_group=0, epilogue=0, accumulate=False):
     """out = epilogue(a @ w.T) through de_gemm (accumulate=True: out += ..., fp32 dense output only).  a: bf16 [M,K] (or NHWC [B,H,W,Cin] with conv=(B,H,W,Cin));
     w: bf16 [N,K].  See include/depth_b200.h for the epilogue contract."""
     _need_cuda(a, w, out, bias, add1, add2, out_relu)
@@ -182,7 +186,7 @@ def gemm(a: torch.Tensor, w: torch.Tensor, out: torch.Tensor, *, M=None, N=None,
         g.head_b = float(hb)
     g.block_n = int(block_n)
     g.cta_group = int(cta_group)
-    g.debug = int(debug)
+    g.epilogue = int(epilogue)
     g.accumulate = 1 if accumulate else 0
     _lib.check(_lib.load().de_gemm(C.byref(g), _stream()), "de_gemm")
     return out
@@ -200,11 +204,10 @@ def layernorm(x: torch.Tensor, gamma, beta, eps: float, out, y: torch.Tensor | N
     return out
 
 
-def attention(qkv: torch.Tensor, out: torch.Tensor, B: int, T: int, heads: int, scale: float, legacy_mma: bool = False):
+def attention(qkv: torch.Tensor, out: torch.Tensor, B: int, T: int, heads: int, scale: float):
     _need_cuda(qkv, out)
     assert qkv.dtype == torch.bfloat16 and out.dtype == torch.bfloat16 and qkv.is_contiguous() and out.is_contiguous()
-    fn = _lib.load().de_attention_mma if legacy_mma else _lib.load().de_attention
-    _lib.check(fn(qkv.data_ptr(), out.data_ptr(), B, T, heads, float(scale), _stream()), "de_attention")
+    _lib.check(_lib.load().de_attention(qkv.data_ptr(), out.data_ptr(), B, T, heads, float(scale), _stream()), "de_attention")
     return out
 
 
@@ -250,6 +253,13 @@ def subsample(x: torch.Tensor, out: torch.Tensor, stride: int):
     B, H, W, Cc = x.shape
     _lib.check(_lib.load().de_subsample(x.data_ptr(), out.data_ptr(), B, H, W, Cc, stride, _stream()), "de_subsample")
     return out
+
+
+def groupnorm_ws_bytes(B: int, HW: int, C_: int, groups: int = 32) -> int:
+    n = int(_lib.load().de_groupnorm_ws_bytes(B, HW, C_, groups))
+    if n <= 0:
+        raise RuntimeError(f"de_groupnorm_ws_bytes: unsupported shape B={B} HW={HW} C={C_} groups={groups}")
+    return n
 
 
 def groupnorm(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, out: torch.Tensor | None, ws: torch.Tensor,

@@ -122,7 +122,8 @@ typedef struct DeGemm {
   const float* head_w;
   float head_b;
   int block_n; /* 0 = auto; else 32/64/128/256 */
-  int debug;     /* 0 in production; perf experiments: bit0 skip epilogue body, bit1 skip global stores */
+  int epilogue;  /* 0 = auto (TMA-store epilogue whenever the call is bias + activation -> dense output); 1 = always
+                  * the general register epilogue (cross-check of the two code paths) */
   int cta_group; /* 0 = auto; 1 = one CTA per 128-row tile; 2 = CTA pair per 256-row tile (block_n 256) */
   int accumulate; /* 1: out += epilogue(A W^T) instead of out = ... (fp32 dense output, a_mode 0, bias + activation
                    * only): the tile leaves through a TMA reduce-add, so the ViT residual stream x += proj(..) /
@@ -142,8 +143,6 @@ int de_layernorm(float* x, int64_t ldx, const void* y, int y_dtype, int64_t ldy,
  * softmax(q k^T * scale) v, non-causal, fp32 softmax. head_dim must be 64.
  * tcgen05/TMEM flash kernel: S and O tiles in tensor memory, Q/K/V by TMA, V consumed MN-major. */
 int de_attention(const void* qkv, void* out, int B, int T, int heads, float scale, void* stream);
-/* Same contract on the legacy mma.sync tensor path (flash-attention-2 style); kept as a cross-check. */
-int de_attention_mma(const void* qkv, void* out, int B, int T, int heads, float scale, void* stream);
 
 /* ---- small bandwidth kernels used between the GEMMs ---- */
 /* fp32 [rows, dim] (ldx) -> bf16 [rows', dim]: drops the first `skip` rows of every group of `grp`
@@ -168,11 +167,11 @@ int de_subsample(const void* x, void* out, int B, int H, int W, int C, int strid
  * [hi | hi | lo] with hi = bf16(y), lo = bf16(y - hi), which against weights packed [Wh | Wl | Wh] along K gives a
  * bf16x3 (~16 mantissa bit) product on the ordinary bf16 GEMM (DPT_Hybrid's ResNetV2 stages); out_f32 - fp32 copy
  * (the ResNetV2 residual stream); out_plain - bf16 [.., C] copy (decoder input).  Deterministic (fixed-order
- * reductions).  ws: device scratch of at least
- * 8*B*groups + 16*B*groups*ceil(HW/max(ceil(HW/148), 4*256/(C/8))) + 32 + 4*B bytes.  Its last 4*B bytes are
- * arrival counters: they must be ZERO before the first call (cudaMemset the buffer once) and every call leaves them
- * zero; calls sharing a workspace must be ordered on one stream.
+ * reductions).  ws: device scratch of at least de_groupnorm_ws_bytes(B, HW, C, groups) bytes.  Its first 16 KB are
+ * per-sample arrival counters: they must be ZERO before the first call (cudaMemset the buffer once) and every call
+ * leaves them zero; calls sharing a workspace must be ordered on one stream.  B <= 4096.
  * (timm GroupNormAct, eps 1e-5, 32 groups.) */
+int64_t de_groupnorm_ws_bytes(int B, int HW, int C, int groups); /* 0 for unsupported arguments */
 int de_groupnorm(const void* x, int x_dtype, const float* gamma, const float* beta, const void* add, int add_dtype,
                  void* out, int out_mode, float* out_f32, void* out_plain, int B, int HW, int C, int groups, float eps,
                  int act, void* ws, int64_t ws_bytes, void* stream);

@@ -3,8 +3,10 @@
 rwightman/gen-efficientnet-pytorch, as loaded by ``/root/reference/depth_midas.py:10`` for
 model_type "MiDaS_small" (hub: features=64, exportable=True, non_negative=True, blocks={'expand':True}).
 Neither upstream is vendored - published algorithm restated with upstream key names.
-PARITY UNPINNED by the reference (no tests) and without an independent local cross-check (SURVEY 8c C3);
-TF-"same" padding is unit-tested by hand in tests/test_oracle_models.py.
+PARITY UNPINNED by the reference itself (it has no tests or fixtures).  Pins that exist: the encoder
+equals HF transformers' independent EfficientNet implementation configured into Lite3 bit for bit on all four taps
+(tests/test_oracle_lite3_crosscheck.py); the decoder blocks are the oracle/dpt.py code pinned against HF's DPT neck
+(tests/test_oracle_hf_crosscheck.py); TF-"same" padding on odd extents is checked by hand in tests/test_oracle_cpu.py.
 """
 from __future__ import annotations
 

@@ -7,8 +7,8 @@ dev = torch.device("cuda:0")
 for (B, T, H) in ((32, 577, 16), (8, 1009, 16), (1, 577, 12)):
     qkv = torch.randn(B * T, 3 * H * 64, device=dev).bfloat16()
     out = torch.empty(B * T, H * 64, device=dev, dtype=torch.bfloat16)
-    for legacy in (False, True):
-        f = lambda: ops.attention(qkv, out, B, T, H, 0.125, legacy_mma=legacy)
+    for legacy in (False,):
+        f = lambda: ops.attention(qkv, out, B, T, H, 0.125)
         for _ in range(3): f()
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

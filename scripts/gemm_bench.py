@@ -29,12 +29,12 @@ def bench(name, N, K, cg, bn=256, **kw):
     ms = e0.elapsed_time(e1) / n
     print(f"{name:28s} N={N:5d} K={K:5d} cg={cg} bn={bn}: {ms*1e3:8.1f} us  {2.0*M*N*K/ms/1e9:7.1f} TFLOP/s", flush=True)
 
-for dbg in (0, 4):
-    print("debug flags", dbg, "(4 = force general epilogue)")
+for dbg in (0, 1):
+    print("epilogue", dbg, "(1 = force general epilogue)")
     for cg in (1, 2):
-        bench("qkv  bf16+bias", 3072, 1024, cg, debug=dbg)
-        bench("fc1  bf16+bias+gelu", 4096, 1024, cg, act=2, debug=dbg)
-        bench("proj f32+bias (no res)", 1024, 1024, cg, out_dtype=torch.float32, debug=dbg)
-        bench("fc2  f32+bias (no res)", 1024, 4096, cg, out_dtype=torch.float32, debug=dbg)
+        bench("qkv  bf16+bias", 3072, 1024, cg, epilogue=dbg)
+        bench("fc1  bf16+bias+gelu", 4096, 1024, cg, act=2, epilogue=dbg)
+        bench("proj f32+bias (no res)", 1024, 1024, cg, out_dtype=torch.float32, epilogue=dbg)
+        bench("fc2  f32+bias (no res)", 1024, 4096, cg, out_dtype=torch.float32, epilogue=dbg)
 bench("proj f32+bias+res(inplace)", 1024, 1024, 2, out_dtype=torch.float32, inplace_add=True)
 bench("fc2  f32+bias+res(inplace)", 1024, 4096, 2, out_dtype=torch.float32, inplace_add=True)

@@ -22,9 +22,21 @@ CASES = [
 
 
 def _errs(y, ref):
-    rel = float(np.abs(y - ref).max() / np.abs(ref).max())
-    dyn = float(np.abs(y - ref).max() / (ref.max() - ref.min()))
-    return rel, dyn
+    """SURVEY 8d D7 in full: rel = max|y-y*|/max(y*); pix = max per-pixel relative error over y* > 1e-2 max(y*);
+    dyn = the same absolute error against the dynamic range (reported; the bias-lifted maps make it ~10x rel)."""
+    d = np.abs(y - ref)
+    rel = float(d.max() / np.abs(ref).max())
+    m = ref > 1e-2 * ref.max()
+    pix = float((d[m] / ref[m]).max())
+    dyn = float(d.max() / (ref.max() - ref.min()))
+    return rel, pix, dyn
+
+
+# north_star: relative inverse depth within 1e-3 (fp32 accumulate) - max-normalised AND per pixel (D7).  `dyn` is
+# asserted against 1.5x the value measured when the case was added, so a regression that grows the error against
+# the signal cannot hide behind the bias-lifted maximum (ADVICE r1).
+REL_TOL = PIX_TOL = 1e-3
+DYN_TOL = {"DPT_Large": 2.0e-2, "DPT_Hybrid": 1.0e-2, "MiDaS_small": 1.5e-2}
 
 
 @pytest.mark.parametrize("mt,W,H,kind", CASES)
@@ -43,13 +55,9 @@ def test_predict_matches_oracle(mt, W, H, kind):
     out = est.predict(frame)
     assert out.shape == ref.shape == (H, W) and out.dtype == np.float32
     assert (ref > 0).mean() > 0.9
-    rel, dyn = _errs(out, ref)
-    print(f"{mt} {W}x{H} {kind}: rel={rel:.3e} dyn={dyn:.3e}")
-    # north_star: relative inverse depth within 1e-3 (fp32 accumulate).  DPT_Hybrid: its ResNetV2 stages run as bf16x3
-    # (plain bf16 operands drift 25 % at the stage-3 output under random init - the oracle with bf16 rounding injected
-    # reproduces that - and gave 5.8e-3 here); what is left (1.3e-3) is the shared bf16 decoder on an output whose
-    # maximum is small against its own dynamic range: in `dyn` terms the hybrid (4e-3) is 3x tighter than DPT_Large.
-    assert rel < (2e-3 if mt == "DPT_Hybrid" else 1e-3), (rel, dyn)
+    rel, pix, dyn = _errs(out, ref)
+    print(f"{mt} {W}x{H} {kind}: rel={rel:.3e} pix={pix:.3e} dyn={dyn:.3e}")
+    assert rel < REL_TOL and pix < PIX_TOL and dyn < DYN_TOL[mt], (rel, pix, dyn)
     # graph replay gives the same answer, and the batched / metric / sample outputs agree
     out2 = est.predict(frame)
     assert np.array_equal(out, out2)
@@ -58,6 +66,69 @@ def test_predict_matches_oracle(mt, W, H, kind):
     assert np.array_equal(maps[0], out)
     assert samples[0, 0] == out[H // 2, W // 3] and samples[0, 1] == out[H - 1, W - 1]
     assert np.abs(metric[0] - ref / 2.54).max() / np.abs(ref / 2.54).max() < 1e-2
+
+
+def test_bench_configuration_matches_oracle():
+    """The configuration bench.py times - predict_batch on 32 DPT_Large 384^2 frames, i.e. M = 18464 token rows through
+    the CTA-pair 256-wide GEMM tiles - checked against the oracle on frames 0, 13 and 31 of the batch."""
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    from depth_estimation_b200.depth_midas import DepthEstimator
+    from oracle.predict import OracleDepthEstimator, build_model, synthetic_frame
+    model = build_model("DPT_Large", seed=0)
+    est = DepthEstimator("DPT_Large", weights=model.state_dict())
+    frames = np.stack([synthetic_frame(384, 384, 100 + i, "S" if i % 2 else "U") for i in range(32)])
+    maps = est.predict_batch(frames)
+    assert maps.shape == (32, 384, 384)
+    orc = OracleDepthEstimator("DPT_Large", model=model)
+    for i in (0, 13, 31):
+        ref = orc.predict(frames[i])
+        rel, pix, dyn = _errs(maps[i], ref)
+        print(f"DPT_Large B=32 frame {i}: rel={rel:.3e} pix={pix:.3e} dyn={dyn:.3e}")
+        assert rel < REL_TOL and pix < PIX_TOL and dyn < DYN_TOL["DPT_Large"], (i, rel, pix, dyn)
+    # the device-resident entry point bench.py's `value` times returns the same maps
+    dev_maps = est.predict_device(torch.from_numpy(frames).to(est.device)).cpu().numpy()
+    assert np.array_equal(dev_maps, maps)
+
+
+def test_alternating_geometries_share_one_estimator():
+    """Landscape and portrait frames with the same token count (24x32 / 32x24 grids) through one estimator: every
+    geometry keeps its own work buffers, so the graph captured for the first one is not left pointing at freed
+    memory when the second one is planned (Reassemble._buf)."""
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    from depth_estimation_b200.depth_midas import DepthEstimator
+    rng = np.random.default_rng(77)
+    a = rng.integers(0, 256, (480, 640, 3), dtype=np.uint8)
+    b = rng.integers(0, 256, (640, 480, 3), dtype=np.uint8)
+    for mt in ("DPT_Large", "DPT_Hybrid", "MiDaS_small"):
+        est = DepthEstimator(mt, seed=2)
+        a1, b1 = est.predict(a), est.predict(b)
+        torch.cuda.empty_cache()
+        a2, b2, a3 = est.predict(a), est.predict(b), est.predict(a)
+        fresh = DepthEstimator(mt, seed=2)
+        bf, af = fresh.predict(b), fresh.predict(a)
+        assert np.array_equal(a1, a2) and np.array_equal(a1, a3) and np.array_equal(b1, b2), mt
+        assert np.array_equal(a1, af) and np.array_equal(b1, bf), mt
+
+
+def test_reference_surface_transforms():
+    """est.transform / est.midas_transforms.* called the way the reference calls them (RGB frame in, depth_midas.py:22-23)
+    return the hub transforms' float32 [1,3,h,w] tensor (sizes incl. default_transform = 384 upper_bound ImageNet)."""
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    from depth_estimation_b200.depth_midas import DepthEstimator
+    from oracle import transforms as T
+    from oracle.predict import synthetic_frame
+    est = DepthEstimator("MiDaS_small", seed=0)
+    frame = synthetic_frame(640, 480, 9, "S")
+    rgb = np.ascontiguousarray(frame[:, :, ::-1])
+    for name in ("small_transform", "dpt_transform", "default_transform"):
+        got = getattr(est.midas_transforms, name)(rgb)
+        want = T.midas_transform(rgb, name)
+        assert got.dtype == torch.float32 and tuple(got.shape) == tuple(want.shape) and got.is_cuda
+        assert np.abs(got.cpu().numpy() - want).max() < 2e-5, name
+    assert tuple(est.transform(rgb).shape) == (1, 3, 192, 256)
 
 
 def test_predict_stream_matches_predict_batch():
