@@ -160,81 +160,29 @@ def run_reference(args):
 
 # ---------------------------------------------------------------------------------------------- our arm
 def instrumented_step(est, frames_dev, B, H, W):
-    """One extra (untimed) step with CUDA events around every library launch: per-kernel time shares and
-    the GEMM kernel's achieved TFLOP/s (algorithmic 2*M*N*K of each launch / its event duration)."""
+    """One extra (untimed) eager step with the library's per-operator profiler on (de_profile_start / de_profile_stop:
+    CUDA events around every operator call, on the stream it is launched on): per-kernel time shares and the GEMM
+    kernel's achieved TFLOP/s (algorithmic 2*M*N*K of each launch / its event duration)."""
     import torch
-    from depth_estimation_b200 import ops
-    rec = []
-    orig = {}
-
-    def wrap(name, flops_fn=None):
-        fn = getattr(ops, name)
-        orig[name] = fn
-
-        def inner(*a, **k):
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            r = fn(*a, **k)
-            e1.record()
-            rec.append((name, e0, e1, flops_fn(*a, **k) if flops_fn else 0.0))
-            return r
-        setattr(ops, name, inner)
-
-    shapes = []
-
-    def gemm_flops(a, w, out, **k):
-        N = k.get("N") or w.shape[0]
-        if k.get("conv") is not None:
-            b, h, ww, cin = k["conv"]
-            shapes.append(("conv3x3", b * h * ww, N, 9 * cin, k.get("act", 0)))
-            return 2.0 * b * h * ww * N * 9 * cin
-        M = k.get("M") or a.shape[0]
-        K = k.get("K") or a.shape[1]
-        shapes.append(("gemm", M, N, K, k.get("act", 0)))
-        return 2.0 * M * N * K
-
-    def head_flops(x, *a, **k):
-        return 2.0 * x.shape[0] * x.shape[1] * x.shape[2] * 32 * 9 * x.shape[3]
-
-    def attn_flops(qkv, out, B_, T, heads, *a, **k):
-        return 4.0 * B_ * heads * T * T * 64
-
-    def head_up_flops(x, *a, **k):
-        return 2.0 * x.shape[0] * 4 * x.shape[1] * x.shape[2] * 32 * 9 * x.shape[3]
-
-    wrap("head_conv", head_flops)
-    wrap("head_up_conv", head_up_flops)
-    wrap("attention", attn_flops)
-    for n in ("preprocess", "postprocess", "layernorm", "cast_tokens", "fill_cls", "upsample2x",
-              "im2col3x3", "stem_conv", "stem_im2col_split3", "depthwise", "maxpool3x3s2", "groupnorm"):
-        if hasattr(ops, n):
-            wrap(n)
-    wrap("gemm", gemm_flops)
-    try:
-        est.predict_device(frames_dev, eager=True)   # keeps the GPU busy so the host runs ahead of the recorded pass
-        n_skip = len(rec)
-        est.predict_device(frames_dev, eager=True)
-        torch.cuda.synchronize()
-        rec = rec[n_skip:]
-        shapes = shapes[len(shapes) // 2:]
-    finally:
-        for n, fn in orig.items():
-            setattr(ops, n, fn)
+    from depth_estimation_b200 import _lib
+    est.predict_device(frames_dev, eager=True)       # keeps the GPU busy so the host runs ahead of the recorded pass
+    _lib.profile_start()
+    est.predict_device(frames_dev, eager=True)
+    rec = _lib.profile_stop()
+    torch.cuda.synchronize()
     agg = {}
     per_shape = {}
-    gi = 0
-    for name, e0, e1, fl in rec:
+    for name, ms, fl, dims in rec:
         d = agg.setdefault(name, {"launches": 0, "ms": 0.0, "flops": 0.0})
         d["launches"] += 1
-        ms = e0.elapsed_time(e1)
         d["ms"] += ms
         d["flops"] += fl
         if name == "gemm":
-            ps = per_shape.setdefault(shapes[gi], [0, 0.0, 0.0])
+            key = ("conv3x3" if dims[3] >= 100 else "gemm", dims[0], dims[1], dims[2], dims[3] % 100)
+            ps = per_shape.setdefault(key, [0, 0.0, 0.0])
             ps[0] += 1
             ps[1] += ms
             ps[2] += fl
-            gi += 1
     if os.environ.get("BENCH_DETAIL"):
         for k, (n, ms, fl) in sorted(per_shape.items(), key=lambda kv: -kv[1][1]):
             print(f"  {k}: launches={n} ms={ms:.3f} TFLOP/s={fl / (ms * 1e-3) / 1e12 if ms > 0 else 0:.1f}", file=sys.stderr)

@@ -31,15 +31,43 @@ class DeGemm(C.Structure):
         ("out_rowmode", C.c_int), ("grp", C.c_int), ("pad", C.c_int), ("off", C.c_int),
         ("ps_gh", C.c_int), ("ps_gw", C.c_int), ("ps_s", C.c_int), ("ps_cout", C.c_int),
         ("head_w", C.c_void_p), ("head_b", C.c_float),
-        ("block_n", C.c_int), ("epilogue", C.c_int), ("cta_group", C.c_int), ("accumulate", C.c_int),
+        ("block_n", C.c_int), ("epilogue", C.c_int), ("cta_group", C.c_int),
+        ("out_split", C.c_int), ("relu_split", C.c_int), ("ld_relu", C.c_int64), ("add2_dtype", C.c_int), ("ld_add2", C.c_int64),
+        ("accumulate", C.c_int),
     ]
 
+
+class DePredictIO(C.Structure):
+    _fields_ = [
+        ("frames", C.c_void_p), ("row_stride", C.c_int64), ("frame_stride", C.c_int64),
+        ("uv", C.c_void_p), ("uv_row_stride", C.c_int64), ("uv_frame_stride", C.c_int64),
+        ("out_map", C.c_void_p), ("out_metric", C.c_void_p), ("metric_scale", C.c_float), ("metric_shift", C.c_float),
+        ("out_vis", C.c_void_p), ("sample_rc", C.c_void_p), ("n_samples", C.c_int), ("out_samples", C.c_void_p),
+    ]
+
+
+class DeProfileRecord(C.Structure):
+    _fields_ = [("name", C.c_char * 24), ("ms", C.c_double), ("flops", C.c_double), ("dims", C.c_int64 * 4)]
+
+
+DE_PRECISION_DEFAULT, DE_PRECISION_BF16 = 0, 1
 
 # name -> (restype, argtypes); must list every symbol include/depth_b200.h declares
 SIGNATURES = {
     "de_last_error": (C.c_char_p, []),
     "de_version": (C.c_int, []),
     "de_launch_count": (C.c_int64, []),
+    "de_create": (C.c_int, [C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]),
+    "de_set_weight": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p, C.POINTER(C.c_int64), C.c_int, C.c_int]),
+    "de_finalize_weights": (C.c_int, [C.c_void_p]),
+    "de_plan": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "de_predict": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(DePredictIO), C.c_int, C.c_void_p]),
+    "de_forward": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                             C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_int, C.c_void_p]),
+    "de_engine_info": (C.c_int, [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "de_destroy": (None, [C.c_void_p]),
+    "de_profile_start": (C.c_int, []),
+    "de_profile_stop": (C.c_int, [C.POINTER(DeProfileRecord), C.c_int, C.POINTER(C.c_int)]),
     "de_get_size": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "de_cubic_taps": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "de_preprocess": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_int, C.c_int,
@@ -57,6 +85,8 @@ SIGNATURES = {
     "de_cast_tokens": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "de_fill_cls": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "de_upsample2x": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "de_upsample2x_ex": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                   C.c_void_p]),
     "de_im2col3x3": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                C.c_int, C.c_int, C.c_void_p]),
     "de_subsample": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
@@ -103,6 +133,18 @@ def check(rc: int, what: str = "") -> None:
     if rc != 0:
         msg = load().de_last_error().decode(errors="replace")
         raise RuntimeError(f"libdepthb200 {what} failed ({rc}): {msg}")
+
+
+def profile_start() -> None:
+    check(load().de_profile_start(), "de_profile_start")
+
+
+def profile_stop(max_records: int = 65536):
+    """[(name, ms, flops, (d0, d1, d2, d3))] for every operator call since profile_start (synchronises the device)."""
+    buf = (DeProfileRecord * max_records)()
+    n = C.c_int()
+    check(load().de_profile_stop(buf, max_records, C.byref(n)), "de_profile_stop")
+    return [(buf[i].name.decode(), buf[i].ms, buf[i].flops, tuple(buf[i].dims)) for i in range(n.value)]
 
 
 def launch_count() -> int:

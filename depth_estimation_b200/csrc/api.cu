@@ -5,6 +5,8 @@
 #include <stdio.h>
 
 #include <atomic>
+#include <mutex>
+#include <vector>
 
 #include "depth_b200.h"
 #include "host_util.h"
@@ -37,6 +39,39 @@ int cuda_check_launch(const char* what) {
   return DE_OK;
 }
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+void add_launches(int64_t n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+// ---- per-operator profiler
+struct ProfRec {
+  char name[24];
+  double flops;
+  int64_t dims[4];
+  cudaEvent_t e0, e1;
+};
+static std::atomic<bool> g_prof_on{false};
+static std::mutex g_prof_mu;
+static std::vector<ProfRec> g_prof;
+
+ProfScope::ProfScope(const char* name, double flops, void* st, int64_t d0, int64_t d1, int64_t d2, int64_t d3) {
+  if (!g_prof_on.load(std::memory_order_relaxed)) return;
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(reinterpret_cast<cudaStream_t>(st), &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) return;
+  ProfRec r{};
+  snprintf(r.name, sizeof(r.name), "%s", name);
+  r.flops = flops;
+  r.dims[0] = d0; r.dims[1] = d1; r.dims[2] = d2; r.dims[3] = d3;
+  if (cudaEventCreate(&r.e0) != cudaSuccess || cudaEventCreate(&r.e1) != cudaSuccess) return;
+  cudaEventRecord(r.e0, reinterpret_cast<cudaStream_t>(st));
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  idx = (int)g_prof.size();
+  stream = st;
+  g_prof.push_back(r);
+}
+ProfScope::~ProfScope() {
+  if (idx < 0) return;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  if (idx < (int)g_prof.size()) cudaEventRecord(g_prof[idx].e1, reinterpret_cast<cudaStream_t>(stream));
+}
 
 int num_sms() {
   static int cache[32] = {0};                  // per device
@@ -54,7 +89,7 @@ bool pdl_enabled(int cls) {
   static int mask = -1;
   if (mask < 0) {
     const char* e = getenv("DEB_PDL");
-    mask = e ? atoi(e) : 3;   // LayerNorm off: early-scheduled GEMM CTAs squat on the SMs and cost it occupancy (measured)
+    mask = e ? atoi(e) : 11;  // LayerNorm off: early-scheduled GEMM CTAs squat on the SMs and cost it occupancy (measured)
   }
   return (mask & cls) != 0;
 }
@@ -79,6 +114,40 @@ TensorMapEncodeTiledFn get_tensor_map_encoder() {
 extern "C" const char* de_last_error(void) { return deb::g_err; }
 extern "C" int de_version(void) { return 1; }
 extern "C" int64_t de_launch_count(void) { return deb::g_launches.load(); }
+
+extern "C" int de_profile_start(void) {
+  std::lock_guard<std::mutex> lk(deb::g_prof_mu);
+  for (auto& r : deb::g_prof) {
+    cudaEventDestroy(r.e0);
+    cudaEventDestroy(r.e1);
+  }
+  deb::g_prof.clear();
+  deb::g_prof_on.store(true);
+  return DE_OK;
+}
+extern "C" int de_profile_stop(DeProfileRecord* out, int max_records, int* n_records) {
+  deb::g_prof_on.store(false);
+  cudaError_t e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) return deb::cuda_fail(e, "de_profile_stop: cudaDeviceSynchronize");
+  std::lock_guard<std::mutex> lk(deb::g_prof_mu);
+  int n = 0;
+  for (auto& r : deb::g_prof) {
+    float ms = 0.f;
+    if (out && n < max_records && cudaEventElapsedTime(&ms, r.e0, r.e1) == cudaSuccess) {
+      snprintf(out[n].name, sizeof(out[n].name), "%s", r.name);
+      out[n].ms = ms;
+      out[n].flops = r.flops;
+      for (int k = 0; k < 4; ++k) out[n].dims[k] = r.dims[k];
+      ++n;
+    }
+    cudaEventDestroy(r.e0);
+    cudaEventDestroy(r.e1);
+  }
+  const int total = (int)deb::g_prof.size();
+  deb::g_prof.clear();
+  if (n_records) *n_records = out ? n : total;
+  return DE_OK;
+}
 
 // [UPSTREAM] midas/transforms.py Resize.constrain_to_multiple_of / get_size (keep_aspect_ratio=True,
 // ensure_multiple_of=32).  nearbyint() under the default rounding mode is round-half-to-even == np.round.

@@ -437,6 +437,7 @@ attention_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const WsParams p)
 }  // namespace deb
 
 extern "C" int de_attention(const void* qkv, void* out, int B, int T, int heads, float scale, void* stream) {
+  deb::ProfScope prof_("attention", 4.0 * B * heads * (double)T * T * 64, stream, B, T, heads);
   using namespace deb;
   if (!qkv || !out || B <= 0 || T <= 0 || heads <= 0) return fail(DE_ERR_INVALID, "de_attention: bad args");
   if (!(scale > 0.f)) return fail(DE_ERR_INVALID, "de_attention: scale must be positive");

@@ -6,7 +6,7 @@ cd "$(dirname "$0")"
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 OUT=${OUT:-../libdepthb200.so}
 OBJ=${OBJ:-build}
-SRCS="api.cu resample_plan.cu preprocess.cu postprocess.cu gemm_tcgen05.cu attention_ws.cu misc.cu conv_direct.cu head_conv.cu $EXTRA_SRCS"
+SRCS="api.cu resample_plan.cu preprocess.cu postprocess.cu gemm_tcgen05.cu attention_ws.cu misc.cu conv_direct.cu depthwise.cu head_conv.cu engine.cu engine_nets.cu $EXTRA_SRCS"
 FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -I../../include -I. ${NVCC_EXTRA}"
 mkdir -p $OBJ
 echo "$FLAGS" > $OBJ/.flags.new
@@ -29,3 +29,7 @@ for p in "${pids[@]}"; do wait $p || rc=1; done
 if [ $rc != 0 ]; then echo "nvcc compile failed"; exit 1; fi
 $NVCC -gencode arch=compute_100a,code=sm_100a -shared -Xcompiler -fPIC -o $OUT $objs -lcudart_static -ldl -lrt -lpthread 2>&1
 echo "built $OUT"
+# the no-Python host of the handle-level ABI (tests/c/engine_demo.c): plain C, linked against the library
+gcc -O2 -std=c99 -I../../include -I/usr/local/cuda/include -o $OBJ/engine_demo ../../tests/c/engine_demo.c \
+  -L.. -l:libdepthb200.so -L/usr/local/cuda/lib64 -lcudart -Wl,-rpath,'$ORIGIN/../..' 2>&1
+echo "built $OBJ/engine_demo"

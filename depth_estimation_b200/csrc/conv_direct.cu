@@ -1,9 +1,7 @@
 // Direct (CUDA-core) convolution kernels for the shapes that are not dense contractions:
 //   * the 3-channel stems (EfficientNet-Lite3 3x3 s2, ResNetV2 7x7 s2) - K = 27 / 147, reads the NCHW
 //     bf16 tensor K1 writes, emits NHWC bf16;
-//   * depthwise k3 / k5, stride 1 / 2, TF-"same" padding with folded BatchNorm + ReLU6 (MBConv middle),
-//     NHWC bf16, 8 channels (16 B) per thread, weights tap-major so every access is a coalesced 16-byte
-//     transaction - an HBM/L2 bandwidth kernel;
+//   * (the depthwise convolutions of the MBConv blocks live in depthwise.cu);
 //   * MaxPool 3x3 s2 TF-same (ResNetV2 stem).
 // Restates [UPSTREAM] geffnet Conv2dSame / timm StdConv2dSame+MaxPool2dSame padding rule:
 //   pad_total = max((ceil(i/s)-1)*s + k - i, 0), pad_before = pad_total / 2 (extra pixel bottom/right).
@@ -178,57 +176,6 @@ __global__ void __launch_bounds__(256) stem_im2col_split3_kernel(const float* __
   }
 }
 
-// ---------------------------------------------------------------- depthwise, NHWC bf16
-template <int K>
-__global__ void __launch_bounds__(256) depthwise_kernel(const __nv_bfloat16* __restrict__ x,
-                                                        const __nv_bfloat16* __restrict__ w,  // [K*K][C] tap-major
-                                                        const float* __restrict__ bias, __nv_bfloat16* __restrict__ out,
-                                                        int B, int H, int W, int C, int stride, int Ho, int Wo, int pad_y,
-                                                        int pad_x, int act) {
-  const int cgs = C >> 3;
-  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= (long long)B * Ho * Wo * cgs) return;
-  const int c = static_cast<int>(idx % cgs) * 8;
-  long long t = idx / cgs;
-  const int ox = static_cast<int>(t % Wo);
-  t /= Wo;
-  const int oy = static_cast<int>(t % Ho);
-  const int b = static_cast<int>(t / Ho);
-  float acc[8];
-  {
-    const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias + c));
-    const float4 b1 = __ldg(reinterpret_cast<const float4*>(bias + c + 4));
-    acc[0] = b0.x; acc[1] = b0.y; acc[2] = b0.z; acc[3] = b0.w;
-    acc[4] = b1.x; acc[5] = b1.y; acc[6] = b1.z; acc[7] = b1.w;
-  }
-  const __nv_bfloat16* xb = x + (long long)b * H * W * C + c;
-#pragma unroll
-  for (int ky = 0; ky < K; ++ky) {
-    const int iy = oy * stride + ky - pad_y;
-    if (iy < 0 || iy >= H) continue;
-#pragma unroll
-    for (int kx = 0; kx < K; ++kx) {
-      const int ix = ox * stride + kx - pad_x;
-      if (ix < 0 || ix >= W) continue;
-      const uint4 v = __ldg(reinterpret_cast<const uint4*>(xb + ((long long)iy * W + ix) * C));
-      const uint4 ww = __ldg(reinterpret_cast<const uint4*>(w + (ky * K + kx) * C + c));
-      acc[0] = fmaf(bf16_lo(v.x), bf16_lo(ww.x), acc[0]); acc[1] = fmaf(bf16_hi(v.x), bf16_hi(ww.x), acc[1]);
-      acc[2] = fmaf(bf16_lo(v.y), bf16_lo(ww.y), acc[2]); acc[3] = fmaf(bf16_hi(v.y), bf16_hi(ww.y), acc[3]);
-      acc[4] = fmaf(bf16_lo(v.z), bf16_lo(ww.z), acc[4]); acc[5] = fmaf(bf16_hi(v.z), bf16_hi(ww.z), acc[5]);
-      acc[6] = fmaf(bf16_lo(v.w), bf16_lo(ww.w), acc[6]); acc[7] = fmaf(bf16_hi(v.w), bf16_hi(ww.w), acc[7]);
-    }
-  }
-  if (act == DE_ACT_RELU6) {
-#pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] = fminf(fmaxf(acc[j], 0.f), 6.f);
-  } else if (act == DE_ACT_RELU) {
-#pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] = fmaxf(acc[j], 0.f);
-  }
-  *reinterpret_cast<uint4*>(out + (((long long)b * Ho + oy) * Wo + ox) * C + c) =
-      make_uint4(pack_bf16(acc[0], acc[1]), pack_bf16(acc[2], acc[3]), pack_bf16(acc[4], acc[5]), pack_bf16(acc[6], acc[7]));
-}
-
 // ---------------------------------------------------------------- maxpool 3x3 s2 TF-same, NHWC bf16
 // in: bf16 or fp32 NHWC.  out_mode 0: bf16 NHWC; 1: the [hi | hi | lo] split3 operand layout (misc.cu store_split3).
 __global__ void maxpool3x3s2_kernel(const void* __restrict__ x, int x_f32, __nv_bfloat16* __restrict__ out, int out_mode,
@@ -289,6 +236,7 @@ using namespace deb;
 
 extern "C" int de_stem_conv(const void* x_nchw, int x_dtype, const float* w, const float* bias, void* out_nhwc, int out_dtype,
                             int B, int H, int W, int Cout, int k, int stride, int act, void* stream) {
+  deb::ProfScope prof_("stem_conv", 0.0, stream, B, H, W, Cout);
   if (!x_nchw || !w || !out_nhwc || Cout % kStemCo != 0 || k < 1 || k > 7)
     return fail(DE_ERR_INVALID, "de_stem_conv: bad args (Cout %% 16, k <= 7)");
   const int Ho = (H + stride - 1) / stride, Wo = (W + stride - 1) / stride;
@@ -302,6 +250,7 @@ extern "C" int de_stem_conv(const void* x_nchw, int x_dtype, const float* w, con
 
 extern "C" int de_stem_im2col_split3(const float* x_nchw, void* out_bf16, int B, int H, int W, int k, int stride, int kp,
                                      void* stream) {
+  deb::ProfScope prof_("stem_im2col_split3", 0.0, stream, B, H, W, kp);
   if (!x_nchw || !out_bf16 || B <= 0 || k < 1 || stride < 1 || kp % 8 != 0 || kp < k * k * 3 || kp > 64 * kStemMaxJ)
     return fail(DE_ERR_INVALID, "de_stem_im2col_split3: bad args (kp %% 8 == 0, 3*k*k <= kp <= 192)");
   const int Ho = (H + stride - 1) / stride, Wo = (W + stride - 1) / stride;
@@ -314,26 +263,9 @@ extern "C" int de_stem_im2col_split3(const float* x_nchw, void* out_bf16, int B,
   return cuda_check_launch("stem_im2col_split3_kernel");
 }
 
-extern "C" int de_depthwise(const void* x, const void* w_tapmajor, const float* bias, void* out, int B, int H, int W,
-                            int C, int k, int stride, int act, void* stream) {
-  if (!x || !w_tapmajor || !bias || !out || C % 8 != 0) return fail(DE_ERR_INVALID, "de_depthwise: bad args (C %% 8)");
-  const int Ho = (H + stride - 1) / stride, Wo = (W + stride - 1) / stride;
-  const long long n = (long long)B * Ho * Wo * (C / 8);
-  const unsigned grid = (unsigned)((n + 255) / 256);
-  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  const int py = same_pad_before(H, k, stride), px = same_pad_before(W, k, stride);
-  auto xp = reinterpret_cast<const __nv_bfloat16*>(x);
-  auto wp = reinterpret_cast<const __nv_bfloat16*>(w_tapmajor);
-  auto op = reinterpret_cast<__nv_bfloat16*>(out);
-  if (k == 3) depthwise_kernel<3><<<grid, 256, 0, st>>>(xp, wp, bias, op, B, H, W, C, stride, Ho, Wo, py, px, act);
-  else if (k == 5) depthwise_kernel<5><<<grid, 256, 0, st>>>(xp, wp, bias, op, B, H, W, C, stride, Ho, Wo, py, px, act);
-  else return fail(DE_ERR_UNSUPPORTED, "de_depthwise: k=%d (3 or 5)", k);
-  count_launch();
-  return cuda_check_launch("depthwise_kernel");
-}
-
 extern "C" int de_maxpool3x3s2(const void* x, int x_dtype, void* out, int out_mode, int B, int H, int W, int C,
                                void* stream) {
+  deb::ProfScope prof_("maxpool3x3s2", 0.0, stream, B, H, W, C);
   if (!x || !out || C % 8 != 0) return fail(DE_ERR_INVALID, "de_maxpool3x3s2: bad args");
   const int Ho = (H + 1) / 2, Wo = (W + 1) / 2;
   const long long n = (long long)B * Ho * Wo * (C / 8);

@@ -36,11 +36,15 @@ struct GemmParams {
   const void* add1;
   int add1_dtype, add1_rowmode, add1_pre;
   long long ld_add1;
-  const __nv_bfloat16* add2;
+  const void* add2;
+  int add2_dtype;
   void* out;
   int out_dtype;
   long long ldo;
   __nv_bfloat16* out_relu;
+  // general epilogue: storage offset of a row = unit * pitch (unit = storage row, or the pixel of a pixel-shuffle store)
+  long long out_pitch, relu_pitch, add2_pitch;
+  int out_split, relu_split, split_c;   // split3 stores: [hi | hi | lo], each split_c wide
   int out_rowmode, grp, pad, off;
   int ps_gh, ps_gw, ps_s, ps_cout;
   const float* head_w;
@@ -435,17 +439,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         long long arow = orow;
         if (p.add1_rowmode == 1) arow = m / p.grp;
         else if (p.add1_rowmode == 2) arow = (m % p.grp) + p.off;
-        long long ro;
+        long long ro = orow;                       // storage unit: row, or the top-left output pixel of a pixel shuffle
         if (p.out_rowmode == 2) {
           const int per = p.ps_gh * p.ps_gw;
           const int ps_b = static_cast<int>(m / per), t = static_cast<int>(m % per);
           const int ps_y = t / p.ps_gw, ps_x = t % p.ps_gw;
-          ro = ((static_cast<long long>(ps_b) * p.ps_gh * p.ps_s + ps_y * p.ps_s) * (p.ps_gw * p.ps_s) + ps_x * p.ps_s) *
-               p.ps_cout;
-        } else if (p.head_w) {
-          ro = orow;
-        } else {
-          ro = orow * p.ldo;
+          ro = (static_cast<long long>(ps_b) * p.ps_gh * p.ps_s + ps_y * p.ps_s) * (p.ps_gw * p.ps_s) + ps_x * p.ps_s;
         }
         __syncwarp();
         s_ro[lane] = valid ? ro : -1;
@@ -484,10 +483,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         const int n0 = n_tile * BN + c * 32;
         if (n0 >= p.N) continue;
         const bool col_ok = cc < p.N - n0;       // N % 8 == 0 and cc % 4 == 0: whole float4 in or out
-        long long colpart = n0 + cc;
+        long long colpart = n0 + cc, colpart_r = n0 + cc, colpart2 = n0 + cc;
         if (p.out_rowmode == 2) {
           const int g = n0 / p.ps_cout, co = n0 % p.ps_cout;
-          colpart = (static_cast<long long>(g / p.ps_s) * (p.ps_gw * p.ps_s) + g % p.ps_s) * p.ps_cout + co + cc;
+          const long long px = static_cast<long long>(g / p.ps_s) * (p.ps_gw * p.ps_s) + g % p.ps_s;
+          colpart = px * p.out_pitch + co + cc;
+          colpart_r = px * p.relu_pitch + co + cc;
+          colpart2 = px * p.add2_pitch + co + cc;
         }
         float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f), hw4 = bias4;
         if (p.bias) bias4 = *reinterpret_cast<const float4*>(s_bias + (c - c_begin) * 32 + cc);
@@ -512,7 +514,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               a1_[i] = make_float4(bf16_lo(t.x), bf16_hi(t.x), bf16_lo(t.y), bf16_hi(t.y));
             }
           }
-          if (p.add2 && ro_[i] >= 0) a2_[i] = *reinterpret_cast<const uint2*>(p.add2 + ro_[i] + colpart);
+          if (p.add2 && ro_[i] >= 0) {               // same rows / pitch as a plain `out`
+            const long long o2 = ro_[i] * p.add2_pitch + colpart2;
+            if (p.add2_dtype == DE_DTYPE_F32) {
+              const float4 t = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.add2) + o2);
+              a1_[i].x += t.x; a1_[i].y += t.y; a1_[i].z += t.z; a1_[i].w += t.w;     // (only with add1_pre == 0)
+            } else {
+              a2_[i] = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(p.add2) + o2);
+            }
+          }
         }
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
@@ -534,17 +544,30 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             continue;
           }
           if (ro < 0) continue;
-          const long long o = ro + colpart;
+          const long long o = ro * p.out_pitch + colpart;
           v.x += bf16_lo(a2_[i].x); v.y += bf16_hi(a2_[i].x); v.z += bf16_lo(a2_[i].y); v.w += bf16_hi(a2_[i].y);
           if (p.out_dtype == DE_DTYPE_F32) {
             *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + o) = v;
           } else {
-            *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.out) + o) =
-                make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
+            const uint2 hi = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
+            __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(p.out) + o;
+            *reinterpret_cast<uint2*>(op) = hi;
+            if (p.out_split) {                       // [hi | hi | lo]: the bf16x3 operand layout
+              *reinterpret_cast<uint2*>(op + p.split_c) = hi;
+              *reinterpret_cast<uint2*>(op + 2 * p.split_c) =
+                  make_uint2(pack_bf16(v.x - bf16_lo(hi.x), v.y - bf16_hi(hi.x)), pack_bf16(v.z - bf16_lo(hi.y), v.w - bf16_hi(hi.y)));
+            }
           }
           if (p.out_relu) {
-            *reinterpret_cast<uint2*>(p.out_relu + o) =
-                make_uint2(pack_bf16(fmaxf(v.x, 0.f), fmaxf(v.y, 0.f)), pack_bf16(fmaxf(v.z, 0.f), fmaxf(v.w, 0.f)));
+            const float4 rv = make_float4(fmaxf(v.x, 0.f), fmaxf(v.y, 0.f), fmaxf(v.z, 0.f), fmaxf(v.w, 0.f));
+            const uint2 hi = make_uint2(pack_bf16(rv.x, rv.y), pack_bf16(rv.z, rv.w));
+            __nv_bfloat16* rp = p.out_relu + ro * p.relu_pitch + colpart_r;
+            *reinterpret_cast<uint2*>(rp) = hi;
+            if (p.relu_split) {
+              *reinterpret_cast<uint2*>(rp + p.split_c) = hi;
+              *reinterpret_cast<uint2*>(rp + 2 * p.split_c) =
+                  make_uint2(pack_bf16(rv.x - bf16_lo(hi.x), rv.y - bf16_hi(hi.x)), pack_bf16(rv.z - bf16_lo(hi.y), rv.w - bf16_hi(hi.y)));
+            }
           }
         }
       }
@@ -647,6 +670,7 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMa
 }  // namespace deb
 
 extern "C" int de_gemm(const DeGemm* g, void* stream) {
+  deb::ProfScope prof_("gemm", g ? (g->a_mode == 1 ? 2.0 * g->B * g->H * g->W * (double)g->N * 9 * g->Cin : 2.0 * g->M * (double)g->N * g->K) : 0.0, stream, g ? (g->a_mode == 1 ? (int64_t)g->B * g->H * g->W : g->M) : 0, g ? g->N : 0, g ? (g->a_mode == 1 ? 9 * g->Cin : g->K) : 0, g ? g->a_mode * 100 + g->act * 10 + (g->accumulate ? 1 : 0) : 0);
   using namespace deb;
   if (!g || !g->a || !g->w || !g->out) return fail(DE_ERR_INVALID, "de_gemm: null pointer");
   if (g->N % 8 != 0) return fail(DE_ERR_INVALID, "de_gemm: N=%d must be a multiple of 8", g->N);
@@ -715,11 +739,32 @@ extern "C" int de_gemm(const DeGemm* g, void* stream) {
   p.add1_rowmode = g->add1_rowmode;
   p.add1_pre = g->add1_pre;
   p.ld_add1 = g->ld_add1;
-  p.add2 = reinterpret_cast<const __nv_bfloat16*>(g->add2);
+  p.add2 = g->add2;
+  p.add2_dtype = g->add2_dtype;
+  if (g->add2 && g->add2_dtype == DE_DTYPE_F32 && g->add1_pre) return fail(DE_ERR_INVALID, "de_gemm: fp32 add2 with add1_pre is not supported");
   p.out = g->out;
   p.out_dtype = g->out_dtype;
   p.ldo = g->ldo;
   p.out_relu = reinterpret_cast<__nv_bfloat16*>(g->out_relu);
+  // split3 stores ([hi | hi | lo] rows, the bf16x3 operand layout): out and / or out_relu
+  p.out_split = g->out_split ? 1 : 0;
+  p.relu_split = g->relu_split ? 1 : 0;
+  p.split_c = g->out_rowmode == 2 ? g->ps_cout : g->N;
+  if (p.out_split && (g->out_dtype != DE_DTYPE_BF16 || g->head_w || g->accumulate || (g->out_rowmode != 2 && g->ldo < 3LL * g->N)))
+    return fail(DE_ERR_INVALID, "de_gemm: out_split needs a bf16 output with ldo >= 3N");
+  if (p.relu_split && !g->out_relu) return fail(DE_ERR_INVALID, "de_gemm: relu_split without out_relu");
+  {
+    const long long ldr = g->ld_relu > 0 ? g->ld_relu : g->ldo;
+    if (g->out_relu && g->out_rowmode != 2 && ldr < (p.relu_split ? 3LL : 1LL) * g->N) return fail(DE_ERR_INVALID, "de_gemm: ld_relu too small");
+    if (g->out_rowmode == 2) {
+      p.out_pitch = (long long)(g->ps_cout > 0 ? g->ps_cout : 1) * (p.out_split ? 3 : 1);
+      p.relu_pitch = (long long)(g->ps_cout > 0 ? g->ps_cout : 1) * (p.relu_split ? 3 : 1);
+    } else {
+      p.out_pitch = g->head_w ? 1 : g->ldo;
+      p.relu_pitch = ldr;
+    }
+    p.add2_pitch = g->out_rowmode == 2 ? (long long)(g->ps_cout > 0 ? g->ps_cout : 1) : (g->ld_add2 > 0 ? g->ld_add2 : g->ldo);
+  }
   p.out_rowmode = g->out_rowmode;
   p.grp = g->grp > 0 ? g->grp : 1;
   p.pad = g->pad;
@@ -731,7 +776,7 @@ extern "C" int de_gemm(const DeGemm* g, void* stream) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   // epilogue flavour: the TMA-store epilogue covers "bias + activation -> dense output"
   const int es = g->out_dtype == DE_DTYPE_F32 ? 4 : 2;
-  bool store_epi = !g->add1 && !g->add2 && !g->out_relu && !g->head_w && g->out_rowmode == 0 && bn >= 64 &&
+  bool store_epi = !g->add1 && !g->add2 && !g->out_relu && !g->head_w && g->out_rowmode == 0 && bn >= 64 && !g->out_split &&
                    (g->ldo * es) % 16 == 0 && (reinterpret_cast<uintptr_t>(g->out) & 15) == 0 &&
                    (g->a_mode == 0 || g->ldo == g->N) && g->epilogue != 1;
   if (g->accumulate && (!store_epi || g->a_mode != 0 || g->out_dtype != DE_DTYPE_F32))

@@ -520,6 +520,7 @@ static bool hc_make_map(CUtensorMap* map, const void* base, int rank, const uint
 
 extern "C" int de_head_conv(const void* x, const void* w, int64_t ldw, const float* bias, const float* head_w,
                             float head_b, float* out, int B, int H, int W, int Cin, void* stream) {
+  deb::ProfScope prof_("head_conv", 2.0 * B * H * W * 32.0 * 9 * Cin, stream, B, H, W, Cin);
   using namespace deb;
   if (!x || !w || !head_w || !out) return fail(DE_ERR_INVALID, "de_head_conv: null pointer");
   if (B < 1 || H < 1 || W < 1 || Cin < 64 || Cin % 64 != 0) return fail(DE_ERR_UNSUPPORTED, "de_head_conv: Cin=%d must be a multiple of 64", Cin);
@@ -567,6 +568,7 @@ extern "C" int de_head_conv(const void* x, const void* w, int64_t ldw, const flo
 
 extern "C" int de_head_up_conv(const void* x, const void* w, int64_t ldw, const float* bias, const float* head_w,
                                float head_b, float* out, int B, int Hs, int Ws, int Cin, int align_corners, void* stream) {
+  deb::ProfScope prof_("head_up_conv", 2.0 * B * 4.0 * Hs * Ws * 32 * 9 * Cin, stream, B, Hs, Ws, Cin);
   using namespace deb;
   if (!x || !w || !head_w || !out) return fail(DE_ERR_INVALID, "de_head_up_conv: null pointer");
   if (B < 1 || Hs < 1 || Ws < 1 || Cin < 64 || Cin % 64 != 0) return fail(DE_ERR_UNSUPPORTED, "de_head_up_conv: Cin=%d must be a multiple of 64", Cin);

@@ -13,8 +13,18 @@ int cuda_fail(cudaError_t e, const char* what);
 int cuda_check_launch(const char* what);
 void count_launch();
 int num_sms();
-// programmatic dependent launch per kernel class (1 GEMM, 2 attention / head, 4 LayerNorm); DEB_PDL=<mask>, default 3
+// programmatic dependent launch per kernel class (1 GEMM, 2 attention / head, 4 LayerNorm, 8 depthwise); DEB_PDL=<mask>,
+// default 11
 bool pdl_enabled(int cls);
+
+// Optional per-operator timing (de_profile_start / de_profile_stop): when enabled, every operator entry point brackets
+// its launches with CUDA events on the stream it was given.  Off by default; not usable during stream capture.
+struct ProfScope {
+  int idx = -1;
+  void* stream = nullptr;
+  ProfScope(const char* name, double flops, void* stream, int64_t d0 = 0, int64_t d1 = 0, int64_t d2 = 0, int64_t d3 = 0);
+  ~ProfScope();
+};
 
 typedef CUresult (*TensorMapEncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                            const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,

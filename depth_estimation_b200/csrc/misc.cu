@@ -258,6 +258,46 @@ DEV void store_split3(__nv_bfloat16* out, long long row, int C, int c0, const fl
   *reinterpret_cast<uint4*>(o + 2 * C) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
 }
 
+// Bilinear x2 for the bf16x3 ("split3") decoder: fp32 or bf16 NHWC in; fp32 NHWC, plain bf16 or split3 [hi | hi | lo] out.
+// One thread per (output pixel, 8 channels); same coordinate rule as upsample2x_kernel.
+__global__ void __launch_bounds__(256) upsample2x_ex_kernel(const void* __restrict__ x, int x_f32, void* __restrict__ out,
+                                                            int out_mode, int B, int H, int W, int C, int align_corners) {
+  const int cg = C >> 3;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int OH = 2 * H, OW = 2 * W;
+  if (i >= (long long)B * OH * OW * cg) return;
+  const int c = static_cast<int>(i % cg) * 8;
+  const long long pix = i / cg;
+  const int ox = static_cast<int>(pix % OW);
+  const int oy = static_cast<int>((pix / OW) % OH);
+  const int b = static_cast<int>(pix / ((long long)OW * OH));
+  const float rh = OH > 1 ? (float)(H - 1) / (float)(OH - 1) : 0.f;
+  const float rw = OW > 1 ? (float)(W - 1) / (float)(OW - 1) : 0.f;
+  const float sx = align_corners ? rw * ox : fmaxf(0.5f * (ox + 0.5f) - 0.5f, 0.f);
+  const float sy = align_corners ? rh * oy : fmaxf(0.5f * (oy + 0.5f) - 0.5f, 0.f);
+  const int x0 = min(static_cast<int>(sx), W - 1), x1 = min(x0 + 1, W - 1);
+  const int y0 = min(static_cast<int>(sy), H - 1), y1 = min(y0 + 1, H - 1);
+  const float lx = sx - x0, hx = 1.f - lx, ly = sy - y0, hy = 1.f - ly;
+  const long long base = (long long)b * H * W;
+  float a[8], bb[8], cc[8], d[8], f[8];
+  load8(x, x_f32, ((base + (long long)y0 * W + x0) * C) + c, a);
+  load8(x, x_f32, ((base + (long long)y0 * W + x1) * C) + c, bb);
+  load8(x, x_f32, ((base + (long long)y1 * W + x0) * C) + c, cc);
+  load8(x, x_f32, ((base + (long long)y1 * W + x1) * C) + c, d);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) f[j] = hy * (hx * a[j] + lx * bb[j]) + ly * (hx * cc[j] + lx * d[j]);
+  if (out_mode == 2) {
+    float* o = reinterpret_cast<float*>(out) + pix * C + c;
+    *reinterpret_cast<float4*>(o) = make_float4(f[0], f[1], f[2], f[3]);
+    *reinterpret_cast<float4*>(o + 4) = make_float4(f[4], f[5], f[6], f[7]);
+  } else if (out_mode == 1) {
+    store_split3(reinterpret_cast<__nv_bfloat16*>(out), pix, C, c, f);
+  } else {
+    *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(out) + pix * C + c) =
+        make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+  }
+}
+
 // Pass 1 of 2: per-CTA partial sums; the LAST CTA of a sample to finish (arrival counter in the workspace, left at
 // zero again) reduces that sample's partials in a fixed order - one warp per group, lane-strided double sums and a
 // shuffle tree - and writes (mean, rstd).  Deterministic, and no separate finalize launch: at batch 1 the old
@@ -408,6 +448,7 @@ using namespace deb;
 
 extern "C" int de_layernorm(float* x, int64_t ldx, const void* y, int y_dtype, int64_t ldy, const float* gamma,
                             const float* beta, int rows, int dim, float eps, void* out_bf16, int64_t ldo, void* stream) {
+  deb::ProfScope prof_("layernorm", 0.0, stream, rows, dim);
   if (!x || rows <= 0 || (out_bf16 && (!gamma || !beta)) || (!out_bf16 && !y))
     return fail(DE_ERR_INVALID, "de_layernorm: bad args");
   if (dim % 128 != 0 || dim > 1024 || ldx % 4 != 0 || ldo % 4 != 0 || (y && ldy % 4 != 0))
@@ -426,6 +467,7 @@ extern "C" int de_layernorm(float* x, int64_t ldx, const void* y, int y_dtype, i
 
 extern "C" int de_cast_tokens(const float* x, int64_t ldx, int rows, int dim, int grp, int skip, void* out_bf16,
                               void* stream) {
+  deb::ProfScope prof_("cast_tokens", 0.0, stream, rows, dim);
   if (!x || !out_bf16 || rows <= 0 || dim % 8 != 0) return fail(DE_ERR_INVALID, "de_cast_tokens: bad args");
   long long out_rows = rows;
   if (grp > 0) {
@@ -441,6 +483,7 @@ extern "C" int de_cast_tokens(const float* x, int64_t ldx, int rows, int dim, in
 
 extern "C" int de_fill_cls(float* x, int64_t ldx, int B, int T, int dim, const float* cls, const float* pos,
                            void* stream) {
+  deb::ProfScope prof_("fill_cls", 0.0, stream, B, T, dim);
   if (!x || !cls || !pos) return fail(DE_ERR_INVALID, "de_fill_cls: bad args");
   fill_cls_kernel<<<(B * dim + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(x, ldx, B, T, dim, cls, pos);
   count_launch();
@@ -448,6 +491,7 @@ extern "C" int de_fill_cls(float* x, int64_t ldx, int B, int T, int dim, const f
 }
 
 extern "C" int de_upsample2x(const void* x, void* out, int B, int H, int W, int C, int align_corners, void* stream) {
+  deb::ProfScope prof_("upsample2x", 0.0, stream, B, H, W, C);
   if (!x || !out || C % 8 != 0) return fail(DE_ERR_INVALID, "de_upsample2x: bad args (C %% 8)");
   if (B > 65535 || 2 * H > 65535) return fail(DE_ERR_UNSUPPORTED, "de_upsample2x: B / 2H exceed the grid limits");
   const bool wide = C % 16 == 0 && ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out)) & 31) == 0;
@@ -466,8 +510,21 @@ extern "C" int de_upsample2x(const void* x, void* out, int B, int H, int W, int 
   return cuda_check_launch("upsample2x_kernel");
 }
 
+extern "C" int de_upsample2x_ex(const void* x, int x_dtype, void* out, int out_mode, int B, int H, int W, int C,
+                                int align_corners, void* stream) {
+  deb::ProfScope prof_("upsample2x_ex", 0.0, stream, B, H, W, C);
+  if (!x || !out || C % 8 != 0 || out_mode < 0 || out_mode > 2 || (x_dtype != DE_DTYPE_BF16 && x_dtype != DE_DTYPE_F32))
+    return fail(DE_ERR_INVALID, "de_upsample2x_ex: bad args (C %% 8, out_mode 0..2)");
+  const long long n = 4LL * B * H * W * (C / 8);
+  upsample2x_ex_kernel<<<(unsigned)((n + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      x, x_dtype == DE_DTYPE_F32, out, out_mode, B, H, W, C, align_corners);
+  count_launch();
+  return cuda_check_launch("upsample2x_ex_kernel");
+}
+
 extern "C" int de_im2col3x3(const void* x, void* out, int B, int H, int W, int C, int stride, int pad_y, int pad_x,
                             int Ho, int Wo, void* stream) {
+  deb::ProfScope prof_("im2col3x3", 0.0, stream, B, H, W, C);
   if (!x || !out || C % 8 != 0 || stride < 1 || Ho < 1 || Wo < 1) return fail(DE_ERR_INVALID, "de_im2col3x3: bad args");
   const long long n = (long long)B * Ho * Wo * 9 * (C / 8);
   im2col3x3_kernel<<<(unsigned)((n + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
@@ -478,6 +535,7 @@ extern "C" int de_im2col3x3(const void* x, void* out, int B, int H, int W, int C
 }
 
 extern "C" int de_subsample(const void* x, void* out, int B, int H, int W, int C, int stride, void* stream) {
+  deb::ProfScope prof_("subsample", 0.0, stream, B, H, W, C);
   if (!x || !out || C % 8 != 0 || stride < 1) return fail(DE_ERR_INVALID, "de_subsample: bad args");
   const int Ho = (H + stride - 1) / stride, Wo = (W + stride - 1) / stride;
   const long long n = (long long)B * Ho * Wo * (C / 8);
@@ -511,6 +569,7 @@ extern "C" int64_t de_groupnorm_ws_bytes(int B, int HW, int C, int groups) {
 extern "C" int de_groupnorm(const void* x, int x_dtype, const float* gamma, const float* beta, const void* add,
                             int add_dtype, void* out, int out_mode, float* out_f32, void* out_plain, int B, int HW, int C,
                             int groups, float eps, int act, void* ws, int64_t ws_bytes, void* stream) {
+  deb::ProfScope prof_("groupnorm", 0.0, stream, B, HW, C);
   if (!x || !gamma || !beta || !ws || (!out && !out_f32 && !out_plain)) return fail(DE_ERR_INVALID, "de_groupnorm: null pointer");
   if (C % 8 != 0 || C > 2048 || groups > 64 || groups < 1 || C % groups != 0 || 256 % (C / 8) != 0)
     return fail(DE_ERR_UNSUPPORTED, "de_groupnorm: C=%d groups=%d unsupported", C, groups);

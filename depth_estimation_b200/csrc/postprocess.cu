@@ -254,6 +254,7 @@ __global__ void sample_kernel(const PostParams p, int B, const int32_t* sample_r
 extern "C" int de_postprocess(const void* pred, int in_dtype, int B, int h, int w, int H, int W, float* out_map,
                               void* out_metric, float metric_scale, float metric_shift, uint8_t* out_vis, const int32_t* sample_rc,
                               int n_samples, float* out_samples, void* stream) {
+  deb::ProfScope prof_("postprocess", 0.0, stream, B, h * w, H, W);
   using namespace deb;
   if (!pred || B <= 0 || h <= 0 || w <= 0 || H <= 0 || W <= 0) return fail(DE_ERR_INVALID, "de_postprocess: bad args");
   if (in_dtype != DE_DTYPE_F32 && in_dtype != DE_DTYPE_BF16) return fail(DE_ERR_INVALID, "de_postprocess: in_dtype");

@@ -349,6 +349,7 @@ __global__ void __launch_bounds__(256) preprocess_copy16_kernel(const PreParams 
 static int run_preprocess(const uint8_t* bgr, const uint8_t* uv, int64_t uv_row_stride, int64_t uv_frame_stride, int B,
                           int H, int W, int64_t row_stride, int64_t frame_stride, int net_h, int net_w,
                           const float* mean_host, const float* std_host, int layout, void* out, void* stream) {
+  deb::ProfScope prof_("preprocess", 0.0, stream, B, H, W, (int64_t)net_h * net_w);
   using namespace deb;
   const int format = uv ? 1 : 0;
   if (!bgr || !out || B <= 0 || H <= 0 || W <= 0) return fail(DE_ERR_INVALID, "de_preprocess: bad args");

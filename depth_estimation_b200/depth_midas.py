@@ -4,7 +4,8 @@
 
 What changes underneath (and nothing else): cvtColor + the MiDaS transform chain (:22-23) is one fused
 kernel (K1), the hub model forward (:25-26) is the tcgen05 GEMM / implicit-conv / attention launch
-sequence in dpt.py / midas_small.py, and the bicubic resize back to the frame size (:28-33) is K8.  There
+sequence of the C++ engine (csrc/engine_nets.cu, reached through de_predict), and the bicubic resize back to the
+frame size (:28-33) is K8.  There
 is no CPU fallback: without a CUDA device or the built library the constructor raises.
 """
 from __future__ import annotations
@@ -16,6 +17,7 @@ import numpy as np
 import torch
 
 from . import ops
+from .engine import Engine
 from .init import random_state_dict
 
 MODEL_TYPES = ("DPT_Large", "DPT_Hybrid", "MiDaS_small")
@@ -41,10 +43,16 @@ class _Transforms:
 
 
 class DepthEstimator(object):
-    def __init__(self, model_type, *, weights=None, seed=0, device=None, use_cuda_graph=True):
+    def __init__(self, model_type, *, weights=None, seed=0, device=None, use_cuda_graph=True, precision=None):
         """model_type: "DPT_Large" | "DPT_Hybrid" | "MiDaS_small" (anything else gets the small transform,
         as at depth_midas.py:13-16, and is rejected by the model factory).
-        weights: upstream-format state_dict, a path to one (torch.load), or None for seeded random init."""
+        weights: upstream-format state_dict, a path to one (torch.load), or None for seeded random init.
+        precision: None = the model's default arithmetic (bf16 operands / fp32 accumulate; DPT_Hybrid: ResNetV2 stages
+        and decoder as bf16x3); "bf16" = plain bf16 operands wherever the model tolerates them (DPT_Hybrid: decoder in
+        bf16 - faster, 1.3e-3 from the fp32 reference instead of < 1e-3)."""
+        if precision not in (None, "bf16"):
+            raise ValueError(f"precision {precision!r}: expected None or 'bf16'")
+        self.precision = precision
         self.model_type = model_type
         print(f'Loading model: {self.model_type}')
         if not torch.cuda.is_available():
@@ -56,8 +64,12 @@ class DepthEstimator(object):
         else:
             from .weights import load_checkpoint
             weights = load_checkpoint(weights, model_type)      # path or mapping in upstream naming, validated
+        if model_type not in MODEL_TYPES:
+            raise ValueError(f"unknown model_type {model_type!r}; expected one of {MODEL_TYPES}")
         with torch.cuda.device(self.device):
-            self.estimator = _build_net(model_type, weights, self.device)
+            # the C++ engine behind the handle-level C ABI (de_create .. de_predict): packed weights, work buffers,
+            # launch sequences of the hub model - what `torch.hub.load` returns at depth_midas.py:10
+            self.estimator = Engine(model_type, weights, self.device, precision)
         print('Loading transforms...')
         self.midas_transforms = _Transforms(self)
         if self.model_type == "DPT_Large" or self.model_type == "DPT_Hybrid":
@@ -139,11 +151,8 @@ class DepthEstimator(object):
             t = torch.from_numpy(a).to(self.device)
             y = t[:, :H]
             uv = t[:, H:].reshape(B, H // 2, W // 2, 2)
-            net_w, net_h = ops.get_size(W, H, self.model_type)
-            mean, std = self._norm
-            x = ops.preprocess_nv12(y, uv, net_h, net_w, mean, std, self.estimator.preprocess_layout)
-            pred = self.estimator.forward(x, B, net_h, net_w)
-            out, _, _ = ops.postprocess(pred, H, W)
+            out = torch.empty((B, H, W), dtype=torch.float32, device=self.device)
+            self.estimator.predict(B, H, W, y, uv=uv, out_map=out)
             res = out.cpu().numpy()
         return res[0] if single else res
 
@@ -254,16 +263,20 @@ class _Plan:
         self.graph = None
         self._dev_graph = None
         self._warm = False
+        self._d_samples = None
+        est.estimator.plan(B, H, W)                             # work buffers + warm-up now, not inside a capture
 
     def _compute(self, src):
+        """K1 -> network -> K8 on the current stream: one call into the engine (de_predict)."""
         est = self.est
-        mean, std = est._norm
-        net = est.estimator
-        x = ops.preprocess(src, self.net_h, self.net_w, mean, std, net.preprocess_layout)
-        pred = net.forward(x, self.B, self.net_h, self.net_w)
-        rc = self.d_rc if self.n_samples else None
-        _, _, samples = ops.postprocess(pred, self.H, self.W, want_map=True, want_metric=self.want_metric,
-                                        metric_scale=est.metric_affine[0], metric_shift=est.metric_affine[1], sample_rc=rc, out_map=self.d_map, out_metric=self.d_metric, out_vis=self.d_vis)
+        samples = None
+        if self.n_samples:
+            if self._d_samples is None:
+                self._d_samples = torch.empty((self.B, self.n_samples), dtype=torch.float32, device=est.device)
+            samples = self._d_samples
+        est.estimator.predict(self.B, self.H, self.W, src, out_map=self.d_map, out_metric=self.d_metric,
+                              metric_scale=est.metric_affine[0], metric_shift=est.metric_affine[1], out_vis=self.d_vis,
+                              sample_rc=self.d_rc if self.n_samples else None, out_samples=samples)
         return samples
 
     def _body(self):
@@ -411,19 +424,6 @@ class _Done:
 
     def result(self):
         return self._value
-
-
-def _build_net(model_type, sd, device):
-    if model_type == "DPT_Large":
-        from .dpt import DPTLargeNet
-        return DPTLargeNet(sd, device)
-    if model_type == "DPT_Hybrid":
-        from .dpt_hybrid import DPTHybridNet
-        return DPTHybridNet(sd, device)
-    if model_type == "MiDaS_small":
-        from .midas_small import MidasSmallNet
-        return MidasSmallNet(sd, device)
-    raise ValueError(f"unknown model_type {model_type!r}; expected one of {MODEL_TYPES}")
 
 
 class VidStream(object):

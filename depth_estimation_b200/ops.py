@@ -134,7 +134,8 @@ def postprocess(pred: torch.Tensor, H: int, W: int, want_map: bool = True, want_
 # ------------------------------------------------------------------------------- GEMM / conv
 def gemm(a: torch.Tensor, w: torch.Tensor, out: torch.Tensor, *, M=None, N=None, K=None, bias=None, act=ACT_NONE,
          add1=None, add1_rowmode=0, add1_pre=False, ld_add1=None, add2=None, out_relu=None, out_rowmode=0, grp=0,
-         pad=0, off=0, ldo=None, conv=None, pixel_shuffle=None, bias_mod=0, head=None, block_n=0, cta_group=0, epilogue=0, accumulate=False):
+         pad=0, off=0, ldo=None, conv=None, pixel_shuffle=None, bias_mod=0, head=None, block_n=0, cta_group=0, epilogue=0, accumulate=False,
+         out_split=False, relu_split=False, ld_relu=None):
     """out = epilogue(a @ w.T) through de_gemm (accumulate=True: out += ..., fp32 dense output only).  a: bf16 [M,K] (or NHWC [B,H,W,Cin] with conv=(B,H,W,Cin));
     w: bf16 [N,K].  See include/depth_b200.h for the epilogue contract."""
     _need_cuda(a, w, out, bias, add1, add2, out_relu)
@@ -166,14 +167,18 @@ def gemm(a: torch.Tensor, w: torch.Tensor, out: torch.Tensor, *, M=None, N=None,
         g.add1_rowmode = int(add1_rowmode)
         g.add1_pre = 1 if add1_pre else 0
     if add2 is not None:
-        assert add2.dtype == torch.bfloat16
         g.add2 = add2.data_ptr()
+        g.add2_dtype = _dt(add2)
+        g.ld_add2 = int(add2.stride(-2)) if pixel_shuffle is None else 0
     g.out = out.data_ptr()
     g.out_dtype = _dt(out)
     g.ldo = int(ldo if ldo is not None else (out.stride(-2) if out.dim() >= 2 else 1))
     if out_relu is not None:
         assert out_relu.dtype == torch.bfloat16
         g.out_relu = out_relu.data_ptr()
+        g.ld_relu = int(ld_relu if ld_relu is not None else (out_relu.stride(-2) if pixel_shuffle is None else 0))
+    g.out_split = 1 if out_split else 0
+    g.relu_split = 1 if relu_split else 0
     g.out_rowmode = int(out_rowmode)
     g.grp, g.pad, g.off = int(grp), int(pad), int(off)
     if pixel_shuffle is not None:
@@ -233,6 +238,18 @@ def upsample2x(x: torch.Tensor, out: torch.Tensor, align_corners: bool):
     assert x.dtype == torch.bfloat16 and x.is_contiguous() and out.is_contiguous()
     _lib.check(_lib.load().de_upsample2x(x.data_ptr(), out.data_ptr(), B, H, W, Cc, 1 if align_corners else 0,
                                          _stream()), "de_upsample2x")
+    return out
+
+
+def upsample2x_ex(x: torch.Tensor, out: torch.Tensor, align_corners: bool, split: bool = False):
+    """x: bf16 / f32 NHWC [B,H,W,C] -> out: f32 [B,2H,2W,C], bf16 [B,2H,2W,C], or (split) the split3 operand [B,2H,2W,3C]."""
+    _need_cuda(x, out)
+    B, H, W, Cc = x.shape
+    assert x.is_contiguous() and out.is_contiguous()
+    mode = 2 if out.dtype == torch.float32 else (1 if split else 0)
+    assert out.shape[-1] == (3 * Cc if mode == 1 else Cc) and (mode == 2 or out.dtype == torch.bfloat16)
+    _lib.check(_lib.load().de_upsample2x_ex(x.data_ptr(), _dt(x), out.data_ptr(), mode, B, H, W, Cc,
+                                            1 if align_corners else 0, _stream()), "de_upsample2x_ex")
     return out
 
 

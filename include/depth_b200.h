@@ -38,6 +38,19 @@ int de_version(void);
 /* Number of kernels this library has launched in the calling process (bench.py "gpu_launches"). */
 int64_t de_launch_count(void);
 
+/* Per-operator timing for measurement runs (bench.py's roofline): between de_profile_start and de_profile_stop every
+ * operator entry point of this library brackets its launches with CUDA events on the stream it is given (eager launches
+ * only; calls recorded into a stream capture are skipped).  de_profile_stop synchronises the device and returns one
+ * record per call in issue order.  dims: operator-specific extents (de_gemm: M, N, K, a_mode*100 + act*10 + accumulate). */
+typedef struct DeProfileRecord {
+  char name[24];
+  double ms;
+  double flops; /* algorithmic 2*MACs of the call; 0 for bandwidth operators */
+  int64_t dims[4];
+} DeProfileRecord;
+int de_profile_start(void);
+int de_profile_stop(DeProfileRecord* out, int max_records, int* n_records);
+
 /* ---- get_size: [UPSTREAM] midas/transforms.py Resize.get_size, reached from depth_midas.py:23.
  * method 0 = "upper_bound" (small_transform, T=256), 1 = "minimal" (dpt_transform, T=384). */
 int de_get_size(int width, int height, int target, int method, int* net_w, int* net_h);
@@ -111,11 +124,11 @@ typedef struct DeGemm {
   int64_t ld_add1;
   int add1_rowmode;
   int add1_pre;
-  const void* add2; /* bf16, storage row of out, ld = ldo */
+  const void* add2; /* bf16 or f32 (add2_dtype), storage row of out, pitch ld_add2 */
   void* out;
   int out_dtype;
   int64_t ldo;
-  void* out_relu; /* bf16, same rows/ld as out */
+  void* out_relu; /* bf16, same rows as out, pitch ld_relu */
   int out_rowmode;
   int grp, pad, off;
   int ps_gh, ps_gw, ps_s, ps_cout; /* out_rowmode 2 */
@@ -125,6 +138,14 @@ typedef struct DeGemm {
   int epilogue;  /* 0 = auto (TMA-store epilogue whenever the call is bias + activation -> dense output); 1 = always
                   * the general register epilogue (cross-check of the two code paths) */
   int cta_group; /* 0 = auto; 1 = one CTA per 128-row tile; 2 = CTA pair per 256-row tile (block_n 256) */
+  /* bf16x3 ("split3") plumbing, general epilogue only.  A split3 operand row is [hi | hi | lo] (hi = bf16(v),
+   * lo = bf16(v - hi)), each part N (pixel shuffle: ps_cout) wide; against weights packed [Wh | Wl | Wh] along K the
+   * ordinary bf16 MMA accumulates Ah*Wh + Ah*Wl + Al*Wh in fp32 (~16 mantissa bits). */
+  int out_split;     /* 1: `out` (bf16, ldo >= 3N) is written as a split3 row */
+  int relu_split;    /* 1: `out_relu` is written as a split3 row */
+  int64_t ld_relu;   /* row pitch of out_relu in elements; 0 = ldo */
+  int add2_dtype;    /* DE_DTYPE_BF16 (default) or DE_DTYPE_F32 (requires add1_pre == 0) */
+  int64_t ld_add2;   /* row pitch of add2 in elements; 0 = ldo (pixel shuffle: ps_cout) */
   int accumulate; /* 1: out += epilogue(A W^T) instead of out = ... (fp32 dense output, a_mode 0, bias + activation
                    * only): the tile leaves through a TMA reduce-add, so the ViT residual stream x += proj(..) /
                    * x += fc2(..) needs neither a bf16 branch buffer nor an add pass.  Each element receives exactly one
@@ -154,6 +175,10 @@ int de_fill_cls(float* x, int64_t ldx, int B, int T, int dim, const float* cls, 
                 void* stream);
 /* bilinear x2 upsample NHWC bf16 [B,H,W,C] -> [B,2H,2W,C]; align_corners 1/0. */
 int de_upsample2x(const void* x, void* out, int B, int H, int W, int C, int align_corners, void* stream);
+/* The same resampling for the bf16x3 decoder: x NHWC bf16 or f32 (x_dtype); out_mode 0: bf16 [B,2H,2W,C]; 1: split3 bf16
+ * [B,2H,2W,3C] = [hi | hi | lo] (see DeGemm.out_split); 2: f32 [B,2H,2W,C]. */
+int de_upsample2x_ex(const void* x, int x_dtype, void* out, int out_mode, int B, int H, int W, int C, int align_corners,
+                     void* stream);
 /* im2col for a 3x3 window, stride s, explicit leading pad: NHWC bf16 -> [B*Ho*Wo, 9*C], k = tap*C + c.
  * torch Conv2d(k3,s2,p1) (act_postprocess4): pad 1, Ho = (H-1)/2+1.  TF-same s2 (ResNetV2): pad
  * ((ceil(H/2)-1)*2+3-H)/2, Ho = ceil(H/2). */
@@ -207,6 +232,58 @@ int de_depthwise(const void* x, const void* w_tapmajor, const float* bias, void*
                  int k, int stride, int act, void* stream);
 /* MaxPool 3x3 stride 2 TF-same, NHWC bf16 or f32 in; out bf16 [.., C] (out_mode 0) or split3 [.., 3C] (1). */
 int de_maxpool3x3s2(const void* x, int x_dtype, void* out, int out_mode, int B, int H, int W, int C, void* stream);
+
+/* ================================================================================================================
+ * Handle-level API: the whole of DepthEstimator (/root/reference/depth_midas.py:6-35) for a host
+ * that is not Python.  de_create == `__init__` up to the hub load (:7-19), de_set_weight / de_finalize_weights take the
+ * place of `torch.hub.load(...)`'s checkpoint (upstream state_dict naming; BatchNorm / weight standardisation folded
+ * and everything repacked into the kernel-native layouts once), de_predict == `predict` (:21-35) for B frames that are
+ * already in device memory.  One handle per GPU; calls on one handle must be serialised by the caller; distinct handles
+ * may be used from distinct threads.  Nothing throws across the ABI.
+ * ================================================================================================================ */
+typedef struct de_engine* de_handle;
+
+#define DE_PRECISION_DEFAULT 0 /* bf16 operands / fp32 accumulate; DPT_Hybrid: ResNetV2 stages + decoder as bf16x3 */
+#define DE_PRECISION_BF16 1    /* DPT_Hybrid: decoder on plain bf16 operands (faster; 1.3e-3 instead of < 1e-3) */
+
+/* model_type: "DPT_Large" | "DPT_Hybrid" | "MiDaS_small" (the strings of depth_midas.py:91-93). */
+int de_create(const char* model_type, int device, int precision, de_handle* out);
+/* One tensor of the model's state_dict under its upstream key (e.g. "pretrained.model.blocks.0.attn.qkv.weight",
+ * "scratch.refinenet1.out_conv.bias"; SURVEY.md 8a footer), host memory, dtype DE_DTYPE_F32 or DE_DTYPE_BF16.  The
+ * data is copied.  Keys the forward pass never reads are accepted and ignored. */
+int de_set_weight(de_handle h, const char* upstream_key, const void* host_ptr, const int64_t* shape, int ndim, int dtype);
+/* Validates that every tensor the architecture needs is present with the right shape, folds and repacks, uploads.
+ * Fails with the offending key in de_last_error(). */
+int de_finalize_weights(de_handle h);
+/* Prepares the geometry (B frames of H x W): Resize.get_size, work buffers, one eager warm-up pass (synchronous).
+ * Optional - de_predict plans on first use - but required before a de_predict that is issued inside a stream capture. */
+int de_plan(de_handle h, int B, int H, int W, int* net_h, int* net_w);
+
+typedef struct DePredictIO {
+  const uint8_t* frames;  /* device: uint8 BGR [B,H,W,3] as cv2 delivers it - or, with uv != NULL, the NV12 Y plane [B,H,W] */
+  int64_t row_stride;     /* bytes; 0 = dense */
+  int64_t frame_stride;   /* bytes; 0 = dense */
+  const uint8_t* uv;      /* device: NV12 interleaved UV plane [B,H/2,W/2,2], or NULL for BGR input */
+  int64_t uv_row_stride, uv_frame_stride; /* bytes; 0 = dense */
+  float* out_map;         /* device float [B,H,W]: relative inverse depth at source resolution (depth_midas.py:28-34), or NULL */
+  void* out_metric;       /* device bf16 [B,H,W] = map * metric_scale + metric_shift (face.py:137: 1/2.54, 0), or NULL */
+  float metric_scale, metric_shift;
+  uint8_t* out_vis;       /* device uint8 [B,H,W]: to_video_frame grey level (midas_mediapipe.py:141-150), or NULL */
+  const int32_t* sample_rc; /* device int32 [B,n_samples,2] (row, col) into the output map, or NULL */
+  int n_samples;
+  float* out_samples;     /* device float [B,n_samples] */
+} DePredictIO;
+/* K1 -> network -> K8 for B frames, enqueued on `stream`, no synchronisation once the geometry is planned.
+ * use_graph != 0: the launch sequence for this (geometry, IO pointers) is captured into a CUDA graph on first use
+ * and replayed afterwards (keep the buffers stable).  When `stream` is itself being captured, the kernels are simply
+ * recorded into the caller's graph. */
+int de_predict(de_handle h, int B, int H, int W, const DePredictIO* io, int use_graph, void* stream);
+/* The network alone (depth_midas.py:25-26): returns the plan's input buffer (what de_preprocess must write for this
+ * model: de_engine_info layout) and its output buffer float [B,net_h,net_w]; run != 0 enqueues the forward pass. */
+int de_forward(de_handle h, int B, int H, int W, void** net_input, float** pred, int* net_h, int* net_w, int run, void* stream);
+/* layout: the de_preprocess layout this model consumes; bytes of packed weights / of all planned work buffers. */
+int de_engine_info(de_handle h, int* layout, int64_t* weight_bytes, int64_t* work_bytes);
+void de_destroy(de_handle h);
 
 #ifdef __cplusplus
 }

@@ -68,6 +68,25 @@ def test_predict_matches_oracle(mt, W, H, kind):
     assert np.abs(metric[0] - ref / 2.54).max() / np.abs(ref / 2.54).max() < 1e-2
 
 
+def test_hybrid_plain_bf16_decoder_option():
+    """precision="bf16" keeps DPT_Hybrid's decoder on plain bf16 operands (the faster round-1 arithmetic): same map up to
+    the documented 2e-3, and measurably further from the oracle than the default bf16x3 decoder."""
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    from depth_estimation_b200.depth_midas import DepthEstimator
+    from oracle.predict import OracleDepthEstimator, build_model, synthetic_frame
+    model = build_model("DPT_Hybrid", seed=0)
+    frame = synthetic_frame(384, 384, 3, "S")
+    ref = OracleDepthEstimator("DPT_Hybrid", model=model).predict(frame)
+    fast = DepthEstimator("DPT_Hybrid", weights=model.state_dict(), precision="bf16").predict(frame)
+    best = DepthEstimator("DPT_Hybrid", weights=model.state_dict()).predict(frame)
+    (r_fast, _, _), (r_best, _, _) = _errs(fast, ref), _errs(best, ref)
+    print(f"DPT_Hybrid decoder bf16: rel={r_fast:.3e}; bf16x3 (default): rel={r_best:.3e}")
+    assert r_fast < 2e-3 and r_best < REL_TOL and r_best < r_fast
+    with pytest.raises(ValueError):
+        DepthEstimator("DPT_Hybrid", precision="fp64")
+
+
 def test_bench_configuration_matches_oracle():
     """The configuration bench.py times - predict_batch on 32 DPT_Large 384^2 frames, i.e. M = 18464 token rows through
     the CTA-pair 256-wide GEMM tiles - checked against the oracle on frames 0, 13 and 31 of the batch."""

@@ -761,6 +761,83 @@ def test_split3_gemm_precision(conv):
     assert e3 < 3e-5 and e3 < e1 / 30
 
 
+def _split3_ref(v):
+    hi = v.bfloat16()
+    lo = (v - hi.float()).bfloat16()
+    return torch.cat([hi, hi, lo], dim=-1)
+
+
+@pytest.mark.parametrize("pixel_shuffle", [False, True])
+def test_gemm_split3_outputs(pixel_shuffle):
+    """General epilogue writing split3 rows: `out` as [hi | hi | lo] of v, `out_relu` as the split3 of relu(v) next to
+    an fp32 `out`, fp32 add1 + fp32 add2 skip inputs - the plumbing of the bf16x3 decoder."""
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    B, H, W, Cin, Cout = 2, 12, 20, 128, 64
+    a = _rand((B, H, W, Cin), dev, seed=81).bfloat16()
+    w = _rand((Cout, Cin, 3, 3), dev, 0.05, seed=82)
+    bias = _rand((Cout,), dev, seed=83)
+    add1 = _rand((B, H, W, Cout), dev, seed=84)
+    add2 = _rand((B, H, W, Cout), dev, seed=85)
+    from depth_estimation_b200.weights import pack_conv3x3
+    wp = pack_conv3x3(w)
+    ref = F.conv2d(a.float().permute(0, 3, 1, 2), w.bfloat16().float(), bias, padding=1).permute(0, 2, 3, 1) + add1 + add2
+    if not pixel_shuffle:
+        # (1) fp32 out + split3 relu copy
+        o32 = torch.empty((B, H, W, Cout), dtype=torch.float32, device=dev)
+        r3 = torch.full((B, H, W, 3 * Cout), float("nan"), dtype=torch.bfloat16, device=dev)
+        ops.gemm(a, wp, o32.view(-1, Cout), conv=(B, H, W, Cin), N=Cout, bias=bias, add1=add1.view(-1, Cout), add2=add2,
+                 out_relu=r3, relu_split=True)
+        torch.cuda.synchronize()
+        assert _relerr(o32, ref) < 1e-5
+        assert torch.equal(r3, _split3_ref(F.relu(o32)))
+        # (2) split3 out (+ plain bf16 relu copy)
+        o3 = torch.full((B, H, W, 3 * Cout), float("nan"), dtype=torch.bfloat16, device=dev)
+        rp = torch.empty((B, H, W, Cout), dtype=torch.bfloat16, device=dev)
+        ops.gemm(a, wp, o3.view(-1, 3 * Cout), conv=(B, H, W, Cin), N=Cout, bias=bias, add1=add1.view(-1, Cout), add2=add2,
+                 out_split=True, out_relu=rp)
+        torch.cuda.synchronize()
+        assert torch.equal(o3, _split3_ref(o32)) and torch.equal(rp, F.relu(o32).bfloat16())
+        hi, lo = o3[..., :Cout].float(), o3[..., 2 * Cout:].float()
+        assert _relerr(hi + lo, ref) < 3e-5                        # hi + lo carries ~16 mantissa bits
+        with pytest.raises(RuntimeError):
+            ops.gemm(a, wp, o32.view(-1, Cout), conv=(B, H, W, Cin), N=Cout, out_split=True)
+    else:
+        # ConvTranspose(k == s) pixel shuffle into split3 pixels [B, gh*s, gw*s, 3*cout]
+        gh, gw, s_, cin, cout = 6, 5, 2, 64, 32
+        x = _rand((B * gh * gw, cin), dev, seed=86).bfloat16()
+        wt = _rand((cin, cout, s_, s_), dev, 0.1, seed=87)
+        bt = _rand((cout,), dev, seed=88)
+        from depth_estimation_b200.weights import pack_conv_transpose
+        o3 = torch.full((B, gh * s_, gw * s_, 3 * cout), float("nan"), dtype=torch.bfloat16, device=dev)
+        ops.gemm(x, pack_conv_transpose(wt), o3, bias=bt, bias_mod=cout, pixel_shuffle=(gh, gw, s_, cout), out_split=True)
+        ref = F.conv_transpose2d(x.float().view(B, gh, gw, cin).permute(0, 3, 1, 2), wt.bfloat16().float(), bt, stride=s_)
+        ref = ref.permute(0, 2, 3, 1)
+        torch.cuda.synchronize()
+        assert torch.isfinite(o3.float()).all()
+        hi, lo = o3[..., :cout].float(), o3[..., 2 * cout:].float()
+        assert torch.equal(o3[..., :cout], o3[..., cout:2 * cout])
+        assert _relerr(hi + lo, ref) < 3e-5
+
+
+@pytest.mark.parametrize("ac", [True, False])
+def test_upsample2x_ex(ac):
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    x = _rand((2, 13, 21, 64), dev, seed=90)
+    ref = F.interpolate(x.permute(0, 3, 1, 2), scale_factor=2, mode="bilinear", align_corners=ac).permute(0, 2, 3, 1).contiguous()
+    o32 = torch.empty((2, 26, 42, 64), dtype=torch.float32, device=dev)
+    ops.upsample2x_ex(x, o32, ac)
+    o3 = torch.empty((2, 26, 42, 192), dtype=torch.bfloat16, device=dev)
+    ops.upsample2x_ex(x, o3, ac, split=True)
+    ob = torch.empty((2, 26, 42, 64), dtype=torch.bfloat16, device=dev)
+    ops.upsample2x_ex(x.bfloat16(), ob, ac)
+    torch.cuda.synchronize()
+    assert _relerr(o32, ref) < 1e-6
+    assert torch.equal(o3, _split3_ref(o32))
+    assert _relerr(ob, ref) < 1e-2
+
+
 # ------------------------------------------------------------------ SURVEY 8f N4: NV12 ingest, calibrated metric scale
 @pytest.mark.parametrize("H,W,mt,layout", [(480, 640, "MiDaS_small", 0), (360, 642, "DPT_Large", 1), (384, 384, "DPT_Large", 1),
                                            (256, 256, "MiDaS_small", 2)])
