@@ -43,7 +43,17 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-latency", action="store_true")
     ap.add_argument("--cpu-frames", type=int, default=0, help="frames in the bounded CPU sample (0 = auto)")
-    return ap.parse_args()
+    ap.add_argument("--workload", default="batch", choices=["batch", "stream720p"],
+                    help="stream720p = BASELINE config #4: MiDaS_small on a synthetic 1280x720 stream with iris points, "
+                         "through midas_mediapipe.VidStream (face/iris metric scaling per frame)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="strong: --batch is the TOTAL number of frames per step, sharded over the ranks (config #3: 32 -> 4/GPU x 8)")
+    ap.add_argument("--gather", action="store_true",
+                    help="gather every rank's maps on rank 0 over NCCL inside the timed step (sharding.gather_frames)")
+    a = ap.parse_args()
+    if a.workload == "stream720p":
+        a.model, a.width, a.height = "MiDaS_small", 1280, 720
+    return a
 
 
 def peaks():
@@ -189,6 +199,88 @@ def instrumented_step(est, frames_dev, B, H, W):
     return agg
 
 
+class _SyntheticIrisDetector:
+    """Stands in for detectors.PersonDetector (MediaPipe, host-side glue that is out of scope and not installable here):
+    SURVEY 8d D2 #4 - iris centres (x, y) drawn uniformly in-frame, radii 6-20 px, a face on every frame."""
+    HEAD = (0, 1)
+
+    def __init__(self, face, n, h, w, seed=20244):
+        import numpy as np
+        rng = np.random.default_rng(seed)
+        self.face = face
+        self.i = 0
+        # the reference indexes the map [x, y] (face.py:106-107), so x must stay below the row count
+        self.l = np.stack([rng.uniform(0, h - 1, n), rng.uniform(0, w - 1, n)], 1)
+        self.r = np.stack([rng.uniform(0, h - 1, n), rng.uniform(0, w - 1, n)], 1)
+        self.rad = rng.uniform(6, 20, (n, 2))
+        self.mesh = rng.uniform(0, min(h, w) - 1, (n, 2, 2))
+
+    def findIris(self, frame):
+        i = self.i % len(self.l)
+        self.i += 1
+        self.face.mesh = {0: tuple(self.mesh[i, 0]), 1: tuple(self.mesh[i, 1])}
+        self.face.l_iris = {"center": (float(self.l[i, 0]), float(self.l[i, 1])), "radius": float(self.rad[i, 0])}
+        self.face.r_iris = {"center": (float(self.r[i, 0]), float(self.r[i, 1])), "radius": float(self.rad[i, 1])}
+
+    def findBody(self, frame):
+        return frame, ((12, 30), (40, 34))
+
+    def visualize(self, frame):
+        pass
+
+
+def stream_workload(est, args, B, H, W, rank, world, dev, barrier):
+    """BASELINE config #4: the reference's stream loop (midas_mediapipe.py:32-129 - detector -> predict -> get_depth ->
+    rel2abs per frame) over a synthetic 720p stream, through depth_estimation_b200.midas_mediapipe.VidStream.  Timed:
+    host frames in, per-frame ri_depth / abs_depth + the uint8 video grey level out (fused K8 outputs, `batch` frames
+    per submission).  Video composition / codecs are out of scope (keep_outputs off).  Beside it: the strictly serial
+    loop of the reference (one blocking predict per frame) and equality of the numbers the two loops hand to FaceDet."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from depth_estimation_b200 import midas_mediapipe
+    from depth_estimation_b200.face import FaceDet
+    n_frames = B * args.steps
+    pool = synthetic_frames(64, H, W, 300 + rank)                 # 64 distinct frames (177 MB), cycled
+
+    def frames(n):
+        for i in range(n):
+            yield pool[i % 64]
+
+    def run(n, **kw):
+        face = FaceDet(20, [505, 504, 675, 501])
+        vs = midas_mediapipe.VidStream(est, _SyntheticIrisDetector(face, n, H, W), face, frames(n), None)
+        vs.keep_outputs = False
+        t0 = time.perf_counter()
+        vs.stream(max_frames=n, **kw)
+        torch.cuda.synchronize()
+        return face, vs, time.perf_counter() - t0
+
+    run(2 * B, fused=True, batch=B)                               # plans, graphs, pinned buffers
+    barrier()
+    face, vs, dt = run(n_frames, fused=True, batch=B)
+    assert vs.cnt == n_frames and len(face.ri_depths) == n_frames
+    n_ser = min(n_frames, 48)
+    run(4, pipelined=False)
+    face_s, vs_s, dt_s = run(n_ser, pipelined=False)
+    lat = np.sort(np.asarray(vs_s.performance["depth"])) * 1e3
+    equal = bool(face.ri_depths[:n_ser] == face_s.ri_depths and face.abs_depths[:n_ser] == face_s.abs_depths)
+    t = torch.tensor([dt], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dt = float(t.item())
+    e2e = {"value": world * n_frames / dt, "unit": UNIT, "h2d_bytes_per_step": int(B * H * W * 3 + B * 16),
+           "d2h_bytes_per_step": int(B * H * W + B * 8), "ms_per_step": 1e3 * dt / args.steps,
+           "api": f"midas_mediapipe.VidStream.stream(fused=True, batch={B}) over DepthEstimator.predict_stream_fused: "
+                  "K8 gathers the two iris samples and emits the uint8 grey level; the fp32 map stays on the device"}
+    stream = {"frames": n_frames, "frames_per_submission": B, "fused_fps": world * n_frames / dt,
+              "serial_loop": {"frames": n_ser, "fps": n_ser / dt_s, "p50_ms": float(lat[len(lat) // 2]),
+                              "what": "reference order, one blocking DepthEstimator.predict per frame (fp32 map to the host)"},
+              "ri_depth_abs_depth_equal_to_serial_loop": equal,
+              "ri_depth_first3": [float(x) for x in face.ri_depths[:3]], "abs_depth_first3": [float(x) for x in face.abs_depths[:3]]}
+    return e2e, stream
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -205,6 +297,10 @@ def run_ours(args):
     from depth_estimation_b200.depth_midas import DepthEstimator
 
     B, H, W = args.batch, args.height, args.width
+    if args.scaling == "strong":
+        if B % world != 0:
+            raise SystemExit(f"--scaling strong: --batch {B} must be divisible by the {world} ranks")
+        B //= world
     est = DepthEstimator(args.model, seed=0) if rank == 0 else None
     if rank != 0:
         import contextlib
@@ -228,11 +324,28 @@ def run_ours(args):
     clocks = ClockSampler(local)
     clocks.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    gather_ms = None
+    if args.gather:
+        from depth_estimation_b200 import sharding
+        sharding.gather_frames(est.predict_device(dev_sets[0]), world * B)         # NCCL communicator warm-up
+        barrier()
+    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    gsum = 0.0
     e0.record()
     for i in range(args.steps):
-        est.predict_device(dev_sets[i % n_sets])
+        maps_dev = est.predict_device(dev_sets[i % n_sets])
+        if args.gather:                              # north_star: "NCCL used only to gather per-frame outputs"
+            g0.record()
+            gathered = sharding.gather_frames(maps_dev, world * B)
+            g1.record()
+            if i == args.steps - 1:
+                g1.synchronize()
+                gsum = g0.elapsed_time(g1)
     e1.record()
     barrier()
+    if args.gather:
+        assert rank != 0 or tuple(gathered.shape) == (world * B, H, W)
+        gather_ms = gsum
     clk = clocks.stop()
     launches = est.kernel_launches() - l0
     ms = e0.elapsed_time(e1)
@@ -246,7 +359,10 @@ def run_ours(args):
     # predict_stream keeps two batches in flight (H2D / kernels / D2H of neighbouring steps overlap); the
     # blocking single-call form (predict_batch, the reference's own synchronous shape) is reported beside it.
     e2e = None
-    if not args.no_e2e:
+    stream = None
+    if args.workload == "stream720p" and not args.no_e2e:
+        e2e, stream = stream_workload(est, args, B, H, W, rank, world, dev, barrier)
+    elif not args.no_e2e:
         for _ in est.predict_stream([host_sets[i % n_sets] for i in range(3)]):
             pass
         barrier()
@@ -322,7 +438,7 @@ def run_ours(args):
                                                     for k in ("attention", "head_conv", "head_up_conv") if k in agg and agg[k]["ms"] > 0}}
         gf = GFLOP_PER_FRAME.get((args.model, W, H))
         cpu = None
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and world == 1:     # contract: rank 0 at N=1 only (torchrun pins OMP_NUM_THREADS=1)
             nfr = args.cpu_frames or (3 if args.model != "MiDaS_small" else 20)
             fps, dt = cpu_oracle_fps(args.model, H, W, nfr)
             cpu = {"value": fps, "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port",
@@ -331,15 +447,20 @@ def run_ours(args):
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "scaling": args.scaling, "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": f"{args.model} {W}x{H} uint8 BGR frames -> K1 -> net -> K8 bicubic to {W}x{H}, "
                                    f"{B} frames/GPU/step, random-init weights (seed 0)",
-                       "frames_per_gpu_per_step": B, "parallelism": f"frame data-parallel x{world}, no collective",
+                       "frames_per_gpu_per_step": B,
+                       "parallelism": f"frame data-parallel x{world}, " + (
+                           f"maps gathered on rank 0 by one NCCL all_gather per step ({gather_ms:.3f} ms on rank 0, last step)"
+                           if args.gather else "no collective"),
                        "l2": "working set per step (0.7 GB weights + >3 GB activations) >> 126 MB L2; "
                              "inputs rotate over 4 distinct frame batches"},
             "clocks": clk, "gpu_launches": int(launches), "e2e": e2e, "latency": latency, "roofline": roofline,
             "cpu_baseline": cpu,
         }
+        if stream is not None:
+            line["stream"] = stream
         if gf:
             line["model_tflops"] = value / world * gf / 1e3
             line["model_frac_of_peak"] = line["model_tflops"] / peak

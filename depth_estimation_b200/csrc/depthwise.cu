@@ -42,7 +42,7 @@ struct DwParams {
 };
 
 template <int K, int S>
-__global__ void __launch_bounds__(kDwThreads) depthwise_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwParams p) {
+__global__ void __launch_bounds__(kDwThreads, S == 1 ? 3 : 1) depthwise_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwParams p) {
   using Cfg = DwCfg<K, S>;
   extern __shared__ uint8_t dw_smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(dw_smem_raw) + 127) & ~static_cast<uintptr_t>(127));
@@ -74,12 +74,15 @@ __global__ void __launch_bounds__(kDwThreads) depthwise_tma_kernel(const __grid_
   };
 
   pdl_wait();                                 // x is the previous kernel's output
-  int t = blockIdx.x;
-  if (tid == 0 && t < p.ntiles) issue(t, 0);
+  // blocked partition: a CTA walks a contiguous range of work items - neighbouring tiles of one (chunk, image), so the
+  // tap table is reloaded only when the range crosses a channel chunk and halo rows are re-read from L2 while hot
+  int t = static_cast<int>((long long)blockIdx.x * p.ntiles / gridDim.x);
+  const int t_end = static_cast<int>((long long)(blockIdx.x + 1) * p.ntiles / gridDim.x);
+  if (tid == 0 && t < t_end) issue(t, 0);
   int cur_chunk = -1;
-  for (int n = 0; t < p.ntiles; t += gridDim.x, ++n) {
+  for (int n = 0; t < t_end; ++t, ++n) {
     const int s = n & 1;
-    if (tid == 0 && t + (int)gridDim.x < p.ntiles) issue(t + gridDim.x, s ^ 1);   // stage s^1 was drained at the end of n-1
+    if (tid == 0 && t + 1 < t_end) issue(t + 1, s ^ 1);   // stage s^1 was drained at the end of n-1
     const int chunk = t / per_chunk;
     int r = t - chunk * per_chunk;
     const int b = r / (p.tiles_y * p.tiles_x);

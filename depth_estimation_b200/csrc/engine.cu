@@ -274,10 +274,28 @@ void Engine::build_decoder(const int* cin, const int* feat, int head_mid, bool h
     r.cout = (int)fo;
   }
   const std::string oc = "scratch.output_conv.";
-  d.h0_c = head_mid;
-  d.h0_w = p3(W(oc + "0.weight", {head_mid, feat[0], 3, 3}), split3);
-  d.h0_b = f32(oc + "0.bias", {head_mid});
-  d.h2_w = p3(W(oc + "2.weight", {32, head_mid, 3, 3}), split3);
+  if (!split3 && head_mid < 64) {
+    // MiDaS_small (32 head channels): pad output_conv.0 to 64 output channels (zero filters, zero bias) so the head tail
+    // runs on the halo-tiled fused kernel (de_head_up_conv needs Cin % 64 == 0) instead of upsample + a 32-wide GEMM
+    // whose epilogue dominated it (0.23 of the 1.8 ms MiDaS_small step).  The padded channels are exact zeros.
+    const HostT& w0 = W(oc + "0.weight", {head_mid, feat[0], 3, 3});
+    HostT wp;
+    wp.shape = {64, feat[0], 3, 3};
+    wp.v.assign((size_t)64 * feat[0] * 9, 0.f);
+    memcpy(wp.v.data(), w0.v.data(), w0.v.size() * sizeof(float));
+    FVec bp(64, 0.f);
+    const FVec& b0 = W(oc + "0.bias", {head_mid}).v;
+    memcpy(bp.data(), b0.data(), b0.size() * sizeof(float));
+    d.h0_c = 64;
+    d.h0_w = wpool.put(pack_conv3x3(wp));
+    d.h0_b = wpool.put(bp);
+    d.h2_w = wpool.put(pack_conv3x3(W(oc + "2.weight", {32, head_mid, 3, 3})));   // Cin padded to 64 with zeros by the packer
+  } else {
+    d.h0_c = head_mid;
+    d.h0_w = p3(W(oc + "0.weight", {head_mid, feat[0], 3, 3}), split3);
+    d.h0_b = f32(oc + "0.bias", {head_mid});
+    d.h2_w = p3(W(oc + "2.weight", {32, head_mid, 3, 3}), split3);
+  }
   d.h2_b = f32(oc + "2.bias", {32});
   d.h4_w = f32(oc + "4.weight", {1, 32, 1, 1});
   d.h4_b = W(oc + "4.bias", {1}).v[0];
@@ -529,21 +547,25 @@ static void predict(Engine& e, int B, int H, int W, const DePredictIO& io, int u
       for (auto& kv : p.graphs) cudaGraphExecDestroy(kv.second.exec);
       p.graphs.clear();
     }
-    run_io(e, p, io, st);                                     // tap tables of K1 / K8 for this geometry, eagerly
-    ENG_CUDA(cudaStreamSynchronize(st));
+    // This call runs eagerly (which also builds K1 / K8's tap tables for the geometry); the same launch sequence is
+    // then recorded on the engine's own stream - a capture executes nothing, and the instantiated graph can be
+    // replayed on any stream, including the legacy default stream that cannot itself be captured.
+    run_io(e, p, io, st);
+    if (!e.side) ENG_CUDA(cudaStreamCreateWithFlags(&e.side, cudaStreamNonBlocking));
     GraphEntry ge;
     cudaGraph_t g = nullptr;
     const int64_t n0 = de_launch_count();
-    ENG_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+    ENG_CUDA(cudaStreamBeginCapture(e.side, cudaStreamCaptureModeThreadLocal));
     try {
-      run_io(e, p, io, st);
+      run_io(e, p, io, e.side);
     } catch (...) {
-      cudaStreamEndCapture(st, &g);
+      cudaStreamEndCapture(e.side, &g);
       if (g) cudaGraphDestroy(g);
       throw;
     }
-    ENG_CUDA(cudaStreamEndCapture(st, &g));
+    ENG_CUDA(cudaStreamEndCapture(e.side, &g));
     ge.launches = de_launch_count() - n0;
+    add_launches(-ge.launches);                               // recorded, not executed
     cudaError_t ie = cudaGraphInstantiate(&ge.exec, g, 0);
     cudaGraphDestroy(g);
     if (ie != cudaSuccess) raise(DE_ERR_CUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(ie));

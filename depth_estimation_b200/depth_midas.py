@@ -179,35 +179,60 @@ class DepthEstimator(object):
         stream, compute on a second, D2H on a third, chained by events, so the host-side memcpys and the PCIe
         transfers of batch i+1 / i-1 overlap the kernels of batch i.  Every frame still crosses the host
         boundary in both directions; only the serialisation point of depth_midas.py:23,34 is gone."""
+        for res in self.predict_stream_fused(((b, None) for b in batches), depth=depth, n_samples=0, want_vis=False,
+                                             want_map=True):
+            yield res.maps
+
+    def predict_stream_fused(self, items, depth=2, n_samples=2, want_vis=True, want_map=False):
+        """The pipelined loop with K8's fused outputs instead of the full-resolution fp32 map: `items` yields
+        (frames, rc) - frames uint8 [B,H,W,3] (or a sequence of B [H,W,3] frames), rc int [B,n_samples,2] (row, col)
+        points into the output map (`FaceDet.sample_indices`, face.py:94-107) - and a StreamResult comes back per
+        item, in order: the sampled map values (what `FaceDet.get_depth` reads), the uint8 grey level of
+        `to_video_frame` (midas_mediapipe.py:141-150) and, only with want_map, the map itself.  Without it a 720p
+        frame costs 0.9 MB of device->host traffic instead of 3.7 MB and no host pass over the map at all."""
         depth = max(1, int(depth))
         pending = []                                  # (slot, future -> the slot's D2H-done event)
         pipe = None
         idx = 0
         last = None
-        it = iter(batches)
+        it = iter(items)
         with torch.cuda.device(self.device):
             while True:
                 if last is not None:
-                    last.result()                     # previous batch staged and enqueued: its source array is free again
+                    last.result()                     # previous batch staged and enqueued: its source arrays are free again
                 try:
-                    frames = next(it)
+                    frames, rc = next(it)
                 except StopIteration:
                     break
-                frames = np.ascontiguousarray(frames)
-                if frames.ndim != 4 or frames.shape[3] != 3 or frames.dtype != np.uint8:
+                if isinstance(frames, np.ndarray):
+                    frames = np.ascontiguousarray(frames)
+                    shape = frames.shape
+                    ok = frames.ndim == 4 and frames.shape[3] == 3 and frames.dtype == np.uint8
+                else:
+                    frames = list(frames)
+                    ok = len(frames) > 0 and all(isinstance(f, np.ndarray) and f.dtype == np.uint8 and f.ndim == 3
+                                                 and f.shape == frames[0].shape and f.shape[2] == 3 for f in frames)
+                    shape = (len(frames),) + tuple(frames[0].shape) if ok else None
+                if not ok:
                     raise TypeError("predict_stream expects uint8 [B,H,W,3] BGR batches")
-                if pipe is None or pipe.shape != frames.shape or pipe.depth != depth:
+                if n_samples:
+                    rc = np.asarray(rc, dtype=np.int32)
+                    if rc.shape != (shape[0], n_samples, 2):
+                        raise ValueError(f"sample points must be [B,{n_samples},2] (row, col), got {rc.shape}")
+                key = (tuple(shape), depth, n_samples, want_vis, want_map)
+                if pipe is None or pipe.key != key:
                     while pending:                    # geometry change: drain, then rebuild the slots
                         yield pipe.collect(*pending.pop(0))
-                    pipe = self._pipes.get((frames.shape, depth))
+                    pipe = self._pipes.get(key)
                     if pipe is None:
-                        pipe = _Pipeline(self, frames.shape, depth)
-                        self._pipes[(frames.shape, depth)] = pipe
+                        pipe = _Pipeline(self, shape, depth, n_samples, want_vis, want_map)
+                        pipe.key = key
+                        self._pipes[key] = pipe
                     idx = 0
                 # depth + 1 slots: the batch collected below (idx - depth) and the one being staged (idx) never share
                 # buffers, so the host copy into pinned memory (worker thread) overlaps the copy out of it (this thread)
                 slot = idx % pipe.nslots
-                last = pipe.submit_async(slot, frames)
+                last = pipe.submit_async(slot, frames, rc if n_samples else None)
                 pending.append((slot, last))
                 idx += 1
                 if len(pending) > depth:
@@ -240,7 +265,7 @@ class _Plan:
     """Static buffers + (optionally) a captured CUDA graph for one (B,H,W) geometry:
     pinned host frame -> H2D -> K1 -> net -> K8 -> D2H pinned."""
 
-    def __init__(self, est: DepthEstimator, B, H, W, n_samples, want_metric, want_vis=False):
+    def __init__(self, est: DepthEstimator, B, H, W, n_samples, want_metric, want_vis=False, host_map=True):
         self.est = est
         dev = est.device
         self.B, self.H, self.W = B, H, W
@@ -248,7 +273,7 @@ class _Plan:
         self.h_in = torch.empty((B, H, W, 3), dtype=torch.uint8).pin_memory()
         self.d_in = torch.empty((B, H, W, 3), dtype=torch.uint8, device=dev)
         self.d_map = torch.empty((B, H, W), dtype=torch.float32, device=dev)
-        self.h_map = torch.empty((B, H, W), dtype=torch.float32).pin_memory()
+        self.h_map = torch.empty((B, H, W), dtype=torch.float32).pin_memory() if host_map else None
         self.want_metric = want_metric
         self.d_metric = torch.empty((B, H, W), dtype=torch.bfloat16, device=dev) if want_metric else None
         self.h_metric = torch.empty((B, H, W), dtype=torch.bfloat16).pin_memory() if want_metric else None
@@ -263,17 +288,13 @@ class _Plan:
         self.graph = None
         self._dev_graph = None
         self._warm = False
-        self._d_samples = None
+        self._d_samples = torch.empty((B, n_samples), dtype=torch.float32, device=dev) if n_samples else None
         est.estimator.plan(B, H, W)                             # work buffers + warm-up now, not inside a capture
 
     def _compute(self, src):
         """K1 -> network -> K8 on the current stream: one call into the engine (de_predict)."""
         est = self.est
-        samples = None
-        if self.n_samples:
-            if self._d_samples is None:
-                self._d_samples = torch.empty((self.B, self.n_samples), dtype=torch.float32, device=est.device)
-            samples = self._d_samples
+        samples = self._d_samples
         est.estimator.predict(self.B, self.H, self.W, src, out_map=self.d_map, out_metric=self.d_metric,
                               metric_scale=est.metric_affine[0], metric_shift=est.metric_affine[1], out_vis=self.d_vis,
                               sample_rc=self.d_rc if self.n_samples else None, out_samples=samples)
@@ -284,7 +305,8 @@ class _Plan:
         if self.n_samples:
             self.d_rc.copy_(self.h_rc, non_blocking=True)
         samples = self._compute(self.d_in)
-        self.h_map.copy_(self.d_map, non_blocking=True)
+        if self.h_map is not None:
+            self.h_map.copy_(self.d_map, non_blocking=True)
         if self.want_metric:
             self.h_metric.copy_(self.d_metric, non_blocking=True)
         if self.want_vis:
@@ -340,17 +362,32 @@ class _Plan:
         return self.d_map
 
 
+class StreamResult:
+    """One batch out of the pipelined loop.  `maps` (float32 [B,H,W], a copy) is present unless the stream was opened
+    with want_map=False; `vis` is the uint8 grey level of the reference's to_video_frame (a view into pinned memory,
+    valid until the next result is taken); `samples` float32 [B,S] are the map values at the requested (row, col)
+    points.  map_pixel reads single elements of the device-resident map (a device sync; the rare body-pose branch of
+    midas_mediapipe.py:95-117 needs two pixels whose position is not known when the frame is submitted)."""
+
+    def __init__(self, plan, maps, vis, samples):
+        self._plan, self.maps, self.vis, self.samples = plan, maps, vis, samples
+
+    def map_pixel(self, b, r, c):
+        return float(self._plan.d_map[b, r, c].item())
+
+
 class _Pipeline:
     """`depth` in-flight slots for predict_stream: per slot a pinned input / output pair, device input / output
     buffers and a CUDA graph of the compute; three streams (H2D, compute, D2H) chained by events.  The network's
     work buffers are shared between slots - safe because all compute is ordered on the one compute stream."""
 
-    def __init__(self, est: DepthEstimator, shape, depth):
+    def __init__(self, est: DepthEstimator, shape, depth, n_samples=0, want_vis=False, want_map=True):
         self.est, self.shape, self.depth = est, tuple(shape), depth
+        self.n_samples, self.want_vis, self.want_map = n_samples, want_vis, want_map
         B, H, W, _ = shape
         dev = est.device
         self.nslots = n = depth + 1
-        self.plans = [_Plan(est, B, H, W, 0, False) for _ in range(n)]
+        self.plans = [_Plan(est, B, H, W, n_samples, False, want_vis, host_map=want_map) for _ in range(n)]
         self.s_in, self.s_compute, self.s_out = (torch.cuda.Stream(dev) for _ in range(3))
         self.ev_in = [torch.cuda.Event() for _ in range(n)]
         self.ev_done = [torch.cuda.Event() for _ in range(n)]
@@ -359,10 +396,14 @@ class _Pipeline:
         # one worker thread stages frames into pinned memory and enqueues the slot's work (numpy's memcpy releases the
         # GIL).  Worth it when the copies are long: MiDaS_small at 720p (88 MB in, 118 MB out per 32 frames) goes from
         # 990 to 1235 frames/s end to end; at 14 MB per batch (DPT_Large 384^2) the hand-off costs more than it hides,
-        # so small batches are staged inline.  DEB_STAGE_THREAD=0 / 1 forces either.
+        # so small batches are staged inline.  DEB_STAGE_THREAD=0 / 1 forces either.  Large batches are additionally
+        # split over a few copy threads (a single memcpy stream moves ~10 GB/s; 720p frames at 5000 frames/s need 14).
         mode = os.environ.get("DEB_STAGE_THREAD")
         threaded = mode == "1" or (mode != "0" and B * H * W * 3 >= (32 << 20))
         self._pool = ThreadPoolExecutor(1, "deb-stage") if threaded else None
+        ncopy = int(os.environ.get("DEB_COPY_THREADS", "0")) or min(4, max(1, (os.cpu_count() or 2) // 2))
+        self._copiers = ThreadPoolExecutor(ncopy, "deb-copy") if (threaded and ncopy > 1 and B > 1) else None
+        self._ncopy = ncopy
         cur = torch.cuda.current_stream(dev)
         self.s_compute.wait_stream(cur)
         with torch.cuda.stream(self.s_compute):
@@ -379,25 +420,47 @@ class _Pipeline:
         for e in self.ev_done + self.ev_out:                    # so the first waits are no-ops
             e.record(self.s_compute)
 
-    def submit_async(self, slot, frames):
+    def submit_async(self, slot, frames, rc=None):
         """Future of submit(slot, frames) (already completed when the worker thread is disabled)."""
         if self._pool is not None:
-            return self._pool.submit(self._submit_on_device, slot, frames)
-        return _Done(self.submit(slot, frames))
+            return self._pool.submit(self._submit_on_device, slot, frames, rc)
+        return _Done(self.submit(slot, frames, rc))
 
-    def _submit_on_device(self, slot, frames):
+    def _submit_on_device(self, slot, frames, rc):
         with torch.cuda.device(self.est.device):
-            return self.submit(slot, frames)
+            return self.submit(slot, frames, rc)
 
-    def submit(self, slot, frames):
+    def _stage(self, dst, frames):
+        """frames: one [B,H,W,3] array or a sequence of B [H,W,3] frames -> the slot's pinned buffer."""
+        B = dst.shape[0]
+        if self._copiers is None:
+            if isinstance(frames, np.ndarray):
+                dst[...] = frames
+            else:
+                for i, f in enumerate(frames):
+                    dst[i] = f
+            return
+        step = -(-B // self._ncopy)
+
+        def part(lo):
+            for i in range(lo, min(B, lo + step)):
+                np.copyto(dst[i], frames[i])
+        for f in [self._copiers.submit(part, lo) for lo in range(0, B, step)]:
+            f.result()
+
+    def submit(self, slot, frames, rc=None):
         p = self.plans[slot]
-        p.h_in.numpy()[...] = frames                            # slot is free: its previous result was collected
+        self._stage(p.h_in.numpy(), frames)                     # slot is free: its previous result was collected
+        if self.n_samples:
+            p.h_rc.numpy()[...] = rc
         self.s_in.wait_event(self.ev_done[slot])                # previous compute on this slot has consumed d_in
         with torch.cuda.stream(self.s_in):
             p.d_in.copy_(p.h_in, non_blocking=True)
+            if self.n_samples:
+                p.d_rc.copy_(p.h_rc, non_blocking=True)
             self.ev_in[slot].record()
         self.s_compute.wait_event(self.ev_in[slot])
-        self.s_compute.wait_event(self.ev_out[slot])            # previous D2H of this slot has drained d_map
+        self.s_compute.wait_event(self.ev_out[slot])            # previous D2H of this slot has drained its outputs
         with torch.cuda.stream(self.s_compute):
             if self.graphs[slot] is not None:
                 self.graphs[slot].replay()
@@ -407,13 +470,21 @@ class _Pipeline:
             self.ev_done[slot].record()
         self.s_out.wait_event(self.ev_done[slot])
         with torch.cuda.stream(self.s_out):
-            p.h_map.copy_(p.d_map, non_blocking=True)
+            if self.want_map:
+                p.h_map.copy_(p.d_map, non_blocking=True)
+            if self.want_vis:
+                p.h_vis.copy_(p.d_vis, non_blocking=True)
+            if self.n_samples:
+                p.h_samples.copy_(p._d_samples, non_blocking=True)
             self.ev_out[slot].record()
         return self.ev_out[slot]
 
     def collect(self, slot, fut):
         fut.result().synchronize()                              # enqueued (worker exceptions surface here), then D2H done
-        return self.plans[slot].h_map.numpy().copy()
+        p = self.plans[slot]
+        return StreamResult(p, p.h_map.numpy().copy() if self.want_map else None,
+                            p.h_vis.numpy() if self.want_vis else None,
+                            p.h_samples.numpy().copy() if self.n_samples else None)
 
 
 class _Done:

@@ -13,7 +13,12 @@ the two HEAD mesh points) and the body branch (`:96-120`), `to_video_frame` (`:1
   * `stream(pipelined=True)` (default) keeps two frames in flight through `DepthEstimator.predict_stream`: the
     detector of frame i+1 runs on the host while the GPU works on frame i.  Frame order and every number handed
     to `FaceDet` are unchanged - `pipelined=False` is the reference's strictly serial loop, and the two are tested to
-    agree bit for bit.
+    agree bit for bit;
+  * `stream(fused=True, batch=N)` additionally takes K8's fused outputs instead of the fp32 map: the two map values
+    `FaceDet.get_depth` reads (face.py:106-107) are gathered on the device at the points `FaceDet.sample_indices`
+    names, and `to_video_frame`'s wrapping uint8 grey level (:141-150) arrives as 1 byte per pixel - the full map never
+    crosses PCIe and the host makes no pass over it.  N frames per submission amortise the per-launch latency of the
+    small network.  The numbers handed to `FaceDet` are the same floats (K8's samples are bit-identical to the map).
 The detector stays the reference's host code (`detectors.PersonDetector`, MediaPipe - not installable here); any
 object with `findIris(frame)` / `findBody(frame)` / `visualize(frame)` / `HEAD` that fills `face.mesh`,
 `face.l_iris`, `face.r_iris` works, which is what the tests use.
@@ -37,6 +42,26 @@ def _resize_half(img: np.ndarray, size) -> np.ndarray:
         ys = (np.arange(h) * img.shape[0] / h).astype(int)
         xs = (np.arange(w) * img.shape[1] / w).astype(int)
         return img[ys][:, xs]
+
+
+class _MapProxy:
+    """What `FaceDet.get_depth` sees in place of the depth map when the stream runs fused: `.shape` and `[i, j]`.
+    The two points requested from K8 come back with the batch; any other index (body-pose branch, indices numpy would
+    wrap) is read from the device-resident map with numpy's indexing rules."""
+
+    def __init__(self, shape, res, b, pts):
+        self.shape, self._res, self._b, self._pts = tuple(shape), res, b, pts
+
+    def __getitem__(self, ij):
+        i, j = int(ij[0]), int(ij[1])
+        if self._pts is not None:
+            for k in (0, 1):
+                if (i, j) == tuple(self._pts[k]):
+                    return self._res.samples[self._b, k]
+        H, W = self.shape
+        if not (-H <= i < H and -W <= j < W):
+            raise IndexError(f"index ({i}, {j}) is out of bounds for a map of shape {self.shape}")
+        return np.float32(self._res.map_pixel(self._b, i % H, j % W))
 
 
 class VidStream(object):
@@ -69,6 +94,7 @@ class VidStream(object):
         self.cnt = 0
         self.performance = {'iris': list(), 'body': list(), 'depth': list()}
         self._det_state = None
+        self.keep_outputs = True      # False: skip the side-by-side video frame (codec / overlay work is out of scope)
 
     # ------------------------------------------------------------------ frame source / sink
     def _read(self):
@@ -85,6 +111,8 @@ class VidStream(object):
         return True, f
 
     def write_output(self, depth_frame):
+        if not self.keep_outputs and self.output is None:
+            return
         combo = self.side_by_side(self.frame, depth_frame)
         if self.output is not None:
             import cv2
@@ -142,7 +170,9 @@ class VidStream(object):
             self.performance['body'].append(perf_counter() - t0)
             self.face.get_headw(head_pts[0], head_pts[1])
             self.face.s2c_dist(median(self.face.head_measurements), self.face.head_w)
-        if vis is not None:                                         # grey level already produced by K8 (same bytes)
+        if vis is not None and not self.keep_outputs and self.output is None:
+            depth_vis = vis                                         # consumer does not want the 3-channel video frame
+        elif vis is not None:                                       # grey level already produced by K8 (same bytes)
             depth_vis = np.stack([vis, vis, vis], axis=-1)
         else:
             depth_vis = self.to_video_frame(depth_frame)
@@ -164,8 +194,10 @@ class VidStream(object):
         return (self.face.mesh, dict(self.face.l_iris), dict(self.face.r_iris))
 
     # ------------------------------------------------------------------ the loop (midas_mediapipe.py:32-129)
-    def stream(self, pipelined=True, max_frames=None):
-        if pipelined and hasattr(self.estimator, "predict_stream"):
+    def stream(self, pipelined=True, max_frames=None, fused=False, batch=1):
+        if fused and hasattr(self.estimator, "predict_stream_fused"):
+            self._stream_fused(max_frames, max(1, int(batch)))
+        elif pipelined and hasattr(self.estimator, "predict_stream"):
             self._stream_pipelined(max_frames)
         else:
             self._stream_serial(max_frames)
@@ -204,6 +236,53 @@ class VidStream(object):
             frame, state, t0 = pending.popleft()
             self.performance['depth'].append(perf_counter() - t0)
             self._consume(frame, state, maps[0])
+
+    def _stream_fused(self, max_frames, batch):
+        pending = deque()                                            # (frames, detector states, requested points, t0)
+
+        def points(state, shape):
+            """(row, col) x 2 that `FaceDet.get_depth` will read for this frame, or None when they are not known at
+            submission time (body-pose branch: the head points come from an earlier frame's findBody) or not valid
+            numpy indices of the map (the reference would wrap / raise: left to `_MapProxy`)."""
+            mesh, l_iris, r_iris = state
+            if mesh is None:
+                return None
+            saved = (self.face.mesh, self.face.l_iris, self.face.r_iris)
+            self.face.mesh, self.face.l_iris, self.face.r_iris = mesh, l_iris, r_iris
+            try:
+                a, b = self.face.sample_indices(shape)
+            finally:
+                self.face.mesh, self.face.l_iris, self.face.r_iris = saved
+            ok = all(0 <= p[0] < shape[0] and 0 <= p[1] < shape[1] for p in (a, b))
+            return (a, b) if ok else None
+
+        def feed():
+            while True:
+                frames, states, pts = [], [], []
+                while len(frames) < batch and (max_frames is None or self.cnt < max_frames):
+                    self.status, frame = self._read()
+                    if not self.status:
+                        break
+                    self.cnt += 1
+                    state = self._detect(frame)
+                    frames.append(frame)
+                    states.append(state)
+                    pts.append(points(state, frame.shape[:2]))
+                if not frames:
+                    return
+                rc = np.zeros((len(frames), 2, 2), dtype=np.int32)
+                for i, p in enumerate(pts):
+                    if p is not None:
+                        rc[i] = p
+                pending.append((frames, states, pts, perf_counter()))
+                yield frames, rc
+
+        for res in self.estimator.predict_stream_fused(feed(), depth=2, n_samples=2, want_vis=True, want_map=False):
+            frames, states, pts, t0 = pending.popleft()
+            dt = (perf_counter() - t0) / len(frames)
+            for b, (frame, state, p) in enumerate(zip(frames, states, pts)):
+                self.performance['depth'].append(dt)
+                self._consume(frame, state, _MapProxy(frame.shape[:2], res, b, p), vis=res.vis[b])
 
     def report(self):
         """The reference prints `1 // median(...)` FPS per stage at the end of the stream (:121-125)."""

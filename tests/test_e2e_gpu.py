@@ -191,6 +191,16 @@ def test_stream_loop_and_fused_video_frame():
     (fa, va), (fb, vb) = runs
     assert fa.ri_depths == fb.ri_depths and fa.abs_depths == fb.abs_depths and fa.head_measurements == fb.head_measurements
     assert all(np.array_equal(x, y) for x, y in zip(va.outputs, vb.outputs))
+    # fused loop: K8's gathered iris samples + uint8 grey level instead of the fp32 map (no map D2H), 4 frames per
+    # submission with a ragged tail; the body-pose frames read their two pixels from the device-resident map
+    for batch in (4, 1):
+        face = FaceDet(20, [505, 504, 675, 501])
+        vs = midas_mediapipe.VidStream(est, _FakeDetector(face), face, frames, None)
+        vs.stream(fused=True, batch=batch)
+        assert face.ri_depths == fa.ri_depths and face.abs_depths == fa.abs_depths
+        assert face.head_measurements == fa.head_measurements and face.s2c_ds == fa.s2c_ds
+        assert len(vs.outputs) == len(va.outputs) and all(np.array_equal(x, y) for x, y in zip(vs.outputs, va.outputs))
+        assert vs.messages == va.messages
     maps, vis = est.predict_batch(np.stack(frames[:2]), want_vis=True)
     want = va.to_video_frame(maps * 37.0)[..., 0] if False else va.to_video_frame(maps)[..., 0]
     assert vis.dtype == np.uint8 and np.array_equal(vis, want)
@@ -243,3 +253,36 @@ def test_batch_is_independent_frames(mt, W, H, B):
     for i in (0, B - 1):
         single = est.predict(frames[i])
         assert np.abs(single - maps[i]).max() <= 1e-5 * np.abs(maps[i]).max()
+
+
+def test_nccl_gather_two_ranks(tmp_path):
+    """north_star: "NCCL used only to gather per-frame outputs" - sharding.gather_frames over NCCL on GPU tensors, two
+    ranks (one per GPU), ragged shards; rank 0 must end up with every frame in order.  Needs 2 GPUs."""
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 CUDA devices")
+    import os
+    import subprocess
+    import sys
+    script = tmp_path / "gather2.py"
+    script.write_text('''
+import os, sys, torch, torch.distributed as dist
+sys.path.insert(0, os.environ["REPO_ROOT"])
+from depth_estimation_b200 import sharding
+rank = int(os.environ["RANK"]); torch.cuda.set_device(rank)
+dist.init_process_group("nccl", device_id=torch.device("cuda", rank))
+for mode in ("slab", "stream"):
+    n = 7
+    idx = sharding.owned_indices(n, rank, 2, mode)
+    local = torch.stack([torch.full((5, 6), float(i), device="cuda") for i in idx]) if len(idx) else torch.empty((0, 5, 6), device="cuda")
+    out = sharding.gather_frames(local, n, mode)
+    if rank == 0:
+        assert out.shape == (n, 5, 6) and all(float(out[i, 0, 0]) == i for i in range(n)), mode
+    else:
+        assert out is None
+dist.barrier(); dist.destroy_process_group(); print("ok", rank)
+''')
+    env = dict(os.environ, REPO_ROOT=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    res = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29533", str(script)],
+                         capture_output=True, text=True, env=env, timeout=300)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]

@@ -351,7 +351,7 @@ def test_head_conv(B, H, W, Cin):
 
 
 @pytest.mark.parametrize("B,Hs,Ws,Cin,ac", [(1, 32, 48, 128, True), (2, 10, 20, 128, True), (1, 19, 27, 64, True),
-                                             (2, 12, 8, 128, False), (1, 48, 48, 128, True)])
+                                             (2, 12, 8, 128, False), (1, 48, 48, 128, True), (2, 16, 32, 64, False)])
 def test_head_up_conv(B, Hs, Ws, Cin, ac):
     """Fused bilinear x2 + head tail vs the two-kernel path (bit-identical interpolation, same MMAs) and vs torch."""
     from depth_estimation_b200 import ops
