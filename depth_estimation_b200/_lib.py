@@ -33,6 +33,7 @@ class DeGemm(C.Structure):
         ("head_w", C.c_void_p), ("head_b", C.c_float),
         ("block_n", C.c_int), ("epilogue", C.c_int), ("cta_group", C.c_int),
         ("out_split", C.c_int), ("relu_split", C.c_int), ("ld_relu", C.c_int64), ("add2_dtype", C.c_int), ("ld_add2", C.c_int64),
+        ("k_splits", C.c_int), ("splitk_ws", C.c_void_p), ("splitk_ws_bytes", C.c_int64),
         ("accumulate", C.c_int),
     ]
 

@@ -50,6 +50,7 @@ struct GemmParams {
   const float* head_w;
   float head_b;
   int accumulate;  // store epilogue only: TMA reduce-add instead of store
+  int k_splits, kb_per_split;  // split-K: work item = (tile, split); split s covers k-blocks [s*kb_per_split, ...)
 };
 
 // EPI 0: "store" epilogue - bias + activation only, output tile staged in 128B-swizzled smem and written
@@ -134,7 +135,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   const int lane = threadIdx.x & 31;
   const uint32_t cta_rank = CG == 2 ? cluster_ctarank() : 0u;
   const int unit = blockIdx.x / CG, num_units = gridDim.x / CG;
-  const int num_tiles = ((p.m_tiles + CG - 1) / CG) * p.n_tiles;
+  const int num_work = ((p.m_tiles + CG - 1) / CG) * p.n_tiles * p.k_splits;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -173,7 +174,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       int stage = 0;
       uint32_t phase = 0;
       const uint32_t a_bytes = p.a_mode == 0 ? C::kABytes : p.bw * p.bh * BK * 2;
-      for (int tile = unit; tile < num_tiles; tile += num_units) {
+      for (int work = unit; work < num_work; work += num_units) {
+        const int tile = work / p.k_splits, split = work - tile * p.k_splits;
         const int m_tile = (tile / p.n_tiles) * CG + cta_rank, n_tile = tile % p.n_tiles;
         int b = 0, y0 = 0, x0 = 0;
         if (p.a_mode == 1) {
@@ -184,7 +186,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           x0 = (t % p.tiles_x) * p.bw;
         }
         const int n_row = n_tile * BN + cta_rank * C::kBRows;
-        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+        const int kb0 = split * p.kb_per_split, kb1 = min(kb0 + p.kb_per_split, p.num_k_blocks);
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* da = sA + stage * C::kABytes;
           uint8_t* db = sB + stage * C::kBBytes;
@@ -224,11 +227,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       uint32_t phase = 0;
       int as = 0;
       uint32_t aphase = 0;
-      for (int tile = unit; tile < num_tiles; tile += num_units) {
+      for (int work = unit; work < num_work; work += num_units) {
+        const int split = work % p.k_splits;
+        const int kb0 = split * p.kb_per_split, kb1 = min(kb0 + p.kb_per_split, p.num_k_blocks);
         mbar_wait(&tempty[as], aphase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * BN;
-        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
           // elect_one in a converged warp (not `lane == 0`): ptxas then knows the operands are warp-uniform and
@@ -239,15 +244,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           if (elect_one()) {
 #pragma unroll
             for (int k = 0; k < BK / 16; ++k) {
-              if (CG == 2) umma_bf16_cg2(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
-              else umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+              if (CG == 2) umma_bf16_cg2(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, ((kb - kb0) | k) != 0);
+              else umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, ((kb - kb0) | k) != 0);
             }
             if (CG == 2) {
               umma_commit_cg2(&empty[stage], 3);
-              if (kb == p.num_k_blocks - 1) umma_commit_cg2(&tfull[as], 3);
+              if (kb == kb1 - 1) umma_commit_cg2(&tfull[as], 3);
             } else {
               umma_commit(&empty[stage]);
-              if (kb == p.num_k_blocks - 1) umma_commit(&tfull[as]);
+              if (kb == kb1 - 1) umma_commit(&tfull[as]);
             }
           }
           __syncwarp();
@@ -281,13 +286,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     int as = 0;
     uint32_t aphase = 0;
     bool pending = false;                                      // this group has a store in flight on sbuf
-    for (int tile = unit; tile < num_tiles; tile += num_units) {
+    for (int work = unit; work < num_work; work += num_units) {
+      const int tile = work / p.k_splits, split = work - tile * p.k_splits;
       const int m_tile = (tile / p.n_tiles) * CG + cta_rank, n_tile = tile % p.n_tiles;
       // bias slice of this group's units, fetched while the main loop of the tile is still running
+      // (split-K: the partial sums are reduce-added into the output; only split 0 contributes the bias)
       for (int u = grp; u < units; u += 2) {
         if (gtid < ucols) {
           const int n = n_tile * BN + u * ucols + gtid;
-          s_bias[u * ucols + gtid] = (p.bias && n < p.N) ? __ldg(p.bias + (n % bias_mod)) : 0.f;
+          s_bias[u * ucols + gtid] = (p.bias && n < p.N && split == 0) ? __ldg(p.bias + (n % bias_mod)) : 0.f;
         }
       }
       int b = 0, y0 = 0, x0 = 0;
@@ -383,8 +390,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         if (gtid == 0) {
           if (m_tile < p.m_tiles) {
             const int col0 = n_tile * BN + u * ucols;
-            if (p.accumulate) tma_reduce_add_2d(&tmC, sbuf, col0, m_tile * BM);
-            else if (p.a_mode == 0) tma_store_2d(&tmC, sbuf, col0, m_tile * BM);
+            if (p.accumulate) {
+              if (p.a_mode == 0) tma_reduce_add_2d(&tmC, sbuf, col0, m_tile * BM);
+              else tma_reduce_add_4d(&tmC, sbuf, col0, x0, y0, b);
+            } else if (p.a_mode == 0) tma_store_2d(&tmC, sbuf, col0, m_tile * BM);
             else tma_store_4d(&tmC, sbuf, col0, x0, y0, b);
           }
           tma_store_commit();            // one (possibly empty) group per unit: wait_read<N> counts units, not stores
@@ -418,7 +427,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const int sub = lane >> 3, cc = (lane & 7) * 4;                           // read-back mapping
     int as = 0;
     uint32_t aphase = 0;
-    for (int tile = unit; tile < num_tiles; tile += num_units) {
+    for (int tile = unit; tile < num_work; tile += num_units) {   // k_splits == 1 on this path (checked on the host)
       const int m_tile = (tile / p.n_tiles) * CG + cta_rank, n_tile = tile % p.n_tiles;
       {
         // row-owner phase: logical row index m of accumulator row r, validity, storage offsets
@@ -644,7 +653,7 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMa
     cudaError_t e = ensure_smem(optin, gemm_kernel<BN, CG, EPI>, (int)C::kSmemBytes);
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(gemm)");
   }
-  const int tiles = ((p.m_tiles + CG - 1) / CG) * p.n_tiles;
+  const int tiles = ((p.m_tiles + CG - 1) / CG) * p.n_tiles * p.k_splits;
   int units = num_sms() / CG;
   if (tiles < units) units = tiles;
   cudaLaunchConfig_t cfg{};
@@ -665,6 +674,109 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMa
   count_launch();
   if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(gemm_kernel)");
   return cuda_check_launch("gemm_kernel");
+}
+
+// ------------------------------------------------------------------------------------------------ split-K finalize
+// Second half of a split-K call: the K-slices have reduce-added their fp32 partial tiles into the workspace `acc`
+// [M, N]; this kernel applies the call's epilogue (the contract of DeGemm: bias, add1 before / after the activation,
+// add2, row maps, pixel shuffle, split3 stores, ReLU copy) to it and leaves the workspace zeroed for the next call.
+// One thread per (row, 4 columns).
+struct FinalizeParams {
+  float* acc;
+  int M, N;
+  const float* bias;
+  int bias_mod, act;
+  const void* add1;
+  int add1_dtype, add1_rowmode, add1_pre;
+  long long ld_add1;
+  const void* add2;
+  int add2_dtype;
+  void* out;
+  int out_dtype;
+  __nv_bfloat16* out_relu;
+  long long out_pitch, relu_pitch, add2_pitch;
+  int out_split, relu_split, split_c;
+  int out_rowmode, grp, pad, off;
+  int ps_gh, ps_gw, ps_s, ps_cout;
+};
+__global__ void __launch_bounds__(256) splitk_finalize_kernel(const FinalizeParams p) {
+  const int n4 = p.N >> 2;
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long long)p.M * n4) return;
+  const long long m = idx / n4;
+  const int n = static_cast<int>(idx - m * n4) * 4;
+  float4* ap = reinterpret_cast<float4*>(p.acc + m * p.N + n);
+  float4 v = *ap;
+  *ap = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (p.bias) {
+    const int bm = p.bias_mod > 0 ? p.bias_mod : p.N;
+    v.x += __ldg(p.bias + (n % bm)); v.y += __ldg(p.bias + ((n + 1) % bm));
+    v.z += __ldg(p.bias + ((n + 2) % bm)); v.w += __ldg(p.bias + ((n + 3) % bm));
+  }
+  long long unit = m;
+  if (p.out_rowmode == 1) unit = m + (m / p.grp) * p.pad + p.off;
+  long long colpart = n, colpart_r = n, colpart2 = n;
+  if (p.out_rowmode == 2) {
+    const int per = p.ps_gh * p.ps_gw;
+    const int ps_b = static_cast<int>(m / per), t = static_cast<int>(m % per);
+    const int ps_y = t / p.ps_gw, ps_x = t % p.ps_gw;
+    unit = (static_cast<long long>(ps_b) * p.ps_gh * p.ps_s + ps_y * p.ps_s) * (p.ps_gw * p.ps_s) + ps_x * p.ps_s;
+    const int g = n / p.ps_cout, co = n % p.ps_cout;
+    const long long px = static_cast<long long>(g / p.ps_s) * (p.ps_gw * p.ps_s) + g % p.ps_s;
+    colpart = px * p.out_pitch + co;
+    colpart_r = px * p.relu_pitch + co;
+    colpart2 = px * p.add2_pitch + co;
+  }
+  float4 a1 = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (p.add1) {
+    long long arow = unit;
+    if (p.add1_rowmode == 1) arow = m / p.grp;
+    else if (p.add1_rowmode == 2) arow = (m % p.grp) + p.off;
+    const long long ao = arow * p.ld_add1 + n;
+    if (p.add1_dtype == DE_DTYPE_F32) {
+      a1 = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.add1) + ao);
+    } else {
+      const uint2 t = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(p.add1) + ao);
+      a1 = make_float4(bf16_lo(t.x), bf16_hi(t.x), bf16_lo(t.y), bf16_hi(t.y));
+    }
+  }
+  if (p.add1_pre) { v.x += a1.x; v.y += a1.y; v.z += a1.z; v.w += a1.w; }
+  if (p.act != DE_ACT_NONE) v = apply_act4(v, p.act);
+  if (!p.add1_pre) { v.x += a1.x; v.y += a1.y; v.z += a1.z; v.w += a1.w; }
+  if (p.add2) {
+    const long long o2 = unit * p.add2_pitch + colpart2;
+    if (p.add2_dtype == DE_DTYPE_F32) {
+      const float4 t = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.add2) + o2);
+      v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+    } else {
+      const uint2 t = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(p.add2) + o2);
+      v.x += bf16_lo(t.x); v.y += bf16_hi(t.x); v.z += bf16_lo(t.y); v.w += bf16_hi(t.y);
+    }
+  }
+  const long long o = unit * p.out_pitch + colpart;
+  if (p.out_dtype == DE_DTYPE_F32) {
+    *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + o) = v;
+  } else {
+    const uint2 hi = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
+    __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(p.out) + o;
+    *reinterpret_cast<uint2*>(op) = hi;
+    if (p.out_split) {
+      *reinterpret_cast<uint2*>(op + p.split_c) = hi;
+      *reinterpret_cast<uint2*>(op + 2 * p.split_c) =
+          make_uint2(pack_bf16(v.x - bf16_lo(hi.x), v.y - bf16_hi(hi.x)), pack_bf16(v.z - bf16_lo(hi.y), v.w - bf16_hi(hi.y)));
+    }
+  }
+  if (p.out_relu) {
+    const float4 rv = make_float4(fmaxf(v.x, 0.f), fmaxf(v.y, 0.f), fmaxf(v.z, 0.f), fmaxf(v.w, 0.f));
+    const uint2 hi = make_uint2(pack_bf16(rv.x, rv.y), pack_bf16(rv.z, rv.w));
+    __nv_bfloat16* rp = p.out_relu + unit * p.relu_pitch + colpart_r;
+    *reinterpret_cast<uint2*>(rp) = hi;
+    if (p.relu_split) {
+      *reinterpret_cast<uint2*>(rp + p.split_c) = hi;
+      *reinterpret_cast<uint2*>(rp + 2 * p.split_c) =
+          make_uint2(pack_bf16(rv.x - bf16_lo(hi.x), rv.y - bf16_hi(hi.x)), pack_bf16(rv.z - bf16_lo(hi.y), rv.w - bf16_hi(hi.y)));
+    }
+  }
 }
 
 }  // namespace deb
@@ -713,9 +825,33 @@ extern "C" int de_gemm(const DeGemm* g, void* stream) {
   } else {
     return fail(DE_ERR_INVALID, "de_gemm: bad a_mode %d", g->a_mode);
   }
+  // Split-K for small grids (the batch-1 latency path, the coarse decoder levels): when the tiles cover less than half
+  // of the SMs and K is long, K-slices of a tile run on different SMs and reduce-add their fp32 partial tiles through
+  // TMA - straight into `out` when the call is an accumulate (ViT proj / fc2: out += ..., bias from slice 0), else into
+  // the caller's zeroed workspace, which splitk_finalize_kernel then turns into the call's real epilogue.
+  int k_splits = 1;
+  bool split_ws = false;
+  if (g->k_splits != 1 && !g->head_w && g->epilogue != 1) {
+    const long long acc_bytes = (long long)p.M * g->N * 4;
+    const bool direct = g->accumulate != 0;
+    const bool ws_ok = g->splitk_ws && g->splitk_ws_bytes >= acc_bytes && g->N % 4 == 0 &&
+                       (reinterpret_cast<uintptr_t>(g->splitk_ws) & 15) == 0;
+    if (direct || ws_ok) {
+      const int bn_s = g->block_n ? bn : (g->N >= 256 ? 256 : bn);
+      const int tiles = p.m_tiles * ((g->N + bn_s - 1) / bn_s);
+      int want = g->k_splits > 1 ? g->k_splits : num_sms() / (tiles > 0 ? tiles : 1);
+      if (want > p.num_k_blocks / 2) want = p.num_k_blocks / 2;       // at least two k-blocks per slice
+      if (want > 16) want = 16;
+      if (want >= 2 && (g->k_splits > 1 || (tiles * 2 <= num_sms() && p.num_k_blocks >= 8))) {
+        k_splits = want;
+        split_ws = !direct;
+        bn = bn_s;                                                    // wide tiles + K-slices instead of narrow tiles
+      }
+    }
+  }
   // small problems (the batch-1 latency path: 5 row tiles at T=577): halve the tile width until the grid covers at
   // least half of the SMs - a 45-CTA launch of 256-wide tiles leaves 100 SMs idle and every CTA streams 2x the weights
-  if (g->block_n == 0 && !g->head_w) {
+  if (g->block_n == 0 && !g->head_w && k_splits == 1) {
     const int half_sms = num_sms() / 2;
     while (bn > 64 && g->N % (bn / 2) == 0 && p.m_tiles * ((g->N + bn - 1) / bn) < half_sms) bn >>= 1;
   }
@@ -724,7 +860,7 @@ extern "C" int de_gemm(const DeGemm* g, void* stream) {
     const uint64_t dims[2] = {(uint64_t)ktot, (uint64_t)g->N};
     const uint64_t strides[1] = {(uint64_t)g->ldw * 2};
     // pair mode: N a multiple of 256 and enough 256-row tile pairs to occupy the 74 SM pairs
-    if (cg == 0) cg = ((bn == 256 || bn == 128) && g->N % bn == 0 && ((p.m_tiles + 1) / 2) * (g->N / bn) >= 64) ? 2 : 1;
+    if (cg == 0) cg = (k_splits == 1 && (bn == 256 || bn == 128) && g->N % bn == 0 && ((p.m_tiles + 1) / 2) * (g->N / bn) >= 64) ? 2 : 1;
     if (cg == 2 && ((bn != 256 && bn != 128) || g->N % bn != 0))
       return fail(DE_ERR_INVALID, "de_gemm: cta_group 2 needs block_n 128 / 256 and N %% block_n == 0");
     const uint32_t box[2] = {BK, (uint32_t)(bn / cg)};
@@ -773,7 +909,52 @@ extern "C" int de_gemm(const DeGemm* g, void* stream) {
   p.head_w = g->head_w;
   p.head_b = g->head_b;
   p.accumulate = g->accumulate;
+  p.k_splits = k_splits;
+  p.kb_per_split = (p.num_k_blocks + k_splits - 1) / k_splits;
+  p.k_splits = (p.num_k_blocks + p.kb_per_split - 1) / p.kb_per_split;   // no empty slice
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (split_ws) {
+    // phase 1 writes raw partial sums into the workspace; the epilogue proper runs in splitk_finalize_kernel
+    FinalizeParams f{};
+    f.acc = reinterpret_cast<float*>(g->splitk_ws);
+    f.M = p.M; f.N = g->N;
+    f.bias = p.bias; f.bias_mod = p.bias_mod; f.act = p.act;
+    f.add1 = p.add1; f.add1_dtype = p.add1_dtype; f.add1_rowmode = p.add1_rowmode; f.add1_pre = p.add1_pre; f.ld_add1 = p.ld_add1;
+    f.add2 = p.add2; f.add2_dtype = p.add2_dtype;
+    f.out = p.out; f.out_dtype = p.out_dtype; f.out_relu = p.out_relu;
+    f.out_pitch = p.out_pitch; f.relu_pitch = p.relu_pitch; f.add2_pitch = p.add2_pitch;
+    f.out_split = p.out_split; f.relu_split = p.relu_split; f.split_c = p.split_c;
+    f.out_rowmode = p.out_rowmode; f.grp = p.grp; f.pad = p.pad; f.off = p.off;
+    f.ps_gh = p.ps_gh; f.ps_gw = p.ps_gw; f.ps_s = p.ps_s; f.ps_cout = p.ps_cout;
+    p.bias = nullptr; p.act = DE_ACT_NONE; p.add1 = nullptr; p.add2 = nullptr; p.out_relu = nullptr;
+    p.out = g->splitk_ws; p.out_dtype = DE_DTYPE_F32; p.ldo = g->N; p.out_split = 0; p.relu_split = 0; p.out_rowmode = 0;
+    p.accumulate = 1;
+    CUtensorMap tcw;
+    const uint32_t ucols = 32;
+    if (g->a_mode == 0) {
+      const uint64_t dims[2] = {(uint64_t)g->N, (uint64_t)p.M};
+      const uint64_t strides[1] = {(uint64_t)g->N * 4};
+      const uint32_t box[2] = {ucols, BM};
+      if (!make_map(&tcw, g->splitk_ws, 2, dims, strides, box, CU_TENSOR_MAP_DATA_TYPE_FLOAT32)) return DE_ERR_CUDA;
+    } else {
+      const uint64_t dims[4] = {(uint64_t)g->N, (uint64_t)g->W, (uint64_t)g->H, (uint64_t)g->B};
+      const uint64_t strides[3] = {(uint64_t)g->N * 4, (uint64_t)g->W * g->N * 4, (uint64_t)g->H * g->W * g->N * 4};
+      const uint32_t box[4] = {ucols, (uint32_t)p.bw, (uint32_t)p.bh, 1};
+      if (!make_map(&tcw, g->splitk_ws, 4, dims, strides, box, CU_TENSOR_MAP_DATA_TYPE_FLOAT32)) return DE_ERR_CUDA;
+    }
+    int rc;
+    switch (bn) {
+      case 256: rc = launch<256, 1, 0>(ta, tb, tcw, p, st); break;
+      case 128: rc = launch<128, 1, 0>(ta, tb, tcw, p, st); break;
+      case 64: rc = launch<64, 1, 0>(ta, tb, tcw, p, st); break;
+      default: return fail(DE_ERR_INVALID, "de_gemm: split-K needs block_n >= 64");
+    }
+    if (rc != DE_OK) return rc;
+    const long long nthr = (long long)f.M * (f.N / 4);
+    splitk_finalize_kernel<<<(unsigned)((nthr + 255) / 256), 256, 0, st>>>(f);
+    count_launch();
+    return cuda_check_launch("splitk_finalize_kernel");
+  }
   // epilogue flavour: the TMA-store epilogue covers "bias + activation -> dense output"
   const int es = g->out_dtype == DE_DTYPE_F32 ? 4 : 2;
   bool store_epi = !g->add1 && !g->add2 && !g->out_relu && !g->head_w && g->out_rowmode == 0 && bn >= 64 && !g->out_split &&

@@ -1,6 +1,8 @@
 // Bandwidth-bound helper kernels between the tensor-core GEMMs: LayerNorm, token casts, cls fill,
 // bilinear x2 upsample (NHWC), strided 3x3 im2col.  All are 16-byte vectorised and grid-stride free
 // (one element group per thread, grids far larger than 148 SMs at the BASELINE shapes).
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "depth_b200.h"
 #include "host_util.h"
@@ -442,6 +444,164 @@ __global__ void groupnorm_apply_kernel(const void* __restrict__ x, int x_f32, co
   }
 }
 
+// One-launch GroupNorm for grids that are co-resident on the GPU (the batch-1 latency path: 49 GroupNorms per DPT_Hybrid
+// frame, two launches each before).  Same partial sums, same fixed-order reduction - hence the same (mean, rstd) bits -
+// as the two-kernel path, but every CTA keeps its pixels in shared memory (fp32), waits on the sample's arrival counter
+// until all partials are published, reduces them itself and normalises straight out of shared memory: x is read once,
+// and the second launch, its tail and its launch gap are gone.  The spin is safe because the host only picks this
+// kernel when gridDim.x * gridDim.y CTAs fit on the device at once (cudaOccupancy...), so every CTA the waiters depend
+// on is running or will be scheduled as soon as an unrelated kernel frees an SM.  Counters: arrive[b] at counters[b],
+// depart[b] at counters[2048 + b]; the last CTA to leave resets both.
+__global__ void __launch_bounds__(256) groupnorm_fused_kernel(const void* __restrict__ x, int x_f32, int HW, int C, int groups,
+                                                              int px_per_block, double* __restrict__ partial,
+                                                              unsigned* __restrict__ counters, double n, float eps,
+                                                              const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                              const void* __restrict__ add, int add_dtype,
+                                                              __nv_bfloat16* __restrict__ out, int out_mode,
+                                                              float* __restrict__ out_f32, __nv_bfloat16* __restrict__ out_plain,
+                                                              int act) {
+  extern __shared__ __align__(16) float gn_tile[];             // [px_per_block][C] fp32
+  __shared__ __align__(16) float s_su[256 * 8], s_sq[256 * 8];
+  __shared__ float2 s_stats[64];
+  __shared__ bool s_last;
+  const int b = blockIdx.y;
+  const int vec = C >> 3, lanes = 256 / vec;
+  const int v = threadIdx.x % vec, pl = threadIdx.x / vec;
+  const int p0 = blockIdx.x * px_per_block;
+  const int p1 = min(p0 + px_per_block, HW);
+  float su[8], sq[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) su[j] = sq[j] = 0.f;
+  for (int p = p0 + pl; p < p1; p += 4 * lanes) {
+    float f[4][8];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (p + u * lanes < p1) load8(x, x_f32, ((long long)b * HW + p + u * lanes) * C + v * 8, f[u]);
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (p + u * lanes < p1) {
+        float* t = gn_tile + (size_t)(p + u * lanes - p0) * C + v * 8;
+        *reinterpret_cast<float4*>(t) = make_float4(f[u][0], f[u][1], f[u][2], f[u][3]);
+        *reinterpret_cast<float4*>(t + 4) = make_float4(f[u][4], f[u][5], f[u][6], f[u][7]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { su[j] += f[u][j]; sq[j] = fmaf(f[u][j], f[u][j], sq[j]); }
+      }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    s_su[pl * C + v * 8 + j] = su[j];
+    s_sq[pl * C + v * 8 + j] = sq[j];
+  }
+  __syncthreads();
+  if (threadIdx.x < groups) {
+    const int cpg = C / groups, g = threadIdx.x;
+    double a = 0.0, q = 0.0;
+    for (int c = g * cpg; c < (g + 1) * cpg; ++c)
+      for (int l = 0; l < lanes; ++l) {
+        a += (double)s_su[l * C + c];
+        q += (double)s_sq[l * C + c];
+      }
+    double* o = partial + (((long long)b * gridDim.x + blockIdx.x) * groups + g) * 2;
+    o[0] = a;
+    o[1] = q;
+    __threadfence();
+  }
+  __syncthreads();
+  const unsigned nblocks = gridDim.x;
+  if (threadIdx.x == 0) {
+    atomicAdd(counters + b, 1u);
+    unsigned spins = 0;
+    while (*reinterpret_cast<volatile unsigned*>(counters + b) < nblocks) {
+      __nanosleep(64);
+      if (++spins > (1u << 24)) __trap();                      // ~1 s: a protocol bug must not hang the GPU
+    }
+    __threadfence();
+  }
+  __syncthreads();
+  // every CTA reduces the sample's partials in the same fixed order as the two-kernel path's last CTA
+  {
+    double2* s_red = reinterpret_cast<double2*>(s_su);
+    const int slices = 256 / groups;
+    const int g = threadIdx.x % groups, sl = threadIdx.x / groups;
+    if (sl < slices) {
+      double a = 0.0, q = 0.0;
+      const double2* pp = reinterpret_cast<const double2*>(partial) + (long long)b * nblocks * groups + g;
+#pragma unroll 4
+      for (int k = sl; k < (int)nblocks; k += slices) {
+        const double2 t = __ldcg(pp + (long long)k * groups);
+        a += t.x;
+        q += t.y;
+      }
+      s_red[sl * groups + g] = make_double2(a, q);
+    }
+    __syncthreads();
+    if (threadIdx.x < groups) {
+      double a = 0.0, q = 0.0;
+      for (int i = 0; i < slices; ++i) {
+        const double2 t = s_red[i * groups + threadIdx.x];
+        a += t.x;
+        q += t.y;
+      }
+      const double m = a / n;
+      double var = q / n - m * m;
+      if (var < 0) var = 0;
+      s_stats[threadIdx.x] = make_float2((float)m, (float)(1.0 / sqrt(var + (double)eps)));
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {                                      // done with the partials and the arrival counter
+    const unsigned prev = atomicAdd(counters + 2048 + b, 1u);
+    if (prev == nblocks - 1) {
+      counters[b] = 0;
+      counters[2048 + b] = 0;
+    }
+  }
+  // normalise out of shared memory
+  const int cpg = C / groups, c0 = v * 8;
+  float ga[8], be[8];
+  float2 st[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    ga[j] = __ldg(gamma + c0 + j);
+    be[j] = __ldg(beta + c0 + j);
+    st[j] = s_stats[(c0 + j) / cpg];
+  }
+  for (int p = p0 + pl; p < p1; p += lanes) {
+    const long long i8 = ((long long)b * HW + p) * C + c0;
+    const float* t = gn_tile + (size_t)(p - p0) * C + c0;
+    const float4 t0 = *reinterpret_cast<const float4*>(t), t1 = *reinterpret_cast<const float4*>(t + 4);
+    float f[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
+    float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (add) {
+      if (add_dtype == DE_DTYPE_F32) {
+        const float4 u0 = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(add) + i8);
+        const float4 u1 = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(add) + i8 + 4);
+        a[0] = u0.x; a[1] = u0.y; a[2] = u0.z; a[3] = u0.w; a[4] = u1.x; a[5] = u1.y; a[6] = u1.z; a[7] = u1.w;
+      } else {
+        const uint4 u = *reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(add) + i8);
+        a[0] = bf16_lo(u.x); a[1] = bf16_hi(u.x); a[2] = bf16_lo(u.y); a[3] = bf16_hi(u.y);
+        a[4] = bf16_lo(u.z); a[5] = bf16_hi(u.z); a[6] = bf16_lo(u.w); a[7] = bf16_hi(u.w);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float y = (f[j] - st[j].x) * st[j].y * ga[j] + be[j] + a[j];
+      if (act == DE_ACT_RELU) y = fmaxf(y, 0.f);
+      f[j] = y;
+    }
+    const uint4 plain = make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+    if (out) {
+      if (out_mode == 1) store_split3(out, (long long)b * HW + p, C, c0, f);
+      else *reinterpret_cast<uint4*>(out + i8) = plain;
+    }
+    if (out_plain) *reinterpret_cast<uint4*>(out_plain + i8) = plain;
+    if (out_f32) {
+      *reinterpret_cast<float4*>(out_f32 + i8) = make_float4(f[0], f[1], f[2], f[3]);
+      *reinterpret_cast<float4*>(out_f32 + i8 + 4) = make_float4(f[4], f[5], f[6], f[7]);
+    }
+  }
+}
+
 }  // namespace deb
 
 using namespace deb;
@@ -587,6 +747,28 @@ extern "C" int de_groupnorm(const void* x, int x_dtype, const float* gamma, cons
   float2* stats = reinterpret_cast<float2*>(reinterpret_cast<char*>(ws) + kGnCounterBytes);
   double* partial = reinterpret_cast<double*>(reinterpret_cast<char*>(ws) + kGnCounterBytes + L.stats_bytes);
   dim3 grid(nblocks, B);
+  {
+    // one-launch path when the whole grid is co-resident (batch-1 latency path); DEB_GN_FUSED=0 disables it
+    static int fused_on = -1;
+    if (fused_on < 0) {
+      const char* e = getenv("DEB_GN_FUSED");
+      fused_on = (e && e[0] == '0') ? 0 : 1;
+    }
+    const size_t tile_bytes = (size_t)px_per_block * C * sizeof(float);
+    if (fused_on && B <= 2048 && tile_bytes <= 160 * 1024) {
+      static SmemOptIn optin;
+      int occ = 0;
+      if (ensure_smem(optin, groupnorm_fused_kernel, (int)tile_bytes) == cudaSuccess &&
+          cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, groupnorm_fused_kernel, 256, tile_bytes) == cudaSuccess &&
+          (long long)occ * num_sms() >= (long long)nblocks * B) {
+        groupnorm_fused_kernel<<<grid, 256, tile_bytes, st>>>(
+            x, x_f32, HW, C, groups, px_per_block, partial, counters, (double)HW * (C / groups), eps, gamma, beta, add,
+            add_dtype, reinterpret_cast<__nv_bfloat16*>(out), out_mode, out_f32, reinterpret_cast<__nv_bfloat16*>(out_plain), act);
+        count_launch();
+        return cuda_check_launch("groupnorm_fused_kernel");
+      }
+    }
+  }
   groupnorm_partial_kernel<<<grid, 256, 0, st>>>(x, x_f32, HW, C, groups, px_per_block, partial, counters, stats,
                                                  (double)HW * (C / groups), eps);
   count_launch();

@@ -479,10 +479,24 @@ class _Pipeline:
             self.ev_out[slot].record()
         return self.ev_out[slot]
 
+    def _copy_out(self, src):
+        """Pinned result -> a fresh array the caller owns; large maps are split over the copy threads."""
+        if self._copiers is None or src.nbytes < (32 << 20):
+            return src.copy()
+        out = np.empty_like(src)
+        B = src.shape[0]
+        step = -(-B // self._ncopy)
+
+        def part(lo):
+            np.copyto(out[lo:lo + step], src[lo:lo + step])
+        for f in [self._copiers.submit(part, lo) for lo in range(0, B, step)]:
+            f.result()
+        return out
+
     def collect(self, slot, fut):
         fut.result().synchronize()                              # enqueued (worker exceptions surface here), then D2H done
         p = self.plans[slot]
-        return StreamResult(p, p.h_map.numpy().copy() if self.want_map else None,
+        return StreamResult(p, self._copy_out(p.h_map.numpy()) if self.want_map else None,
                             p.h_vis.numpy() if self.want_vis else None,
                             p.h_samples.numpy().copy() if self.n_samples else None)
 

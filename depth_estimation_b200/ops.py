@@ -135,7 +135,7 @@ def postprocess(pred: torch.Tensor, H: int, W: int, want_map: bool = True, want_
 def gemm(a: torch.Tensor, w: torch.Tensor, out: torch.Tensor, *, M=None, N=None, K=None, bias=None, act=ACT_NONE,
          add1=None, add1_rowmode=0, add1_pre=False, ld_add1=None, add2=None, out_relu=None, out_rowmode=0, grp=0,
          pad=0, off=0, ldo=None, conv=None, pixel_shuffle=None, bias_mod=0, head=None, block_n=0, cta_group=0, epilogue=0, accumulate=False,
-         out_split=False, relu_split=False, ld_relu=None):
+         out_split=False, relu_split=False, ld_relu=None, k_splits=1, splitk_ws=None):
     """out = epilogue(a @ w.T) through de_gemm (accumulate=True: out += ..., fp32 dense output only).  a: bf16 [M,K] (or NHWC [B,H,W,Cin] with conv=(B,H,W,Cin));
     w: bf16 [N,K].  See include/depth_b200.h for the epilogue contract."""
     _need_cuda(a, w, out, bias, add1, add2, out_relu)
@@ -178,6 +178,11 @@ def gemm(a: torch.Tensor, w: torch.Tensor, out: torch.Tensor, *, M=None, N=None,
         g.out_relu = out_relu.data_ptr()
         g.ld_relu = int(ld_relu if ld_relu is not None else (out_relu.stride(-2) if pixel_shuffle is None else 0))
     g.out_split = 1 if out_split else 0
+    g.k_splits = int(k_splits)
+    if splitk_ws is not None:
+        assert splitk_ws.is_cuda and splitk_ws.is_contiguous()
+        g.splitk_ws = splitk_ws.data_ptr()
+        g.splitk_ws_bytes = splitk_ws.numel() * splitk_ws.element_size()
     g.relu_split = 1 if relu_split else 0
     g.out_rowmode = int(out_rowmode)
     g.grp, g.pad, g.off = int(grp), int(pad), int(off)

@@ -146,6 +146,13 @@ typedef struct DeGemm {
   int64_t ld_relu;   /* row pitch of out_relu in elements; 0 = ldo */
   int add2_dtype;    /* DE_DTYPE_BF16 (default) or DE_DTYPE_F32 (requires add1_pre == 0) */
   int64_t ld_add2;   /* row pitch of add2 in elements; 0 = ldo (pixel shuffle: ps_cout) */
+  /* Split-K (small grids: the batch-1 latency path).  k_splits 0 = automatic, 1 = off, > 1 = forced.  K-slices reduce-add
+   * fp32 partial tiles through TMA: directly into `out` for accumulate calls, otherwise into splitk_ws - a device
+   * buffer of at least M*N*4 bytes (a_mode 1: B*H*W*N*4), 16-byte aligned, ZERO before the call and left zero by it -
+   * followed by one finalize launch that applies the epilogue.  Without a workspace non-accumulate calls never split. */
+  int k_splits;
+  void* splitk_ws;
+  int64_t splitk_ws_bytes;
   int accumulate; /* 1: out += epilogue(A W^T) instead of out = ... (fp32 dense output, a_mode 0, bias + activation
                    * only): the tile leaves through a TMA reduce-add, so the ViT residual stream x += proj(..) /
                    * x += fc2(..) needs neither a bf16 branch buffer nor an add pass.  Each element receives exactly one
