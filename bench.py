@@ -265,6 +265,8 @@ def stream_workload(est, args, B, H, W, rank, world, dev, barrier):
     face_s, vs_s, dt_s = run(n_ser, pipelined=False)
     lat = np.sort(np.asarray(vs_s.performance["depth"])) * 1e3
     equal = bool(face.ri_depths[:n_ser] == face_s.ri_depths and face.abs_depths[:n_ser] == face_s.abs_depths)
+    a, b = np.asarray(face.ri_depths[:n_ser], dtype=np.float64), np.asarray(face_s.ri_depths, dtype=np.float64)
+    max_rel = float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-12)))
     t = torch.tensor([dt], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -276,7 +278,7 @@ def stream_workload(est, args, B, H, W, rank, world, dev, barrier):
     stream = {"frames": n_frames, "frames_per_submission": B, "fused_fps": world * n_frames / dt,
               "serial_loop": {"frames": n_ser, "fps": n_ser / dt_s, "p50_ms": float(lat[len(lat) // 2]),
                               "what": "reference order, one blocking DepthEstimator.predict per frame (fp32 map to the host)"},
-              "ri_depth_abs_depth_equal_to_serial_loop": equal,
+              "ri_depth_abs_depth_equal_to_serial_loop": equal, "ri_depth_max_rel_diff_vs_serial_loop": max_rel,
               "ri_depth_first3": [float(x) for x in face.ri_depths[:3]], "abs_depth_first3": [float(x) for x in face.abs_depths[:3]]}
     return e2e, stream
 

@@ -478,6 +478,8 @@ static Plan& get_plan(Engine& e, int B, int H, int W) {
   p->x_in = p->ws.pool.alloc(in_bytes);
   ENG_CUDA(cudaMemset(p->x_in, 0, in_bytes));
   p->pred = reinterpret_cast<float*>(p->ws.pool.alloc(px * 4));
+  p->splitk_ws_bytes = 64 << 20;                              // K-slice partial tiles of the GEMMs small enough to be split
+  p->splitk_ws = p->ws.pool.alloc((size_t)p->splitk_ws_bytes);
   Plan& ref = *p;
   e.plans[key] = std::move(p);
   return ref;

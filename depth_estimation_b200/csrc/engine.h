@@ -197,6 +197,8 @@ struct Plan {
   WorkSet ws;
   void* x_in = nullptr;                                        // K1 output (network input)
   float* pred = nullptr;                                       // network output [B, net_h, net_w]
+  void* splitk_ws = nullptr;                                   // fp32 scratch for the K-slices of split-K GEMMs
+  int64_t splitk_ws_bytes = 0;
   bool warm = false;
   std::map<std::vector<uint64_t>, GraphEntry> graphs;          // keyed on the IO pointers / scalars baked into the capture
   ~Plan();

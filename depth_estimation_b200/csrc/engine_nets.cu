@@ -56,8 +56,6 @@ inline Gemm conv3(const void* a, int B, int H, int W, int cin, const void* w, in
   g.ldo = ldo;
   return g;
 }
-inline void run(const Gemm& g, cudaStream_t st) { ENG_CK(de_gemm(&g, st)); }
-
 struct Ctx {
   Engine& e;
   Plan& p;
@@ -69,6 +67,13 @@ struct Ctx {
     return reinterpret_cast<T*>(p.ws.get(key, bytes));
   }
 };
+
+// every GEMM may use the plan's split-K workspace (de_gemm decides; small grids only)
+inline void run(Gemm g, Ctx& c) {
+  g.splitk_ws = c.p.splitk_ws;
+  g.splitk_ws_bytes = c.p.splitk_ws_bytes;
+  ENG_CK(de_gemm(&g, c.st));
+}
 
 struct Feat {
   void* p = nullptr;
@@ -92,7 +97,7 @@ void vit_blocks(Ctx& c, float* x, int B, int T, Hook on_hook) {
     {
       Gemm g = dense(xn, D, M, D, w.qkv_w, D, 3 * D, qkv, DE_DTYPE_BF16, 3 * D);
       g.bias = w.qkv_b;
-      run(g, c.st);
+      run(g, c);
     }
     ENG_CK(de_attention(qkv, att, B, T, v.heads, scale, c.st));
     {
@@ -100,20 +105,20 @@ void vit_blocks(Ctx& c, float* x, int B, int T, Hook on_hook) {
       Gemm g = dense(att, D, M, D, w.proj_w, D, D, x, DE_DTYPE_F32, D);
       g.bias = w.proj_b;
       g.accumulate = 1;
-      run(g, c.st);
+      run(g, c);
     }
     ENG_CK(de_layernorm(x, D, nullptr, 0, 0, w.n2w, w.n2b, M, D, 1e-6f, xn, D, c.st));
     {
       Gemm g = dense(xn, D, M, D, w.fc1_w, D, 4 * D, hid, DE_DTYPE_BF16, 4 * D);
       g.bias = w.fc1_b;
       g.act = DE_ACT_GELU;
-      run(g, c.st);
+      run(g, c);
     }
     {
       Gemm g = dense(hid, 4 * D, M, 4 * D, w.fc2_w, 4 * D, D, x, DE_DTYPE_F32, D);
       g.bias = w.fc2_b;
       g.accumulate = 1;
-      run(g, c.st);
+      run(g, c);
     }
     on_hook(i);
   }
@@ -130,7 +135,7 @@ Feat reassemble(Ctx& c, const ReasmW& r, int idx, const float* x, int B, int gh,
   {
     Gemm g = dense(cls, D, B, D, reinterpret_cast<const uint16_t*>(r.w_read) + D, 2 * D, D, cproj, DE_DTYPE_F32, D);
     g.bias = r.b_read;
-    run(g, c.st);
+    run(g, c);
   }
   void* rr = c.buf("ra%d.r", (size_t)B * N * D * 2, idx);
   {
@@ -142,13 +147,13 @@ Feat reassemble(Ctx& c, const ReasmW& r, int idx, const float* x, int B, int gh,
     g.add1_rowmode = 1;
     g.add1_pre = 1;
     g.grp = N;
-    run(g, c.st);
+    run(g, c);
   }
   void* pp = c.buf("ra%d.p", (size_t)B * N * co * 2, idx);
   {
     Gemm g = dense(rr, D, B * N, D, r.w1, D, co, pp, DE_DTYPE_BF16, co);
     g.bias = r.b1;
-    run(g, c.st);
+    run(g, c);
   }
   Feat f;
   f.C = co;
@@ -169,7 +174,7 @@ Feat reassemble(Ctx& c, const ReasmW& r, int idx, const float* x, int B, int gh,
     g.ps_gw = gw;
     g.ps_s = s;
     g.ps_cout = co;
-    run(g, c.st);
+    run(g, c);
     f.p = out;
     f.H = gh * s;
     f.W = gw * s;
@@ -182,7 +187,7 @@ Feat reassemble(Ctx& c, const ReasmW& r, int idx, const float* x, int B, int gh,
   {
     Gemm g = dense(col, 9 * co, B * ho * wo, 9 * co, r.w4, 9 * co, co, out, DE_DTYPE_BF16, co);
     g.bias = r.b4;
-    run(g, c.st);
+    run(g, c);
   }
   f.p = out;
   f.H = ho;
@@ -205,7 +210,7 @@ void decoder_plain(Ctx& c, const Feat* feats) {
     rel[i].p = c.buf("dec.rnr%d", n, i);
     Gemm g = conv3(x.p, B, x.H, x.W, x.C, d.rn_w[i], f, raw[i].p, DE_DTYPE_BF16, f);
     g.out_relu = rel[i].p;
-    run(g, c.st);
+    run(g, c);
   }
   // conv2(relu(conv1(relu(x)))) + x [+ extra]; returns the raw sum, optionally its ReLU copy
   auto rcu = [&](int lvl, int unit, const void* x_raw, const void* x_relu, int H, int W, int C, const void* extra, void** out_relu) {
@@ -216,7 +221,7 @@ void decoder_plain(Ctx& c, const Feat* feats) {
       Gemm g = conv3(x_relu, B, H, W, C, r.w[unit][0], C, t, DE_DTYPE_BF16, C);
       g.bias = r.b[unit][0];
       g.act = DE_ACT_RELU;
-      run(g, c.st);
+      run(g, c);
     }
     void* o = c.buf("dec.l%d.u%d.o", n, lvl, unit);
     void* orl = out_relu ? c.buf("dec.l%d.u%d.or", n, lvl, unit) : nullptr;
@@ -229,7 +234,7 @@ void decoder_plain(Ctx& c, const Feat* feats) {
       g.add2 = extra;
       g.add2_dtype = DE_DTYPE_BF16;
       g.out_relu = orl;
-      run(g, c.st);
+      run(g, c);
     }
     if (out_relu) *out_relu = orl;
     return o;
@@ -250,7 +255,7 @@ void decoder_plain(Ctx& c, const Feat* feats) {
     {
       Gemm g = dense(u, C, B * H * W, C, r.out_w, C, co, v, DE_DTYPE_BF16, co);
       g.bias = r.out_b;
-      run(g, c.st);
+      run(g, c);
     }
     path = Feat{c.buf("dec.l%d.up", (size_t)B * 4 * H * W * co * 2, i), 2 * H, 2 * W, co};
     ENG_CK(de_upsample2x(v, path.p, B, H, W, co, 1, c.st));
@@ -260,7 +265,7 @@ void decoder_plain(Ctx& c, const Feat* feats) {
   {
     Gemm g = conv3(path.p, B, H, W, path.C, d.h0_w, d.h0_c, h0, DE_DTYPE_BF16, d.h0_c);
     g.bias = d.h0_b;
-    run(g, c.st);
+    run(g, c);
   }
   if (d.h0_c % 64 == 0 && d.h0_c <= 128) {      // DPT: upsample + head tail in one halo-tiled kernel
     ENG_CK(de_head_up_conv(h0, d.h2_w, (int64_t)9 * d.h0_c, d.h2_b, d.h4_w, d.h4_b, c.p.pred, B, H, W, d.h0_c, d.head_ac ? 1 : 0, c.st));
@@ -272,7 +277,7 @@ void decoder_plain(Ctx& c, const Feat* feats) {
     g.act = DE_ACT_RELU;
     g.head_w = d.h4_w;
     g.head_b = d.h4_b;
-    run(g, c.st);
+    run(g, c);
   }
 }
 
@@ -294,7 +299,7 @@ void decoder_split3(Ctx& c, const Feat* feats) {
     g.out_relu = rel[i].p;
     g.relu_split = 1;
     g.ld_relu = 3 * f;
-    run(g, c.st);
+    run(g, c);
   }
   // last == false: (fp32 sum, split3 relu(sum)); last == true: the sum as a split3 operand
   auto rcu = [&](int lvl, int unit, const void* x_raw, const void* x_relu, int H, int W, int C, const void* extra, bool last,
@@ -307,7 +312,7 @@ void decoder_split3(Ctx& c, const Feat* feats) {
       g.bias = r.b[unit][0];
       g.act = DE_ACT_RELU;
       g.out_split = 1;
-      run(g, c.st);
+      run(g, c);
     }
     Gemm g = conv3(t, B, H, W, 3 * C, r.w[unit][1], C, nullptr, 0, 0);
     g.bias = r.b[unit][1];
@@ -334,7 +339,7 @@ void decoder_split3(Ctx& c, const Feat* feats) {
       g.ld_relu = 3 * C;
       *out_relu = orl;
     }
-    run(g, c.st);
+    run(g, c);
     return o;
   };
   Feat path;
@@ -353,7 +358,7 @@ void decoder_split3(Ctx& c, const Feat* feats) {
     {
       Gemm g = dense(u, 3 * C, B * H * W, 3 * C, r.out_w, 3 * C, co, v, DE_DTYPE_F32, co);
       g.bias = r.out_b;
-      run(g, c.st);
+      run(g, c);
     }
     if (i > 0) {
       path = Feat{c.buf("dec3.l%d.up", (size_t)B * 4 * H * W * co * 4, i), 2 * H, 2 * W, co};
@@ -368,7 +373,7 @@ void decoder_split3(Ctx& c, const Feat* feats) {
   {
     Gemm g = conv3(path.p, B, H, W, path.C, d.h0_w, d.h0_c, h0, DE_DTYPE_F32, d.h0_c);
     g.bias = d.h0_b;
-    run(g, c.st);
+    run(g, c);
   }
   void* h1 = c.buf("dec3.h1", (size_t)B * 4 * H * W * 3 * d.h0_c * 2);
   ENG_CK(de_upsample2x_ex(h0, DE_DTYPE_F32, h1, 1, B, H, W, d.h0_c, d.head_ac ? 1 : 0, c.st));
@@ -377,7 +382,7 @@ void decoder_split3(Ctx& c, const Feat* feats) {
   g.act = DE_ACT_RELU;
   g.head_w = d.h4_w;
   g.head_b = d.h4_b;
-  run(g, c.st);
+  run(g, c);
 }
 
 void decoder(Ctx& c, const Feat* feats) {
@@ -413,7 +418,7 @@ void forward_large(Engine& e, Plan& p, cudaStream_t st) {
     g.grp = N;
     g.pad = 1;
     g.off = 1;
-    run(g, st);
+    run(g, c);
   }
   ENG_CK(de_fill_cls(x, D, B, T, D, e.vit.cls, pos, st));
   Feat feats[4];
@@ -460,7 +465,7 @@ void forward_hybrid(Engine& e, Plan& p, cudaStream_t st) {
     void* col = c.buf("stemcol", (size_t)B * H * W * 3 * 152 * 2);
     ENG_CK(de_stem_im2col_split3(reinterpret_cast<const float*>(p.x_in), col, B, p.net_h, p.net_w, 7, 2, 152, st));
     Gemm g = dense(col, 3 * 152, B * H * W, 3 * 152, hw.stem_w3, 3 * 152, 64, s0, DE_DTYPE_F32, 64);
-    run(g, st);
+    run(g, c);
   }
   float* s1 = c.buf<float>("stemn", (size_t)B * H * W * 64 * 4);
   ENG_CK(de_groupnorm(s0, DE_DTYPE_F32, hw.stem_g, hw.stem_b, nullptr, 0, nullptr, 0, s1, nullptr, B, H * W, 64, 32, 1e-5f,
@@ -488,28 +493,28 @@ void forward_hybrid(Engine& e, Plan& p, cudaStream_t st) {
           xs = sub;
         }
         float* dconv = c.buf<float>("s%d.b%d.dc", pout * cout * 4, si, bi);
-        run(dense(xs, 3 * cin, (int)pout, 3 * cin, k.wd, 3 * cin, cout, dconv, DE_DTYPE_F32, cout), st);
+        run(dense(xs, 3 * cin, (int)pout, 3 * cin, k.wd, 3 * cin, cout, dconv, DE_DTYPE_F32, cout), c);
         float* sc = c.buf<float>("s%d.b%d.dn", pout * cout * 4, si, bi);
         ENG_CK(de_groupnorm(dconv, DE_DTYPE_F32, k.ndg, k.ndb, nullptr, 0, nullptr, 0, sc, nullptr, B, Ho * Wo, cout, 32, 1e-5f,
                             DE_ACT_NONE, hr.gn_ws, hr.gn_ws_bytes, st));
         shortcut = sc;
       }
       float* t = c.buf<float>("s%d.b%d.c1", pin * mid * 4, si, bi);
-      run(dense(x, 3 * cin, (int)pin, 3 * cin, k.w1, 3 * cin, mid, t, DE_DTYPE_F32, mid), st);
+      run(dense(x, 3 * cin, (int)pin, 3 * cin, k.w1, 3 * cin, mid, t, DE_DTYPE_F32, mid), c);
       void* t3 = c.buf("s%d.b%d.n1", pin * 3 * mid * 2, si, bi);
       hr.gn(t, k.ng[0], k.nb[0], H * W, mid, DE_ACT_RELU, nullptr, t3, nullptr, nullptr);
       float* u = c.buf<float>("s%d.b%d.c2", pout * mid * 4, si, bi);
       if (s == 1) {
-        run(conv3(t3, B, H, W, 3 * mid, k.w2, mid, u, DE_DTYPE_F32, mid), st);
+        run(conv3(t3, B, H, W, 3 * mid, k.w2, mid, u, DE_DTYPE_F32, mid), c);
       } else {
         void* col = c.buf("s%d.b%d.col", pout * 27 * mid * 2, si, bi);
         ENG_CK(de_im2col3x3(t3, col, B, H, W, 3 * mid, s, same_pad_before(H, 3, s), same_pad_before(W, 3, s), Ho, Wo, st));
-        run(dense(col, 27 * mid, (int)pout, 27 * mid, k.w2, 27 * mid, mid, u, DE_DTYPE_F32, mid), st);
+        run(dense(col, 27 * mid, (int)pout, 27 * mid, k.w2, 27 * mid, mid, u, DE_DTYPE_F32, mid), c);
       }
       void* u3 = c.buf("s%d.b%d.n2", pout * 3 * mid * 2, si, bi);
       hr.gn(u, k.ng[1], k.nb[1], Ho * Wo, mid, DE_ACT_RELU, nullptr, u3, nullptr, nullptr);
       float* v = c.buf<float>("s%d.b%d.c3", pout * cout * 4, si, bi);
-      run(dense(u3, 3 * mid, (int)pout, 3 * mid, k.w3, 3 * mid, cout, v, DE_DTYPE_F32, cout), st);
+      run(dense(u3, 3 * mid, (int)pout, 3 * mid, k.w3, 3 * mid, cout, v, DE_DTYPE_F32, cout), c);
       void* y3 = c.buf("s%d.b%d.n3", pout * 3 * cout * 2, si, bi);
       float* y32 = c.buf<float>("s%d.b%d.n3f", pout * cout * 4, si, bi);
       // stages 0 / 1 also feed the decoder: as the split3 operand they already are, or as a plain bf16 copy
@@ -539,7 +544,7 @@ void forward_hybrid(Engine& e, Plan& p, cudaStream_t st) {
     g.grp = N;
     g.pad = 1;
     g.off = 1;
-    run(g, st);
+    run(g, c);
   }
   ENG_CK(de_fill_cls(tok, D, B, T, D, e.vit.cls, pos, st));
   vit_blocks(c, tok, B, T, [&](int i) {
@@ -571,7 +576,7 @@ void forward_small(Engine& e, Plan& p, cudaStream_t st) {
       Gemm g = dense(x, m.cin, (int)pin, m.cin, m.exp_w, m.cin, m.mid, ex, DE_DTYPE_BF16, m.mid);
       g.bias = m.exp_b;
       g.act = DE_ACT_RELU6;
-      run(g, st);
+      run(g, c);
       t = ex;
     }
     void* dwo = c.buf("mb%d.d", pout * m.mid * 2, bi);
@@ -585,7 +590,7 @@ void forward_small(Engine& e, Plan& p, cudaStream_t st) {
         g.add1_dtype = DE_DTYPE_BF16;
         g.ld_add1 = m.cin;
       }
-      run(g, st);
+      run(g, c);
     }
     x = y;
     H = Ho;

@@ -51,6 +51,7 @@ struct GemmParams {
   float head_b;
   int accumulate;  // store epilogue only: TMA reduce-add instead of store
   int k_splits, kb_per_split;  // split-K: work item = (tile, split); split s covers k-blocks [s*kb_per_split, ...)
+  int split_rows, split_b;     // split-K partial tiles go to slice `split` of the workspace: row / image offset per slice
 };
 
 // EPI 0: "store" epilogue - bias + activation only, output tile staged in 128B-swizzled smem and written
@@ -290,11 +291,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const int tile = work / p.k_splits, split = work - tile * p.k_splits;
       const int m_tile = (tile / p.n_tiles) * CG + cta_rank, n_tile = tile % p.n_tiles;
       // bias slice of this group's units, fetched while the main loop of the tile is still running
-      // (split-K: the partial sums are reduce-added into the output; only split 0 contributes the bias)
       for (int u = grp; u < units; u += 2) {
         if (gtid < ucols) {
           const int n = n_tile * BN + u * ucols + gtid;
-          s_bias[u * ucols + gtid] = (p.bias && n < p.N && split == 0) ? __ldg(p.bias + (n % bias_mod)) : 0.f;
+          s_bias[u * ucols + gtid] = (p.bias && n < p.N) ? __ldg(p.bias + (n % bias_mod)) : 0.f;
         }
       }
       int b = 0, y0 = 0, x0 = 0;
@@ -390,10 +390,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         if (gtid == 0) {
           if (m_tile < p.m_tiles) {
             const int col0 = n_tile * BN + u * ucols;
-            if (p.accumulate) {
-              if (p.a_mode == 0) tma_reduce_add_2d(&tmC, sbuf, col0, m_tile * BM);
-              else tma_reduce_add_4d(&tmC, sbuf, col0, x0, y0, b);
-            } else if (p.a_mode == 0) tma_store_2d(&tmC, sbuf, col0, m_tile * BM);
+            if (p.k_splits > 1) {                // K-slice: raw partial tile into its own slice of the workspace
+              if (p.a_mode == 0) tma_store_2d(&tmC, sbuf, col0, split * p.split_rows + m_tile * BM);
+              else tma_store_4d(&tmC, sbuf, col0, x0, y0, split * p.split_b + b);
+            } else if (p.accumulate) tma_reduce_add_2d(&tmC, sbuf, col0, m_tile * BM);
+            else if (p.a_mode == 0) tma_store_2d(&tmC, sbuf, col0, m_tile * BM);
             else tma_store_4d(&tmC, sbuf, col0, x0, y0, b);
           }
           tma_store_commit();            // one (possibly empty) group per unit: wait_read<N> counts units, not stores
@@ -677,12 +678,16 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMa
 }
 
 // ------------------------------------------------------------------------------------------------ split-K finalize
-// Second half of a split-K call: the K-slices have reduce-added their fp32 partial tiles into the workspace `acc`
-// [M, N]; this kernel applies the call's epilogue (the contract of DeGemm: bias, add1 before / after the activation,
-// add2, row maps, pixel shuffle, split3 stores, ReLU copy) to it and leaves the workspace zeroed for the next call.
-// One thread per (row, 4 columns).
+// Second half of a split-K call: every K-slice has stored its fp32 partial tiles into its own slice of the workspace
+// `acc` [splits][rows_per_slice][N]; this kernel adds the slices in a FIXED order (bitwise reproducible - a reduce-add
+// of the slices into one buffer would not be) and applies the call's epilogue (the contract of DeGemm: bias, add1
+// before / after the activation, add2, row maps, pixel shuffle, split3 stores, ReLU copy; accumulate: += into the
+// fp32 output).  One thread per (row, 4 columns).
 struct FinalizeParams {
-  float* acc;
+  const float* acc;
+  int splits;
+  long long slice_stride;   // elements between slices
+  int accumulate;
   int M, N;
   const float* bias;
   int bias_mod, act;
@@ -705,9 +710,12 @@ __global__ void __launch_bounds__(256) splitk_finalize_kernel(const FinalizePara
   if (idx >= (long long)p.M * n4) return;
   const long long m = idx / n4;
   const int n = static_cast<int>(idx - m * n4) * 4;
-  float4* ap = reinterpret_cast<float4*>(p.acc + m * p.N + n);
-  float4 v = *ap;
-  *ap = make_float4(0.f, 0.f, 0.f, 0.f);
+  const float* ap = p.acc + m * p.N + n;
+  float4 v = *reinterpret_cast<const float4*>(ap);
+  for (int sl = 1; sl < p.splits; ++sl) {
+    const float4 t = *reinterpret_cast<const float4*>(ap + sl * p.slice_stride);
+    v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+  }
   if (p.bias) {
     const int bm = p.bias_mod > 0 ? p.bias_mod : p.N;
     v.x += __ldg(p.bias + (n % bm)); v.y += __ldg(p.bias + ((n + 1) % bm));
@@ -755,7 +763,12 @@ __global__ void __launch_bounds__(256) splitk_finalize_kernel(const FinalizePara
   }
   const long long o = unit * p.out_pitch + colpart;
   if (p.out_dtype == DE_DTYPE_F32) {
-    *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + o) = v;
+    float4* op = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + o);
+    if (p.accumulate) {
+      const float4 old = *op;
+      v.x += old.x; v.y += old.y; v.z += old.z; v.w += old.w;
+    }
+    *op = v;
   } else {
     const uint2 hi = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
     __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(p.out) + o;
@@ -825,30 +838,26 @@ extern "C" int de_gemm(const DeGemm* g, void* stream) {
   } else {
     return fail(DE_ERR_INVALID, "de_gemm: bad a_mode %d", g->a_mode);
   }
-  // Split-K for small grids (the batch-1 latency path, the coarse decoder levels): when the tiles cover less than half
-  // of the SMs and K is long, K-slices of a tile run on different SMs and reduce-add their fp32 partial tiles through
-  // TMA - straight into `out` when the call is an accumulate (ViT proj / fc2: out += ..., bias from slice 0), else into
-  // the caller's zeroed workspace, which splitk_finalize_kernel then turns into the call's real epilogue.
+  // Split-K for small grids (the batch-1 latency path, the coarse decoder levels): when the tiles cover a fraction of the
+  // SMs and K is long, K-slices of a tile run on different SMs and store their fp32 partial tiles into per-slice
+  // regions of the caller's workspace; splitk_finalize_kernel adds the slices in a fixed order and applies the epilogue.
   int k_splits = 1;
-  bool split_ws = false;
-  if (g->k_splits != 1 && !g->head_w && g->epilogue != 1) {
-    const long long acc_bytes = (long long)p.M * g->N * 4;
-    const bool direct = g->accumulate != 0;
-    const bool ws_ok = g->splitk_ws && g->splitk_ws_bytes >= acc_bytes && g->N % 4 == 0 &&
-                       (reinterpret_cast<uintptr_t>(g->splitk_ws) & 15) == 0;
-    if (direct || ws_ok) {
-      const int bn_s = g->block_n ? bn : (g->N >= 256 ? 256 : bn);
-      const int tiles = p.m_tiles * ((g->N + bn_s - 1) / bn_s);
-      int want = g->k_splits > 1 ? g->k_splits : num_sms() / (tiles > 0 ? tiles : 1);
-      if (want > p.num_k_blocks / 2) want = p.num_k_blocks / 2;       // at least two k-blocks per slice
-      if (want > 16) want = 16;
-      if (want >= 2 && (g->k_splits > 1 || (tiles * 2 <= num_sms() && p.num_k_blocks >= 8))) {
-        k_splits = want;
-        split_ws = !direct;
-        bn = bn_s;                                                    // wide tiles + K-slices instead of narrow tiles
-      }
+  if (g->k_splits != 1 && !g->head_w && g->epilogue != 1 && g->splitk_ws && g->N % 4 == 0 &&
+      (reinterpret_cast<uintptr_t>(g->splitk_ws) & 15) == 0 && (!g->accumulate || (g->act == DE_ACT_NONE && g->out_dtype == DE_DTYPE_F32))) {
+    const int bn_s = g->block_n ? bn : (g->N >= 256 ? 256 : bn);
+    const int tiles = p.m_tiles * ((g->N + bn_s - 1) / bn_s);
+    const long long slice_bytes = (g->a_mode == 0 ? (long long)p.m_tiles * BM : (long long)p.M) * g->N * 4;
+    int want = g->k_splits > 1 ? g->k_splits : num_sms() / (tiles > 0 ? tiles : 1);
+    if (want > p.num_k_blocks / 2) want = p.num_k_blocks / 2;         // at least two k-blocks per slice
+    if (want > 16) want = 16;
+    if (slice_bytes > 0 && want > g->splitk_ws_bytes / slice_bytes) want = (int)(g->splitk_ws_bytes / slice_bytes);
+    const bool worth = tiles * 3 <= num_sms() && p.num_k_blocks >= 24;   // the finalize launch must pay for itself
+    if (want >= 2 && bn_s >= 64 && (g->k_splits > 1 || worth)) {
+      k_splits = want;
+      bn = bn_s;                                                      // wide tiles + K-slices instead of narrow tiles
     }
   }
+  const bool split_ws = k_splits > 1;
   // small problems (the batch-1 latency path: 5 row tiles at T=577): halve the tile width until the grid covers at
   // least half of the SMs - a 45-CTA launch of 256-wide tiles leaves 100 SMs idle and every CTA streams 2x the weights
   if (g->block_n == 0 && !g->head_w && k_splits == 1) {
@@ -914,9 +923,13 @@ extern "C" int de_gemm(const DeGemm* g, void* stream) {
   p.k_splits = (p.num_k_blocks + p.kb_per_split - 1) / p.kb_per_split;   // no empty slice
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (split_ws) {
-    // phase 1 writes raw partial sums into the workspace; the epilogue proper runs in splitk_finalize_kernel
+    // phase 1 stores raw partial tiles into workspace slices; the epilogue proper runs in splitk_finalize_kernel
+    const long long slice_rows = g->a_mode == 0 ? (long long)p.m_tiles * BM : (long long)p.M;
     FinalizeParams f{};
-    f.acc = reinterpret_cast<float*>(g->splitk_ws);
+    f.acc = reinterpret_cast<const float*>(g->splitk_ws);
+    f.splits = p.k_splits;
+    f.slice_stride = slice_rows * g->N;
+    f.accumulate = g->accumulate;
     f.M = p.M; f.N = g->N;
     f.bias = p.bias; f.bias_mod = p.bias_mod; f.act = p.act;
     f.add1 = p.add1; f.add1_dtype = p.add1_dtype; f.add1_rowmode = p.add1_rowmode; f.add1_pre = p.add1_pre; f.ld_add1 = p.ld_add1;
@@ -928,16 +941,18 @@ extern "C" int de_gemm(const DeGemm* g, void* stream) {
     f.ps_gh = p.ps_gh; f.ps_gw = p.ps_gw; f.ps_s = p.ps_s; f.ps_cout = p.ps_cout;
     p.bias = nullptr; p.act = DE_ACT_NONE; p.add1 = nullptr; p.add2 = nullptr; p.out_relu = nullptr;
     p.out = g->splitk_ws; p.out_dtype = DE_DTYPE_F32; p.ldo = g->N; p.out_split = 0; p.relu_split = 0; p.out_rowmode = 0;
-    p.accumulate = 1;
+    p.accumulate = 0;
+    p.split_rows = (int)slice_rows;
+    p.split_b = g->B;
     CUtensorMap tcw;
     const uint32_t ucols = 32;
     if (g->a_mode == 0) {
-      const uint64_t dims[2] = {(uint64_t)g->N, (uint64_t)p.M};
+      const uint64_t dims[2] = {(uint64_t)g->N, (uint64_t)(slice_rows * p.k_splits)};
       const uint64_t strides[1] = {(uint64_t)g->N * 4};
       const uint32_t box[2] = {ucols, BM};
       if (!make_map(&tcw, g->splitk_ws, 2, dims, strides, box, CU_TENSOR_MAP_DATA_TYPE_FLOAT32)) return DE_ERR_CUDA;
     } else {
-      const uint64_t dims[4] = {(uint64_t)g->N, (uint64_t)g->W, (uint64_t)g->H, (uint64_t)g->B};
+      const uint64_t dims[4] = {(uint64_t)g->N, (uint64_t)g->W, (uint64_t)g->H, (uint64_t)g->B * p.k_splits};
       const uint64_t strides[3] = {(uint64_t)g->N * 4, (uint64_t)g->W * g->N * 4, (uint64_t)g->H * g->W * g->N * 4};
       const uint32_t box[4] = {ucols, (uint32_t)p.bw, (uint32_t)p.bh, 1};
       if (!make_map(&tcw, g->splitk_ws, 4, dims, strides, box, CU_TENSOR_MAP_DATA_TYPE_FLOAT32)) return DE_ERR_CUDA;

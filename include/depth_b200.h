@@ -146,10 +146,11 @@ typedef struct DeGemm {
   int64_t ld_relu;   /* row pitch of out_relu in elements; 0 = ldo */
   int add2_dtype;    /* DE_DTYPE_BF16 (default) or DE_DTYPE_F32 (requires add1_pre == 0) */
   int64_t ld_add2;   /* row pitch of add2 in elements; 0 = ldo (pixel shuffle: ps_cout) */
-  /* Split-K (small grids: the batch-1 latency path).  k_splits 0 = automatic, 1 = off, > 1 = forced.  K-slices reduce-add
-   * fp32 partial tiles through TMA: directly into `out` for accumulate calls, otherwise into splitk_ws - a device
-   * buffer of at least M*N*4 bytes (a_mode 1: B*H*W*N*4), 16-byte aligned, ZERO before the call and left zero by it -
-   * followed by one finalize launch that applies the epilogue.  Without a workspace non-accumulate calls never split. */
+  /* Split-K (small grids: the batch-1 latency path).  k_splits 0 = automatic, 1 = off, > 1 = forced.  Each K-slice stores
+   * its fp32 partial tiles into its own region of splitk_ws (device scratch, 16-byte aligned, no initial contents
+   * required; a slice is ceil128(M)*N*4 bytes, a_mode 1: B*H*W*N*4; the slice count is capped by the size given) and
+   * one finalize launch adds the slices in a fixed order - bitwise reproducible - and applies the epilogue (accumulate
+   * included).  Without a workspace a call never splits. */
   int k_splits;
   void* splitk_ws;
   int64_t splitk_ws_bytes;

@@ -761,6 +761,78 @@ def test_split3_gemm_precision(conv):
     assert e3 < 3e-5 and e3 < e1 / 30
 
 
+@pytest.mark.parametrize("M,N,K,ks", [(577, 768, 3072, 0), (577, 768, 768, 4), (300, 256, 2304, 3), (128, 64, 512, 16)])
+def test_gemm_splitk_accumulate(M, N, K, ks):
+    """Split-K of an accumulate call (ViT proj / fc2 at batch 1): the finalize pass adds the K-slices in a fixed order
+    into the fp32 stream.  k_splits 0 = automatic choice.  Bitwise reproducible run to run."""
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    a = _rand((M, K), dev, seed=91).bfloat16()
+    w = _rand((N, K), dev, 0.05, seed=92).bfloat16()
+    bias = _rand((N,), dev, seed=93)
+    x0 = _rand((M, N), dev, seed=94)
+    x1, x2, x3 = x0.clone(), x0.clone(), x0.clone()
+    ws = torch.empty(32 << 20, dtype=torch.uint8, device=dev).fill_(0x7f)       # no initial contents required
+    ops.gemm(a, w, x1, bias=bias, accumulate=True, k_splits=1)
+    ops.gemm(a, w, x2, bias=bias, accumulate=True, k_splits=ks, splitk_ws=ws)
+    ws.fill_(0xff)
+    ops.gemm(a, w, x3, bias=bias, accumulate=True, k_splits=ks, splitk_ws=ws)
+    ref = x0.double() + a.double() @ w.double().t() + bias.double()
+    torch.cuda.synchronize()
+    assert _relerr(x1, ref) < 1e-5 and _relerr(x2, ref) < 1e-5
+    assert _relerr(x2, x1) < 1e-5 and torch.equal(x2, x3)
+
+
+@pytest.mark.parametrize("case", ["dense_bias_gelu", "conv_residual_relu", "conv_split3", "pixel_shuffle"])
+def test_gemm_splitk_workspace(case):
+    """Split-K through the sliced workspace + finalize launch reproduces the single-pass epilogue (bias, activation,
+    fp32 / bf16 skip inputs, ReLU copy, split3 stores, pixel shuffle)."""
+    from depth_estimation_b200 import ops
+    from depth_estimation_b200.weights import pack_conv3x3, pack_conv_transpose
+    dev = _dev()
+    ws = torch.empty(32 << 20, dtype=torch.uint8, device=dev).fill_(0x7f)
+    if case == "dense_bias_gelu":
+        M, N, K = 577, 768, 1536
+        a, w, bias = _rand((M, K), dev, seed=95).bfloat16(), _rand((N, K), dev, 0.05, seed=96).bfloat16(), _rand((N,), dev, seed=97)
+        o1 = torch.empty((M, N), dtype=torch.bfloat16, device=dev)
+        o2 = torch.full_like(o1, float("nan"))
+        ops.gemm(a, w, o1, bias=bias, act=ops.ACT_GELU)
+        ops.gemm(a, w, o2, bias=bias, act=ops.ACT_GELU, k_splits=4, splitk_ws=ws)
+    elif case in ("conv_residual_relu", "conv_split3"):
+        B, H, W, Cin, Cout = 2, 12, 12, 256, 64
+        a = _rand((B, H, W, Cin), dev, seed=98).bfloat16()
+        wp = pack_conv3x3(_rand((Cout, Cin, 3, 3), dev, 0.03, seed=99))
+        bias, add1 = _rand((Cout,), dev, seed=100), _rand((B, H, W, Cout), dev, seed=101)
+        add2 = _rand((B, H, W, Cout), dev, seed=102)
+        if case == "conv_residual_relu":
+            o1 = torch.empty((B, H, W, Cout), dtype=torch.float32, device=dev)
+            o2 = torch.full_like(o1, float("nan"))
+            r1 = torch.empty((B, H, W, 3 * Cout), dtype=torch.bfloat16, device=dev)
+            r2 = torch.full_like(r1, float("nan"))
+            for o, r, kw in ((o1, r1, {}), (o2, r2, dict(k_splits=6, splitk_ws=ws))):
+                ops.gemm(a, wp, o.view(-1, Cout), conv=(B, H, W, Cin), N=Cout, bias=bias, add1=add1.view(-1, Cout), add2=add2,
+                         out_relu=r, relu_split=True, **kw)
+            torch.cuda.synchronize()
+            assert _relerr(r2, r1) < 1e-2 and torch.isfinite(r2.float()).all()
+        else:
+            o1 = torch.empty((B, H, W, 3 * Cout), dtype=torch.bfloat16, device=dev)
+            o2 = torch.full_like(o1, float("nan"))
+            for o, kw in ((o1, {}), (o2, dict(k_splits=0, splitk_ws=ws))):           # automatic: 3 row tiles, K = 36 blocks
+                ops.gemm(a, wp, o.view(-1, 3 * Cout), conv=(B, H, W, Cin), N=Cout, bias=bias, act=ops.ACT_RELU,
+                         add1=add1.bfloat16().view(-1, Cout), out_split=True, **kw)
+    else:
+        B, gh, gw, s_, cin, cout = 2, 6, 5, 2, 512, 64
+        x = _rand((B * gh * gw, cin), dev, seed=103).bfloat16()
+        wt, bt = _rand((cin, cout, s_, s_), dev, 0.05, seed=104), _rand((cout,), dev, seed=105)
+        o1 = torch.empty((B, gh * s_, gw * s_, cout), dtype=torch.bfloat16, device=dev)
+        o2 = torch.full_like(o1, float("nan"))
+        for o, kw in ((o1, {}), (o2, dict(k_splits=4, splitk_ws=ws))):
+            ops.gemm(x, pack_conv_transpose(wt), o, bias=bt, bias_mod=cout, pixel_shuffle=(gh, gw, s_, cout), **kw)
+    torch.cuda.synchronize()
+    assert torch.isfinite(o2.float()).all()
+    assert _relerr(o2, o1) < (1e-2 if o1.dtype == torch.bfloat16 else 1e-5), _relerr(o2, o1)
+
+
 def _split3_ref(v):
     hi = v.bfloat16()
     lo = (v - hi.float()).bfloat16()
