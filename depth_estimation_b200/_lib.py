@@ -51,7 +51,7 @@ class DeProfileRecord(C.Structure):
     _fields_ = [("name", C.c_char * 24), ("ms", C.c_double), ("flops", C.c_double), ("dims", C.c_int64 * 4)]
 
 
-DE_PRECISION_DEFAULT, DE_PRECISION_BF16 = 0, 1
+DE_PRECISION_DEFAULT, DE_PRECISION_BF16, DE_PRECISION_BF16X3 = 0, 1, 2
 
 # name -> (restype, argtypes); must list every symbol include/depth_b200.h declares
 SIGNATURES = {
@@ -82,6 +82,11 @@ SIGNATURES = {
     "de_gemm": (C.c_int, [C.POINTER(DeGemm), C.c_void_p]),
     "de_layernorm": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                C.c_float, C.c_void_p, C.c_int64, C.c_void_p]),
+    "de_layernorm_split3": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_void_p,
+                                      C.c_int64, C.c_void_p]),
+    "de_attention_split3": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_void_p]),
+    "de_cast_tokens_split3": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
+    "de_patchify_split3": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "de_attention": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_void_p]),
     "de_cast_tokens": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "de_fill_cls": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),

@@ -87,6 +87,7 @@ struct WsBars {                    // one set per stream
 struct WsParams {
   __nv_bfloat16* out;
   int T, heads, qtiles, nblk, ntiles;
+  int out_split;    // 1: out rows are split3 operands [hi | hi | lo] (3*heads*64 wide)
   long long* dbg;   // DEB_ATTN_TRACE: per-block clock64 stamps of CTA 0 (debug only)
   float scale_log2e;
 };
@@ -402,7 +403,8 @@ attention_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const WsParams p)
       tc_fence_after();
       const float inv = 1.f / l_run;
       const int qrow_in_img = q_row - kv_row + r;
-      __nv_bfloat16* op = p.out + (static_cast<long long>(q_row) + r) * D + hcol;
+      // out_split: the row is written as the bf16x3 operand [hi | hi | lo] (each D wide) the proj GEMM consumes
+      __nv_bfloat16* op = p.out + (static_cast<long long>(q_row) + r) * (p.out_split ? 3 * D : D) + hcol;
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
         uint32_t ov[32];
@@ -411,12 +413,19 @@ attention_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const WsParams p)
         if (qrow_in_img < p.T) {
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
+            float f[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(ov[8 * i + j]) * inv;
             uint4 v;
-            v.x = pack_bf16(__uint_as_float(ov[8 * i]) * inv, __uint_as_float(ov[8 * i + 1]) * inv);
-            v.y = pack_bf16(__uint_as_float(ov[8 * i + 2]) * inv, __uint_as_float(ov[8 * i + 3]) * inv);
-            v.z = pack_bf16(__uint_as_float(ov[8 * i + 4]) * inv, __uint_as_float(ov[8 * i + 5]) * inv);
-            v.w = pack_bf16(__uint_as_float(ov[8 * i + 6]) * inv, __uint_as_float(ov[8 * i + 7]) * inv);
+            v.x = pack_bf16(f[0], f[1]); v.y = pack_bf16(f[2], f[3]); v.z = pack_bf16(f[4], f[5]); v.w = pack_bf16(f[6], f[7]);
             *reinterpret_cast<uint4*>(op + c * 32 + 8 * i) = v;
+            if (p.out_split) {
+              uint4 lo;
+              lo.x = pack_bf16(f[0] - bf16_lo(v.x), f[1] - bf16_hi(v.x)); lo.y = pack_bf16(f[2] - bf16_lo(v.y), f[3] - bf16_hi(v.y));
+              lo.z = pack_bf16(f[4] - bf16_lo(v.z), f[5] - bf16_hi(v.z)); lo.w = pack_bf16(f[6] - bf16_lo(v.w), f[7] - bf16_hi(v.w));
+              *reinterpret_cast<uint4*>(op + D + c * 32 + 8 * i) = v;
+              *reinterpret_cast<uint4*>(op + 2 * D + c * 32 + 8 * i) = lo;
+            }
           }
         }
       }
@@ -436,7 +445,14 @@ attention_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const WsParams p)
 
 }  // namespace deb
 
+static int attention_impl(const void* qkv, void* out, int B, int T, int heads, float scale, int out_split, void* stream);
 extern "C" int de_attention(const void* qkv, void* out, int B, int T, int heads, float scale, void* stream) {
+  return attention_impl(qkv, out, B, T, heads, scale, 0, stream);
+}
+extern "C" int de_attention_split3(const void* qkv, void* out_split3, int B, int T, int heads, float scale, void* stream) {
+  return attention_impl(qkv, out_split3, B, T, heads, scale, 1, stream);
+}
+static int attention_impl(const void* qkv, void* out, int B, int T, int heads, float scale, int out_split, void* stream) {
   deb::ProfScope prof_("attention", 4.0 * B * heads * (double)T * T * 64, stream, B, T, heads);
   using namespace deb;
   if (!qkv || !out || B <= 0 || T <= 0 || heads <= 0) return fail(DE_ERR_INVALID, "de_attention: bad args");
@@ -459,6 +475,7 @@ extern "C" int de_attention(const void* qkv, void* out, int B, int T, int heads,
   }
   WsParams p{};
   p.out = reinterpret_cast<__nv_bfloat16*>(out);
+  p.out_split = out_split;
   p.T = T;
   p.heads = heads;
   p.qtiles = (T + 127) / 128;

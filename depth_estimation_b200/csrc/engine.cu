@@ -58,6 +58,15 @@ BfVec pack_conv_transpose(const HostT& w) {
         for (int64_t j = 0; j < s; ++j) o[((i * s + j) * co + n) * ci + c] = f2bf(w.v[((c * co + n) * s + i) * s + j]);
   return o;
 }
+FVec conv_transpose_rows(const HostT& w) {
+  const int64_t ci = w.dim(0), co = w.dim(1), s = w.dim(2);
+  FVec o((size_t)(s * s * co * ci));
+  for (int64_t c = 0; c < ci; ++c)
+    for (int64_t n = 0; n < co; ++n)
+      for (int64_t i = 0; i < s; ++i)
+        for (int64_t j = 0; j < s; ++j) o[((i * s + j) * co + n) * ci + c] = w.v[((c * co + n) * s + i) * s + j];
+  return o;
+}
 BfVec split3_rows(const float* w, int64_t rows, int64_t cols) {
   BfVec o((size_t)(rows * 3 * cols));
   for (int64_t r = 0; r < rows; ++r)
@@ -163,10 +172,14 @@ const HostT& Engine::W(const std::string& key, std::initializer_list<int64_t> sh
 }
 float* Engine::f32(const std::string& key, std::initializer_list<int64_t> shape) { return wpool.put(W(key, shape).v); }
 
-void Engine::build_vit(const std::string& pre, int dim, int depth, int heads) {
+void Engine::build_vit(const std::string& pre, int dim, int depth, int heads, bool x3v) {
   vit.dim = dim;
   vit.depth = depth;
   vit.heads = heads;
+  vit.x3 = x3v;
+  auto lin = [&](const HostT& w, int64_t n, int64_t k) -> void* {
+    return x3v ? (void*)wpool.put(split3_rows(w.v.data(), n, k)) : (void*)wpool.put(pack_plain(w.v.data(), n * k));
+  };
   vit.cls = f32(pre + "cls_token", {1, 1, dim});
   vit.pos_raw = W(pre + "pos_embed", {1, 577, dim});
   const int64_t D = dim;
@@ -175,15 +188,15 @@ void Engine::build_vit(const std::string& pre, int dim, int depth, int heads) {
     VitBlockW b{};
     b.n1w = f32(p + "norm1.weight", {D});
     b.n1b = f32(p + "norm1.bias", {D});
-    b.qkv_w = wpool.put(pack_plain(W(p + "attn.qkv.weight", {3 * D, D}).v.data(), 3 * D * D));
+    b.qkv_w = lin(W(p + "attn.qkv.weight", {3 * D, D}), 3 * D, D);
     b.qkv_b = f32(p + "attn.qkv.bias", {3 * D});
-    b.proj_w = wpool.put(pack_plain(W(p + "attn.proj.weight", {D, D}).v.data(), D * D));
+    b.proj_w = lin(W(p + "attn.proj.weight", {D, D}), D, D);
     b.proj_b = f32(p + "attn.proj.bias", {D});
     b.n2w = f32(p + "norm2.weight", {D});
     b.n2b = f32(p + "norm2.bias", {D});
-    b.fc1_w = wpool.put(pack_plain(W(p + "mlp.fc1.weight", {4 * D, D}).v.data(), 4 * D * D));
+    b.fc1_w = lin(W(p + "mlp.fc1.weight", {4 * D, D}), 4 * D, D);
     b.fc1_b = f32(p + "mlp.fc1.bias", {4 * D});
-    b.fc2_w = wpool.put(pack_plain(W(p + "mlp.fc2.weight", {D, 4 * D}).v.data(), 4 * D * D));
+    b.fc2_w = lin(W(p + "mlp.fc2.weight", {D, 4 * D}), D, 4 * D);
     b.fc2_b = f32(p + "mlp.fc2.bias", {D});
     vit.blocks.push_back(b);
   }
@@ -221,7 +234,7 @@ float* Engine::pos_embed(int gh, int gw) {
   return d;
 }
 
-void Engine::build_reasm(int idx, int dim, int cout, int kind, int s) {
+void Engine::build_reasm(int idx, int dim, int cout, int kind, int s, bool x3r) {
   const std::string p = "pretrained.act_postprocess" + std::to_string(idx) + ".";
   const int64_t D = dim, c = cout;
   ReasmW r{};
@@ -229,15 +242,36 @@ void Engine::build_reasm(int idx, int dim, int cout, int kind, int s) {
   r.cout = cout;
   r.kind = kind;
   r.s = s;
-  r.w_read = wpool.put(pack_plain(W(p + "0.project.0.weight", {D, 2 * D}).v.data(), 2 * D * D));
+  r.x3 = x3r;
+  const HostT& wr = W(p + "0.project.0.weight", {D, 2 * D});                // [D, 2D] = [tokens | cls]
   r.b_read = f32(p + "0.project.0.bias", {D});
-  r.w1 = wpool.put(pack_plain(W(p + "3.weight", {c, D, 1, 1}).v.data(), c * D));
+  const HostT& w1 = W(p + "3.weight", {c, D, 1, 1});
   r.b1 = f32(p + "3.bias", {c});
+  if (!x3r) {
+    r.w_read = wpool.put(pack_plain(wr.v.data(), 2 * D * D));
+    r.w1 = wpool.put(pack_plain(w1.v.data(), c * D));
+  } else {
+    FVec wt((size_t)(D * D)), wc((size_t)(D * D));
+    for (int64_t n = 0; n < D; ++n) {
+      memcpy(&wt[n * D], &wr.v[n * 2 * D], sizeof(float) * D);
+      memcpy(&wc[n * D], &wr.v[n * 2 * D + D], sizeof(float) * D);
+    }
+    r.w_tok3 = wpool.put(split3_rows(wt.data(), D, D));
+    r.w_cls3 = wpool.put(split3_rows(wc.data(), D, D));
+    r.w1 = wpool.put(split3_rows(w1.v.data(), c, D));
+  }
   if (kind == 1) {
-    r.w4 = wpool.put(pack_conv_transpose(W(p + "4.weight", {c, c, s, s})));
+    const HostT& w4 = W(p + "4.weight", {c, c, s, s});
+    if (x3r) {
+      const FVec rows = conv_transpose_rows(w4);
+      r.w4 = wpool.put(split3_rows(rows.data(), (int64_t)s * s * c, c));
+    } else {
+      r.w4 = wpool.put(pack_conv_transpose(w4));
+    }
     r.b4 = f32(p + "4.bias", {c});
   } else if (kind == 2) {
-    r.w4 = wpool.put(pack_conv3x3_flat(W(p + "4.weight", {c, c, 3, 3})));
+    const HostT& w4 = W(p + "4.weight", {c, c, 3, 3});
+    r.w4 = x3r ? (void*)wpool.put(split3_conv3x3(w4.v.data(), c, c)) : (void*)wpool.put(pack_conv3x3_flat(w4));
     r.b4 = f32(p + "4.bias", {c});
   }
   reasm.push_back(r);
@@ -428,26 +462,30 @@ void Engine::finalize() {
   if (finalized) raise(DE_ERR_INVALID, "de_finalize_weights: already finalized");
   ENG_CUDA(cudaSetDevice(device));
   const int f256[4] = {256, 256, 256, 256};
+  x3 = precision == DE_PRECISION_BF16X3;
+  const bool all3[4] = {true, true, true, true};
   if (kind == kLarge) {
-    build_vit("pretrained.model.", 1024, 24, 16);
-    pe_w = wpool.put(pack_plain(W("pretrained.model.patch_embed.proj.weight", {1024, 3, 16, 16}).v.data(), 1024 * 768));
+    build_vit("pretrained.model.", 1024, 24, 16, x3);
+    const HostT& pw = W("pretrained.model.patch_embed.proj.weight", {1024, 3, 16, 16});
+    pe_w = x3 ? (void*)wpool.put(split3_rows(pw.v.data(), 1024, 768)) : (void*)wpool.put(pack_plain(pw.v.data(), 1024 * 768));
     pe_b = f32("pretrained.model.patch_embed.proj.bias", {1024});
-    build_reasm(1, 1024, 256, 1, 4);
-    build_reasm(2, 1024, 512, 1, 2);
-    build_reasm(3, 1024, 1024, 0, 0);
-    build_reasm(4, 1024, 1024, 2, 0);
+    build_reasm(1, 1024, 256, 1, 4, x3);
+    build_reasm(2, 1024, 512, 1, 2, x3);
+    build_reasm(3, 1024, 1024, 0, 0, x3);
+    build_reasm(4, 1024, 1024, 2, 0, x3);
     const int cin[4] = {256, 512, 1024, 1024};
-    build_decoder(cin, f256, 128, true, false, nullptr);
+    build_decoder(cin, f256, 128, true, x3, all3);
   } else if (kind == kHybrid) {
     build_hybrid();
-    build_vit("pretrained.model.", 768, 12, 12);
-    build_reasm(3, 768, 768, 0, 0);
-    build_reasm(4, 768, 768, 2, 0);
+    build_vit("pretrained.model.", 768, 12, 12, x3);
+    build_reasm(3, 768, 768, 0, 0, x3);
+    build_reasm(4, 768, 768, 2, 0, x3);
     const int cin[4] = {256, 512, 768, 768};
     const bool sp_in[4] = {true, true, false, false};
     hyb.decoder_split3 = precision != DE_PRECISION_BF16;
-    build_decoder(cin, f256, 128, true, hyb.decoder_split3, sp_in);
+    build_decoder(cin, f256, 128, true, hyb.decoder_split3, x3 ? all3 : sp_in);
   } else {
+    if (x3) raise(DE_ERR_UNSUPPORTED, "DE_PRECISION_BF16X3 is available for DPT_Large and DPT_Hybrid (MiDaS_small's 24 / 48 / 136-channel maps do not form 64-channel split3 operands)");
     build_small();
     const int cin[4] = {32, 48, 136, 384}, feat[4] = {64, 128, 256, 512};
     build_decoder(cin, feat, 32, false, false, nullptr);
@@ -611,7 +649,8 @@ Engine* as_engine(de_handle h) {
 extern "C" int de_create(const char* model_type, int device, int precision, de_handle* out) {
   return guarded([&] {
     if (!model_type || !out) raise(DE_ERR_INVALID, "de_create: null argument");
-    if (precision != DE_PRECISION_DEFAULT && precision != DE_PRECISION_BF16) raise(DE_ERR_INVALID, "de_create: precision %d", precision);
+    if (precision != DE_PRECISION_DEFAULT && precision != DE_PRECISION_BF16 && precision != DE_PRECISION_BF16X3)
+      raise(DE_ERR_INVALID, "de_create: precision %d", precision);
     int ndev = 0;
     ENG_CUDA(cudaGetDeviceCount(&ndev));
     if (device < 0 || device >= ndev) raise(DE_ERR_INVALID, "de_create: device %d of %d", device, ndev);
@@ -622,7 +661,8 @@ extern "C" int de_create(const char* model_type, int device, int precision, de_h
       e->kind = mt == "DPT_Large" ? kLarge : kHybrid;
       e->target = 384;
       e->method = 1;
-      e->layout = mt == "DPT_Large" ? 1 : 2;                   // ViT patch matrix | fp32 NCHW for the bf16x3 stem
+      // K1 output: ViT patch matrix | fp32 NCHW (the hybrid's bf16x3 stem; DPT_Large at bf16x3, re-tiled by de_patchify_split3)
+      e->layout = (mt == "DPT_Large" && precision != DE_PRECISION_BF16X3) ? 1 : 2;
       memcpy(e->mean, half, sizeof(half));
       memcpy(e->stdv, half, sizeof(half));
     } else if (mt == "MiDaS_small") {                         // small_transform (:15-16): 256, "upper_bound", ImageNet

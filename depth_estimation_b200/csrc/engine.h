@@ -67,6 +67,7 @@ BfVec pack_plain(const float* w, int64_t n);                               // bf
 BfVec pack_conv3x3(const HostT& w);                                        // [Cout,Cin,3,3] -> [Cout, 9*ceil64(Cin)] tap-major
 BfVec pack_conv3x3_flat(const HostT& w);                                   // -> [Cout, 9*Cin] (im2col + GEMM)
 BfVec pack_conv_transpose(const HostT& w);                                 // [Cin,Cout,s,s] -> [(i*s+j)*Cout+co, Cin]
+FVec conv_transpose_rows(const HostT& w);                                  // the same matrix in fp32
 BfVec split3_rows(const float* w, int64_t rows, int64_t cols);             // [rows, cols] -> [rows, 3*cols] = [Wh | Wl | Wh]
 BfVec split3_conv3x3(const float* w, int64_t cout, int64_t cin);           // [Cout,Cin,3,3] -> [Cout, 9*3*Cin] per tap [Wh | Wl | Wh]
 void fold_bn(FVec& w, int64_t cout, const FVec& g, const FVec& b, const FVec& mean, const FVec& var, float eps, FVec& bias_out);
@@ -98,6 +99,7 @@ struct VitBlockW {
 };
 struct VitW {
   int dim = 0, depth = 0, heads = 0;
+  bool x3 = false;                                             // bf16x3: weights [Wh | Wl | Wh] along K, activations split3
   float* cls = nullptr;
   HostT pos_raw;                                              // [1, 1+g*g, D]
   std::vector<VitBlockW> blocks;
@@ -105,7 +107,9 @@ struct VitW {
 };
 struct ReasmW {
   int dim = 0, cout = 0, kind = 0, s = 0;                      // kind 0 same, 1 up (ConvT k == s), 2 down2 (conv3x3 s2)
+  bool x3 = false;
   void *w_read = nullptr, *w1 = nullptr, *w4 = nullptr;        // w_read bf16 [D, 2D] = [tokens | cls]
+  void *w_tok3 = nullptr, *w_cls3 = nullptr;                   // bf16x3: the two halves packed separately, [D, 3D] each
   float *b_read = nullptr, *b1 = nullptr, *b4 = nullptr;
 };
 struct RefineW {
@@ -167,7 +171,8 @@ struct Engine {
   DecoderW dec;
   HybridW hyb;
   SmallW small;
-  void* pe_w = nullptr;                                        // DPT_Large patch-embed [D, 768]
+  bool x3 = false;                                             // DE_PRECISION_BF16X3
+  void* pe_w = nullptr;                                        // DPT_Large patch-embed [D, 768] (bf16x3: [D, 3*768])
   float* pe_b = nullptr;
   float mean[3], stdv[3];
   int target = 384, method = 1, layout = 0;                    // transform: get_size target / method, K1 output layout
@@ -179,8 +184,8 @@ struct Engine {
   const HostT& W(const std::string& key, std::initializer_list<int64_t> shape);
   float* f32(const std::string& key, std::initializer_list<int64_t> shape);
   void finalize();
-  void build_vit(const std::string& prefix, int dim, int depth, int heads);
-  void build_reasm(int idx, int dim, int cout, int kind, int s);
+  void build_vit(const std::string& prefix, int dim, int depth, int heads, bool x3);
+  void build_reasm(int idx, int dim, int cout, int kind, int s, bool x3);
   void build_decoder(const int* cin, const int* feat, int head_mid, bool head_ac, bool split3, const bool* split3_in);
   void build_hybrid();
   void build_small();

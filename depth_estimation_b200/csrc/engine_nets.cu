@@ -86,36 +86,43 @@ template <typename Hook>
 void vit_blocks(Ctx& c, float* x, int B, int T, Hook on_hook) {
   const VitW& v = c.e.vit;
   const int D = v.dim, M = B * T;
-  void* xn = c.buf("vit.xn", (size_t)M * D * 2);
+  const int kx = v.x3 ? 3 : 1;                  // bf16x3: GEMM operands are split3 rows [hi | hi | lo], K is 3x
+  void* xn = c.buf("vit.xn", (size_t)M * kx * D * 2);
   void* qkv = c.buf("vit.qkv", (size_t)M * 3 * D * 2);
-  void* att = c.buf("vit.att", (size_t)M * D * 2);
-  void* hid = c.buf("vit.hid", (size_t)M * 4 * D * 2);
+  void* att = c.buf("vit.att", (size_t)M * kx * D * 2);
+  void* hid = c.buf("vit.hid", (size_t)M * kx * 4 * D * 2);
   const float scale = 1.0f / sqrtf((float)(D / v.heads));
+  auto ln = [&](const float* g, const float* b) {
+    if (v.x3) ENG_CK(de_layernorm_split3(x, D, g, b, M, D, 1e-6f, xn, 3 * D, c.st));
+    else ENG_CK(de_layernorm(x, D, nullptr, 0, 0, g, b, M, D, 1e-6f, xn, D, c.st));
+  };
   for (int i = 0; i < v.depth; ++i) {
     const VitBlockW& w = v.blocks[i];
-    ENG_CK(de_layernorm(x, D, nullptr, 0, 0, w.n1w, w.n1b, M, D, 1e-6f, xn, D, c.st));
+    ln(w.n1w, w.n1b);
     {
-      Gemm g = dense(xn, D, M, D, w.qkv_w, D, 3 * D, qkv, DE_DTYPE_BF16, 3 * D);
+      Gemm g = dense(xn, kx * D, M, kx * D, w.qkv_w, kx * D, 3 * D, qkv, DE_DTYPE_BF16, 3 * D);
       g.bias = w.qkv_b;
       run(g, c);
     }
-    ENG_CK(de_attention(qkv, att, B, T, v.heads, scale, c.st));
+    if (v.x3) ENG_CK(de_attention_split3(qkv, att, B, T, v.heads, scale, c.st));
+    else ENG_CK(de_attention(qkv, att, B, T, v.heads, scale, c.st));
     {
       // the branch output is ADDED into the fp32 stream by the GEMM itself (TMA reduce-add epilogue)
-      Gemm g = dense(att, D, M, D, w.proj_w, D, D, x, DE_DTYPE_F32, D);
+      Gemm g = dense(att, kx * D, M, kx * D, w.proj_w, kx * D, D, x, DE_DTYPE_F32, D);
       g.bias = w.proj_b;
       g.accumulate = 1;
       run(g, c);
     }
-    ENG_CK(de_layernorm(x, D, nullptr, 0, 0, w.n2w, w.n2b, M, D, 1e-6f, xn, D, c.st));
+    ln(w.n2w, w.n2b);
     {
-      Gemm g = dense(xn, D, M, D, w.fc1_w, D, 4 * D, hid, DE_DTYPE_BF16, 4 * D);
+      Gemm g = dense(xn, kx * D, M, kx * D, w.fc1_w, kx * D, 4 * D, hid, DE_DTYPE_BF16, kx * 4 * D);
       g.bias = w.fc1_b;
       g.act = DE_ACT_GELU;
+      g.out_split = v.x3 ? 1 : 0;
       run(g, c);
     }
     {
-      Gemm g = dense(hid, 4 * D, M, 4 * D, w.fc2_w, 4 * D, D, x, DE_DTYPE_F32, D);
+      Gemm g = dense(hid, kx * 4 * D, M, kx * 4 * D, w.fc2_w, kx * 4 * D, D, x, DE_DTYPE_F32, D);
       g.bias = w.fc2_b;
       g.accumulate = 1;
       run(g, c);
@@ -127,19 +134,27 @@ void vit_blocks(Ctx& c, float* x, int B, int T, Hook on_hook) {
 // [UPSTREAM] act_postprocessN: ProjectReadout -> 1x1 conv -> {ConvT k4s4, ConvT k2s2, id, conv3x3 s2}
 Feat reassemble(Ctx& c, const ReasmW& r, int idx, const float* x, int B, int gh, int gw) {
   const int D = r.dim, N = gh * gw, T = N + 1, co = r.cout;
-  void* tok = c.buf("ra%d.tok", (size_t)B * N * D * 2, idx);
-  ENG_CK(de_cast_tokens(x, D, B * T, D, T, 1, tok, c.st));
-  void* cls = c.buf("ra%d.cls", (size_t)B * D * 2, idx);
-  ENG_CK(de_cast_tokens(x, (int64_t)T * D, B, D, 0, 0, cls, c.st));            // row stride T*D: the cls rows
+  const int kx = r.x3 ? 3 : 1;                  // bf16x3: every operand row is [hi | hi | lo], every output a split3 row
+  void* tok = c.buf("ra%d.tok", (size_t)B * N * kx * D * 2, idx);
+  void* cls = c.buf("ra%d.cls", (size_t)B * kx * D * 2, idx);
+  if (r.x3) {
+    ENG_CK(de_cast_tokens_split3(x, D, B * T, D, T, 1, tok, c.st));
+    ENG_CK(de_cast_tokens_split3(x, (int64_t)T * D, B, D, 0, 0, cls, c.st));
+  } else {
+    ENG_CK(de_cast_tokens(x, D, B * T, D, T, 1, tok, c.st));
+    ENG_CK(de_cast_tokens(x, (int64_t)T * D, B, D, 0, 0, cls, c.st));          // row stride T*D: the cls rows
+  }
   float* cproj = c.buf<float>("ra%d.cproj", (size_t)B * D * 4, idx);
   {
-    Gemm g = dense(cls, D, B, D, reinterpret_cast<const uint16_t*>(r.w_read) + D, 2 * D, D, cproj, DE_DTYPE_F32, D);
+    Gemm g = r.x3 ? dense(cls, 3 * D, B, 3 * D, r.w_cls3, 3 * D, D, cproj, DE_DTYPE_F32, D)
+                  : dense(cls, D, B, D, reinterpret_cast<const uint16_t*>(r.w_read) + D, 2 * D, D, cproj, DE_DTYPE_F32, D);
     g.bias = r.b_read;
     run(g, c);
   }
-  void* rr = c.buf("ra%d.r", (size_t)B * N * D * 2, idx);
+  void* rr = c.buf("ra%d.r", (size_t)B * N * kx * D * 2, idx);
   {
-    Gemm g = dense(tok, D, B * N, D, r.w_read, 2 * D, D, rr, DE_DTYPE_BF16, D);
+    Gemm g = r.x3 ? dense(tok, 3 * D, B * N, 3 * D, r.w_tok3, 3 * D, D, rr, DE_DTYPE_BF16, 3 * D)
+                  : dense(tok, D, B * N, D, r.w_read, 2 * D, D, rr, DE_DTYPE_BF16, D);
     g.act = DE_ACT_GELU;
     g.add1 = cproj;
     g.add1_dtype = DE_DTYPE_F32;
@@ -147,16 +162,18 @@ Feat reassemble(Ctx& c, const ReasmW& r, int idx, const float* x, int B, int gh,
     g.add1_rowmode = 1;
     g.add1_pre = 1;
     g.grp = N;
+    g.out_split = r.x3 ? 1 : 0;
     run(g, c);
   }
-  void* pp = c.buf("ra%d.p", (size_t)B * N * co * 2, idx);
+  void* pp = c.buf("ra%d.p", (size_t)B * N * kx * co * 2, idx);
   {
-    Gemm g = dense(rr, D, B * N, D, r.w1, D, co, pp, DE_DTYPE_BF16, co);
+    Gemm g = dense(rr, kx * D, B * N, kx * D, r.w1, kx * D, co, pp, DE_DTYPE_BF16, kx * co);
     g.bias = r.b1;
+    g.out_split = r.x3 ? 1 : 0;
     run(g, c);
   }
   Feat f;
-  f.C = co;
+  f.C = kx * co;
   if (r.kind == 0) {
     f.p = pp;
     f.H = gh;
@@ -165,8 +182,8 @@ Feat reassemble(Ctx& c, const ReasmW& r, int idx, const float* x, int B, int gh,
   }
   if (r.kind == 1) {
     const int s = r.s;
-    void* out = c.buf("ra%d.o", (size_t)B * N * s * s * co * 2, idx);
-    Gemm g = dense(pp, co, B * N, co, r.w4, co, s * s * co, out, DE_DTYPE_BF16, co);
+    void* out = c.buf("ra%d.o", (size_t)B * N * s * s * kx * co * 2, idx);
+    Gemm g = dense(pp, kx * co, B * N, kx * co, r.w4, kx * co, s * s * co, out, DE_DTYPE_BF16, kx * co);
     g.bias = r.b4;
     g.bias_mod = co;
     g.out_rowmode = 2;
@@ -174,6 +191,7 @@ Feat reassemble(Ctx& c, const ReasmW& r, int idx, const float* x, int B, int gh,
     g.ps_gw = gw;
     g.ps_s = s;
     g.ps_cout = co;
+    g.out_split = r.x3 ? 1 : 0;
     run(g, c);
     f.p = out;
     f.H = gh * s;
@@ -181,12 +199,13 @@ Feat reassemble(Ctx& c, const ReasmW& r, int idx, const float* x, int B, int gh,
     return f;
   }
   const int ho = (gh - 1) / 2 + 1, wo = (gw - 1) / 2 + 1;
-  void* col = c.buf("ra%d.col", (size_t)B * ho * wo * 9 * co * 2, idx);
-  ENG_CK(de_im2col3x3(pp, col, B, gh, gw, co, 2, 1, 1, ho, wo, c.st));
-  void* out = c.buf("ra%d.o", (size_t)B * ho * wo * co * 2, idx);
+  void* col = c.buf("ra%d.col", (size_t)B * ho * wo * 9 * kx * co * 2, idx);
+  ENG_CK(de_im2col3x3(pp, col, B, gh, gw, kx * co, 2, 1, 1, ho, wo, c.st));
+  void* out = c.buf("ra%d.o", (size_t)B * ho * wo * kx * co * 2, idx);
   {
-    Gemm g = dense(col, 9 * co, B * ho * wo, 9 * co, r.w4, 9 * co, co, out, DE_DTYPE_BF16, co);
+    Gemm g = dense(col, 9 * kx * co, B * ho * wo, 9 * kx * co, r.w4, 9 * kx * co, co, out, DE_DTYPE_BF16, kx * co);
     g.bias = r.b4;
+    g.out_split = r.x3 ? 1 : 0;
     run(g, c);
   }
   f.p = out;
@@ -408,7 +427,15 @@ void forward_large(Engine& e, Plan& p, cudaStream_t st) {
   float* x = c.buf<float>("x", (size_t)B * T * D * 4);
   float* pos = e.pos_embed(gh, gw);
   {
-    Gemm g = dense(p.x_in, 768, B * N, 768, e.pe_w, 768, D, x, DE_DTYPE_F32, D);
+    const void* patches = p.x_in;
+    int kp = 768;
+    if (e.x3) {                                   // K1 wrote fp32 NCHW: re-tile it into the split3 patch matrix
+      void* p3 = c.buf("patch3", (size_t)B * N * 3 * 768 * 2);
+      ENG_CK(de_patchify_split3(reinterpret_cast<const float*>(p.x_in), p3, B, p.net_h, p.net_w, st));
+      patches = p3;
+      kp = 3 * 768;
+    }
+    Gemm g = dense(patches, kp, B * N, kp, e.pe_w, kp, D, x, DE_DTYPE_F32, D);
     g.bias = e.pe_b;
     g.add1 = pos;
     g.add1_dtype = DE_DTYPE_F32;

@@ -17,7 +17,7 @@ template <int VEC>  // VEC float4 per lane: dim = 128*VEC
 __global__ void __launch_bounds__(256) layernorm_kernel(float* __restrict__ x, long long ldx, const void* __restrict__ y,
                                                         int y_bf16, long long ldy, const float* __restrict__ gamma,
                                                         const float* __restrict__ beta, int rows, float eps,
-                                                        __nv_bfloat16* __restrict__ out, long long ldo) {
+                                                        __nv_bfloat16* __restrict__ out, long long ldo, int split) {
   const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   pdl_launch();
@@ -65,16 +65,25 @@ __global__ void __launch_bounds__(256) layernorm_kernel(float* __restrict__ x, l
   for (int i = 0; i < VEC; ++i) {
     const float4 g = __ldg(reinterpret_cast<const float4*>(gamma) + lane + i * 32);
     const float4 bb = __ldg(reinterpret_cast<const float4*>(beta) + lane + i * 32);
+    const float y0 = (v[i].x - mean) * rstd * g.x + bb.x, y1 = (v[i].y - mean) * rstd * g.y + bb.y;
+    const float y2 = (v[i].z - mean) * rstd * g.z + bb.z, y3 = (v[i].w - mean) * rstd * g.w + bb.w;
     uint2 o;
-    o.x = pack_bf16((v[i].x - mean) * rstd * g.x + bb.x, (v[i].y - mean) * rstd * g.y + bb.y);
-    o.y = pack_bf16((v[i].z - mean) * rstd * g.z + bb.z, (v[i].w - mean) * rstd * g.w + bb.w);
+    o.x = pack_bf16(y0, y1);
+    o.y = pack_bf16(y2, y3);
     orow[lane + i * 32] = o;
+    if (split) {                                   // [hi | hi | lo], each 128*VEC wide (bf16x3 operand)
+      orow[32 * VEC + lane + i * 32] = o;
+      uint2 lo;
+      lo.x = pack_bf16(y0 - bf16_lo(o.x), y1 - bf16_hi(o.x));
+      lo.y = pack_bf16(y2 - bf16_lo(o.y), y3 - bf16_hi(o.y));
+      orow[64 * VEC + lane + i * 32] = lo;
+    }
   }
 }
 
 // ---------------------------------------------------------------- fp32 -> bf16 token cast (drop cls)
 __global__ void cast_tokens_kernel(const float* __restrict__ x, long long ldx, long long out_rows, int dim, int grp,
-                                   int skip, __nv_bfloat16* __restrict__ out) {
+                                   int skip, __nv_bfloat16* __restrict__ out, int split) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;  // one 8-element group per thread
   const int per_row = dim >> 3;
   if (i >= out_rows * per_row) return;
@@ -86,7 +95,41 @@ __global__ void cast_tokens_kernel(const float* __restrict__ x, long long ldx, l
   const float4 b = *reinterpret_cast<const float4*>(x + irow * ldx + c + 4);
   uint4 o;
   o.x = pack_bf16(a.x, a.y); o.y = pack_bf16(a.z, a.w); o.z = pack_bf16(b.x, b.y); o.w = pack_bf16(b.z, b.w);
-  *reinterpret_cast<uint4*>(out + orow * dim + c) = o;
+  if (!split) {
+    *reinterpret_cast<uint4*>(out + orow * dim + c) = o;
+    return;
+  }
+  uint4 lo;
+  lo.x = pack_bf16(a.x - bf16_lo(o.x), a.y - bf16_hi(o.x)); lo.y = pack_bf16(a.z - bf16_lo(o.y), a.w - bf16_hi(o.y));
+  lo.z = pack_bf16(b.x - bf16_lo(o.z), b.y - bf16_hi(o.z)); lo.w = pack_bf16(b.z - bf16_lo(o.w), b.w - bf16_hi(o.w));
+  __nv_bfloat16* op = out + orow * 3 * dim + c;
+  *reinterpret_cast<uint4*>(op) = o;
+  *reinterpret_cast<uint4*>(op + dim) = o;
+  *reinterpret_cast<uint4*>(op + 2 * dim) = lo;
+}
+
+// fp32 NCHW network input [B,3,h,w] (K1 layout 2) -> split3 ViT patch matrix [B*(h/16)*(w/16), 3*768] = [hi | hi | lo],
+// column = c*256 + py*16 + px - the bf16x3 form of K1's layout 1.  One thread per (patch, channel, patch row): 16 pixels.
+__global__ void patchify_split3_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, int B, int h, int w) {
+  const int gw = w >> 4, gh = h >> 4;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long long)B * gh * gw * 48) return;
+  const int py = static_cast<int>(i % 16), c = static_cast<int>((i / 16) % 3);
+  const long long patch = i / 48;
+  const int gx = static_cast<int>(patch % gw), gy = static_cast<int>((patch / gw) % gh), b = static_cast<int>(patch / ((long long)gw * gh));
+  const float* src = x + (((long long)b * 3 + c) * h + gy * 16 + py) * w + gx * 16;
+  __nv_bfloat16* dst = out + patch * (3 * 768) + c * 256 + py * 16;
+#pragma unroll
+  for (int v = 0; v < 2; ++v) {
+    const float4 a = *reinterpret_cast<const float4*>(src + 8 * v), bq = *reinterpret_cast<const float4*>(src + 8 * v + 4);
+    uint4 o, lo;
+    o.x = pack_bf16(a.x, a.y); o.y = pack_bf16(a.z, a.w); o.z = pack_bf16(bq.x, bq.y); o.w = pack_bf16(bq.z, bq.w);
+    lo.x = pack_bf16(a.x - bf16_lo(o.x), a.y - bf16_hi(o.x)); lo.y = pack_bf16(a.z - bf16_lo(o.y), a.w - bf16_hi(o.y));
+    lo.z = pack_bf16(bq.x - bf16_lo(o.z), bq.y - bf16_hi(o.z)); lo.w = pack_bf16(bq.z - bf16_lo(o.w), bq.w - bf16_hi(o.w));
+    *reinterpret_cast<uint4*>(dst + 8 * v) = o;
+    *reinterpret_cast<uint4*>(dst + 768 + 8 * v) = o;
+    *reinterpret_cast<uint4*>(dst + 1536 + 8 * v) = lo;
+  }
 }
 
 __global__ void fill_cls_kernel(float* __restrict__ x, long long ldx, int B, int T, int dim,
@@ -606,9 +649,10 @@ __global__ void __launch_bounds__(256) groupnorm_fused_kernel(const void* __rest
 
 using namespace deb;
 
-extern "C" int de_layernorm(float* x, int64_t ldx, const void* y, int y_dtype, int64_t ldy, const float* gamma,
-                            const float* beta, int rows, int dim, float eps, void* out_bf16, int64_t ldo, void* stream) {
+static int layernorm_impl(float* x, int64_t ldx, const void* y, int y_dtype, int64_t ldy, const float* gamma,
+                          const float* beta, int rows, int dim, float eps, void* out_bf16, int64_t ldo, int split, void* stream) {
   deb::ProfScope prof_("layernorm", 0.0, stream, rows, dim);
+  if (split && (!out_bf16 || ldo < 3LL * dim)) return fail(DE_ERR_INVALID, "de_layernorm_split3: needs an output with ldo >= 3*dim");
   if (!x || rows <= 0 || (out_bf16 && (!gamma || !beta)) || (!out_bf16 && !y))
     return fail(DE_ERR_INVALID, "de_layernorm: bad args");
   if (dim % 128 != 0 || dim > 1024 || ldx % 4 != 0 || ldo % 4 != 0 || (y && ldy % 4 != 0))
@@ -617,7 +661,7 @@ extern "C" int de_layernorm(float* x, int64_t ldx, const void* y, int y_dtype, i
   __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out_bf16);
   const int grid = (rows + 7) / 8;
   switch (dim / 128) {
-#define LN_CASE(V) case V: launch_pdl(4, layernorm_kernel<V>, dim3(grid), dim3(256), 0, st, x, (long long)ldx, y, y_dtype == DE_DTYPE_BF16 ? 1 : 0, (long long)ldy, gamma, beta, rows, eps, o, (long long)ldo); break;
+#define LN_CASE(V) case V: launch_pdl(4, layernorm_kernel<V>, dim3(grid), dim3(256), 0, st, x, (long long)ldx, y, y_dtype == DE_DTYPE_BF16 ? 1 : 0, (long long)ldy, gamma, beta, rows, eps, o, (long long)ldo, split); break;
     LN_CASE(1) LN_CASE(2) LN_CASE(3) LN_CASE(4) LN_CASE(5) LN_CASE(6) LN_CASE(7) LN_CASE(8)
 #undef LN_CASE
   }
@@ -625,8 +669,17 @@ extern "C" int de_layernorm(float* x, int64_t ldx, const void* y, int y_dtype, i
   return cuda_check_launch("layernorm_kernel");
 }
 
-extern "C" int de_cast_tokens(const float* x, int64_t ldx, int rows, int dim, int grp, int skip, void* out_bf16,
-                              void* stream) {
+extern "C" int de_layernorm(float* x, int64_t ldx, const void* y, int y_dtype, int64_t ldy, const float* gamma,
+                            const float* beta, int rows, int dim, float eps, void* out_bf16, int64_t ldo, void* stream) {
+  return layernorm_impl(x, ldx, y, y_dtype, ldy, gamma, beta, rows, dim, eps, out_bf16, ldo, 0, stream);
+}
+extern "C" int de_layernorm_split3(float* x, int64_t ldx, const float* gamma, const float* beta, int rows, int dim, float eps,
+                                   void* out_split3, int64_t ldo, void* stream) {
+  return layernorm_impl(x, ldx, nullptr, 0, 0, gamma, beta, rows, dim, eps, out_split3, ldo, 1, stream);
+}
+
+static int cast_tokens_impl(const float* x, int64_t ldx, int rows, int dim, int grp, int skip, void* out_bf16, int split,
+                            void* stream) {
   deb::ProfScope prof_("cast_tokens", 0.0, stream, rows, dim);
   if (!x || !out_bf16 || rows <= 0 || dim % 8 != 0) return fail(DE_ERR_INVALID, "de_cast_tokens: bad args");
   long long out_rows = rows;
@@ -636,9 +689,27 @@ extern "C" int de_cast_tokens(const float* x, int64_t ldx, int rows, int dim, in
   }
   const long long n = out_rows * (dim / 8);
   cast_tokens_kernel<<<(unsigned)((n + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      x, ldx, out_rows, dim, grp, skip, reinterpret_cast<__nv_bfloat16*>(out_bf16));
+      x, ldx, out_rows, dim, grp, skip, reinterpret_cast<__nv_bfloat16*>(out_bf16), split);
   count_launch();
   return cuda_check_launch("cast_tokens_kernel");
+}
+extern "C" int de_cast_tokens(const float* x, int64_t ldx, int rows, int dim, int grp, int skip, void* out_bf16,
+                              void* stream) {
+  return cast_tokens_impl(x, ldx, rows, dim, grp, skip, out_bf16, 0, stream);
+}
+extern "C" int de_cast_tokens_split3(const float* x, int64_t ldx, int rows, int dim, int grp, int skip, void* out_split3,
+                                     void* stream) {
+  return cast_tokens_impl(x, ldx, rows, dim, grp, skip, out_split3, 1, stream);
+}
+extern "C" int de_patchify_split3(const float* x_nchw, void* out_split3, int B, int h, int w, void* stream) {
+  deb::ProfScope prof_("patchify_split3", 0.0, stream, B, h, w);
+  if (!x_nchw || !out_split3 || B < 1 || h % 16 != 0 || w % 16 != 0 || h < 16 || w < 16)
+    return fail(DE_ERR_INVALID, "de_patchify_split3: bad args (h, w multiples of 16)");
+  const long long n = (long long)B * (h / 16) * (w / 16) * 48;
+  patchify_split3_kernel<<<(unsigned)((n + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      x_nchw, reinterpret_cast<__nv_bfloat16*>(out_split3), B, h, w);
+  count_launch();
+  return cuda_check_launch("patchify_split3_kernel");
 }
 
 extern "C" int de_fill_cls(float* x, int64_t ldx, int B, int T, int dim, const float* cls, const float* pos,

@@ -49,9 +49,11 @@ class DepthEstimator(object):
         weights: upstream-format state_dict, a path to one (torch.load), or None for seeded random init.
         precision: None = the model's default arithmetic (bf16 operands / fp32 accumulate; DPT_Hybrid: ResNetV2 stages
         and decoder as bf16x3); "bf16" = plain bf16 operands wherever the model tolerates them (DPT_Hybrid: decoder in
-        bf16 - faster, 1.3e-3 from the fp32 reference instead of < 1e-3)."""
-        if precision not in (None, "bf16"):
-            raise ValueError(f"precision {precision!r}: expected None or 'bf16'")
+        bf16 - faster, 1.3e-3 from the fp32 reference instead of < 1e-3); "bf16x3" (DPT_Large / DPT_Hybrid) = every
+        Linear / convolution on hi+lo bf16 operand pairs (~16 mantissa bits, 3x the tensor work) for maps whose dynamic
+        range is wide against their maximum, where bf16 operands alone cost more than north_star's 1e-3."""
+        if precision not in (None, "bf16", "bf16x3"):
+            raise ValueError(f"precision {precision!r}: expected None, 'bf16' or 'bf16x3'")
         self.precision = precision
         self.model_type = model_type
         print(f'Loading model: {self.model_type}')

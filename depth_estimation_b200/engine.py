@@ -8,7 +8,7 @@ import ctypes as C
 import torch
 
 from . import _lib
-from ._lib import DE_DTYPE_BF16, DE_DTYPE_F32, DE_PRECISION_BF16, DE_PRECISION_DEFAULT, DePredictIO
+from ._lib import DE_DTYPE_BF16, DE_DTYPE_F32, DE_PRECISION_BF16, DE_PRECISION_BF16X3, DE_PRECISION_DEFAULT, DePredictIO
 
 
 class Engine:
@@ -19,7 +19,7 @@ class Engine:
         self.model_type = model_type
         self.device = device
         self._h = C.c_void_p()
-        prec = DE_PRECISION_BF16 if precision == "bf16" else DE_PRECISION_DEFAULT
+        prec = {None: DE_PRECISION_DEFAULT, "bf16": DE_PRECISION_BF16, "bf16x3": DE_PRECISION_BF16X3}[precision]
         idx = device.index if device.index is not None else torch.cuda.current_device()
         _lib.check(lib.de_create(model_type.encode(), int(idx), prec, C.byref(self._h)), "de_create")
         try:

@@ -214,9 +214,41 @@ def layernorm(x: torch.Tensor, gamma, beta, eps: float, out, y: torch.Tensor | N
     return out
 
 
-def attention(qkv: torch.Tensor, out: torch.Tensor, B: int, T: int, heads: int, scale: float):
+def layernorm_split3(x: torch.Tensor, gamma, beta, eps: float, out3: torch.Tensor):
+    """out3 bf16 [rows, 3*dim] = [hi | hi | lo] of LN(x)."""
+    _need_cuda(x, gamma, beta, out3)
+    assert x.dtype == torch.float32 and x.dim() == 2 and out3.dtype == torch.bfloat16 and out3.shape[1] == 3 * x.shape[1]
+    _lib.check(_lib.load().de_layernorm_split3(x.data_ptr(), x.stride(0), gamma.data_ptr(), beta.data_ptr(), x.shape[0],
+                                               x.shape[1], float(eps), out3.data_ptr(), out3.stride(0), _stream()),
+               "de_layernorm_split3")
+    return out3
+
+
+def cast_tokens_split3(x: torch.Tensor, out3: torch.Tensor, grp: int = 0, skip: int = 0):
+    _need_cuda(x, out3)
+    assert x.dtype == torch.float32 and out3.dtype == torch.bfloat16 and x.dim() == 2 and out3.is_contiguous()
+    _lib.check(_lib.load().de_cast_tokens_split3(x.data_ptr(), x.stride(0), x.shape[0], x.shape[1], grp, skip,
+                                                 out3.data_ptr(), _stream()), "de_cast_tokens_split3")
+    return out3
+
+
+def patchify_split3(x_nchw: torch.Tensor, out3: torch.Tensor):
+    _need_cuda(x_nchw, out3)
+    B, _, h, w = x_nchw.shape
+    assert x_nchw.dtype == torch.float32 and x_nchw.is_contiguous() and out3.dtype == torch.bfloat16 and out3.is_contiguous()
+    assert tuple(out3.shape) == (B * (h // 16) * (w // 16), 3 * 768)
+    _lib.check(_lib.load().de_patchify_split3(x_nchw.data_ptr(), out3.data_ptr(), B, h, w, _stream()), "de_patchify_split3")
+    return out3
+
+
+def attention(qkv: torch.Tensor, out: torch.Tensor, B: int, T: int, heads: int, scale: float, split: bool = False):
     _need_cuda(qkv, out)
     assert qkv.dtype == torch.bfloat16 and out.dtype == torch.bfloat16 and qkv.is_contiguous() and out.is_contiguous()
+    if split:
+        assert out.shape[-1] == 3 * heads * 64
+        _lib.check(_lib.load().de_attention_split3(qkv.data_ptr(), out.data_ptr(), B, T, heads, float(scale), _stream()),
+                   "de_attention_split3")
+        return out
     _lib.check(_lib.load().de_attention(qkv.data_ptr(), out.data_ptr(), B, T, heads, float(scale), _stream()), "de_attention")
     return out
 

@@ -167,17 +167,31 @@ int de_gemm(const DeGemm* g, void* stream);
 int de_layernorm(float* x, int64_t ldx, const void* y, int y_dtype, int64_t ldy, const float* gamma, const float* beta,
                  int rows, int dim, float eps, void* out_bf16, int64_t ldo, void* stream);
 
+/* LayerNorm whose output row is the bf16x3 ("split3") operand [hi | hi | lo] (each `dim` wide, ldo >= 3*dim) - see
+ * DeGemm.out_split; used by precision DE_PRECISION_BF16X3. */
+int de_layernorm_split3(float* x, int64_t ldx, const float* gamma, const float* beta, int rows, int dim, float eps,
+                        void* out_split3, int64_t ldo, void* stream);
+
 /* ---- multi-head self-attention on a packed qkv buffer (timm Attention.forward):
  * qkv: bf16 [B*T, 3*heads*64] (q | k | v, each heads x 64), out: bf16 [B*T, heads*64].
  * softmax(q k^T * scale) v, non-causal, fp32 softmax. head_dim must be 64.
  * tcgen05/TMEM flash kernel: S and O tiles in tensor memory, Q/K/V by TMA, V consumed MN-major. */
 int de_attention(const void* qkv, void* out, int B, int T, int heads, float scale, void* stream);
 
+/* The same attention with the output row written as a split3 operand: out bf16 [B*T, 3*heads*64] = [hi | hi | lo] of the
+ * fp32 result (the qkv input and the probabilities stay bf16). */
+int de_attention_split3(const void* qkv, void* out_split3, int B, int T, int heads, float scale, void* stream);
+
 /* ---- small bandwidth kernels used between the GEMMs ---- */
 /* fp32 [rows, dim] (ldx) -> bf16 [rows', dim]: drops the first `skip` rows of every group of `grp`
  * rows (cls token removal for the reassemble readout).  grp=0: plain cast. */
 int de_cast_tokens(const float* x, int64_t ldx, int rows, int dim, int grp, int skip, void* out_bf16,
                    void* stream);
+/* de_cast_tokens with split3 output rows: bf16 [rows', 3*dim] = [hi | hi | lo]. */
+int de_cast_tokens_split3(const float* x, int64_t ldx, int rows, int dim, int grp, int skip, void* out_split3, void* stream);
+/* fp32 NCHW network input [B,3,h,w] (de_preprocess layout 2) -> split3 ViT patch matrix bf16 [B*(h/16)*(w/16), 3*768],
+ * column = c*256+py*16+px inside each part: the bf16x3 form of de_preprocess layout 1. */
+int de_patchify_split3(const float* x_nchw, void* out_split3, int B, int h, int w, void* stream);
 /* x[b*T + 0, :] = cls[:] + pos[0, :] (fp32 token stream) */
 int de_fill_cls(float* x, int64_t ldx, int B, int T, int dim, const float* cls, const float* pos,
                 void* stream);
@@ -253,6 +267,9 @@ typedef struct de_engine* de_handle;
 
 #define DE_PRECISION_DEFAULT 0 /* bf16 operands / fp32 accumulate; DPT_Hybrid: ResNetV2 stages + decoder as bf16x3 */
 #define DE_PRECISION_BF16 1    /* DPT_Hybrid: decoder on plain bf16 operands (faster; 1.3e-3 instead of < 1e-3) */
+#define DE_PRECISION_BF16X3 2  /* DPT_Large / DPT_Hybrid: every Linear / convolution as bf16x3 (split3 operands, ~16 mantissa
+                                * bits, 3x the tensor work); attention's QK^T / PV stay bf16.  For maps whose dynamic range
+                                * is wide against their maximum, where bf16 operands alone cost > 1e-3 */
 
 /* model_type: "DPT_Large" | "DPT_Hybrid" | "MiDaS_small" (the strings of depth_midas.py:91-93). */
 int de_create(const char* model_type, int device, int precision, de_handle* out);

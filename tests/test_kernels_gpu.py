@@ -892,6 +892,51 @@ def test_gemm_split3_outputs(pixel_shuffle):
         assert _relerr(hi + lo, ref) < 3e-5
 
 
+def test_split3_vit_operators():
+    """LayerNorm / token cast / attention / patchify with split3 output rows: hi == the plain bf16 result, hi + lo carries
+    the fp32 value to ~2^-16."""
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    M, D = 300, 768
+    x = _rand((M, D), dev, 2.0, seed=110)
+    g, b = _rand((D,), dev, seed=111), _rand((D,), dev, seed=112)
+    plain = torch.empty((M, D), dtype=torch.bfloat16, device=dev)
+    ops.layernorm(x, g, b, 1e-6, plain)
+    o3 = torch.full((M, 3 * D), float("nan"), dtype=torch.bfloat16, device=dev)
+    ops.layernorm_split3(x, g, b, 1e-6, o3)
+    ref = F.layer_norm(x, (D,), g, b, 1e-6)
+    torch.cuda.synchronize()
+    assert torch.equal(o3[:, :D], plain) and torch.equal(o3[:, D:2 * D], plain)
+    assert _relerr(o3[:, :D].float() + o3[:, 2 * D:].float(), ref) < 2e-5
+    # token cast (drop the first row of every group of 10)
+    c3 = torch.full((270, 3 * D), float("nan"), dtype=torch.bfloat16, device=dev)
+    ops.cast_tokens_split3(x, c3, grp=10, skip=1)
+    want = x.view(30, 10, D)[:, 1:].reshape(270, D)
+    torch.cuda.synchronize()
+    assert torch.equal(c3, _split3_ref(want))
+    # attention
+    B, T, heads = 2, 197, 4
+    Dh = heads * 64
+    qkv = _rand((B * T, 3 * Dh), dev, 1.0, seed=113).bfloat16()
+    a1 = torch.empty((B * T, Dh), dtype=torch.bfloat16, device=dev)
+    a3 = torch.full((B * T, 3 * Dh), float("nan"), dtype=torch.bfloat16, device=dev)
+    ops.attention(qkv, a1, B, T, heads, 0.125)
+    ops.attention(qkv, a3, B, T, heads, 0.125, split=True)
+    q, k, v = qkv.float().view(B, T, 3, heads, 64).permute(2, 0, 3, 1, 4)
+    aref = F.scaled_dot_product_attention(q, k, v).transpose(1, 2).reshape(B * T, Dh)
+    torch.cuda.synchronize()
+    assert torch.equal(a3[:, :Dh], a1) and torch.equal(a3[:, Dh:2 * Dh], a1)
+    e1, e3 = _relerr(a1, aref), _relerr(a3[:, :Dh].float() + a3[:, 2 * Dh:].float(), aref)
+    assert torch.isfinite(a3.float()).all() and e3 <= e1 + 1e-6
+    # patchify: fp32 NCHW -> split3 patch matrix (column = c*256 + py*16 + px)
+    img = _rand((2, 3, 32, 48), dev, seed=114)
+    p3 = torch.full((2 * 2 * 3, 3 * 768), float("nan"), dtype=torch.bfloat16, device=dev)
+    ops.patchify_split3(img, p3)
+    want = img.view(2, 3, 2, 16, 3, 16).permute(0, 2, 4, 1, 3, 5).reshape(12, 768)
+    torch.cuda.synchronize()
+    assert torch.equal(p3, _split3_ref(want))
+
+
 @pytest.mark.parametrize("ac", [True, False])
 def test_upsample2x_ex(ac):
     from depth_estimation_b200 import ops
