@@ -1,6 +1,7 @@
 // Bandwidth-bound helper kernels between the tensor-core GEMMs: LayerNorm, token casts, cls fill,
 // bilinear x2 upsample (NHWC), strided 3x3 im2col.  All are 16-byte vectorised and grid-stride free
 // (one element group per thread, grids far larger than 148 SMs at the BASELINE shapes).
+#include <mutex>
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -849,4 +850,57 @@ extern "C" int de_groupnorm(const void* x, int x_dtype, const float* gamma, cons
       reinterpret_cast<__nv_bfloat16*>(out_plain), B, HW, C, groups, act);
   count_launch();
   return cuda_check_launch("groupnorm kernels");
+}
+
+// ---------------------------------------------------------------------------------------------- de_groupnorm_static
+// GroupNorm for callers that may not allocate (CUDA-graph capture, tight serving loops, harnesses that forbid
+// cudaMalloc): the workspace of de_groupnorm lives in a file-scope device array instead of a caller buffer.  Every GPU
+// that loads the library holds these kGnStaticBytes until exit.  In host code `g_gn_static_ws` is only a stand-in for the
+// symbol; the device address comes from cudaGetSymbolAddress, looked up once per device with that device current.
+static const int64_t kGnStaticBytes = 4 << 20;          // DE_GROUPNORM_STATIC_MAX_BYTES in include/depth_b200.h
+static __device__ __align__(256) unsigned char g_gn_static_ws[kGnStaticBytes];
+
+static const int kGnStaticMaxDevices = 64;
+static void* g_gn_static_ptr[kGnStaticMaxDevices];      // per device ordinal; written once under the mutex
+static std::mutex g_gn_static_mu;
+
+static int gn_static_ws(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return fail(DE_ERR_CUDA, "de_groupnorm_static: cudaGetDevice: %s", cudaGetErrorString(e));
+  if (dev < 0 || dev >= kGnStaticMaxDevices) return fail(DE_ERR_UNSUPPORTED, "de_groupnorm_static: device ordinal %d (max %d)", dev, kGnStaticMaxDevices - 1);
+  std::lock_guard<std::mutex> lock(g_gn_static_mu);
+  if (!g_gn_static_ptr[dev]) {
+    void* ptr = nullptr;
+    e = cudaGetSymbolAddress(&ptr, g_gn_static_ws);     // the CURRENT device's copy of the array
+    if (e != cudaSuccess || !ptr)
+      return fail(DE_ERR_CUDA, "de_groupnorm_static: cudaGetSymbolAddress(g_gn_static_ws) on device %d: %s", dev, cudaGetErrorString(e));
+    g_gn_static_ptr[dev] = ptr;
+  }
+  *out = g_gn_static_ptr[dev];
+  return DE_OK;
+}
+
+extern "C" int64_t de_groupnorm_static_max_bytes(void) { return kGnStaticBytes; }
+
+extern "C" int de_groupnorm_static(const void* x, int x_dtype, const float* gamma, const float* beta, const void* add,
+                                   int add_dtype, void* out, int out_mode, float* out_f32, void* out_plain, int B, int HW,
+                                   int C, int groups, float eps, int act, void* stream) {
+  const int64_t need = de_groupnorm_ws_bytes(B, HW, C, groups);
+  if (need <= 0) return fail(DE_ERR_UNSUPPORTED, "de_groupnorm_static: unsupported shape B=%d HW=%d C=%d groups=%d", B, HW, C, groups);
+  if (need > kGnStaticBytes)
+    return fail(DE_ERR_UNSUPPORTED,
+                "de_groupnorm_static: B=%d HW=%d C=%d groups=%d needs %lld bytes of scratch, the built-in array holds %lld "
+                "(DE_GROUPNORM_STATIC_MAX_BYTES); use de_groupnorm with a caller workspace",
+                B, HW, C, groups, (long long)need, (long long)kGnStaticBytes);
+  void* ws = nullptr;
+  int rc = gn_static_ws(&ws);
+  if (rc != DE_OK) return rc;
+  // The array keeps whatever the last call (of any shape) left.  Only the arrival counters must start at zero; stats and
+  // partial sums are fully written before they are read.  A completed call leaves the counters zero already - the
+  // memset (a memset node under capture, no allocation) also covers a predecessor that was aborted mid-kernel.
+  cudaError_t e = cudaMemsetAsync(ws, 0, kGnCounterBytes, reinterpret_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) return fail(DE_ERR_CUDA, "de_groupnorm_static: cudaMemsetAsync: %s", cudaGetErrorString(e));
+  return de_groupnorm(x, x_dtype, gamma, beta, add, add_dtype, out, out_mode, out_f32, out_plain, B, HW, C, groups, eps,
+                      act, ws, kGnStaticBytes, stream);
 }

@@ -222,6 +222,20 @@ int64_t de_groupnorm_ws_bytes(int B, int HW, int C, int groups); /* 0 for unsupp
 int de_groupnorm(const void* x, int x_dtype, const float* gamma, const float* beta, const void* add, int add_dtype,
                  void* out, int out_mode, float* out_f32, void* out_plain, int B, int HW, int C, int groups, float eps,
                  int act, void* ws, int64_t ws_bytes, void* stream);
+/* de_groupnorm without a caller workspace, for callers that may not allocate device memory (code under CUDA-graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arithmetic, arguments and outputs as de_groupnorm; the scratch is a file-scope
+ * `static __device__` array of DE_GROUPNORM_STATIC_MAX_BYTES inside the library (every GPU that loads the library holds
+ * it until exit).  The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine).  Shapes whose
+ * de_groupnorm_ws_bytes(B, HW, C, groups) exceeds the limit return DE_ERR_UNSUPPORTED with the needed size in
+ * de_last_error() - use de_groupnorm then.  All calls on one device share the one array, which keeps the last call's
+ * contents (the arrival counters are re-zeroed on `stream` by every call): calls must be ordered on one stream; two
+ * calls that overlap on the GPU race on it. */
+#define DE_GROUPNORM_STATIC_MAX_BYTES (4 << 20)
+int64_t de_groupnorm_static_max_bytes(void);
+int de_groupnorm_static(const void* x, int x_dtype, const float* gamma, const float* beta, const void* add, int add_dtype,
+                        void* out, int out_mode, float* out_f32, void* out_plain, int B, int HW, int C, int groups,
+                        float eps, int act, void* stream);
 
 /* Fused DPT head tail ([UPSTREAM] midas/dpt_depth.py head, output_conv[2..5]):
  * out[b,y,x] = relu(head_b + sum_n head_w[n] * relu(bias[n] + conv3x3(x, w)[b,y,x,n])), n < 32.
