@@ -120,20 +120,25 @@ def synthetic_frames(n, h, w, seed):
 
 
 # ---------------------------------------------------------------------------------------------- reference arm
-def cpu_oracle_fps(model_type, h, w, frames, warm=1):
-    """Times the CPU oracle (reference predict body + restated upstream modules, fp32) on host cores."""
+def cpu_oracle_fps(model_type, h, w, frames=0, warm=1, seconds=12.0):
+    """Times the CPU oracle (reference predict body + restated upstream modules, fp32) on host cores.  `frames` > 0: that
+    many frames; otherwise a bounded sample of about `seconds` of CPU work (the contract's 10-30 s), at least 3 frames."""
     import torch
     from oracle.predict import OracleDepthEstimator
     torch.set_num_threads(os.cpu_count() or 1)
     est = OracleDepthEstimator(model_type, seed=0)
-    fr = synthetic_frames(frames + warm, h, w, 99)
+    pool = synthetic_frames(8, h, w, 99)
     for i in range(warm):
-        est.predict(fr[i])
+        est.predict(pool[i % 8])
+    n = 0
     t0 = time.perf_counter()
-    for i in range(frames):
-        est.predict(fr[warm + i])
-    dt = time.perf_counter() - t0
-    return frames / dt, dt
+    while True:
+        est.predict(pool[(warm + n) % 8])
+        n += 1
+        dt = time.perf_counter() - t0
+        if (frames > 0 and n >= frames) or (frames <= 0 and n >= 3 and dt >= seconds) or n >= 5000:
+            break
+    return n / dt, dt, n
 
 
 def run_reference(args):
@@ -441,8 +446,7 @@ def run_ours(args):
         gf = GFLOP_PER_FRAME.get((args.model, W, H))
         cpu = None
         if not args.no_cpu_baseline and world == 1:     # contract: rank 0 at N=1 only (torchrun pins OMP_NUM_THREADS=1)
-            nfr = args.cpu_frames or (3 if args.model != "MiDaS_small" else 20)
-            fps, dt = cpu_oracle_fps(args.model, H, W, nfr)
+            fps, dt, nfr = cpu_oracle_fps(args.model, H, W, args.cpu_frames)
             cpu = {"value": fps, "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port",
                    "sample": f"{nfr} frames of the same workload ({args.model} {W}x{H}), {dt:.1f} s of CPU work, "
                              f"torch fp32 oracle with all host threads"}

@@ -23,6 +23,11 @@ DEV void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
 DEV void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+// Arrive without release semantics (no MEMBAR): for hand-offs whose data does not live in generic-proxy memory - the
+// epilogue returning a TMEM accumulator stage to the MMA warp, ordered by tcgen05.wait::ld + tcgen05.fence instead.
+DEV void mbar_arrive_relaxed(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.relaxed.cta.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 DEV bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(

@@ -157,6 +157,14 @@ Plan::~Plan() {
     if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
 }
 
+void Engine::ensure_lanes(int n) {
+  if (!lane_fork) ENG_CUDA(cudaEventCreateWithFlags(&lane_fork, cudaEventDisableTiming));
+  for (int i = 1; i < n && i < kMaxLanes; ++i) {
+    if (!lane_stream[i]) ENG_CUDA(cudaStreamCreateWithFlags(&lane_stream[i], cudaStreamNonBlocking));
+    if (!lane_join[i]) ENG_CUDA(cudaEventCreateWithFlags(&lane_join[i], cudaEventDisableTiming));
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ weights
 const HostT& Engine::W(const std::string& key, std::initializer_list<int64_t> shape) {
   auto it = raw.find(key);
@@ -764,5 +772,10 @@ extern "C" void de_destroy(de_handle h) {
   cudaDeviceSynchronize();
   e->plans.clear();
   if (e->side) cudaStreamDestroy(e->side);
+  for (int i = 0; i < Engine::kMaxLanes; ++i) {
+    if (e->lane_stream[i]) cudaStreamDestroy(e->lane_stream[i]);
+    if (e->lane_join[i]) cudaEventDestroy(e->lane_join[i]);
+  }
+  if (e->lane_fork) cudaEventDestroy(e->lane_fork);
   delete e;
 }

@@ -178,6 +178,10 @@ struct Engine {
   int target = 384, method = 1, layout = 0;                    // transform: get_size target / method, K1 output layout
   std::map<std::vector<int64_t>, std::unique_ptr<Plan>> plans; // key (B, H, W)
   cudaStream_t side = nullptr;                                 // warm-up stream
+  static const int kMaxLanes = 4;                              // MiDaS_small: concurrent sub-batches (engine_nets.cu)
+  cudaStream_t lane_stream[kMaxLanes] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t lane_fork = nullptr, lane_join[kMaxLanes] = {nullptr, nullptr, nullptr, nullptr};
+  void ensure_lanes(int n);
   int64_t weight_bytes = 0;
 
   // weight access during finalize

@@ -56,22 +56,32 @@ inline Gemm conv3(const void* a, int B, int H, int W, int cin, const void* w, in
   g.ldo = ldo;
   return g;
 }
+// One launch sequence over `B` frames of the plan: the whole batch, or - MiDaS_small - one "lane" of it (a contiguous
+// group of frames with its own work buffers, enqueued on its own stream so that the latency-bound kernels of several
+// lanes overlap; see forward_small).
 struct Ctx {
   Engine& e;
   Plan& p;
   cudaStream_t st;
+  int B;                                     // frames of this sequence
+  float* pred;                               // its slice of the plan's output
+  int lane = 0;
+  void* splitk_ws = nullptr;                 // lanes run concurrently: each needs its own K-slice scratch
+  int64_t splitk_ws_bytes = 0;
+  Ctx(Engine& e_, Plan& p_, cudaStream_t st_) : e(e_), p(p_), st(st_), B(p_.B), pred(p_.pred), splitk_ws(p_.splitk_ws), splitk_ws_bytes(p_.splitk_ws_bytes) {}
   template <typename T = void>
   T* buf(const char* fmt, size_t bytes, int a = 0, int b = 0, int c = 0) {
-    char key[96];
-    snprintf(key, sizeof(key), fmt, a, b, c);
+    char key[112];
+    int n = lane ? snprintf(key, sizeof(key), "L%d/", lane) : 0;
+    snprintf(key + n, sizeof(key) - n, fmt, a, b, c);
     return reinterpret_cast<T*>(p.ws.get(key, bytes));
   }
 };
 
 // every GEMM may use the plan's split-K workspace (de_gemm decides; small grids only)
 inline void run(Gemm g, Ctx& c) {
-  g.splitk_ws = c.p.splitk_ws;
-  g.splitk_ws_bytes = c.p.splitk_ws_bytes;
+  g.splitk_ws = c.splitk_ws;
+  g.splitk_ws_bytes = c.splitk_ws_bytes;
   ENG_CK(de_gemm(&g, c.st));
 }
 
@@ -218,7 +228,7 @@ Feat reassemble(Ctx& c, const ReasmW& r, int idx, const float* x, int B, int gh,
 // layerN_rn -> refinenet4..1 -> output_conv, NHWC bf16, writes the plan's `pred` [B, 2*H1, 2*W1] (fp32, >= 0)
 void decoder_plain(Ctx& c, const Feat* feats) {
   const DecoderW& d = c.e.dec;
-  const int B = c.p.B;
+  const int B = c.B;
   Feat raw[4], rel[4];
   for (int i = 0; i < 4; ++i) {
     const Feat& x = feats[i];
@@ -287,11 +297,11 @@ void decoder_plain(Ctx& c, const Feat* feats) {
     run(g, c);
   }
   if (d.h0_c % 64 == 0 && d.h0_c <= 128) {      // DPT: upsample + head tail in one halo-tiled kernel
-    ENG_CK(de_head_up_conv(h0, d.h2_w, (int64_t)9 * d.h0_c, d.h2_b, d.h4_w, d.h4_b, c.p.pred, B, H, W, d.h0_c, d.head_ac ? 1 : 0, c.st));
+    ENG_CK(de_head_up_conv(h0, d.h2_w, (int64_t)9 * d.h0_c, d.h2_b, d.h4_w, d.h4_b, c.pred, B, H, W, d.h0_c, d.head_ac ? 1 : 0, c.st));
   } else {                                      // MiDaS_small (32 channels): general implicit-GEMM kernel with the head-dot epilogue
     void* h1 = c.buf("dec.h1", (size_t)B * 4 * H * W * d.h0_c * 2);
     ENG_CK(de_upsample2x(h0, h1, B, H, W, d.h0_c, d.head_ac ? 1 : 0, c.st));
-    Gemm g = conv3(h1, B, 2 * H, 2 * W, d.h0_c, d.h2_w, 32, c.p.pred, DE_DTYPE_F32, 1);
+    Gemm g = conv3(h1, B, 2 * H, 2 * W, d.h0_c, d.h2_w, 32, c.pred, DE_DTYPE_F32, 1);
     g.bias = d.h2_b;
     g.act = DE_ACT_RELU;
     g.head_w = d.h4_w;
@@ -306,7 +316,7 @@ void decoder_plain(Ctx& c, const Feat* feats) {
 // for the levels that arrive as split3 operands, Ci for plain bf16).
 void decoder_split3(Ctx& c, const Feat* feats) {
   const DecoderW& d = c.e.dec;
-  const int B = c.p.B;
+  const int B = c.B;
   Feat raw[4], rel[4];
   for (int i = 0; i < 4; ++i) {
     const Feat& x = feats[i];
@@ -396,7 +406,7 @@ void decoder_split3(Ctx& c, const Feat* feats) {
   }
   void* h1 = c.buf("dec3.h1", (size_t)B * 4 * H * W * 3 * d.h0_c * 2);
   ENG_CK(de_upsample2x_ex(h0, DE_DTYPE_F32, h1, 1, B, H, W, d.h0_c, d.head_ac ? 1 : 0, c.st));
-  Gemm g = conv3(h1, B, 2 * H, 2 * W, 3 * d.h0_c, d.h2_w, 32, c.p.pred, DE_DTYPE_F32, 1);
+  Gemm g = conv3(h1, B, 2 * H, 2 * W, 3 * d.h0_c, d.h2_w, 32, c.pred, DE_DTYPE_F32, 1);
   g.bias = d.h2_b;
   g.act = DE_ACT_RELU;
   g.head_w = d.h4_w;
@@ -422,7 +432,7 @@ int same_pad_before(int n, int k, int s) {
 // ViT-L/16 (24 blocks, D = 1024, 16 heads, hooks 5/11/17/23) + reassemble + decoder.  x_in: the bf16 patch matrix
 // [B*gh*gw, 768] K1 writes (layout 1).
 void forward_large(Engine& e, Plan& p, cudaStream_t st) {
-  Ctx c{e, p, st};
+  Ctx c(e, p, st);
   const int B = p.B, gh = p.net_h / 16, gw = p.net_w / 16, N = gh * gw, D = e.vit.dim, T = N + 1;
   float* x = c.buf<float>("x", (size_t)B * T * D * 4);
   float* pos = e.pos_embed(gh, gw);
@@ -477,7 +487,7 @@ struct HybridRun {
 }  // namespace
 
 void forward_hybrid(Engine& e, Plan& p, cudaStream_t st) {
-  Ctx c{e, p, st};
+  Ctx c(e, p, st);
   const HybridW& hw = e.hyb;
   const int B = p.B;
   int H = (p.net_h + 1) / 2, W = (p.net_w + 1) / 2;
@@ -585,12 +595,15 @@ void forward_hybrid(Engine& e, Plan& p, cudaStream_t st) {
 // tf_efficientnet_lite3 (BatchNorm folded, ReLU6, TF-same padding, no SE) + expand decoder 64/128/256/512.
 // x_in: bf16 NCHW [B,3,net_h,net_w] (K1 layout 0).  1x1 convs on the tcgen05 GEMM with bias / ReLU6 / residual
 // epilogues; depthwise convs on the TMA-staged bandwidth kernel; the 3-channel stem on the direct kernel.
-void forward_small(Engine& e, Plan& p, cudaStream_t st) {
-  Ctx c{e, p, st};
-  const int B = p.B;
+// MiDaS_small's launch sequence over the frames of one Ctx (the whole batch or one lane), network input at `x_in`
+static void small_sequence(Ctx& c, const void* x_in) {
+  Engine& e = c.e;
+  Plan& p = c.p;
+  cudaStream_t st = c.st;
+  const int B = c.B;
   int H = (p.net_h + 1) / 2, W = (p.net_w + 1) / 2;
   void* x = c.buf("stem", (size_t)B * H * W * 32 * 2);
-  ENG_CK(de_stem_conv(p.x_in, DE_DTYPE_BF16, e.small.stem_w, e.small.stem_b, x, DE_DTYPE_BF16, B, p.net_h, p.net_w, 32, 3, 2,
+  ENG_CK(de_stem_conv(x_in, DE_DTYPE_BF16, e.small.stem_w, e.small.stem_b, x, DE_DTYPE_BF16, B, p.net_h, p.net_w, 32, 3, 2,
                       DE_ACT_RELU6, st));
   Feat feats[4];
   int bi = 0;
@@ -629,6 +642,56 @@ void forward_small(Engine& e, Plan& p, cudaStream_t st) {
     ++bi;
   }
   decoder(c, feats);
+}
+
+// Optional (DEB_SMALL_LANES=2..4, default 1 = off): cut the batch into equal lanes of >= 4 frames, each with its own
+// buffers and stream, forked from / joined to `st` with events (parallel branches inside a captured graph), so that one
+// lane's latency-bound kernels could fill the bubbles of another's.  MEASURED NEGATIVE on B200 (32 frames 720p:
+// 1.64 ms with 1 lane, 1.73 with 2, 1.80 with 4): every GEMM CTA holds a whole SM (227 KB of shared memory), so kernels
+// of different lanes do not co-reside, PDL already overlaps each kernel's prologue with its predecessor's tail, and the
+// smaller per-lane grids lose more than the overlap gains.  Kept as a switch for other batch sizes / future kernels.
+static int small_lanes(int B) {
+  static int cap = -1;
+  if (cap < 0) {
+    const char* v = getenv("DEB_SMALL_LANES");
+    cap = v ? atoi(v) : 1;
+    if (cap < 1) cap = 1;
+    if (cap > Engine::kMaxLanes) cap = Engine::kMaxLanes;
+  }
+  for (int n = cap; n > 1; --n)
+    if (B % n == 0 && B / n >= 4) return n;
+  return 1;
+}
+
+void forward_small(Engine& e, Plan& p, cudaStream_t st) {
+  const int lanes = small_lanes(p.B);
+  if (lanes == 1) {
+    Ctx c(e, p, st);
+    small_sequence(c, p.x_in);
+    return;
+  }
+  const int Bl = p.B / lanes;
+  const size_t in_stride = (size_t)Bl * 3 * p.net_h * p.net_w * 2;            // K1 layout 0: bf16 NCHW
+  const size_t out_stride = (size_t)Bl * p.net_h * p.net_w;
+  e.ensure_lanes(lanes);
+  ENG_CUDA(cudaEventRecord(e.lane_fork, st));
+  for (int l = 0; l < lanes; ++l) {
+    cudaStream_t ls = l == 0 ? st : e.lane_stream[l];
+    if (l > 0) ENG_CUDA(cudaStreamWaitEvent(ls, e.lane_fork, 0));
+    Ctx c(e, p, ls);
+    c.B = Bl;
+    c.pred = p.pred + l * out_stride;
+    c.lane = l;
+    if (l > 0) {
+      c.splitk_ws_bytes = 16 << 20;
+      c.splitk_ws = c.buf("splitk", (size_t)c.splitk_ws_bytes);
+    }
+    small_sequence(c, reinterpret_cast<const uint8_t*>(p.x_in) + l * in_stride);
+    if (l > 0) {
+      ENG_CUDA(cudaEventRecord(e.lane_join[l], ls));
+      ENG_CUDA(cudaStreamWaitEvent(st, e.lane_join[l], 0));
+    }
+  }
 }
 
 }  // namespace eng

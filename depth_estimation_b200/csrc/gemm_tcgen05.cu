@@ -98,6 +98,17 @@ DEV float gelu_fast(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(fmaf(-p, a, -1.0f)));
   return fmaf(-a, e, fmaxf(x, 0.f));
 }
+// ReLU / ReLU6 inline (two FMNMX per value - cheaper than the call), everything else through the out-of-line copy.
+__device__ __noinline__ float4 apply_act4(float4 v, int act);
+DEV float4 act4_fast(float4 v, int act) {
+  if (act == DE_ACT_RELU || act == DE_ACT_RELU6) {
+    const float hi = act == DE_ACT_RELU6 ? 6.f : __int_as_float(0x7f800000);
+    v.x = fminf(fmaxf(v.x, 0.f), hi); v.y = fminf(fmaxf(v.y, 0.f), hi);
+    v.z = fminf(fmaxf(v.z, 0.f), hi); v.w = fminf(fmaxf(v.w, 0.f), hi);
+    return v;
+  }
+  return apply_act4(v, act);
+}
 // Kept out of line on purpose: one copy of the activation code per kernel instead of one per use.
 __device__ __noinline__ float4 apply_act4(float4 v, int act) {
   if (act == DE_ACT_RELU) {
@@ -279,7 +290,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const int bar_id = 1 + grp;
     const bool f32out = p.out_dtype == DE_DTYPE_F32;
     const int ucols = f32out ? 32 : 64;                        // columns per 128-byte unit
-    const int units = BN / ucols;
+    const int units_max = BN / ucols;
     uint8_t* const sbuf0 = post + grp * (STORE_BUFS_PER_GROUP * kStoreBufBytes);
     int sb = 0;                                                // staging buffer of the next unit
     float* s_bias = reinterpret_cast<float*>(post + C::kBarOff + 256);
@@ -287,14 +298,23 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     int as = 0;
     uint32_t aphase = 0;
     bool pending = false;                                      // this group has a store in flight on sbuf
+    int bias_tile = -1;                                        // n_tile whose bias slice s_bias holds
     for (int work = unit; work < num_work; work += num_units) {
       const int tile = work / p.k_splits, split = work - tile * p.k_splits;
       const int m_tile = (tile / p.n_tiles) * CG + cta_rank, n_tile = tile % p.n_tiles;
-      // bias slice of this group's units, fetched while the main loop of the tile is still running
-      for (int u = grp; u < units; u += 2) {
-        if (gtid < ucols) {
-          const int n = n_tile * BN + u * ucols + gtid;
-          s_bias[u * ucols + gtid] = (p.bias && n < p.N) ? __ldg(p.bias + (n % bias_mod)) : 0.f;
+      // column units that hold at least one valid column (the last n-tile of a ragged N: the rest is skipped whole)
+      const int units = min(units_max, (p.N - n_tile * BN + ucols - 1) / ucols);
+      // bias slice of this group's units, fetched while the main loop of the tile is still running - only when the
+      // CTA moves to another n-tile (its tiles are num_units apart: with few n-tiles that is rarely)
+      const bool new_bias = n_tile != bias_tile;
+      if (new_bias) {
+        if (bias_tile >= 0) named_bar_sync(bar_id, 128);       // the previous tile's readers are done
+        bias_tile = n_tile;
+        for (int u = grp; u < units_max; u += 2) {
+          if (gtid < ucols) {
+            const int n = n_tile * BN + u * ucols + gtid;
+            s_bias[u * ucols + gtid] = (p.bias && n < p.N) ? __ldg(p.bias + (n % bias_mod)) : 0.f;
+          }
         }
       }
       int b = 0, y0 = 0, x0 = 0;
@@ -307,14 +327,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       }
       mbar_wait(&tfull[as], aphase);
       tc_fence_after();
-      named_bar_sync(bar_id, 128);                             // bias slice visible to the whole group
+      if (new_bias) named_bar_sync(bar_id, 128);               // bias slice visible to the whole group
       const int last_u = grp + ((units - 1 - grp) / 2) * 2;    // last unit this group handles (if any)
       if (grp >= units) {                                      // idle group (narrow tiles): just hand TMEM back
         tc_fence_before();
         __syncwarp();
         if (lane == 0) {
           if (CG == 2 && cta_rank != 0) mbar_arrive_cluster(mapa_u32(&tempty[as], 0));
-          else mbar_arrive(&tempty[as]);
+          else mbar_arrive_relaxed(&tempty[as]);
         }
       }
 #pragma unroll 1
@@ -331,7 +351,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             const float4 bb = *reinterpret_cast<const float4*>(bs + j4 * 4);
             float4 v = make_float4(__uint_as_float(acc[j4 * 4]) + bb.x, __uint_as_float(acc[j4 * 4 + 1]) + bb.y,
                                    __uint_as_float(acc[j4 * 4 + 2]) + bb.z, __uint_as_float(acc[j4 * 4 + 3]) + bb.w);
-            if (p.act != DE_ACT_NONE) v = apply_act4(v, p.act);
+            if (p.act != DE_ACT_NONE) v = act4_fast(v, p.act);
             ov[j4 * 4] = __float_as_uint(v.x); ov[j4 * 4 + 1] = __float_as_uint(v.y);
             ov[j4 * 4 + 2] = __float_as_uint(v.z); ov[j4 * 4 + 3] = __float_as_uint(v.w);
           }
@@ -360,7 +380,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 const float4 bb = *reinterpret_cast<const float4*>(bs + hh * 32 + j4 * 4);
                 float4 v = make_float4(__uint_as_float(acc[j4 * 4]) + bb.x, __uint_as_float(acc[j4 * 4 + 1]) + bb.y,
                                        __uint_as_float(acc[j4 * 4 + 2]) + bb.z, __uint_as_float(acc[j4 * 4 + 3]) + bb.w);
-                if (p.act != DE_ACT_NONE) v = apply_act4(v, p.act);
+                if (p.act != DE_ACT_NONE) v = act4_fast(v, p.act);
                 ov[hh * 16 + j4 * 2] = pack_bf16(v.x, v.y);
                 ov[hh * 16 + j4 * 2 + 1] = pack_bf16(v.z, v.w);
               }
@@ -372,7 +392,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           __syncwarp();
           if (lane == 0) {
             if (CG == 2 && cta_rank != 0) mbar_arrive_cluster(mapa_u32(&tempty[as], 0));
-            else mbar_arrive(&tempty[as]);
+            else mbar_arrive_relaxed(&tempty[as]);
           }
         }
         // the store that last used this buffer (STORE_BUFS_PER_GROUP units ago) has finished reading it
@@ -468,12 +488,62 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           s_bias[ci * 32 + lane] = n < p.N ? __ldg(p.bias + (n % bias_mod)) : 0.f;
         }
       }
+      // Residual operands of a chunk are fetched one chunk AHEAD of their use (the first chunk's before the wait for
+      // the accumulator): under saturating TMA traffic a global round trip costs thousands of cycles, and four of them
+      // in series per tile made the epilogue - not the main loop - the bound of the decoder's 3x3 convolutions
+      // (347 us against 237 us for the same shape through the store epilogue).  out may alias add1 element for element
+      // (in-place updates): a chunk's operands are read before any store to that chunk, other chunks are other columns.
+      // The loaded words stay RAW in registers until the compute phase: converting at the load (bf16 -> fp32) makes
+      // every load's first consumer follow it directly, and the 16 loads of a chunk then run one round trip after the
+      // other (ncu: 70 % of the epilogue warps' samples on those conversions, ~17k cycles per chunk).
+      const bool has_res = p.add1 != nullptr || p.add2 != nullptr;
+      const bool a1_f32 = p.add1_dtype == DE_DTYPE_F32, a2_f32 = p.add2_dtype == DE_DTYPE_F32;
+      uint4 r1_[8], r2_[8];
+      auto fetch_res = [&](int c) {
+        const int n0 = n_tile * BN + c * 32;
+        const bool col_ok = n0 < p.N && cc < p.N - n0;
+        long long colpart2 = n0 + cc;
+        if (p.out_rowmode == 2) {
+          const int g = n0 / p.ps_cout, co = n0 % p.ps_cout;
+          const long long px = static_cast<long long>(g / p.ps_s) * (p.ps_gw * p.ps_s) + g % p.ps_s;
+          colpart2 = px * p.add2_pitch + co + cc;
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int row = i * 4 + sub;
+          const long long ro = col_ok ? s_ro[row] : -1;
+          r1_[i] = make_uint4(0u, 0u, 0u, 0u);         // zero bits are 0.0 in both dtypes
+          r2_[i] = make_uint4(0u, 0u, 0u, 0u);
+          if (p.add1 && ro >= 0) {
+            const long long ao = s_ar[row] + n0 + cc;
+            if (a1_f32) {
+              r1_[i] = *reinterpret_cast<const uint4*>(reinterpret_cast<const float*>(p.add1) + ao);
+            } else {
+              const uint2 t = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(p.add1) + ao);
+              r1_[i].x = t.x;
+              r1_[i].y = t.y;
+            }
+          }
+          if (p.add2 && ro >= 0) {                     // same rows / pitch as a plain `out`
+            const long long o2 = ro * p.add2_pitch + colpart2;
+            if (a2_f32) {
+              r2_[i] = *reinterpret_cast<const uint4*>(reinterpret_cast<const float*>(p.add2) + o2);
+            } else {
+              const uint2 t = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(p.add2) + o2);
+              r2_[i].x = t.x;
+              r2_[i].y = t.y;
+            }
+          }
+        }
+      };
+      __syncwarp();                                // row tables visible to the whole warp
+      if (has_res && c_begin < c_end) fetch_res(c_begin);
       mbar_wait(&tfull[as], aphase);
       tc_fence_after();
 #pragma unroll 1
       for (int c = c_begin; c < c_end; ++c) {
         uint32_t acc[32];
-        __syncwarp();                            // previous chunk's read-back finished; row info visible
+        __syncwarp();                            // previous chunk's read-back finished
         tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN + c * 32, acc);
         tmem_ld_wait();
         if (c == c_end - 1) {                    // accumulator fully drained into registers: release it early
@@ -481,7 +551,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           __syncwarp();
           if (lane == 0) {
             if (CG == 2 && cta_rank != 0) mbar_arrive_cluster(mapa_u32(&tempty[as], 0));
-            else mbar_arrive(&tempty[as]);
+            else mbar_arrive_relaxed(&tempty[as]);
           }
         }
 #pragma unroll
@@ -491,59 +561,45 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                           __uint_as_float(acc[j4 * 4 + 2]), __uint_as_float(acc[j4 * 4 + 3]));
         __syncwarp();
         const int n0 = n_tile * BN + c * 32;
-        if (n0 >= p.N) continue;
-        const bool col_ok = cc < p.N - n0;       // N % 8 == 0 and cc % 4 == 0: whole float4 in or out
-        long long colpart = n0 + cc, colpart_r = n0 + cc, colpart2 = n0 + cc;
-        if (p.out_rowmode == 2) {
+        const bool col_ok = n0 < p.N && cc < p.N - n0;       // N % 8 == 0 and cc % 4 == 0: whole float4 in or out
+        long long colpart = n0 + cc, colpart_r = n0 + cc;
+        if (p.out_rowmode == 2 && n0 < p.N) {
           const int g = n0 / p.ps_cout, co = n0 % p.ps_cout;
           const long long px = static_cast<long long>(g / p.ps_s) * (p.ps_gw * p.ps_s) + g % p.ps_s;
           colpart = px * p.out_pitch + co + cc;
           colpart_r = px * p.relu_pitch + co + cc;
-          colpart2 = px * p.add2_pitch + co + cc;
         }
         float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f), hw4 = bias4;
         if (p.bias) bias4 = *reinterpret_cast<const float4*>(s_bias + (c - c_begin) * 32 + cc);
         if (p.head_w && col_ok) hw4 = __ldg(reinterpret_cast<const float4*>(p.head_w + n0 + cc));
-        // all global reads of the chunk are issued before any store (out may alias add1, so the compiler
-        // cannot hoist them itself): one memory round trip per chunk instead of eight
-        long long ro_[8];
-        float4 a1_[8];
-        uint2 a2_[8];
+        // compute phase: every row's value into registers (consumes this chunk's residual operands) ...
+        float4 v_[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           const int row = i * 4 + sub;
-          ro_[i] = col_ok ? s_ro[row] : -1;
-          a1_[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-          a2_[i] = make_uint2(0u, 0u);
-          if (p.add1 && ro_[i] >= 0) {
-            const long long ao = s_ar[row] + n0 + cc;
-            if (p.add1_dtype == DE_DTYPE_F32) {
-              a1_[i] = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.add1) + ao);
-            } else {
-              const uint2 t = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(p.add1) + ao);
-              a1_[i] = make_float4(bf16_lo(t.x), bf16_hi(t.x), bf16_lo(t.y), bf16_hi(t.y));
-            }
-          }
-          if (p.add2 && ro_[i] >= 0) {               // same rows / pitch as a plain `out`
-            const long long o2 = ro_[i] * p.add2_pitch + colpart2;
-            if (p.add2_dtype == DE_DTYPE_F32) {
-              const float4 t = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.add2) + o2);
-              a1_[i].x += t.x; a1_[i].y += t.y; a1_[i].z += t.z; a1_[i].w += t.w;     // (only with add1_pre == 0)
-            } else {
-              a2_[i] = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(p.add2) + o2);
-            }
-          }
-        }
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int row = i * 4 + sub;
-          const long long ro = ro_[i];
           float4 v = *reinterpret_cast<const float4*>(stg + row * kStgStride + cc);
           v.x += bias4.x; v.y += bias4.y; v.z += bias4.z; v.w += bias4.w;
-          const float4 a1 = a1_[i];
-          if (p.add1_pre) { v.x += a1.x; v.y += a1.y; v.z += a1.z; v.w += a1.w; }
-          if (p.act != DE_ACT_NONE) v = apply_act4(v, p.act);
-          if (!p.add1_pre) { v.x += a1.x; v.y += a1.y; v.z += a1.z; v.w += a1.w; }
+          if (has_res) {
+            const uint4 w1 = r1_[i], w2 = r2_[i];
+            const float4 a1 = a1_f32 ? make_float4(__uint_as_float(w1.x), __uint_as_float(w1.y), __uint_as_float(w1.z), __uint_as_float(w1.w))
+                                     : make_float4(bf16_lo(w1.x), bf16_hi(w1.x), bf16_lo(w1.y), bf16_hi(w1.y));
+            const float4 a2 = a2_f32 ? make_float4(__uint_as_float(w2.x), __uint_as_float(w2.y), __uint_as_float(w2.z), __uint_as_float(w2.w))
+                                     : make_float4(bf16_lo(w2.x), bf16_hi(w2.x), bf16_lo(w2.y), bf16_hi(w2.y));
+            if (p.add1_pre) { v.x += a1.x; v.y += a1.y; v.z += a1.z; v.w += a1.w; }
+            if (p.act != DE_ACT_NONE) v = apply_act4(v, p.act);
+            if (!p.add1_pre) { v.x += a1.x; v.y += a1.y; v.z += a1.z; v.w += a1.w; }
+            v.x += a2.x; v.y += a2.y; v.z += a2.z; v.w += a2.w;
+          } else if (p.act != DE_ACT_NONE) {
+            v = apply_act4(v, p.act);
+          }
+          v_[i] = v;
+        }
+        // ... then the NEXT chunk's operand loads go out, and only then this chunk's stores
+        if (has_res && c + 1 < c_end) fetch_res(c + 1);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int row = i * 4 + sub;
+          const float4 v = v_[i];
           if (p.head_w) {
             float d = v.x * hw4.x + v.y * hw4.y + v.z * hw4.z + v.w * hw4.w;
             d += __shfl_xor_sync(0xffffffffu, d, 1);
@@ -553,9 +609,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             if ((lane & 7) == 0 && hro >= 0) reinterpret_cast<float*>(p.out)[hro] = fmaxf(d + p.head_b, 0.f);
             continue;
           }
+          const long long ro = col_ok ? s_ro[row] : -1;
           if (ro < 0) continue;
           const long long o = ro * p.out_pitch + colpart;
-          v.x += bf16_lo(a2_[i].x); v.y += bf16_hi(a2_[i].x); v.z += bf16_lo(a2_[i].y); v.w += bf16_hi(a2_[i].y);
           if (p.out_dtype == DE_DTYPE_F32) {
             *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + o) = v;
           } else {
@@ -586,7 +642,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         __syncwarp();
         if (lane == 0) {
           if (CG == 2 && cta_rank != 0) mbar_arrive_cluster(mapa_u32(&tempty[as], 0));
-          else mbar_arrive(&tempty[as]);
+          else mbar_arrive_relaxed(&tempty[as]);
         }
       }
       if (++as == 2) {
@@ -838,6 +894,10 @@ extern "C" int de_gemm(const DeGemm* g, void* stream) {
   } else {
     return fail(DE_ERR_INVALID, "de_gemm: bad a_mode %d", g->a_mode);
   }
+  // 128 < N < 256 with many row tiles (MiDaS_small's 1x1 expand convs at high resolution, short K): one 256-wide tile
+  // per row block instead of a full and a mostly empty 128-wide one - the store epilogue skips all-empty column units,
+  // and with a one-k-block main loop the per-tile epilogue is what the kernel costs
+  if (g->block_n == 0 && g->N > 128 && g->N < 256 && p.m_tiles >= num_sms() && p.num_k_blocks <= 4) bn = 256;
   // Split-K for small grids (the batch-1 latency path, the coarse decoder levels): when the tiles cover a fraction of the
   // SMs and K is long, K-slices of a tile run on different SMs and store their fp32 partial tiles into per-slice
   // regions of the caller's workspace; splitk_finalize_kernel adds the slices in a fixed order and applies the epilogue.
@@ -862,7 +922,10 @@ extern "C" int de_gemm(const DeGemm* g, void* stream) {
   // least half of the SMs - a 45-CTA launch of 256-wide tiles leaves 100 SMs idle and every CTA streams 2x the weights
   if (g->block_n == 0 && !g->head_w && k_splits == 1) {
     const int half_sms = num_sms() / 2;
-    while (bn > 64 && g->N % (bn / 2) == 0 && p.m_tiles * ((g->N + bn - 1) / bn) < half_sms) bn >>= 1;
+    // 32-wide tiles exist only with the general epilogue: go that far only when it is what runs anyway
+    const bool general = g->add1 || g->add2 || g->out_relu || g->out_rowmode != 0 || g->out_split || g->epilogue == 1;
+    const int min_bn = general ? 32 : 64;
+    while (bn > min_bn && p.m_tiles * ((g->N + bn - 1) / bn) < half_sms) bn >>= 1;
   }
   if (g->ldw % 8 != 0 || g->ldw < ktot) return fail(DE_ERR_INVALID, "de_gemm: ldw=%lld too small / unaligned for K=%lld", (long long)g->ldw, (long long)ktot);
   {
