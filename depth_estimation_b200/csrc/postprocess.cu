@@ -98,8 +98,15 @@ DEV void post_store_row(const PostParams& p, const char* hcol, int4 yo, float4 w
   }
 }
 
-template <int kOuts>
-__global__ void __launch_bounds__(kPostThreads, 6) postprocess_kernel(const PostParams p) {   // <= 40 registers: 6 CTAs/SM
+#ifndef K8_MIN_BLOCKS
+#define K8_MIN_BLOCKS 6                                    // 6 CTAs/SM measured above 5 even with a few spilled bytes
+#endif
+// TW = 128: 4 columns per lane, 16-byte stores, every output view.  TW = 256 (fp32 map only, W % 8 == 0): 8 columns per
+// lane and one 32-byte STG.256 per lane and row - a whole sector per store instruction, what took K1's identity path
+// from 0.62 to 0.97 of the copy figure; affordable here because the register window leaves few LDS to conflict.
+template <int kOuts, int TW>
+__global__ void __launch_bounds__(kPostThreads, TW == 256 ? 4 : K8_MIN_BLOCKS) postprocess_kernel(const PostParams p) {
+  constexpr int kPostTW = TW;
   extern __shared__ __align__(16) uint8_t smem[];
   float* s_h = reinterpret_cast<float*>(smem);                        // [max_rows][128]
   int4* s_yo = reinterpret_cast<int4*>(s_h + p.max_rows * kPostTW);   // [TH] s_h offsets of the 4 row taps
@@ -142,15 +149,15 @@ __global__ void __launch_bounds__(kPostThreads, 6) postprocess_kernel(const Post
 
   // ---- phase A: horizontal taps
   {
-    const int c = tid & (kPostTW - 1);
+    const int c = tid % kPostTW;
     const int cx = min(ox0 + c, p.W - 1);               // columns past the edge recompute the last one (never stored)
     int4 xi = __ldg(reinterpret_cast<const int4*>(p.xidx) + cx);
     const float4 w = __ldg(reinterpret_cast<const float4*>(p.xw) + cx);
     xi.x -= xs; xi.y -= xs; xi.z -= xs; xi.w -= xs;
-    const float* row = s_src + ((tid >> 7) << psh);
-    float* dst = s_h + (tid >> 7) * kPostTW + c;
+    const float* row = s_src + ((tid / kPostTW) << psh);
+    float* dst = s_h + (tid / kPostTW) * kPostTW + c;
     const int rstep = (kPostThreads / kPostTW) << psh;
-    for (int rr = tid >> 7; rr < nr; rr += kPostThreads / kPostTW) {
+    for (int rr = tid / kPostTW; rr < nr; rr += kPostThreads / kPostTW) {
       *dst = dot4(row[xi.x], row[xi.y], row[xi.z], row[xi.w], w);
       row += rstep;
       dst += (kPostThreads / kPostTW) * kPostTW;
@@ -159,6 +166,55 @@ __global__ void __launch_bounds__(kPostThreads, 6) postprocess_kernel(const Post
   __syncthreads();
 
   // ---- phase B: vertical taps, stores
+  if (TW == 256) {                                          // host guarantees: fp32 map only, W % 8 == 0, 32-byte aligned
+    const int c8 = (tid & 31) * 8;
+    if (c8 >= ncols) return;                                // W % 8 == 0: a lane's 8 columns are all in or all out
+    const char* hc = reinterpret_cast<const char*>(s_h + c8);
+    const int rpw = (p.TH + kPostThreads / 32 - 1) / (kPostThreads / 32);
+    const int r_begin = (tid >> 5) * rpw, r_end = min(r_begin + rpw, nrows);
+    float* op = p.out_map + ((long long)b * p.H + oy0 + r_begin) * p.W + ox0 + c8;
+    int4 have = make_int4(-1, -1, -1, -1);
+    float4 a[4][2];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) a[k][0] = a[k][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int ry = r_begin; ry < r_end; ++ry, op += p.W) {
+      const int4 yo = s_yo[ry];
+      const float4 w = s_yw[ry];
+      if (yo.x == have.y && yo.y == have.z && yo.z == have.w) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          a[0][h] = a[1][h]; a[1][h] = a[2][h]; a[2][h] = a[3][h];
+          a[3][h] = *reinterpret_cast<const float4*>(hc + yo.w + 16 * h);
+        }
+      } else if (!(yo.x == have.x && yo.y == have.y && yo.z == have.z && yo.w == have.w)) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          a[0][h] = *reinterpret_cast<const float4*>(hc + yo.x + 16 * h);
+          a[1][h] = *reinterpret_cast<const float4*>(hc + yo.y + 16 * h);
+          a[2][h] = *reinterpret_cast<const float4*>(hc + yo.z + 16 * h);
+          a[3][h] = *reinterpret_cast<const float4*>(hc + yo.w + 16 * h);
+        }
+      }
+      have = yo;
+      float2 v[4];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        float2 lo = fmul2(make_float2(a[0][h].x, a[0][h].y), make_float2(w.x, w.x));
+        float2 hi = fmul2(make_float2(a[0][h].z, a[0][h].w), make_float2(w.x, w.x));
+        lo = ffma2(make_float2(a[1][h].x, a[1][h].y), make_float2(w.y, w.y), lo);
+        hi = ffma2(make_float2(a[1][h].z, a[1][h].w), make_float2(w.y, w.y), hi);
+        lo = ffma2(make_float2(a[2][h].x, a[2][h].y), make_float2(w.z, w.z), lo);
+        hi = ffma2(make_float2(a[2][h].z, a[2][h].w), make_float2(w.z, w.z), hi);
+        lo = ffma2(make_float2(a[3][h].x, a[3][h].y), make_float2(w.w, w.w), lo);
+        hi = ffma2(make_float2(a[3][h].z, a[3][h].w), make_float2(w.w, w.w), hi);
+        v[2 * h] = lo;
+        v[2 * h + 1] = hi;
+      }
+      st_stream_256(op, make_uint4(__float_as_uint(v[0].x), __float_as_uint(v[0].y), __float_as_uint(v[1].x), __float_as_uint(v[1].y)),
+                    make_uint4(__float_as_uint(v[2].x), __float_as_uint(v[2].y), __float_as_uint(v[3].x), __float_as_uint(v[3].y)));
+    }
+    return;
+  }
   const int c0 = (tid & 31) * 4;
   if (c0 >= ncols) return;
   const char* hcol = reinterpret_cast<const char*>(s_h + c0);
@@ -166,8 +222,49 @@ __global__ void __launch_bounds__(kPostThreads, 6) postprocess_kernel(const Post
   const int ostep = (kPostThreads / 32) * p.W;
   // 16-byte stores need the quad inside the tile and 4-element alignment of every row start: W % 4 == 0
   if (c0 + 4 <= ncols && (p.W & 3) == 0) {
-    for (int ry = tid >> 5; ry < nrows; ry += kPostThreads / 32, o += ostep)
-      post_store_row<true, kOuts>(p, hcol, s_yo[ry], s_yw[ry], o, 4);
+    // A warp owns CONSECUTIVE output rows and keeps the four source rows of its taps in registers: when upscaling, the
+    // tap window of the next output row is the same one or the same one moved down by a row, so it costs zero or one
+    // LDS.128 instead of four (the window rows are compared by their s_h offsets - border clamping repeats rows, any
+    // other pattern reloads all four).  The vertical dot products run as packed pairs (FMUL2 + 3 FFMA2 per two
+    // columns: same operations and rounding as dot4).  Round 1's loop (4 LDS.128 + 16 FMA per quad, rows strided over
+    // the warps) was issue- and shared-memory-bound at 0.56 of the HBM copy figure for 384x672 -> 1080p.
+    const int rpw = (p.TH + kPostThreads / 32 - 1) / (kPostThreads / 32);
+    const int r_begin = (tid >> 5) * rpw, r_end = min(r_begin + rpw, nrows);
+    long long oo = ((long long)b * p.H + oy0 + r_begin) * p.W + ox0 + c0;
+    int4 have = make_int4(-1, -1, -1, -1);
+    float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0, a2 = a0, a3 = a0;
+    for (int ry = r_begin; ry < r_end; ++ry, oo += p.W) {
+      const int4 yo = s_yo[ry];
+      const float4 w = s_yw[ry];
+      if (yo.x == have.y && yo.y == have.z && yo.z == have.w) {          // window moved down by one row
+        a0 = a1; a1 = a2; a2 = a3;
+        a3 = *reinterpret_cast<const float4*>(hcol + yo.w);
+      } else if (!(yo.x == have.x && yo.y == have.y && yo.z == have.z && yo.w == have.w)) {
+        a0 = *reinterpret_cast<const float4*>(hcol + yo.x);
+        a1 = *reinterpret_cast<const float4*>(hcol + yo.y);
+        a2 = *reinterpret_cast<const float4*>(hcol + yo.z);
+        a3 = *reinterpret_cast<const float4*>(hcol + yo.w);
+      }
+      have = yo;
+      float2 v01 = fmul2(make_float2(a0.x, a0.y), make_float2(w.x, w.x));
+      float2 v23 = fmul2(make_float2(a0.z, a0.w), make_float2(w.x, w.x));
+      v01 = ffma2(make_float2(a1.x, a1.y), make_float2(w.y, w.y), v01);
+      v23 = ffma2(make_float2(a1.z, a1.w), make_float2(w.y, w.y), v23);
+      v01 = ffma2(make_float2(a2.x, a2.y), make_float2(w.z, w.z), v01);
+      v23 = ffma2(make_float2(a2.z, a2.w), make_float2(w.z, w.z), v23);
+      v01 = ffma2(make_float2(a3.x, a3.y), make_float2(w.w, w.w), v01);
+      v23 = ffma2(make_float2(a3.z, a3.w), make_float2(w.w, w.w), v23);
+      if (kOuts & 1) __stcs(reinterpret_cast<float4*>(p.out_map + oo), make_float4(v01.x, v01.y, v23.x, v23.y));
+      if (kOuts & 2)
+        *reinterpret_cast<uint32_t*>(p.out_vis + oo) =
+            vis_byte(v01.x) | (vis_byte(v01.y) << 8) | (vis_byte(v23.x) << 16) | (vis_byte(v23.y) << 24);
+      if (kOuts & 4) {
+        uint2 m;
+        m.x = pack_bf16(fmaf(v01.x, p.metric_scale, p.metric_shift), fmaf(v01.y, p.metric_scale, p.metric_shift));
+        m.y = pack_bf16(fmaf(v23.x, p.metric_scale, p.metric_shift), fmaf(v23.y, p.metric_scale, p.metric_shift));
+        __stcs(reinterpret_cast<uint2*>(p.out_metric + oo), m);
+      }
+    }
   } else {
     for (int ry = tid >> 5; ry < nrows; ry += kPostThreads / 32, o += ostep)
       post_store_row<false, kOuts>(p, hcol, s_yo[ry], s_yw[ry], o, ncols - c0);
@@ -285,17 +382,27 @@ extern "C" int de_postprocess(const void* pred, int in_dtype, int B, int h, int 
     int rc = cuda_check_launch("postprocess_copy_kernel");
     if (rc != DE_OK) return rc;
   } else if (out_map || out_metric || out_vis) {
-    static const int cand[] = {64, 32, 16, 8, 4, 2, 1};       // output rows per tile; 128 columns always
+    static const int cand[] = {64, 32, 16, 8, 4, 2, 1};       // output rows per tile
+    const int outs = (out_map ? 1 : 0) | (out_vis ? 2 : 0) | (out_metric ? 4 : 0);
+    static int wide_on = -1;
+    if (wide_on < 0) {
+      const char* e = getenv("DEB_K8_WIDE");
+      wide_on = (e && e[0] == '0') ? 0 : 1;
+    }
+    // measured: 128x256 -> 720p (5x) 0.71 -> 0.77 of the copy figure with the wide tile, 384x672 -> 1080p (2.86x) 0.55 -> 0.48
+    // (the horizontal pass over the source rows, not the store, is what that case spends its time on)
+    const bool wide = wide_on && outs == 1 && W % 8 == 0 && W >= 256 && W >= 4 * w && (reinterpret_cast<uintptr_t>(out_map) & 31) == 0;
+    const int tw = wide ? 256 : kPostTW;
     size_t smem = 0;
     bool ok = false;
     for (int th : cand) {
-      p.TW = kPostTW;
+      p.TW = tw;
       p.TH = th;
       int psh = 0;                                              // staged-window pitch: power of two >= the column extent
-      while ((1 << psh) < tx->max_extent(kPostTW)) ++psh;
+      while ((1 << psh) < tx->max_extent(tw)) ++psh;
       p.max_cols = psh;
       p.max_rows = ty->max_extent(p.TH);
-      smem = sizeof(float) * (size_t)p.max_rows * (kPostTW + (1 << psh)) + (size_t)p.TH * 32;
+      smem = sizeof(float) * (size_t)p.max_rows * (tw + (1 << psh)) + (size_t)p.TH * 32;
       if (smem <= 40 * 1024) {                                  // several CTAs per SM: the kernel lives on occupancy
         ok = true;
         break;
@@ -303,15 +410,17 @@ extern "C" int de_postprocess(const void* pred, int in_dtype, int B, int h, int 
     }
     if (!ok) return fail(DE_ERR_UNSUPPORTED, "de_postprocess: resampling window too large");
     dim3 grid((W + p.TW - 1) / p.TW, (H + p.TH - 1) / p.TH, B);
-    const int outs = (out_map ? 1 : 0) | (out_vis ? 2 : 0) | (out_metric ? 4 : 0);
     switch (outs) {
-      case 1: postprocess_kernel<1><<<grid, kPostThreads, smem, st>>>(p); break;
-      case 2: postprocess_kernel<2><<<grid, kPostThreads, smem, st>>>(p); break;
-      case 3: postprocess_kernel<3><<<grid, kPostThreads, smem, st>>>(p); break;
-      case 4: postprocess_kernel<4><<<grid, kPostThreads, smem, st>>>(p); break;
-      case 5: postprocess_kernel<5><<<grid, kPostThreads, smem, st>>>(p); break;
-      case 6: postprocess_kernel<6><<<grid, kPostThreads, smem, st>>>(p); break;
-      default: postprocess_kernel<7><<<grid, kPostThreads, smem, st>>>(p); break;
+      case 1:
+        if (wide) postprocess_kernel<1, 256><<<grid, kPostThreads, smem, st>>>(p);
+        else postprocess_kernel<1, 128><<<grid, kPostThreads, smem, st>>>(p);
+        break;
+      case 2: postprocess_kernel<2, 128><<<grid, kPostThreads, smem, st>>>(p); break;
+      case 3: postprocess_kernel<3, 128><<<grid, kPostThreads, smem, st>>>(p); break;
+      case 4: postprocess_kernel<4, 128><<<grid, kPostThreads, smem, st>>>(p); break;
+      case 5: postprocess_kernel<5, 128><<<grid, kPostThreads, smem, st>>>(p); break;
+      case 6: postprocess_kernel<6, 128><<<grid, kPostThreads, smem, st>>>(p); break;
+      default: postprocess_kernel<7, 128><<<grid, kPostThreads, smem, st>>>(p); break;
     }
     count_launch();
     int rc = cuda_check_launch("postprocess_kernel");
