@@ -52,6 +52,10 @@ struct GemmParams {
   int accumulate;  // store epilogue only: TMA reduce-add instead of store
   int k_splits, kb_per_split;  // split-K: work item = (tile, split); split s covers k-blocks [s*kb_per_split, ...)
   int split_rows, split_b;     // split-K partial tiles go to slice `split` of the workspace: row / image offset per slice
+  // 3x3 convolution, halo mode: the stage ring is carved into `na` A slots of `a_slot` bytes - each one (bh + 2) x bw
+  // pixels of one 64-channel block at ONE horizontal tap offset, used by the three vertical taps as views bw rows apart -
+  // and `nb` W-tile slots.  The activation is fetched 3 (bh + 2) / bh times instead of 9.
+  int halo, na, nb, a_slot;
 };
 
 // EPI 0: "store" epilogue - bias + activation only, output tile staged in 128B-swizzled smem and written
@@ -137,11 +141,18 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   uint8_t* sB = smem + C::kStages * C::kABytes;
   uint8_t* post = smem + C::kStages * C::kStageBytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(post + C::kBarOff);
-  uint64_t* full = bars;
-  uint64_t* empty = bars + C::kStages;
-  uint64_t* tfull = bars + 2 * C::kStages;
+  uint64_t* tfull = bars;
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  uint64_t* full = bars + 5;                     // plain mode: kStages full + kStages empty barriers (<= 16 of the 27 left)
+  uint64_t* empty = full + C::kStages;
+  // halo mode: A ring (na slots) and W ring (nb slots) with their own barrier pairs; na + nb <= 13
+  uint64_t* a_full = bars + 5;
+  uint64_t* a_empty = a_full + p.na;
+  uint64_t* b_full = a_empty + p.na;
+  uint64_t* b_empty = b_full + p.nb;
+  uint8_t* sAh = smem;
+  uint8_t* sBh = smem + p.na * p.a_slot;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -154,9 +165,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     tma_prefetch_desc(&tmB);
   }
   if (warp == 1 && lane == 0) {
-    for (int i = 0; i < C::kStages; ++i) {
-      mbar_init(&full[i], 1);
-      mbar_init(&empty[i], 1);
+    if (p.halo) {
+      for (int i = 0; i < 2 * (p.na + p.nb); ++i) mbar_init(&a_full[i], 1);
+    } else {
+      for (int i = 0; i < C::kStages; ++i) {
+        mbar_init(&full[i], 1);
+        mbar_init(&empty[i], 1);
+      }
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);
@@ -182,7 +197,45 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
   if (warp == 0) {
     // ------------------------------------------------------------- TMA producer (one per CTA)
-    if (lane == 0) {
+    if (lane == 0 && p.halo) {
+      int sa = 0, sb = 0;
+      uint32_t pa = 0, pb = 0;
+      const uint32_t a_bytes = p.bw * (p.bh + 2) * BK * 2;
+      for (int work = unit; work < num_work; work += num_units) {
+        const int m_tile = (work / p.n_tiles) * CG + cta_rank, n_tile = work % p.n_tiles;
+        const int per_img = p.tiles_x * p.tiles_y;
+        const int b = m_tile / per_img, t = m_tile % per_img;      // b >= B for the padding tile of an odd pair: zero fill
+        const int y0 = (t / p.tiles_x) * p.bh, x0 = (t % p.tiles_x) * p.bw;
+        const int n_row = n_tile * BN + cta_rank * C::kBRows;
+        for (int dx = 0; dx < 3; ++dx) {
+          for (int cb = 0; cb < p.cin_blocks; ++cb) {
+            mbar_wait(&a_empty[sa], pa ^ 1);
+            uint8_t* da = sAh + sa * p.a_slot;
+            if (CG == 1) {
+              mbar_arrive_expect_tx(&a_full[sa], a_bytes);
+              tma_load_4d(da, &tmA, &a_full[sa], cb * BK, x0 + dx - 1, y0 - 1, b);
+            } else {
+              if (cta_rank == 0) mbar_arrive_expect_tx(&a_full[sa], 2 * a_bytes);
+              tma_load_4d_cg2(da, &tmA, mapa_u32(&a_full[sa], 0), cb * BK, x0 + dx - 1, y0 - 1, b);
+            }
+            if (++sa == p.na) { sa = 0; pa ^= 1; }
+            for (int dy = 0; dy < 3; ++dy) {
+              mbar_wait(&b_empty[sb], pb ^ 1);
+              uint8_t* db = sBh + sb * C::kBBytes;
+              const int kcol = ((dy * 3 + dx) * p.cin_blocks + cb) * BK;
+              if (CG == 1) {
+                mbar_arrive_expect_tx(&b_full[sb], C::kBBytes);
+                tma_load_2d(db, &tmB, &b_full[sb], kcol, n_row);
+              } else {
+                if (cta_rank == 0) mbar_arrive_expect_tx(&b_full[sb], 2 * C::kBBytes);
+                tma_load_2d_cg2(db, &tmB, mapa_u32(&b_full[sb], 0), kcol, n_row);
+              }
+              if (++sb == p.nb) { sb = 0; pb ^= 1; }
+            }
+          }
+        }
+      }
+    } else if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
       const uint32_t a_bytes = p.a_mode == 0 ? C::kABytes : p.bw * p.bh * BK * 2;
@@ -233,7 +286,57 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------- MMA issuer (leader CTA only)
-    if (cta_rank == 0) {
+    if (cta_rank == 0 && p.halo) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM * CG, BN);
+      int sa = 0, sb = 0;
+      uint32_t pa = 0, pb = 0;
+      int as = 0;
+      uint32_t aphase = 0;
+      const uint32_t dy_step = static_cast<uint32_t>(p.bw * BK * 2) >> 4;       // bw pixel rows further down, in 16-byte units
+      for (int work = unit; work < num_work; work += num_units) {
+        mbar_wait(&tempty[as], aphase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BN;
+        for (int dx = 0; dx < 3; ++dx) {
+          for (int cb = 0; cb < p.cin_blocks; ++cb) {
+            mbar_wait(&a_full[sa], pa);
+            tc_fence_after();
+            const uint64_t adesc0 = make_sw128_kmajor_desc(smem_u32(sAh + sa * p.a_slot));
+            for (int dy = 0; dy < 3; ++dy) {
+              mbar_wait(&b_full[sb], pb);
+              tc_fence_after();
+              const uint64_t adesc = adesc0 + dy * dy_step;
+              const uint64_t bdesc = make_sw128_kmajor_desc(smem_u32(sBh + sb * C::kBBytes));
+              const bool first = (dx | cb | dy) == 0;
+              const bool last_a = dy == 2, last_t = last_a && dx == 2 && cb == p.cin_blocks - 1;
+              if (elect_one()) {
+#pragma unroll
+                for (int k = 0; k < BK / 16; ++k) {
+                  if (CG == 2) umma_bf16_cg2(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, !(first && k == 0));
+                  else umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, !(first && k == 0));
+                }
+                if (CG == 2) {
+                  umma_commit_cg2(&b_empty[sb], 3);
+                  if (last_a) umma_commit_cg2(&a_empty[sa], 3);
+                  if (last_t) umma_commit_cg2(&tfull[as], 3);
+                } else {
+                  umma_commit(&b_empty[sb]);
+                  if (last_a) umma_commit(&a_empty[sa]);
+                  if (last_t) umma_commit(&tfull[as]);
+                }
+              }
+              __syncwarp();
+              if (++sb == p.nb) { sb = 0; pb ^= 1; }
+            }
+            if (++sa == p.na) { sa = 0; pa ^= 1; }
+          }
+        }
+        if (++as == 2) {
+          as = 0;
+          aphase ^= 1;
+        }
+      }
+    } else if (cta_rank == 0) {
       constexpr uint32_t idesc = make_idesc_bf16(BM * CG, BN);
       int stage = 0;
       uint32_t phase = 0;
@@ -700,6 +803,42 @@ static void pick_conv_box(int H, int W, int* bw_out, int* bh_out) {
   *bh_out = bbh;
 }
 
+// Halo mode of the 3x3 convolution: box with bw % 8 == 0 (the three vertical-tap views of a slot must start on 1024-byte
+// swizzle atoms) and a (bh + 2) x bw slot of at most 32 KB.  Returns false when no such box keeps the tile efficiency.
+static bool pick_conv_box_halo(int H, int W, int plain_bw, int plain_bh, int* bw_out, int* bh_out) {
+  const long long plain_tiles = (long long)((W + plain_bw - 1) / plain_bw) * ((H + plain_bh - 1) / plain_bh);
+  double best = -1, best_over = 1e9;
+  int bbw = 0, bbh = 0;
+  for (int bw = 8; bw <= 128; bw += 8) {
+    int bh = 128 / bw;
+    if (bh > H) bh = H;
+    if (bh < 1 || (bh + 2) * bw > 256) continue;
+    const long long tiles = (long long)((W + bw - 1) / bw) * ((H + bh - 1) / bh);
+    const double eff = (double)H * W / (double)(tiles * 128);
+    const double over = (double)(bh + 2) / bh;                // activation bytes fetched per byte used
+    if (eff > best + 1e-9 || (eff > best - 1e-9 && over < best_over)) {
+      best = eff;
+      best_over = over;
+      bbw = bw;
+      bbh = bh;
+    }
+  }
+  if (bbw == 0) return false;
+  const long long tiles = (long long)((W + bbw - 1) / bbw) * ((H + bbh - 1) / bbh);
+  if (tiles * 10 > plain_tiles * 11) return false;            // > 10 % more tiles than the free-form box: not worth it
+  *bw_out = bbw;
+  *bh_out = bbh;
+  return true;
+}
+// bytes of the stage ring of gemm_kernel<bn, cg, epi> (mirrors Cfg)
+static int ring_bytes(int bn, int cg, int epi) {
+  const int stage = BM * BK * 2 + (bn / cg) * BK * 2;
+  const int post = epi == 0 ? 2 * STORE_BUFS_PER_GROUP * kStoreBufBytes + 256 + 1024 : 256 + kEpiWarps * kEpiWarpBytes;
+  int stages = (kSmemLimit - 1024 - post) / stage;
+  if (stages > 8) stages = 8;
+  return stages * stage;
+}
+
 template <int BN, int CG, int EPI>
 static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const GemmParams& p,
                   cudaStream_t st) {
@@ -1040,6 +1179,41 @@ extern "C" int de_gemm(const DeGemm* g, void* stream) {
                    (g->a_mode == 0 || g->ldo == g->N) && g->epilogue != 1;
   if (g->accumulate && (!store_epi || g->a_mode != 0 || g->out_dtype != DE_DTYPE_F32))
     return fail(DE_ERR_INVALID, "de_gemm: accumulate needs the dense fp32 store epilogue (a_mode 0, no add1/add2/out_relu/row maps)");
+  // 3x3 convolution in halo mode (see GemmParams): decided here, where tile width, CTA pairing and the epilogue - hence
+  // the bytes of the stage ring - are known.  DEB_CONV_HALO=0 keeps the nine-box main loop.
+  if (g->a_mode == 1 && bn >= 64) {
+    static int halo_on = -1;
+    if (halo_on < 0) {
+      const char* e = getenv("DEB_CONV_HALO");
+      halo_on = (e && e[0] == '0') ? 0 : 1;
+    }
+    int hbw = 0, hbh = 0;
+    if (halo_on && pick_conv_box_halo(g->H, g->W, p.bw, p.bh, &hbw, &hbh)) {
+      const int ring = ring_bytes(bn, cg, store_epi ? 0 : 1), b_bytes = (bn / cg) * BK * 2;
+      const int a_slot = ((hbh + 2) * hbw * BK * 2 + 1023) / 1024 * 1024;
+      int na = 3, nb = (ring - na * a_slot) / b_bytes;
+      if (nb < 5) {
+        na = 2;
+        nb = (ring - na * a_slot) / b_bytes;
+      }
+      if (nb > 13 - na) nb = 13 - na;
+      if (nb >= 4) {
+        p.halo = 1;
+        p.na = na;
+        p.nb = nb;
+        p.a_slot = a_slot;
+        p.bw = hbw;
+        p.bh = hbh;
+        p.tiles_x = (g->W + p.bw - 1) / p.bw;
+        p.tiles_y = (g->H + p.bh - 1) / p.bh;
+        p.m_tiles = g->B * p.tiles_x * p.tiles_y;
+        const uint64_t dims[4] = {(uint64_t)g->Cin, (uint64_t)g->W, (uint64_t)g->H, (uint64_t)g->B};
+        const uint64_t strides[3] = {(uint64_t)g->Cin * 2, (uint64_t)g->W * g->Cin * 2, (uint64_t)g->H * g->W * g->Cin * 2};
+        const uint32_t box[4] = {BK, (uint32_t)p.bw, (uint32_t)(p.bh + 2), 1};
+        if (!make_map(&ta, g->a, 4, dims, strides, box)) return DE_ERR_CUDA;
+      }
+    }
+  }
   CUtensorMap tc = tb;
   if (store_epi) {
     const CUtensorMapDataType dt = es == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
