@@ -1,4 +1,4 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:gemm_kernel --launch-skip 4 -c 1 -f -o gpurun_out/r02_gemm_shortk \
-  python scripts/probe_gemm.py 262144 64 128 > gpurun_out/ncu_shortk.log 2>&1; echo "ncu exit $?"; tail -2 gpurun_out/ncu_shortk.log
+timeout 900 ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k 'regex:gemm_kernel<\(int\)256, \(int\)2, \(int\)1>' --launch-skip 4 -c 1 -f -o gpurun_out/r02_conv_epi1_v2 \
+  python scripts/gemm_small_bench.py convonly > gpurun_out/ncu_conv.log 2>&1; echo "ncu exit $?"; tail -2 gpurun_out/ncu_conv.log
