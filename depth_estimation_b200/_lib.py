@@ -114,6 +114,9 @@ SIGNATURES = {
                                         C.c_void_p]),
     "de_depthwise": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
                                C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "de_dwproject_ws_bytes": (C.c_int64, [C.c_int, C.c_int, C.c_int, C.c_int]),
+    "de_dwproject": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                               C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int64, C.c_void_p]),
     "de_maxpool3x3s2": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                   C.c_void_p]),
 }

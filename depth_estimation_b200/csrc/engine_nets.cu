@@ -595,6 +595,20 @@ void forward_hybrid(Engine& e, Plan& p, cudaStream_t st) {
 // tf_efficientnet_lite3 (BatchNorm folded, ReLU6, TF-same padding, no SE) + expand decoder 64/128/256/512.
 // x_in: bf16 NCHW [B,3,net_h,net_w] (K1 layout 0).  1x1 convs on the tcgen05 GEMM with bias / ReLU6 / residual
 // epilogues; depthwise convs on the TMA-staged bandwidth kernel; the 3-channel stem on the direct kernel.
+// DEB_MBCONV_FUSED=1 runs the stride-1 blocks' depthwise + projection as ONE kernel (de_dwproject, csrc/mbconv.cu).
+// Off by default - MEASURED SLOWER on B200 (32 frames 720p: 1.70 against 1.46 ms; 640x480 batch 1: 0.91 against 0.68 ms):
+// with ~190 KB of shared memory per CTA the fused kernel runs one CTA of 8 compute warps per SM where the stand-alone
+// depthwise kernel runs three, and at 8x16 / 4x8 pixels per frame the few output tiles leave the depthwise arithmetic
+// on a quarter of the warps; the launch it saves (3-6 us) does not pay for that (profiles/r02_mbconv_fused.md).
+static bool small_fused() {
+  static int on = -1;
+  if (on < 0) {
+    const char* v = getenv("DEB_MBCONV_FUSED");
+    on = (v && v[0] == '1') ? 1 : 0;
+  }
+  return on != 0;
+}
+
 // MiDaS_small's launch sequence over the frames of one Ctx (the whole batch or one lane), network input at `x_in`
 static void small_sequence(Ctx& c, const void* x_in) {
   Engine& e = c.e;
@@ -619,9 +633,24 @@ static void small_sequence(Ctx& c, const void* x_in) {
       run(g, c);
       t = ex;
     }
+    void* y = c.buf("mb%d.y", pout * m.cout * 2, bi);
+    if (s == 1 && small_fused()) {
+      // depthwise + projection in one kernel (csrc/mbconv.cu): the 6x-expanded depthwise output stays on the SM
+      const int64_t wsb = de_dwproject_ws_bytes(B, H, W, m.cout);
+      void* ws = c.p.ws.get(std::string(c.lane ? "L" + std::to_string(c.lane) + "/" : "") + "mb.ws" + std::to_string(bi), (size_t)wsb, true);
+      ENG_CK(de_dwproject(t, m.dw_w, m.dw_b, m.pw_w, m.pw_b, m.residual ? x : nullptr, y, B, H, W, m.mid, m.cout, m.k, ws, wsb, st));
+      x = y;
+      H = Ho;
+      W = Wo;
+      if (m.last) {
+        const int lvl = m.stage == 1 ? 0 : m.stage == 2 ? 1 : m.stage == 4 ? 2 : m.stage == 6 ? 3 : -1;
+        if (lvl >= 0) feats[lvl] = Feat{x, H, W, m.cout};
+      }
+      ++bi;
+      continue;
+    }
     void* dwo = c.buf("mb%d.d", pout * m.mid * 2, bi);
     ENG_CK(de_depthwise(t, m.dw_w, m.dw_b, dwo, B, H, W, m.mid, m.k, s, DE_ACT_RELU6, st));
-    void* y = c.buf("mb%d.y", pout * m.cout * 2, bi);
     {
       Gemm g = dense(dwo, m.mid, (int)pout, m.mid, m.pw_w, m.mid, m.cout, y, DE_DTYPE_BF16, m.cout);
       g.bias = m.pw_b;

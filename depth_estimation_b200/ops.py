@@ -302,6 +302,25 @@ def im2col3x3(x: torch.Tensor, out: torch.Tensor, stride: int, pad=(1, 1), out_h
     return out
 
 
+def dwproject(x: torch.Tensor, dw_w: torch.Tensor, dw_b: torch.Tensor, pw_w: torch.Tensor, pw_b: torch.Tensor,
+              out: torch.Tensor, k: int, ws: torch.Tensor, residual: torch.Tensor | None = None):
+    """Fused depthwise k x k (stride 1, + bias, ReLU6) -> 1x1 projection (+ bias [+ residual]).  x NHWC bf16 [B,H,W,C];
+    dw_w bf16 [k*k, C]; pw_w bf16 [cout, C]; out NHWC bf16 [B,H,W,cout]; ws: zeroed torch.uint8 scratch."""
+    _need_cuda(x, dw_w, dw_b, pw_w, pw_b, out, ws, residual)
+    B, H, W, Cc = x.shape
+    cout = pw_w.shape[0]
+    assert x.dtype == torch.bfloat16 and x.is_contiguous() and out.is_contiguous() and pw_w.is_contiguous() and dw_w.is_contiguous()
+    assert tuple(out.shape) == (B, H, W, cout) and ws.dtype == torch.uint8
+    _lib.check(_lib.load().de_dwproject(x.data_ptr(), dw_w.data_ptr(), dw_b.data_ptr(), pw_w.data_ptr(), pw_b.data_ptr(),
+                                        _ptr(residual), out.data_ptr(), B, H, W, Cc, cout, k, ws.data_ptr(), ws.numel(),
+                                        _stream()), "de_dwproject")
+    return out
+
+
+def dwproject_ws_bytes(B: int, H: int, W: int, cout: int) -> int:
+    return int(_lib.load().de_dwproject_ws_bytes(B, H, W, cout))
+
+
 def subsample(x: torch.Tensor, out: torch.Tensor, stride: int):
     _need_cuda(x, out)
     B, H, W, Cc = x.shape

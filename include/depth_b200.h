@@ -266,6 +266,17 @@ int de_stem_im2col_split3(const float* x_nchw, void* out_bf16, int B, int H, int
 /* depthwise k in {3,5}: x NHWC bf16, w bf16 [k*k][C] (tap-major, BN folded), bias float[C]. */
 int de_depthwise(const void* x, const void* w_tapmajor, const float* bias, void* out, int B, int H, int W, int C,
                  int k, int stride, int act, void* stream);
+/* Fused depthwise k3 / k5 (stride 1, TF-same padding, + bias, ReLU6) -> pointwise-linear 1x1 (+ bias [+ residual]) of an
+ * MBConv block ([UPSTREAM] geffnet InvertedResidual conv_dw/bn2/act/conv_pwl/bn3, BatchNorm folded): what
+ * de_depthwise followed by de_gemm computes, without the depthwise output ever reaching global memory.
+ * x: NHWC bf16 [B,H,W,C] (the expanded activation); dw_w: bf16 [k*k][C] tap-major; pw_w: bf16 [cout][C]; residual / out:
+ * NHWC bf16 [B,H,W,cout].  C, cout multiples of 8, cout <= 384.  ws: device scratch of de_dwproject_ws_bytes(B,H,W,cout)
+ * bytes whose first 16 KB (arrival counters) must be zero before the first call; every call leaves them zero; calls
+ * sharing a workspace must be ordered on one stream.  Deterministic (fixed-order sums). */
+int64_t de_dwproject_ws_bytes(int B, int H, int W, int cout);
+int de_dwproject(const void* x, const void* dw_w, const float* dw_b, const void* pw_w, const float* pw_b,
+                 const void* residual, void* out, int B, int H, int W, int C, int cout, int k, void* ws,
+                 int64_t ws_bytes, void* stream);
 /* MaxPool 3x3 stride 2 TF-same, NHWC bf16 or f32 in; out bf16 [.., C] (out_mode 0) or split3 [.., 3C] (1). */
 int de_maxpool3x3s2(const void* x, int x_dtype, void* out, int out_mode, int B, int H, int W, int C, void* stream);
 

@@ -573,6 +573,48 @@ def test_depthwise(k, s, Cc, H, W):
     assert _relerr(out, ref) < 5e-3
 
 
+@pytest.mark.parametrize("k,Cc,cout,B,H,W,res", [
+    (3, 32, 24, 2, 64, 128, False),        # DS block of stage 0: many tiles, one CTA per tile
+    (3, 144, 32, 2, 33, 50, False),        # ragged image, partial last channel chunk (144 = 2.25 x 64)
+    (5, 288, 48, 3, 16, 32, True),         # residual
+    (3, 576, 96, 4, 8, 16, True),          # one tile per frame: chunks split over CTA groups, workspace reduction
+    (5, 816, 136, 4, 8, 16, True),         # cout padded to 144 columns
+    (5, 1392, 232, 5, 4, 8, True),         # tile mostly padding, cout padded to 240
+    (3, 1392, 384, 2, 4, 8, False),        # two MMA column parts (192 + 192), 512 TMEM columns
+])
+def test_dwproject_fused_mbconv_tail(k, Cc, cout, B, H, W, res):
+    """de_dwproject == de_depthwise -> de_gemm (+ residual), the pair it replaces: same depthwise arithmetic (bit for
+    bit up to its bf16 rounding), the projection against torch fp32; twice in a row on one workspace (counters left
+    at zero), and bitwise reproducible."""
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    x = (_rand((B, H, W, Cc), dev, 1.5, seed=120) + 0.2).bfloat16()
+    dw = _rand((k * k, Cc), dev, 0.3, seed=121).bfloat16()
+    db = _rand((Cc,), dev, 0.5, seed=122)
+    pw = _rand((cout, Cc), dev, 0.05, seed=123).bfloat16()
+    pb = _rand((cout,), dev, seed=124)
+    r = _rand((B, H, W, cout), dev, seed=125).bfloat16() if res else None
+    # the unfused pair
+    mid = torch.empty((B, H, W, Cc), dtype=torch.bfloat16, device=dev)
+    ops.depthwise(x, dw, db, mid, k, 1, ops.ACT_RELU6)
+    want = torch.empty((B, H, W, cout), dtype=torch.bfloat16, device=dev)
+    ops.gemm(mid.view(-1, Cc), pw, want.view(-1, cout), bias=pb, add1=r.view(-1, cout) if res else None)
+    ref = F.linear(mid.float(), pw.float(), pb)
+    if res:
+        ref = ref + r.float()
+    ws = torch.zeros(ops.dwproject_ws_bytes(B, H, W, cout), dtype=torch.uint8, device=dev)
+    got = torch.full_like(want, float("nan"))
+    ops.dwproject(x, dw, db, pw, pb, got, k, ws, residual=r)
+    got2 = torch.full_like(want, float("nan"))
+    ops.dwproject(x, dw, db, pw, pb, got2, k, ws, residual=r)
+    torch.cuda.synchronize()
+    assert torch.isfinite(got.float()).all()
+    assert _relerr(got, ref) < 6e-3 and _relerr(want, ref) < 6e-3
+    assert _relerr(got, want) < 6e-3
+    assert torch.equal(got, got2)
+    assert int(ws[:16384].max()) == 0
+
+
 def test_maxpool():
     from depth_estimation_b200 import ops
     dev = _dev()
