@@ -430,11 +430,11 @@ def run_ours(args):
         achieved = g["flops"] / (g["ms"] * 1e-3) / 1e12 if g["ms"] > 0 else 0.0
         peak = float(pk.get("bf16_tflops_sustained", 1400.0))
         traffic, traffic_src = None, None
-        tp = os.path.join(ROOT, "profiles", "r01_gemm_traffic.json")
+        tp = os.path.join(ROOT, "profiles", "r02_gemm_traffic.json")
         if os.path.exists(tp) and (args.model, B, W, H) == ("DPT_Large", 32, 384, 384):
             with open(tp) as f:                     # committed ncu capture of this very workload (not measured live)
                 traffic = json.load(f)["dram_bytes_per_launch"]
-            traffic_src = "profiles/r01_gemm_traffic.json (ncu dram__bytes_read+write, mean over the step's launches)"
+            traffic_src = "profiles/r02_gemm_traffic.json (ncu dram__bytes_read+write, mean over the step's launches)"
         roofline = {"bound": "tensor", "kernel": "deb::gemm_kernel (tcgen05 GEMM / implicit-GEMM conv)",
                     "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
                     "peak_source": pk["_src"] + " bf16_tflops_sustained", "traffic": traffic,

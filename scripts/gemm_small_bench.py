@@ -41,6 +41,8 @@ SHAPES = [
 # 3x3 convolutions of the DPT decoder at 32 frames: (name, B, H, W, C, residuals, relu copy)
 CONVS = [
     ("rcu conv1 96x96 (store epilogue)", 32, 96, 96, 256, 0, False),
+    ("same, forced through the general epilogue", 32, 96, 96, 256, -1, False),
+    ("layer_rn style: raw + relu copy, no residual", 32, 96, 96, 256, 0, True),
     ("rcu conv2 96x96 +x +path, relu copy", 32, 96, 96, 256, 2, True),
     ("rcu conv2 96x96 +x", 32, 96, 96, 256, 1, False),
     ("rcu conv2 48x48 +x +path, relu copy", 32, 48, 48, 256, 2, True),
@@ -75,8 +77,8 @@ def convs(dev):
         orl = torch.empty_like(out) if relu else None
 
         def run():
-            ops.gemm(x, w, out, N=C, conv=(B, H, W, C), bias=b, act=ops.ACT_NONE if nres else ops.ACT_RELU,
-                     add1=r1, ld_add1=C, add2=r2, out_relu=orl, ldo=C)
+            ops.gemm(x, w, out, N=C, conv=(B, H, W, C), bias=b, act=ops.ACT_NONE if nres > 0 else ops.ACT_RELU,
+                     add1=r1, ld_add1=C, add2=r2, out_relu=orl, ldo=C, epilogue=1 if nres < 0 else 0)
         t = time_it(run)
         print(f"| {name} | {t:.1f} | {2.0 * B * H * W * C * 9 * C / t / 1e6:.0f} |", flush=True)
 
