@@ -18,6 +18,9 @@ CASES = [
     ("DPT_Hybrid", 384, 384, "S"),
     ("DPT_Large", 1920, 1080, "S"),            # BASELINE config #5: net 384x672 (1009 tokens), full-res bicubic out
     ("DPT_Hybrid", 640, 480, "U"),
+    ("MiDaS_small", 1000, 600, "S"),           # net 160x256: a 5-row map at the deepest level, ragged depthwise / conv tiles
+    ("DPT_Large", 333, 500, "U"),              # portrait, net 576x384: 36x24 token grid (pos-embed resized to a tall grid)
+    ("DPT_Hybrid", 1000, 600, "S"),            # net 384x640: 24x40 grid through the ResNetV2 stages
 ]
 
 
