@@ -532,6 +532,36 @@ def test_postprocess_vs_torch(h, w, H, W):
     assert _relerr(omap2, ref2) < 1e-5
 
 
+def test_postprocess_random_geometries():
+    """K8 on seeded random geometries - up- and down-scaling, widths that are / are not multiples of 4 and 8, maps wider
+    than one tile, tall and flat aspect ratios - against ATen's bicubic on the CPU; every output view from ONE launch
+    agrees with the fp32 map, and the fp32-only launch (which may take the 256-column tile) equals the multi-output one."""
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    rng = np.random.default_rng(4242)
+    geos = [(64, 96, 320, 480), (128, 256, 720, 1280), (96, 160, 301, 517)]      # fixed: >= 4x (wide tile), ragged output
+    for _ in range(10):
+        h, w = int(rng.integers(24, 200)), int(rng.integers(24, 260))
+        fy, fx = rng.uniform(0.6, 6.0), rng.uniform(0.6, 6.0)
+        geos.append((h, w, max(8, int(h * fy)), max(8, int(w * fx))))
+    for i, (h, w, H, W) in enumerate(geos):
+        pred = _rand((2, h, w), dev, seed=300 + i).abs() * 7 + 0.1
+        ref = F.interpolate(pred.cpu().unsqueeze(1), size=(H, W), mode="bicubic", align_corners=False).squeeze(1).to(dev)
+        vis = torch.empty((2, H, W), dtype=torch.uint8, device=dev)
+        omap, ometric, _ = ops.postprocess(pred, H, W, want_map=True, want_metric=True, out_vis=vis)
+        only, _, _ = ops.postprocess(pred, H, W, want_map=True)
+        torch.cuda.synchronize()
+        assert _relerr(omap, ref) < 1e-5, (h, w, H, W)
+        assert torch.equal(only, omap), (h, w, H, W)
+        assert torch.equal(ometric, (omap * (1.0 / 2.54)).bfloat16()), (h, w, H, W)
+        host = omap.cpu().numpy()
+        with np.errstate(invalid="ignore"):
+            want = host.astype(np.uint8)
+        want *= 5
+        want += 10
+        assert np.array_equal(vis.cpu().numpy(), want), (h, w, H, W)
+
+
 # ------------------------------------------------------------------------------------ direct convs
 def _tf_same_pad(x, k, s, value=0.0):
     ih, iw = x.shape[-2:]
