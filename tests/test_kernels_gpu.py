@@ -270,6 +270,38 @@ def test_conv3x3_implicit_gemm(B, H, W, Cin, Cout):
     assert _relerr(out, ref) < 2e-5, _relerr(out, ref)
 
 
+def test_conv3x3_random_geometries():
+    """Implicit-GEMM 3x3 convolution on seeded random geometries - images narrower than the 8-pixel halo box, prime
+    extents, channel counts that are not multiples of 64 - through both epilogues (fp32 store; bf16 with residual + ReLU
+    copy), against torch fp32.  Exercises the halo mode (bw % 8 == 0 boxes with zero-filled overhang) and its fallback."""
+    from depth_estimation_b200 import ops
+    from depth_estimation_b200.weights import pack_conv3x3
+    dev = _dev()
+    rng = np.random.default_rng(777)
+    geos = [(1, 3, 5, 64, 64), (2, 7, 70, 72, 128), (1, 53, 9, 192, 256), (3, 8, 8, 64, 256)]
+    for _ in range(8):
+        geos.append((int(rng.integers(1, 4)), int(rng.integers(3, 71)), int(rng.integers(3, 71)),
+                     int(rng.choice([64, 72, 128, 136, 192])), int(rng.choice([64, 128, 256]))))
+    for i, (B, H, W, Cin, Cout) in enumerate(geos):
+        x = _rand((B, Cin, H, W), dev, seed=400 + i).bfloat16()
+        wt = _rand((Cout, Cin, 3, 3), dev, 0.05, seed=420 + i).bfloat16()
+        bias = _rand((Cout,), dev, seed=440 + i)
+        x_nhwc = x.permute(0, 2, 3, 1).contiguous()
+        wp = pack_conv3x3(wt)
+        ref = F.conv2d(x.float(), wt.float(), bias, padding=1).permute(0, 2, 3, 1)
+        out = torch.full((B, H, W, Cout), float("nan"), dtype=torch.float32, device=dev)
+        ops.gemm(x_nhwc, wp, out.view(-1, Cout), conv=(B, H, W, Cin), bias=bias, N=Cout)
+        r = _rand((B, H, W, Cout), dev, seed=460 + i).bfloat16()
+        o16 = torch.full((B, H, W, Cout), float("nan"), dtype=torch.bfloat16, device=dev)
+        orl = torch.full_like(o16, float("nan"))
+        ops.gemm(x_nhwc, wp, o16.view(-1, Cout), conv=(B, H, W, Cin), bias=bias, N=Cout, add1=r.view(-1, Cout), out_relu=orl.view(-1, Cout))
+        torch.cuda.synchronize()
+        assert torch.isfinite(out).all() and torch.isfinite(o16.float()).all(), (B, H, W, Cin, Cout)
+        assert _relerr(out, ref) < 2e-5, (B, H, W, Cin, Cout, _relerr(out, ref))
+        assert _relerr(o16, ref + r.float()) < 6e-3, (B, H, W, Cin, Cout)
+        assert torch.equal(orl, F.relu(o16)), (B, H, W, Cin, Cout)
+
+
 def test_conv3x3_rcu_epilogue():
     """RCU tail: conv2(..)+bias + x + path, with raw and relu'd copies stored."""
     from depth_estimation_b200 import ops
