@@ -19,6 +19,20 @@
 
 namespace deb {
 
+template <int V>
+struct IntTag {
+  static constexpr int value = V;
+};
+
+#ifdef GEMM_TRACE
+// developer build only (scripts/gemm_trace.py): clock stamps of one epilogue warp of CTA 0, 16 per column unit
+__device__ long long g_gemm_trace[16384];
+#define GT_STAMP(slot) do { if (trace_on) g_gemm_trace[(trace_n * 16 + (slot)) & 16383] = clock64(); } while (0)
+#define GT_NEXT() do { if (trace_on) ++trace_n; } while (0)
+#else
+#define GT_STAMP(slot) do { } while (0)
+#define GT_NEXT() do { } while (0)
+#endif
 constexpr int BM = 128;
 constexpr int BK = 64;
 constexpr int kEpiWarps = 8;
@@ -417,6 +431,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     int as = 0;
     uint32_t aphase = 0;
     bool pending = false;                                      // this group has a store in flight on sbuf
+#ifdef GEMM_TRACE
+    const bool trace_on = blockIdx.x == 0 && warp == 4 && lane == 0;
+    int trace_n = 0;
+#endif
     int bias_tile = -1;                                        // n_tile whose bias slice s_bias holds
     for (int work = unit; work < num_work; work += num_units) {
       const int tile = work / p.k_splits, split = work - tile * p.k_splits;
@@ -444,8 +462,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         y0 = (t / p.tiles_x) * p.bh;
         x0 = (t % p.tiles_x) * p.bw;
       }
+      GT_STAMP(0);
       mbar_wait(&tfull[as], aphase);
       tc_fence_after();
+      GT_STAMP(1);
       if (new_bias) named_bar_sync(bar_id, 128);               // bias slice visible to the whole group
       const int last_u = grp + ((units - 1 - grp) / 2) * 2;    // last unit this group handles (if any)
       if (grp >= units) {                                      // idle group (narrow tiles): just hand TMEM back
@@ -459,50 +479,69 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll 1
       for (int u = grp; u < units; u += 2) {
         uint32_t ov[32];
+        GT_STAMP(2);
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN + u * ucols;
         const float* bs = s_bias + u * ucols;
+        // The activation is chosen OUTSIDE the column loops (three straight-line variants): with a run-time test - and a
+        // possible call - between the bias loads and their uses, ptxas issued every shared-memory load right before its
+        // consumer, and the 16 loads of a unit ran one latency after the other: 1220 cycles of "math" for 64 columns in
+        // the clock trace (scripts/gemm_trace.py), more than everything else in the unit together.
+        const float act_hi = p.act == DE_ACT_RELU6 ? 6.f : __int_as_float(0x7f800000);
         if (f32out) {
           uint32_t acc[32];
           tmem_ld_32x32(taddr, acc);
           tmem_ld_wait();
+          GT_STAMP(3);
+          auto math = [&](auto tag) {
+            constexpr int A = decltype(tag)::value;              // 0 none, 1 ReLU / ReLU6 (clamp), 2 GELU
 #pragma unroll
-          for (int j4 = 0; j4 < 8; ++j4) {
-            const float4 bb = *reinterpret_cast<const float4*>(bs + j4 * 4);
-            float4 v = make_float4(__uint_as_float(acc[j4 * 4]) + bb.x, __uint_as_float(acc[j4 * 4 + 1]) + bb.y,
-                                   __uint_as_float(acc[j4 * 4 + 2]) + bb.z, __uint_as_float(acc[j4 * 4 + 3]) + bb.w);
-            if (p.act != DE_ACT_NONE) v = act4_fast(v, p.act);
-            ov[j4 * 4] = __float_as_uint(v.x); ov[j4 * 4 + 1] = __float_as_uint(v.y);
-            ov[j4 * 4 + 2] = __float_as_uint(v.z); ov[j4 * 4 + 3] = __float_as_uint(v.w);
-          }
+            for (int j4 = 0; j4 < 8; ++j4) {
+              const float4 bb = *reinterpret_cast<const float4*>(bs + j4 * 4);
+              float v[4] = {__uint_as_float(acc[j4 * 4]) + bb.x, __uint_as_float(acc[j4 * 4 + 1]) + bb.y,
+                            __uint_as_float(acc[j4 * 4 + 2]) + bb.z, __uint_as_float(acc[j4 * 4 + 3]) + bb.w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                if (A == 1) v[e] = fminf(fmaxf(v[e], 0.f), act_hi);
+                if (A == 2) v[e] = gelu_fast(v[e]);
+                ov[j4 * 4 + e] = __float_as_uint(v[e]);
+              }
+            }
+          };
+          if (p.act == DE_ACT_NONE) math(IntTag<0>{});
+          else if (p.act == DE_ACT_GELU) math(IntTag<2>{});
+          else math(IntTag<1>{});
         } else {
           uint32_t acc2[2][32];                              // both halves in flight: one TMEM round trip per unit
           tmem_ld_32x32(taddr, acc2[0]);
           tmem_ld_32x32(taddr + 32, acc2[1]);
           tmem_ld_wait();
+          GT_STAMP(3);
+          auto math = [&](auto tag) {
+            constexpr int A = decltype(tag)::value;
 #pragma unroll
-          for (int hh = 0; hh < 2; ++hh) {
-            const uint32_t* acc = acc2[hh];
-            if (p.act == DE_ACT_GELU) {                        // hot (ViT fc1): GELU inlined, no per-float4 call
+            for (int hh = 0; hh < 2; ++hh) {
+              const uint32_t* acc = acc2[hh];
 #pragma unroll
               for (int j4 = 0; j4 < 8; ++j4) {
                 const float4 bb = *reinterpret_cast<const float4*>(bs + hh * 32 + j4 * 4);
-                const float2 v01 = gelu_fast2(fadd2(make_float2(__uint_as_float(acc[j4 * 4]), __uint_as_float(acc[j4 * 4 + 1])), make_float2(bb.x, bb.y)));
-                const float2 v23 = gelu_fast2(fadd2(make_float2(__uint_as_float(acc[j4 * 4 + 2]), __uint_as_float(acc[j4 * 4 + 3])), make_float2(bb.z, bb.w)));
+                float2 v01 = fadd2(make_float2(__uint_as_float(acc[j4 * 4]), __uint_as_float(acc[j4 * 4 + 1])), make_float2(bb.x, bb.y));
+                float2 v23 = fadd2(make_float2(__uint_as_float(acc[j4 * 4 + 2]), __uint_as_float(acc[j4 * 4 + 3])), make_float2(bb.z, bb.w));
+                if (A == 1) {
+                  v01 = make_float2(fminf(fmaxf(v01.x, 0.f), act_hi), fminf(fmaxf(v01.y, 0.f), act_hi));
+                  v23 = make_float2(fminf(fmaxf(v23.x, 0.f), act_hi), fminf(fmaxf(v23.y, 0.f), act_hi));
+                }
+                if (A == 2) {                                    // hot (ViT fc1): packed GELU
+                  v01 = gelu_fast2(v01);
+                  v23 = gelu_fast2(v23);
+                }
                 ov[hh * 16 + j4 * 2] = pack_bf16(v01.x, v01.y);
                 ov[hh * 16 + j4 * 2 + 1] = pack_bf16(v23.x, v23.y);
               }
-            } else {
-#pragma unroll
-              for (int j4 = 0; j4 < 8; ++j4) {
-                const float4 bb = *reinterpret_cast<const float4*>(bs + hh * 32 + j4 * 4);
-                float4 v = make_float4(__uint_as_float(acc[j4 * 4]) + bb.x, __uint_as_float(acc[j4 * 4 + 1]) + bb.y,
-                                       __uint_as_float(acc[j4 * 4 + 2]) + bb.z, __uint_as_float(acc[j4 * 4 + 3]) + bb.w);
-                if (p.act != DE_ACT_NONE) v = act4_fast(v, p.act);
-                ov[hh * 16 + j4 * 2] = pack_bf16(v.x, v.y);
-                ov[hh * 16 + j4 * 2 + 1] = pack_bf16(v.z, v.w);
-              }
             }
-          }
+          };
+          if (p.act == DE_ACT_NONE) math(IntTag<0>{});
+          else if (p.act == DE_ACT_GELU) math(IntTag<2>{});
+          else math(IntTag<1>{});
         }
         if (u == last_u) {                                     // accumulator drained: release it early
           tc_fence_before();
@@ -513,17 +552,23 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           }
         }
         // the store that last used this buffer (STORE_BUFS_PER_GROUP units ago) has finished reading it
+        GT_STAMP(4);
         if (pending && gtid == 0) tma_store_wait_read<STORE_BUFS_PER_GROUP - 1>();
+        GT_STAMP(5);
         uint8_t* const sbuf = sbuf0 + sb * kStoreBufBytes;
         sb = sb + 1 == STORE_BUFS_PER_GROUP ? 0 : sb + 1;
         named_bar_sync(bar_id, 128);
+        GT_STAMP(6);
         uint8_t* rowp = sbuf + gtid * 128;
 #pragma unroll
         for (int j = 0; j < 8; ++j)
           *reinterpret_cast<uint4*>(rowp + ((j ^ (gtid & 7)) << 4)) =
               make_uint4(ov[j * 4], ov[j * 4 + 1], ov[j * 4 + 2], ov[j * 4 + 3]);
+        GT_STAMP(7);
         fence_proxy_async_smem();
+        GT_STAMP(8);
         named_bar_sync(bar_id, 128);
+        GT_STAMP(9);
         if (gtid == 0) {
           if (m_tile < p.m_tiles) {
             const int col0 = n_tile * BN + u * ucols;
@@ -536,6 +581,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           }
           tma_store_commit();            // one (possibly empty) group per unit: wait_read<N> counts units, not stores
         }
+        GT_STAMP(10);
+        GT_NEXT();
         pending = true;
       }
       if (++as == 2) {
@@ -1003,6 +1050,11 @@ __global__ void __launch_bounds__(256) splitk_finalize_kernel(const FinalizePara
 
 }  // namespace deb
 
+#ifdef GEMM_TRACE
+extern "C" int de_gemm_trace_read(long long* host, int n) {
+  return cudaMemcpyFromSymbol(host, deb::g_gemm_trace, sizeof(long long) * (size_t)n) == cudaSuccess ? 0 : -2;
+}
+#endif
 extern "C" int de_gemm(const DeGemm* g, void* stream) {
   deb::ProfScope prof_("gemm", g ? (g->a_mode == 1 ? 2.0 * g->B * g->H * g->W * (double)g->N * 9 * g->Cin : 2.0 * g->M * (double)g->N * g->K) : 0.0, stream, g ? (g->a_mode == 1 ? (int64_t)g->B * g->H * g->W : g->M) : 0, g ? g->N : 0, g ? (g->a_mode == 1 ? 9 * g->Cin : g->K) : 0, g ? g->a_mode * 100 + g->act * 10 + (g->accumulate ? 1 : 0) : 0);
   using namespace deb;
