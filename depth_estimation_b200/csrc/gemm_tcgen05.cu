@@ -736,28 +736,42 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f), hw4 = bias4;
         if (p.bias) bias4 = *reinterpret_cast<const float4*>(s_bias + (c - c_begin) * 32 + cc);
         if (p.head_w && col_ok) hw4 = __ldg(reinterpret_cast<const float4*>(p.head_w + n0 + cc));
-        // compute phase: every row's value into registers (consumes this chunk's residual operands) ...
+        // compute phase: every row's value into registers (consumes this chunk's residual operands) ...  The activation is
+        // chosen outside the row loop (straight-line variants, as in the store epilogue): an out-of-line call between the
+        // staging loads and their uses serialises them.
         float4 v_[8];
+        const float act_hi = p.act == DE_ACT_RELU6 ? 6.f : __int_as_float(0x7f800000);
+        auto compute = [&](auto tag) {
+          constexpr int A = decltype(tag)::value;                // 0 none, 1 ReLU / ReLU6 (clamp), 2 GELU
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int row = i * 4 + sub;
-          float4 v = *reinterpret_cast<const float4*>(stg + row * kStgStride + cc);
-          v.x += bias4.x; v.y += bias4.y; v.z += bias4.z; v.w += bias4.w;
-          if (has_res) {
-            const uint4 w1 = r1_[i], w2 = r2_[i];
-            const float4 a1 = a1_f32 ? make_float4(__uint_as_float(w1.x), __uint_as_float(w1.y), __uint_as_float(w1.z), __uint_as_float(w1.w))
-                                     : make_float4(bf16_lo(w1.x), bf16_hi(w1.x), bf16_lo(w1.y), bf16_hi(w1.y));
-            const float4 a2 = a2_f32 ? make_float4(__uint_as_float(w2.x), __uint_as_float(w2.y), __uint_as_float(w2.z), __uint_as_float(w2.w))
-                                     : make_float4(bf16_lo(w2.x), bf16_hi(w2.x), bf16_lo(w2.y), bf16_hi(w2.y));
-            if (p.add1_pre) { v.x += a1.x; v.y += a1.y; v.z += a1.z; v.w += a1.w; }
-            if (p.act != DE_ACT_NONE) v = apply_act4(v, p.act);
-            if (!p.add1_pre) { v.x += a1.x; v.y += a1.y; v.z += a1.z; v.w += a1.w; }
-            v.x += a2.x; v.y += a2.y; v.z += a2.z; v.w += a2.w;
-          } else if (p.act != DE_ACT_NONE) {
-            v = apply_act4(v, p.act);
+          for (int i = 0; i < 8; ++i) {
+            const int row = i * 4 + sub;
+            float4 v = *reinterpret_cast<const float4*>(stg + row * kStgStride + cc);
+            v.x += bias4.x; v.y += bias4.y; v.z += bias4.z; v.w += bias4.w;
+            float4 a1 = make_float4(0.f, 0.f, 0.f, 0.f), a2 = a1;
+            if (has_res) {
+              const uint4 w1 = r1_[i], w2 = r2_[i];
+              a1 = a1_f32 ? make_float4(__uint_as_float(w1.x), __uint_as_float(w1.y), __uint_as_float(w1.z), __uint_as_float(w1.w))
+                          : make_float4(bf16_lo(w1.x), bf16_hi(w1.x), bf16_lo(w1.y), bf16_hi(w1.y));
+              a2 = a2_f32 ? make_float4(__uint_as_float(w2.x), __uint_as_float(w2.y), __uint_as_float(w2.z), __uint_as_float(w2.w))
+                          : make_float4(bf16_lo(w2.x), bf16_hi(w2.x), bf16_lo(w2.y), bf16_hi(w2.y));
+              if (p.add1_pre) { v.x += a1.x; v.y += a1.y; v.z += a1.z; v.w += a1.w; }
+            }
+            if (A == 1) {
+              v.x = fminf(fmaxf(v.x, 0.f), act_hi); v.y = fminf(fmaxf(v.y, 0.f), act_hi);
+              v.z = fminf(fmaxf(v.z, 0.f), act_hi); v.w = fminf(fmaxf(v.w, 0.f), act_hi);
+            }
+            if (A == 2) { v.x = gelu_fast(v.x); v.y = gelu_fast(v.y); v.z = gelu_fast(v.z); v.w = gelu_fast(v.w); }
+            if (has_res) {
+              if (!p.add1_pre) { v.x += a1.x; v.y += a1.y; v.z += a1.z; v.w += a1.w; }
+              v.x += a2.x; v.y += a2.y; v.z += a2.z; v.w += a2.w;
+            }
+            v_[i] = v;
           }
-          v_[i] = v;
-        }
+        };
+        if (p.act == DE_ACT_NONE) compute(IntTag<0>{});
+        else if (p.act == DE_ACT_GELU) compute(IntTag<2>{});
+        else compute(IntTag<1>{});
         // ... then the NEXT chunk's operand loads go out, and only then this chunk's stores
         if (has_res && c + 1 < c_end) fetch_res(c + 1);
 #pragma unroll

@@ -32,6 +32,7 @@ print(f"M={M} N={N} K={K} out={'f32' if f32 else 'bf16'} acc={acc}: {len(t)} uni
 names = ["tile top->tfull", "", "(bias bar) ->unit", "tmem_ld", "math+release", "wait_read", "bar D", "STS", "fence", "bar F", "TMA issue"]
 # per-unit deltas: 2->3 tmem, 3->4 math, 4->5 wait_read, 5->6 bar, 6->7 sts, 7->8 fence, 8->9 bar, 9->10 issue; unit period = stamp2[i+1]-stamp2[i]
 d = {}
+d["wait for the accumulator (tfull)"] = t[:, 1] - t[:, 0]
 d["tmem_ld+wait"] = t[:, 3] - t[:, 2]
 d["math (+acc release)"] = t[:, 4] - t[:, 3]
 d["wait_read (prev store)"] = t[:, 5] - t[:, 4]
@@ -43,6 +44,6 @@ d["TMA store issue+commit"] = t[:, 10] - t[:, 9]
 period = t[1:, 2] - t[:-1, 2]
 for k, v in d.items():
     v = v[2:]
-    print(f"  {k:26s} median {int(np.median(v)):6d}  p90 {int(np.percentile(v, 90)):6d} cycles")
+    print(f"  {k:34s} median {int(np.median(v)):6d}  p90 {int(np.percentile(v, 90)):6d} cycles")
 print(f"  {'unit period (start->start)':26s} median {int(np.median(period[2:])):6d}  p90 {int(np.percentile(period[2:], 90)):6d} cycles")
 print(f"  {'sum of the parts':26s} median {int(np.median(sum(v for v in d.values())[2:])):6d}")
