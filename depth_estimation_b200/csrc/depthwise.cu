@@ -5,13 +5,17 @@
 // A bandwidth kernel staged through shared memory (north_star (2)): persistent CTAs walk (channel chunk, image, tile)
 // work items; the input window of a tile - 8x16 outputs x 64 channels plus the k-1 halo - arrives as ONE 4-D TMA box
 // (the tensor map's out-of-bounds zero fill IS the TF-same padding, negative start coordinates included), double
-// buffered on two mbarriers so the next window streams in while the current one is convolved.  Each thread owns 8
+// buffered on two mbarriers so the next window streams in while the current one is convolved.  Low-resolution images
+// (4x8 / 8x8 / 4x16 pixels per frame) use tile shapes that pack four / two frames into one work item, so the last
+// blocks of the network do not convolve 75 % padding.  Each thread owns 8
 // channels (one 16-byte shared-memory vector per pixel; a quarter-warp reads 128 contiguous bytes - conflict free) and a
 // strip of 4 adjacent outputs, so a window row is read and converted once per ky instead of once per tap; the filter
 // taps live in shared memory as fp32 pairs and every MAC is a packed FFMA2 (two channels per issue slot).  The first
 // version of this operator (one thread per output, k*k global 16-byte loads of x and w each) spent ~80 instructions
 // per output element; this one ~10 (k3) / ~25 (k5).
 // Accumulation: fp32, bias first, taps in (ky, kx) order - the same order as the direct kernel it replaces.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "depth_b200.h"
 #include "host_util.h"
@@ -19,16 +23,21 @@
 namespace deb {
 
 constexpr int kDwCC = 64;                     // channels per work item (128 bytes per pixel)
-constexpr int kDwTH = 8, kDwTW = 16;          // output tile
+constexpr int kDwPix = 128;                   // outputs per work item: TH x TW pixels of NB = 128 / (TH * TW) frames
 constexpr int kDwP = 4;                       // outputs per thread along x
 constexpr int kDwThreads = 256;               // 8 channel groups x 32 strips
 
-template <int K, int S>
+// Tile shapes: 8 x 16 pixels of one frame, or - for the low-resolution blocks, where an 8 x 16 tile would be up to 75 %
+// padding (4 x 8 pixels per frame at the end of the 128 x 256 network) - 8 x 8 / 4 x 16 pixels of two frames or 4 x 8
+// pixels of four frames: the TMA box then spans NB frames, each with its own zero-filled halo.
+template <int K, int S, int TH, int TW>
 struct DwCfg {
-  static constexpr int WH = (kDwTH - 1) * S + K;          // staged window, rows
-  static constexpr int WW = (kDwTW - 1) * S + K;          // staged window, columns
+  static constexpr int NB = kDwPix / (TH * TW);           // frames per work item
+  static constexpr int SPR = TW / kDwP;                   // strips per tile row
+  static constexpr int WH = (TH - 1) * S + K;             // staged window of one frame, rows
+  static constexpr int WW = (TW - 1) * S + K;             // staged window, columns
   static constexpr int NC = (kDwP - 1) * S + K;           // window columns one strip touches
-  static constexpr int kStageBytes = WH * WW * kDwCC * 2;
+  static constexpr int kStageBytes = NB * WH * WW * kDwCC * 2;
   static constexpr int kWBytes = K * K * kDwCC * 4;       // fp32 taps of one channel chunk
   static constexpr int kSmem = 2 * kStageBytes + kWBytes + kDwCC * 4 + 128;
 };
@@ -38,12 +47,12 @@ struct DwParams {
   const float* bias;        // [C]
   __nv_bfloat16* out;       // [B,Ho,Wo,C]
   int B, C, Ho, Wo, pad_y, pad_x, act;
-  int tiles_x, tiles_y, chunks, ntiles;
+  int tiles_x, tiles_y, bgroups, chunks, ntiles;
 };
 
-template <int K, int S>
+template <int K, int S, int TH, int TW>
 __global__ void __launch_bounds__(kDwThreads, S == 1 ? 3 : 1) depthwise_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwParams p) {
-  using Cfg = DwCfg<K, S>;
+  using Cfg = DwCfg<K, S, TH, TW>;
   extern __shared__ uint8_t dw_smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(dw_smem_raw) + 127) & ~static_cast<uintptr_t>(127));
   auto stage_ptr = [&](int s) { return smem + s * Cfg::kStageBytes; };
@@ -53,7 +62,7 @@ __global__ void __launch_bounds__(kDwThreads, S == 1 ? 3 : 1) depthwise_tma_kern
 
   const int tid = threadIdx.x;
   const int cg = tid & 7, strip = tid >> 3;
-  const int sy = strip >> 2, sx = (strip & 3) * kDwP;
+  const int sx = (strip % Cfg::SPR) * kDwP, sy = (strip / Cfg::SPR) % TH, nb = strip / (Cfg::SPR * TH);
   if (tid == 0) {
     tma_prefetch_desc(&tmX);
     mbar_init(&full[0], 1);
@@ -61,16 +70,16 @@ __global__ void __launch_bounds__(kDwThreads, S == 1 ? 3 : 1) depthwise_tma_kern
     mbar_fence_init();
   }
   __syncthreads();
-  const int per_chunk = p.B * p.tiles_y * p.tiles_x;
+  const int per_chunk = p.bgroups * p.tiles_y * p.tiles_x;
 
   auto issue = [&](int t, int s) {            // one thread: window of work item t -> stage s
     const int chunk = t / per_chunk;
     int r = t - chunk * per_chunk;
-    const int b = r / (p.tiles_y * p.tiles_x);
-    r -= b * (p.tiles_y * p.tiles_x);
+    const int bg = r / (p.tiles_y * p.tiles_x);
+    r -= bg * (p.tiles_y * p.tiles_x);
     const int ty = r / p.tiles_x, tx = r - ty * p.tiles_x;
-    mbar_arrive_expect_tx(&full[s], Cfg::kStageBytes);
-    tma_load_4d(stage_ptr(s), &tmX, &full[s], chunk * kDwCC, tx * kDwTW * S - p.pad_x, ty * kDwTH * S - p.pad_y, b);
+    mbar_arrive_expect_tx(&full[s], Cfg::kStageBytes);   // frames past B are zero-filled and still count
+    tma_load_4d(stage_ptr(s), &tmX, &full[s], chunk * kDwCC, tx * TW * S - p.pad_x, ty * TH * S - p.pad_y, bg * Cfg::NB);
   };
 
   pdl_wait();                                 // x is the previous kernel's output
@@ -85,9 +94,10 @@ __global__ void __launch_bounds__(kDwThreads, S == 1 ? 3 : 1) depthwise_tma_kern
     if (tid == 0 && t + 1 < t_end) issue(t + 1, s ^ 1);   // stage s^1 was drained at the end of n-1
     const int chunk = t / per_chunk;
     int r = t - chunk * per_chunk;
-    const int b = r / (p.tiles_y * p.tiles_x);
-    r -= b * (p.tiles_y * p.tiles_x);
+    const int bg = r / (p.tiles_y * p.tiles_x);
+    r -= bg * (p.tiles_y * p.tiles_x);
     const int ty = r / p.tiles_x, tx = r - ty * p.tiles_x;
+    const int b = bg * Cfg::NB + nb;
     const int c0 = chunk * kDwCC;
     if (chunk != cur_chunk) {                 // taps + bias of this channel chunk -> fp32 in shared memory
       cur_chunk = chunk;
@@ -120,7 +130,7 @@ __global__ void __launch_bounds__(kDwThreads, S == 1 ? 3 : 1) depthwise_tma_kern
     const uint4* win = reinterpret_cast<const uint4*>(stage_ptr(s));
 #pragma unroll
     for (int ky = 0; ky < K; ++ky) {
-      const uint4* rowp = win + ((sy * S + ky) * Cfg::WW + sx * S) * 8 + cg;
+      const uint4* rowp = win + (((nb * Cfg::WH) + sy * S + ky) * Cfg::WW + sx * S) * 8 + cg;
       float2 in[Cfg::NC][4];
 #pragma unroll
       for (int c = 0; c < Cfg::NC; ++c) {
@@ -138,8 +148,8 @@ __global__ void __launch_bounds__(kDwThreads, S == 1 ? 3 : 1) depthwise_tma_kern
           for (int j = 0; j < 4; ++j) acc[q][j] = ffma2(in[q * S + kx][j], wv[j], acc[q][j]);
       }
     }
-    const int oy = ty * kDwTH + sy, ox0 = tx * kDwTW + sx, c = c0 + cg * 8;
-    if (oy < p.Ho && c < p.C) {
+    const int oy = ty * TH + sy, ox0 = tx * TW + sx, c = c0 + cg * 8;
+    if (oy < p.Ho && c < p.C && b < p.B) {
       __nv_bfloat16* op = p.out + (((long long)b * p.Ho + oy) * p.Wo + ox0) * p.C + c;
 #pragma unroll
       for (int q = 0; q < kDwP; ++q) {
@@ -167,36 +177,42 @@ static int dw_same_pad_before(int in, int k, int s) {
   return total / 2;
 }
 
-template <int K, int S>
+template <int K, int S, int TH, int TW>
 static int launch_depthwise(const void* x, const DwParams& p0, int H, int W, cudaStream_t st) {
-  using Cfg = DwCfg<K, S>;
+  using Cfg = DwCfg<K, S, TH, TW>;
   DwParams p = p0;
+  p.tiles_x = (p.Wo + TW - 1) / TW;
+  p.tiles_y = (p.Ho + TH - 1) / TH;
+  p.bgroups = (p.B + Cfg::NB - 1) / Cfg::NB;
+  const long long nt = (long long)p.chunks * p.bgroups * p.tiles_y * p.tiles_x;
+  if (nt > 0x7fffffffLL) return fail(DE_ERR_UNSUPPORTED, "de_depthwise: too many tiles");
+  p.ntiles = (int)nt;
   auto fn = get_tensor_map_encoder();
   if (!fn) return DE_ERR_CUDA;
   CUtensorMap tm;
   const uint64_t dims[4] = {(uint64_t)p.C, (uint64_t)W, (uint64_t)H, (uint64_t)p.B};
   const uint64_t strides[3] = {(uint64_t)p.C * 2, (uint64_t)W * p.C * 2, (uint64_t)H * W * p.C * 2};
-  const uint32_t box[4] = {kDwCC, (uint32_t)Cfg::WW, (uint32_t)Cfg::WH, 1};
+  const uint32_t box[4] = {kDwCC, (uint32_t)Cfg::WW, (uint32_t)Cfg::WH, (uint32_t)Cfg::NB};
   const uint32_t estr[4] = {1, 1, 1, 1};
   CUresult r = fn(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(x), dims, strides, box, estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(DE_ERR_CUDA, "de_depthwise: cuTensorMapEncodeTiled failed (%d)", (int)r);
   static SmemOptIn optin;
-  cudaError_t e = ensure_smem(optin, depthwise_tma_kernel<K, S>, Cfg::kSmem);
+  cudaError_t e = ensure_smem(optin, depthwise_tma_kernel<K, S, TH, TW>, Cfg::kSmem);
   if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(depthwise)");
   static int occ_cache[32] = {0};
   int dev = 0;
   cudaGetDevice(&dev);
   int occ = (dev >= 0 && dev < 32) ? occ_cache[dev] : 0;
   if (occ == 0) {
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, depthwise_tma_kernel<K, S>, kDwThreads, Cfg::kSmem);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, depthwise_tma_kernel<K, S, TH, TW>, kDwThreads, Cfg::kSmem);
     if (e != cudaSuccess || occ < 1) occ = 1;
     if (dev >= 0 && dev < 32) occ_cache[dev] = occ;
   }
   int grid = num_sms() * occ;
   if (p.ntiles < grid) grid = p.ntiles;
-  e = launch_pdl(8, depthwise_tma_kernel<K, S>, dim3(grid), dim3(kDwThreads), (size_t)Cfg::kSmem, st, tm, p);
+  e = launch_pdl(8, depthwise_tma_kernel<K, S, TH, TW>, dim3(grid), dim3(kDwThreads), (size_t)Cfg::kSmem, st, tm, p);
   count_launch();
   if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(depthwise_tma_kernel)");
   return cuda_check_launch("depthwise_tma_kernel");
@@ -224,15 +240,31 @@ extern "C" int de_depthwise(const void* x, const void* w_tapmajor, const float* 
   p.pad_y = dw_same_pad_before(H, k, stride);
   p.pad_x = dw_same_pad_before(W, k, stride);
   p.act = act;
-  p.tiles_x = (p.Wo + kDwTW - 1) / kDwTW;
-  p.tiles_y = (p.Ho + kDwTH - 1) / kDwTH;
   p.chunks = (C + kDwCC - 1) / kDwCC;
-  const long long nt = (long long)p.chunks * B * p.tiles_y * p.tiles_x;
-  if (nt > 0x7fffffffLL) return fail(DE_ERR_UNSUPPORTED, "de_depthwise: too many tiles");
-  p.ntiles = (int)nt;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  if (k == 3 && stride == 1) return launch_depthwise<3, 1>(x, p, H, W, st);
-  if (k == 3 && stride == 2) return launch_depthwise<3, 2>(x, p, H, W, st);
-  if (k == 5 && stride == 1) return launch_depthwise<5, 1>(x, p, H, W, st);
-  return launch_depthwise<5, 2>(x, p, H, W, st);
+  if (stride == 2) {                                          // stride-2 windows are too large to pack frames
+    if (k == 3) return launch_depthwise<3, 2, 8, 16>(x, p, H, W, st);
+    return launch_depthwise<5, 2, 8, 16>(x, p, H, W, st);
+  }
+  // stride 1: the tile shape with the least padding; several frames per work item only when the batch has them
+  static const int force = getenv("DEB_DW_TILE") ? atoi(getenv("DEB_DW_TILE")) : 0;   // developer A/B: 816 | 808 | 416 | 408
+  int th = 8, tw = 16;
+  if (p.Wo <= 8) tw = 8;
+  if ((p.Ho + 3) / 4 * 4 < (p.Ho + 7) / 8 * 8) th = 4;
+  if (kDwPix / (th * tw) > B) {                               // not enough frames to fill the packed shape
+    if (B >= 2 && th * tw == 32) { if (p.Wo > 8) tw = 16; else th = 8; }
+    else { th = 8; tw = 16; }
+  }
+  if (force) { th = force / 100; tw = force % 100; }
+#define DW_LAUNCH(KK)                                                                         \
+  do {                                                                                        \
+    if (th == 8 && tw == 16) return launch_depthwise<KK, 1, 8, 16>(x, p, H, W, st);           \
+    if (th == 8 && tw == 8) return launch_depthwise<KK, 1, 8, 8>(x, p, H, W, st);             \
+    if (th == 4 && tw == 16) return launch_depthwise<KK, 1, 4, 16>(x, p, H, W, st);           \
+    if (th == 4 && tw == 8) return launch_depthwise<KK, 1, 4, 8>(x, p, H, W, st);             \
+  } while (0)
+  if (k == 3) DW_LAUNCH(3);
+  else DW_LAUNCH(5);
+#undef DW_LAUNCH
+  return fail(DE_ERR_INVALID, "de_depthwise: DEB_DW_TILE=%d", force);
 }

@@ -14,6 +14,7 @@
 // Roles: warp 0 TMA producer, warp 1 MMA issuer, warp 2 TMEM allocator, warps 4..7 epilogue.  Persistent CTAs, one
 // per SM, tiles handed out round-robin (x fastest, so concurrently running CTAs share halo rows in L2).
 #include <cuda.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "depth_b200.h"
@@ -501,6 +502,312 @@ head_up_conv_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_consta
   }
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Second formulation of the fused upsample + head tail: the three HORIZONTAL taps ride in the N dimension.
+// With N = 32 every 128x32x16 MMA reads 4 KB of A and 1 KB of B from shared memory for 8 clocks of math: shared-memory
+// bandwidth (128 B/clk) bounds the kernel above at ~17 % tensor-pipe utilisation, and three dx copies of every halo
+// tile have to be written first.  Here the B operand of a (dy, 64-channel block) step is [dx0 | dx1 | dx2] x 32 filters
+// = 96 columns, so ONE copy of the halo tile is read once per dy for all three dx taps (7 KB per MMA for 3x the math):
+//     P_dx[r, j] = sum_dy sum_c  halo[r + dy, j, c] * w[dy, dx, c, :]             (TMEM, 96 fp32 columns per pixel)
+//     out[r, j]  = P_0[r, j - 1] + P_1[r, j] + P_2[r, j + 1]                        (epilogue: two warp shuffles per value)
+// The accumulator rows are 4 image rows x 32 columns (a warp = one image row, lane = column), columns 0 and 31 are the
+// halo columns: a tile yields 4 x 30 outputs.  Shared-memory traffic per output drops from ~4.1 KB to ~2.3 KB.
+constexpr int kH3TR = 4, kH3TC = 32, kH3OutC = kH3TC - 2;
+constexpr int kH3HaloRows = kH3TR + 2;
+constexpr int kH3UnitBytes = kH3HaloRows * kH3TC * 128;    // 24576: (6 x 32) pixels x 64 channels bf16, one copy
+constexpr int kH3Units = 4;
+constexpr int kH3N = 3 * kHcN;                              // 96 accumulator columns
+constexpr int kH3Acc = 4;                                   // TMEM stages (4 x 96 = 384 of 512 allocated columns)
+constexpr int kH3SrcRows = 5, kH3SrcCols = 18;              // source window of the 6 x 32 halo (x2: <= 3+2 rows, 16+2 columns)
+constexpr int kH3SrcBytes = kH3SrcRows * kH3SrcCols * 128;  // 11520
+constexpr int kH3SrcSlotBytes = 12288;
+constexpr int kH3SrcSlots = 4;
+#ifndef H3_ROW_GROUPS
+#define H3_ROW_GROUPS 1                                     // producer threads per (column, channel group): 1 x 6 or 2 x 3 halo rows
+#endif
+constexpr int kH3RowGroups = H3_ROW_GROUPS;
+constexpr int kH3ProdWarps = 8 * kH3RowGroups;
+constexpr int kH3Threads = 256 + 32 * kH3ProdWarps;
+
+DEV void tmem_ld_32x16(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+
+__global__ void __launch_bounds__(kH3Threads, 1)
+head_up3_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX, const HeadUpParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+  const int w_chunks = 9 * p.cin_blocks;
+  uint8_t* sW = smem;                                        // chunk ((dy * cin_blocks + cb) * 3 + dx): 32 filters x 64 K
+  uint8_t* sA = smem + w_chunks * kHcWChunk;                 // kH3Units halo tiles
+  uint8_t* sX = sA + kH3Units * kH3UnitBytes;                // source windows
+  uint8_t* post = sX + kH3SrcSlots * kH3SrcSlotBytes;
+  uint64_t* full = reinterpret_cast<uint64_t*>(post);
+  uint64_t* empty = full + kH3Units;
+  uint64_t* tfull = empty + kH3Units;
+  uint64_t* tempty = tfull + kH3Acc;
+  uint64_t* wfull = tempty + kH3Acc;
+  uint64_t* xfull = wfull + 1;
+  uint64_t* xempty = xfull + kH3SrcSlots;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(xempty + kH3SrcSlots);
+  float* s_bias = reinterpret_cast<float*>(post + 256);
+  float* s_hw = s_bias + kHcN;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmW);
+    tma_prefetch_desc(&tmX);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < kH3Units; ++i) {
+      mbar_init(&full[i], kH3ProdWarps);
+      mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < kH3SrcSlots; ++i) {
+      mbar_init(&xfull[i], 1);
+      mbar_init(&xempty[i], kH3ProdWarps);
+    }
+    for (int i = 0; i < kH3Acc; ++i) {
+      mbar_init(&tfull[i], 1);
+      mbar_init(&tempty[i], 4);
+    }
+    mbar_init(wfull, 1);
+    mbar_fence_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, 512);
+    tmem_relinquish();
+  }
+  if (warp == 3) {
+    s_bias[lane] = p.bias ? __ldg(p.bias + lane) : 0.f;
+    s_hw[lane] = __ldg(p.head_w + lane);
+  }
+  pdl_launch();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int per_img = p.tiles_x * p.tiles_y;
+  const int units_per_tile = p.cin_blocks;
+  pdl_wait();
+
+  if (warp == 0) {
+    if (lane == 0) {                                         // filter bank once (dx chunks of a (dy, cb) step adjacent), then the source windows
+      mbar_arrive_expect_tx(wfull, w_chunks * kHcWChunk);
+      for (int dy = 0; dy < 3; ++dy)
+        for (int cb = 0; cb < p.cin_blocks; ++cb)
+          for (int dx = 0; dx < 3; ++dx)
+            tma_load_2d(sW + ((dy * p.cin_blocks + cb) * 3 + dx) * kHcWChunk, &tmW, wfull, ((dy * 3 + dx) * p.cin_blocks + cb) * 64, 0);
+      int xs = 0;
+      uint32_t xphase = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        const int b = tile / per_img, t = tile % per_img;
+        const int ysb = hu_src_base((t / p.tiles_x) * kH3TR - 1, p.rh, p.align_corners);
+        const int xsb = hu_src_base((t % p.tiles_x) * kH3OutC - 1, p.rw, p.align_corners);
+        for (int cb = 0; cb < units_per_tile; ++cb) {
+          mbar_wait(&xempty[xs], xphase ^ 1);
+          mbar_arrive_expect_tx(&xfull[xs], kH3SrcBytes);
+          tma_load_4d(sX + xs * kH3SrcSlotBytes, &tmX, &xfull[xs], cb * 64, xsb, ysb, b);
+          if (++xs == kH3SrcSlots) {
+            xs = 0;
+            xphase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer: 3 dy x 4 k-steps of 128 x 96 x 16 per unit
+    constexpr uint32_t idesc = make_idesc_bf16(128, kH3N);
+    mbar_wait(wfull, 0);
+    tc_fence_after();
+    int u = 0;
+    uint32_t phase = 0;
+    int as = 0;
+    uint32_t aphase = 0;
+    const uint32_t w_base = smem_u32(sW);
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      mbar_wait(&tempty[as], aphase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + as * kH3N;
+      for (int cb = 0; cb < units_per_tile; ++cb) {
+        mbar_wait(&full[u], phase);
+        tc_fence_after();
+        const uint64_t adesc = make_sw128_kmajor_desc(smem_u32(sA + u * kH3UnitBytes));
+        if (elect_one()) {
+#pragma unroll
+          for (int dy = 0; dy < 3; ++dy) {
+            const uint64_t bdesc = make_sw128_kmajor_desc(w_base + ((dy * p.cin_blocks + cb) * 3) * kHcWChunk);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              umma_bf16(d_tmem, adesc + dy * ((kH3TC * 128) >> 4) + 2 * k, bdesc + 2 * k, idesc, (cb | dy | k) != 0);
+          }
+          umma_commit(&empty[u]);
+          if (cb == units_per_tile - 1) umma_commit(&tfull[as]);
+        }
+        __syncwarp();
+        if (++u == kH3Units) {
+          u = 0;
+          phase ^= 1;
+        }
+      }
+      if (++as == kH3Acc) {
+        as = 0;
+        aphase ^= 1;
+      }
+    }
+  } else if (warp >= 4 && warp < 8) {
+    // ------------------------------------------------------------------ epilogue: warp = image row of the tile, lane = column
+    const int q = warp & 3;
+    int as = 0;
+    uint32_t aphase = 0;
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      const int b = tile / per_img, t = tile % per_img;
+      const int y = (t / p.tiles_x) * kH3TR + q, x = (t % p.tiles_x) * kH3OutC - 1 + lane;
+      mbar_wait(&tfull[as], aphase);
+      tc_fence_after();
+      const uint32_t tacc = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * kH3N;
+      float s0 = p.head_b, s1 = 0.f;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        uint32_t a0[16], a1[16], a2[16];
+        tmem_ld_32x16(tacc + h * 16, a0);
+        tmem_ld_32x16(tacc + kHcN + h * 16, a1);
+        tmem_ld_32x16(tacc + 2 * kHcN + h * 16, a2);
+        tmem_ld_wait();
+        if (h == 1) {                                        // the accumulator stage is in registers
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tempty[as]);
+        }
+#pragma unroll
+        for (int n = 0; n < 16; n += 2) {
+          const float l0 = __shfl_up_sync(0xffffffffu, __uint_as_float(a0[n]), 1);
+          const float l1 = __shfl_up_sync(0xffffffffu, __uint_as_float(a0[n + 1]), 1);
+          const float r0 = __shfl_down_sync(0xffffffffu, __uint_as_float(a2[n]), 1);
+          const float r1 = __shfl_down_sync(0xffffffffu, __uint_as_float(a2[n + 1]), 1);
+          const float v0 = (l0 + __uint_as_float(a1[n])) + r0;
+          const float v1 = (l1 + __uint_as_float(a1[n + 1])) + r1;
+          s0 = fmaf(fmaxf(v0 + s_bias[h * 16 + n], 0.f), s_hw[h * 16 + n], s0);
+          s1 = fmaf(fmaxf(v1 + s_bias[h * 16 + n + 1], 0.f), s_hw[h * 16 + n + 1], s1);
+        }
+      }
+      if (lane >= 1 && lane <= kH3OutC && y < p.H && x < p.W) p.out[((long long)b * p.H + y) * p.W + x] = fmaxf(s0 + s1, 0.f);
+      if (++as == kH3Acc) {
+        as = 0;
+        aphase ^= 1;
+      }
+    }
+  } else if (warp >= 8) {
+    // ------------------------------------------------------------------ producers: interpolate the halo tile once, swizzled K-major
+    // Thread = (halo column j of 32, 8-channel group q [, row group]); a warp covers 4 columns x 8 groups = four full
+    // 128-byte rows per store (conflict free).  Walking down its rows the horizontally interpolated source row is kept
+    // while the source row index repeats, like in the kernel above.
+    const int ptid = threadIdx.x - 256;
+    const int q = ptid & 7;
+    const int j = (ptid >> 3) & 31;
+    constexpr int kRows = kH3HaloRows / kH3RowGroups;
+    const int hy0 = (ptid >> 8) * kRows;
+    const int soff = j * 128 + ((q ^ (j & 7)) << 4);         // row = hy * 32 + j: swizzle phase (row & 7) = j & 7
+    int u = 0, xs = 0;
+    uint32_t phase = 0, xphase = 0;
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      const int t = tile % per_img;
+      const int y0 = (t / p.tiles_x) * kH3TR - 1, x0 = (t % p.tiles_x) * kH3OutC - 1;
+      const int ysb = hu_src_base(y0, p.rh, p.align_corners), xsb = hu_src_base(x0, p.rw, p.align_corners);
+      const int ox = x0 + j;
+      const bool col_ok = ox >= 0 && ox < p.W;
+      const float sx = p.align_corners ? p.rw * ox : fmaxf(0.5f * (ox + 0.5f) - 0.5f, 0.f);
+      const int xs0 = min(static_cast<int>(sx), p.Ws - 1), xs1 = min(xs0 + 1, p.Ws - 1);
+      const float lx = sx - xs0, hxw = 1.f - lx;
+      const int c0 = (xs0 - xsb) * 128 + q * 16, c1 = (xs1 - xsb) * 128 + q * 16;
+      for (int cb = 0; cb < units_per_tile; ++cb) {
+        mbar_wait(&xfull[xs], xphase);                       // source window landed (TMA)
+        mbar_wait(&empty[u], phase ^ 1);                     // the MMAs are done with this unit
+        uint8_t* ubase = sA + u * kH3UnitBytes + soff;
+        const uint8_t* src = sX + xs * kH3SrcSlotBytes;
+        float h0[8], h1[8];
+        int cy0 = -1, cy1 = -1;                                // source rows held in h0 / h1
+        auto hrow = [&](int ys, float* h) {
+          const uint8_t* rp = src + (ys - ysb) * (kH3SrcCols * 128);
+          const uint4 a = *reinterpret_cast<const uint4*>(rp + c0);
+          const uint4 bq = *reinterpret_cast<const uint4*>(rp + c1);
+          const uint32_t* pa = &a.x;
+          const uint32_t* pb = &bq.x;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            h[2 * k] = hxw * bf16_lo(pa[k]) + lx * bf16_lo(pb[k]);
+            h[2 * k + 1] = hxw * bf16_hi(pa[k]) + lx * bf16_hi(pb[k]);
+          }
+        };
+#pragma unroll
+        for (int i = 0; i < kRows; ++i) {
+          const int hy = hy0 + i;
+          const int oy = y0 + hy;
+          uint4 val = make_uint4(0u, 0u, 0u, 0u);
+          if (col_ok && oy >= 0 && oy < p.H) {
+            const float sy = p.align_corners ? p.rh * oy : fmaxf(0.5f * (oy + 0.5f) - 0.5f, 0.f);
+            const int ys0 = min(static_cast<int>(sy), p.Hs - 1), ys1 = min(ys0 + 1, p.Hs - 1);
+            const float ly = sy - ys0, hyw = 1.f - ly;
+            if (ys0 != cy0) {
+              if (ys0 == cy1) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) h0[k] = h1[k];
+              } else {
+                hrow(ys0, h0);
+              }
+              cy0 = ys0;
+            }
+            if (ys1 != cy1) {
+              if (ys1 == cy0) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) h1[k] = h0[k];
+              } else {
+                hrow(ys1, h1);
+              }
+              cy1 = ys1;
+            }
+            uint32_t o[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k)                        // same expression tree as upsample2x_kernel (misc.cu)
+              o[k] = pack_bf16(hyw * h0[2 * k] + ly * h1[2 * k], hyw * h0[2 * k + 1] + ly * h1[2 * k + 1]);
+            val = make_uint4(o[0], o[1], o[2], o[3]);
+          }
+          *reinterpret_cast<uint4*>(ubase + hy * (kH3TC * 128)) = val;
+        }
+        fence_proxy_async_smem();                              // generic-proxy writes -> visible to the UMMA (async proxy)
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive(&full[u]);
+          mbar_arrive(&xempty[xs]);
+        }
+        if (++u == kH3Units) {
+          u = 0;
+          phase ^= 1;
+        }
+        if (++xs == kH3SrcSlots) {
+          xs = 0;
+          xphase ^= 1;
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
 static bool hc_make_map(CUtensorMap* map, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                         const uint32_t* box, CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
   auto fn = get_tensor_map_encoder();
@@ -577,8 +884,10 @@ extern "C" int de_head_up_conv(const void* x, const void* w, int64_t ldw, const 
   p.x = reinterpret_cast<const __nv_bfloat16*>(x);
   p.B = B; p.Hs = Hs; p.Ws = Ws; p.H = 2 * Hs; p.W = 2 * Ws; p.Cin = Cin;
   p.cin_blocks = Cin / 64;
-  p.tiles_x = (p.W + kHcBW - 1) / kHcBW;
-  p.tiles_y = (p.H + kHcBH - 1) / kHcBH;
+  // DEB_HEAD_UP_V1=1: the first formulation (three dx copies, N = 32 MMAs) for A/B runs
+  static const bool v1 = getenv("DEB_HEAD_UP_V1") && atoi(getenv("DEB_HEAD_UP_V1")) != 0;
+  p.tiles_x = v1 ? (p.W + kHcBW - 1) / kHcBW : (p.W + kH3OutC - 1) / kH3OutC;
+  p.tiles_y = v1 ? (p.H + kHcBH - 1) / kHcBH : (p.H + kH3TR - 1) / kH3TR;
   const long long tiles = (long long)B * p.tiles_x * p.tiles_y;
   if (tiles > 0x7fffffffLL) return fail(DE_ERR_UNSUPPORTED, "de_head_up_conv: too many tiles");
   p.num_tiles = (int)tiles;
@@ -589,14 +898,16 @@ extern "C" int de_head_up_conv(const void* x, const void* w, int64_t ldw, const 
   p.bias = bias; p.head_w = head_w; p.head_b = head_b; p.out = out;
   const int w_bytes = 9 * p.cin_blocks * kHcWChunk;
   const int post_bytes = 256 + 2 * kHcN * 4;
-  const int smem_bytes = 1024 + w_bytes + kHuUnits * kHuUnitBytes + kHuSrcSlots * kHuSrcSlotBytes + post_bytes;
+  const int smem_bytes = v1 ? 1024 + w_bytes + kHuUnits * kHuUnitBytes + kHuSrcSlots * kHuSrcSlotBytes + post_bytes
+                            : 1024 + w_bytes + kH3Units * kH3UnitBytes + kH3SrcSlots * kH3SrcSlotBytes + post_bytes;
   if (smem_bytes > 232448) return fail(DE_ERR_UNSUPPORTED, "de_head_up_conv: Cin=%d does not fit shared memory", Cin);
   CUtensorMap tw, tx;
   {
     const uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)Ws, (uint64_t)Hs, (uint64_t)B};
     const uint64_t strides[3] = {(uint64_t)Cin * 2, (uint64_t)Ws * Cin * 2, (uint64_t)Hs * Ws * Cin * 2};
-    const uint32_t box[4] = {64, kHuSrcCols, kHuSrcRows, 1};
-    if (!hc_make_map(&tx, x, 4, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_NONE)) return DE_ERR_CUDA;
+    const uint32_t box1[4] = {64, kHuSrcCols, kHuSrcRows, 1};
+    const uint32_t box3[4] = {64, kH3SrcCols, kH3SrcRows, 1};
+    if (!hc_make_map(&tx, x, 4, dims, strides, v1 ? box1 : box3, CU_TENSOR_MAP_SWIZZLE_NONE)) return DE_ERR_CUDA;
   }
   {
     const uint64_t dims[2] = {(uint64_t)9 * Cin, (uint64_t)kHcN};
@@ -604,15 +915,22 @@ extern "C" int de_head_up_conv(const void* x, const void* w, int64_t ldw, const 
     const uint32_t box[2] = {64, kHcN};
     if (!hc_make_map(&tw, w, 2, dims, strides, box)) return DE_ERR_CUDA;
   }
-  static SmemOptIn optin;
-  {
-    cudaError_t e = ensure_smem(optin, head_up_conv_kernel, smem_bytes);
-    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(head_up_conv)");
-  }
   int grid = num_sms();
   if (p.num_tiles < grid) grid = p.num_tiles;
-  cudaError_t le = launch_pdl(2, head_up_conv_kernel, dim3(grid), dim3(kHuThreads), (size_t)smem_bytes,
-                              reinterpret_cast<cudaStream_t>(stream), tw, tx, p);
+  cudaError_t le;
+  if (v1) {
+    static SmemOptIn optin;
+    cudaError_t e = ensure_smem(optin, head_up_conv_kernel, smem_bytes);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(head_up_conv)");
+    le = launch_pdl(2, head_up_conv_kernel, dim3(grid), dim3(kHuThreads), (size_t)smem_bytes,
+                    reinterpret_cast<cudaStream_t>(stream), tw, tx, p);
+  } else {
+    static SmemOptIn optin3;
+    cudaError_t e = ensure_smem(optin3, head_up3_kernel, smem_bytes);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(head_up3)");
+    le = launch_pdl(2, head_up3_kernel, dim3(grid), dim3(kH3Threads), (size_t)smem_bytes,
+                    reinterpret_cast<cudaStream_t>(stream), tw, tx, p);
+  }
   count_launch();
   if (le != cudaSuccess) return cuda_fail(le, "cudaLaunchKernelEx(head_up_conv_kernel)");
   return cuda_check_launch("head_up_conv_kernel");

@@ -618,21 +618,51 @@ def test_stem_conv(k, s, Cout, H, W):
     assert _relerr(out, ref) < 5e-3
 
 
-@pytest.mark.parametrize("k,s,Cc,H,W", [(3, 1, 32, 96, 128), (3, 2, 144, 96, 128), (5, 2, 192, 48, 64), (5, 1, 816, 12, 16),
-                                        (5, 2, 816, 12, 16), (3, 1, 1392, 6, 8), (5, 2, 48, 9, 7)])
-def test_depthwise(k, s, Cc, H, W):
+@pytest.mark.parametrize("k,s,Cc,H,W,B", [(3, 1, 32, 96, 128, 2), (3, 2, 144, 96, 128, 2), (5, 2, 192, 48, 64, 2), (5, 1, 816, 12, 16, 2),
+                                          (5, 2, 816, 12, 16, 2), (3, 1, 1392, 6, 8, 2), (5, 2, 48, 9, 7, 2),
+                                          # frame-packed tiles: 4x8 pixels of four frames (ragged batch: the last box reads
+                                          # past B and is zero-filled), 8x8 / 4x16 of two frames, batch too small to pack
+                                          (5, 1, 1392, 4, 8, 7), (3, 1, 1392, 4, 8, 32), (5, 1, 232, 6, 8, 5), (3, 1, 136, 12, 16, 3),
+                                          (5, 1, 96, 4, 8, 1), (3, 1, 96, 4, 8, 2), (5, 1, 72, 3, 5, 6), (3, 1, 64, 11, 7, 4)])
+def test_depthwise(k, s, Cc, H, W, B):
     from depth_estimation_b200 import ops
     dev = _dev()
-    x = _rand((2, Cc, H, W), dev, seed=53).bfloat16()
+    x = _rand((B, Cc, H, W), dev, seed=53).bfloat16()
     w = _rand((Cc, 1, k, k), dev, 0.2, seed=54).bfloat16()
     b = _rand((Cc,), dev, seed=55)
     Ho, Wo = (H + s - 1) // s, (W + s - 1) // s
-    out = torch.empty((2, Ho, Wo, Cc), dtype=torch.bfloat16, device=dev)
-    ops.depthwise(x.permute(0, 2, 3, 1).contiguous(), w.reshape(Cc, k * k).t().contiguous(), b, out, k, s, ops.ACT_RELU6)
+    out = torch.full((B + 1, Ho, Wo, Cc), 7.0, dtype=torch.bfloat16, device=dev)     # one guard frame behind the batch
+    ops.depthwise(x.permute(0, 2, 3, 1).contiguous(), w.reshape(Cc, k * k).t().contiguous(), b, out[:B], k, s, ops.ACT_RELU6)
     ref = F.relu6(F.conv2d(_tf_same_pad(x.float(), k, s), w.float(), b, stride=s, groups=Cc)).permute(0, 2, 3, 1)
     torch.cuda.synchronize()
-    assert out.shape == ref.shape
-    assert _relerr(out, ref) < 5e-3
+    assert out[:B].shape == ref.shape
+    assert _relerr(out[:B], ref) < 5e-3
+    assert bool((out[B] == 7.0).all()), "a packed tile wrote past the last frame"
+
+
+@pytest.mark.parametrize("th_tw", [816, 808, 416, 408])
+def test_depthwise_tile_shapes_agree(th_tw):
+    """Every tile shape of the stride-1 kernel (8x16 of one frame, 8x8 / 4x16 of two, 4x8 of four - selected through the
+    image size) gives the same bits as the 8x16 shape on the same pixels: the accumulation order per output does not
+    depend on the tile."""
+    from depth_estimation_b200 import ops
+    dev = _dev()
+    H, W, B = {816: (16, 32, 3), 808: (8, 8, 4), 416: (4, 16, 4), 408: (4, 8, 8)}[th_tw]
+    Cc, k = 136, 5
+    # embed the image in a larger, zero-bordered one whose tile shape is 8x16: same taps in the same (ky, kx) order on
+    # the same values (zeros where the small image has its TF-same padding)
+    x = _rand((B, Cc, H, W), dev, seed=60).bfloat16()
+    big = torch.zeros((B, Cc, 24, 40), dtype=torch.bfloat16, device=dev)
+    big[:, :, 4:4 + H, 4:4 + W] = x
+    w = _rand((Cc, 1, k, k), dev, 0.2, seed=61).bfloat16()
+    b = _rand((Cc,), dev, seed=62)
+    wt = w.reshape(Cc, k * k).t().contiguous()
+    out = torch.empty((B, H, W, Cc), dtype=torch.bfloat16, device=dev)
+    out_big = torch.empty((B, 24, 40, Cc), dtype=torch.bfloat16, device=dev)
+    ops.depthwise(x.permute(0, 2, 3, 1).contiguous(), wt, b, out, k, 1, ops.ACT_RELU6)
+    ops.depthwise(big.permute(0, 2, 3, 1).contiguous(), wt, b, out_big, k, 1, ops.ACT_RELU6)
+    torch.cuda.synchronize()
+    assert torch.equal(out, out_big[:, 4:4 + H, 4:4 + W, :])
 
 
 @pytest.mark.parametrize("k,Cc,cout,B,H,W,res", [
