@@ -522,11 +522,12 @@ constexpr int kH3SrcRows = 5, kH3SrcCols = 18;              // source window of 
 constexpr int kH3SrcBytes = kH3SrcRows * kH3SrcCols * 128;  // 11520
 constexpr int kH3SrcSlotBytes = 12288;
 constexpr int kH3SrcSlots = 4;
-#ifndef H3_ROW_GROUPS
-#define H3_ROW_GROUPS 1                                     // producer threads per (column, channel group): 1 x 6 or 2 x 3 halo rows
+#ifndef H3_GROUPS
+#define H3_GROUPS 2                                         // producer groups of 8 warps; group g interpolates units g, g + 2, ...
 #endif
-constexpr int kH3RowGroups = H3_ROW_GROUPS;
-constexpr int kH3ProdWarps = 8 * kH3RowGroups;
+constexpr int kH3Groups = H3_GROUPS;
+constexpr int kH3GroupWarps = 8;
+constexpr int kH3ProdWarps = kH3GroupWarps * kH3Groups;
 constexpr int kH3Threads = 256 + 32 * kH3ProdWarps;
 
 DEV void tmem_ld_32x16(uint32_t taddr, uint32_t* r) {
@@ -569,12 +570,12 @@ head_up3_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < kH3Units; ++i) {
-      mbar_init(&full[i], kH3ProdWarps);
+      mbar_init(&full[i], kH3GroupWarps);
       mbar_init(&empty[i], 1);
     }
     for (int i = 0; i < kH3SrcSlots; ++i) {
       mbar_init(&xfull[i], 1);
-      mbar_init(&xempty[i], kH3ProdWarps);
+      mbar_init(&xempty[i], kH3GroupWarps);
     }
     for (int i = 0; i < kH3Acc; ++i) {
       mbar_init(&tfull[i], 1);
@@ -708,78 +709,111 @@ head_up3_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
     }
   } else if (warp >= 8) {
     // ------------------------------------------------------------------ producers: interpolate the halo tile once, swizzled K-major
-    // Thread = (halo column j of 32, 8-channel group q [, row group]); a warp covers 4 columns x 8 groups = four full
-    // 128-byte rows per store (conflict free).  Walking down its rows the horizontally interpolated source row is kept
-    // while the source row index repeats, like in the kernel above.
+    // Thread = (halo column j of 32, 8-channel group q) of one producer GROUP (8 warps = one whole unit); a warp covers
+    // 4 columns x 8 channel groups = four full 128-byte rows per store (conflict free).  Unit n of the CTA belongs to
+    // group n % kH3Groups, so one group's LDS -> math -> STS -> fence.proxy.async -> arrive chain runs under the other
+    // group's arithmetic.  The kernel is issue-bound (ncu: 72 % issue-active, 13 k warp instructions per tile in the
+    // first version of this loop), so the loop is built to execute few instructions:
+    //   * the <= 5 source rows of the window are interpolated horizontally ONCE per unit into registers (H[0..4]); a
+    //     halo row then picks the pair (H[w], H[w+1]) with a warp-uniform switch - no re-loads, no register shuffling;
+    //   * the per-row source index / weight is computed by lane hy of every warp once per tile and broadcast by
+    //     shuffles (every thread of the CTA needs the same six values); tile coordinates advance incrementally;
+    //   * columns outside the image get zero horizontal weights (their bytes come out as +-0) instead of a per-row test.
+    // Arithmetic: FMUL2 / FFMA2 in exactly the operation order of upsample2x_kernel (t = l * second; h * first + t), so
+    // the interpolated bf16 values stay bit-identical to the stand-alone upsample.
+    static_assert(kH3Units % kH3Groups == 0 && kH3SrcSlots == kH3Units, "ring slots are owned by unit index");
     const int ptid = threadIdx.x - 256;
     const int q = ptid & 7;
     const int j = (ptid >> 3) & 31;
-    constexpr int kRows = kH3HaloRows / kH3RowGroups;
-    const int hy0 = (ptid >> 8) * kRows;
+    const int grp = ptid >> 8;
     const int soff = j * 128 + ((q ^ (j & 7)) << 4);         // row = hy * 32 + j: swizzle phase (row & 7) = j & 7
-    int u = 0, xs = 0;
-    uint32_t phase = 0, xphase = 0;
+    constexpr int kRowBytes = kH3SrcCols * 128;
+    int n = 0;                                               // unit counter of the CTA (all groups count every unit)
+    int tx, ty;
+    {
+      const int t = static_cast<int>(blockIdx.x) % per_img;
+      ty = t / p.tiles_x;
+      tx = t - ty * p.tiles_x;
+    }
+    const int dtx = static_cast<int>(gridDim.x) % p.tiles_x, dty = (static_cast<int>(gridDim.x) / p.tiles_x) % p.tiles_y;
     for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-      const int t = tile % per_img;
-      const int y0 = (t / p.tiles_x) * kH3TR - 1, x0 = (t % p.tiles_x) * kH3OutC - 1;
+      const int y0 = ty * kH3TR - 1, x0 = tx * kH3OutC - 1;
+      tx += dtx;
+      if (tx >= p.tiles_x) {
+        tx -= p.tiles_x;
+        ++ty;
+      }
+      ty += dty;
+      if (ty >= p.tiles_y) ty -= p.tiles_y;
       const int ysb = hu_src_base(y0, p.rh, p.align_corners), xsb = hu_src_base(x0, p.rw, p.align_corners);
       const int ox = x0 + j;
       const bool col_ok = ox >= 0 && ox < p.W;
       const float sx = p.align_corners ? p.rw * ox : fmaxf(0.5f * (ox + 0.5f) - 0.5f, 0.f);
-      const int xs0 = min(static_cast<int>(sx), p.Ws - 1), xs1 = min(xs0 + 1, p.Ws - 1);
-      const float lx = sx - xs0, hxw = 1.f - lx;
-      const int c0 = (xs0 - xsb) * 128 + q * 16, c1 = (xs1 - xsb) * 128 + q * 16;
-      for (int cb = 0; cb < units_per_tile; ++cb) {
-        mbar_wait(&xfull[xs], xphase);                       // source window landed (TMA)
-        mbar_wait(&empty[u], phase ^ 1);                     // the MMAs are done with this unit
-        uint8_t* ubase = sA + u * kH3UnitBytes + soff;
-        const uint8_t* src = sX + xs * kH3SrcSlotBytes;
-        float h0[8], h1[8];
-        int cy0 = -1, cy1 = -1;                                // source rows held in h0 / h1
-        auto hrow = [&](int ys, float* h) {
-          const uint8_t* rp = src + (ys - ysb) * (kH3SrcCols * 128);
-          const uint4 a = *reinterpret_cast<const uint4*>(rp + c0);
-          const uint4 bq = *reinterpret_cast<const uint4*>(rp + c1);
+      const int xs0 = max(min(static_cast<int>(sx), p.Ws - 1), 0), xs1 = min(xs0 + 1, p.Ws - 1);
+      const float lx = col_ok ? sx - xs0 : 0.f, hxw = col_ok ? 1.f - lx : 0.f;
+      const float2 lx2 = make_float2(lx, lx), hx2 = make_float2(hxw, hxw);
+      const int c0 = min(max(xs0 - xsb, 0), kH3SrcCols - 1) * 128 + q * 16, c1 = min(max(xs1 - xsb, 0), kH3SrcCols - 1) * 128 + q * 16;
+      // lane hy computes halo row hy: window row of its upper source row (+1; 0: row outside the image) and weight;
+      // the six indices travel as one packed word, the weight is fetched from its lane when the row is written
+      float ly_lane;
+      uint32_t wpack = 0;
+      {
+        const int oy = y0 + lane;
+        const float sy = p.align_corners ? p.rh * oy : fmaxf(0.5f * (oy + 0.5f) - 0.5f, 0.f);
+        const int ys0 = min(static_cast<int>(sy), p.Hs - 1);
+        ly_lane = sy - ys0;
+        const int w1 = (oy >= 0 && oy < p.H) ? min(max(ys0 - ysb, 0), kH3SrcRows - 2) + 1 : 0;
+#pragma unroll
+        for (int hy = 0; hy < kH3HaloRows; ++hy) wpack |= static_cast<uint32_t>(__shfl_sync(0xffffffffu, w1, hy)) << (4 * hy);
+      }
+      // any row on window rows (3, 4)?  (w1 == 4 in some nibble)
+      const bool need4 = ((wpack & 0x444444u) != 0u);
+      // byte offset of window row w: source row min(ysb + w, Hs - 1), i.e. the clamped "+1" neighbour at the bottom border
+      int offw[kH3SrcRows];
+#pragma unroll
+      for (int w = 0; w < kH3SrcRows; ++w) offw[w] = (min(ysb + w, p.Hs - 1) - ysb) * kRowBytes;
+      for (int cb = 0; cb < units_per_tile; ++cb, ++n) {
+        if (n % kH3Groups != grp) continue;
+        const int u = n % kH3Units;
+        const uint32_t par = (n / kH3Units) & 1;
+        mbar_wait(&xfull[u], par);                           // source window landed (TMA)
+        const uint8_t* src = sX + u * kH3SrcSlotBytes;
+        float2 H[kH3SrcRows][4];
+#pragma unroll
+        for (int w = 0; w < kH3SrcRows; ++w) {
+          if (w == kH3SrcRows - 1 && !need4) break;
+          const uint4 a = *reinterpret_cast<const uint4*>(src + offw[w] + c0);
+          const uint4 bq = *reinterpret_cast<const uint4*>(src + offw[w] + c1);
           const uint32_t* pa = &a.x;
           const uint32_t* pb = &bq.x;
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            h[2 * k] = hxw * bf16_lo(pa[k]) + lx * bf16_lo(pb[k]);
-            h[2 * k + 1] = hxw * bf16_hi(pa[k]) + lx * bf16_hi(pb[k]);
-          }
-        };
+          for (int k = 0; k < 4; ++k)
+            H[w][k] = ffma2(make_float2(bf16_lo(pa[k]), bf16_hi(pa[k])), hx2, fmul2(make_float2(bf16_lo(pb[k]), bf16_hi(pb[k])), lx2));
+        }
+        mbar_wait(&empty[u], par ^ 1);                       // the MMAs are done with this unit
+        uint8_t* ubase = sA + u * kH3UnitBytes + soff;
 #pragma unroll
-        for (int i = 0; i < kRows; ++i) {
-          const int hy = hy0 + i;
-          const int oy = y0 + hy;
+        for (int hy = 0; hy < kH3HaloRows; ++hy) {
           uint4 val = make_uint4(0u, 0u, 0u, 0u);
-          if (col_ok && oy >= 0 && oy < p.H) {
-            const float sy = p.align_corners ? p.rh * oy : fmaxf(0.5f * (oy + 0.5f) - 0.5f, 0.f);
-            const int ys0 = min(static_cast<int>(sy), p.Hs - 1), ys1 = min(ys0 + 1, p.Hs - 1);
-            const float ly = sy - ys0, hyw = 1.f - ly;
-            if (ys0 != cy0) {
-              if (ys0 == cy1) {
+          const int w1 = static_cast<int>((wpack >> (4 * hy)) & 7u);
+          if (w1 != 0) {
+            const float ly = __shfl_sync(0xffffffffu, ly_lane, hy);
+            const float2 ly2 = make_float2(ly, ly), hy2 = make_float2(1.f - ly, 1.f - ly);
+            auto emit = [&](const float2* up, const float2* dn) {
+              uint32_t o[4];
 #pragma unroll
-                for (int k = 0; k < 8; ++k) h0[k] = h1[k];
-              } else {
-                hrow(ys0, h0);
+              for (int k = 0; k < 4; ++k) {
+                const float2 v = ffma2(up[k], hy2, fmul2(dn[k], ly2));
+                o[k] = pack_bf16(v.x, v.y);
               }
-              cy0 = ys0;
+              val = make_uint4(o[0], o[1], o[2], o[3]);
+            };
+            switch (w1) {
+              case 1: emit(H[0], H[1]); break;
+              case 2: emit(H[1], H[2]); break;
+              case 3: emit(H[2], H[3]); break;
+              default: emit(H[3], H[4]); break;
             }
-            if (ys1 != cy1) {
-              if (ys1 == cy0) {
-#pragma unroll
-                for (int k = 0; k < 8; ++k) h1[k] = h0[k];
-              } else {
-                hrow(ys1, h1);
-              }
-              cy1 = ys1;
-            }
-            uint32_t o[4];
-#pragma unroll
-            for (int k = 0; k < 4; ++k)                        // same expression tree as upsample2x_kernel (misc.cu)
-              o[k] = pack_bf16(hyw * h0[2 * k] + ly * h1[2 * k], hyw * h0[2 * k + 1] + ly * h1[2 * k + 1]);
-            val = make_uint4(o[0], o[1], o[2], o[3]);
           }
           *reinterpret_cast<uint4*>(ubase + hy * (kH3TC * 128)) = val;
         }
@@ -787,15 +821,7 @@ head_up3_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
         __syncwarp();
         if (lane == 0) {
           mbar_arrive(&full[u]);
-          mbar_arrive(&xempty[xs]);
-        }
-        if (++u == kH3Units) {
-          u = 0;
-          phase ^= 1;
-        }
-        if (++xs == kH3SrcSlots) {
-          xs = 0;
-          xphase ^= 1;
+          mbar_arrive(&xempty[u]);
         }
       }
     }

@@ -383,9 +383,11 @@ def test_head_conv(B, H, W, Cin):
 
 
 @pytest.mark.parametrize("B,Hs,Ws,Cin,ac", [(1, 32, 48, 128, True), (2, 10, 20, 128, True), (1, 19, 27, 64, True),
-                                             (2, 12, 8, 128, False), (1, 48, 48, 128, True), (2, 16, 32, 64, False)])
+                                             (2, 12, 8, 128, False), (1, 48, 48, 128, True), (2, 16, 32, 64, False),
+                                             (3, 45, 61, 128, True), (1, 2, 3, 64, True), (2, 96, 96, 128, True)])
 def test_head_up_conv(B, Hs, Ws, Cin, ac):
-    """Fused bilinear x2 + head tail vs the two-kernel path (bit-identical interpolation, same MMAs) and vs torch."""
+    """Fused bilinear x2 + head tail vs the two-kernel path (bit-identical interpolation; the three horizontal taps are
+    summed in the epilogue instead of inside one accumulator, so fp32 rounding order differs) and vs torch."""
     from depth_estimation_b200 import ops
     from depth_estimation_b200.weights import pack_conv3x3
     dev = _dev()
@@ -403,7 +405,7 @@ def test_head_up_conv(B, Hs, Ws, Cin, ac):
     t = F.relu(F.conv2d(t.bfloat16().float(), wt.float(), bias, padding=1))
     ref = F.relu((t * w2.view(1, 32, 1, 1)).sum(1) + 0.3)
     torch.cuda.synchronize()
-    assert _relerr(out, two) < 1e-6, _relerr(out, two)
+    assert _relerr(out, two) < 1e-5, _relerr(out, two)
     assert _relerr(out, ref) < 5e-3
 
 
