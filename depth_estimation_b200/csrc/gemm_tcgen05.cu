@@ -1117,6 +1117,14 @@ extern "C" int de_gemm(const DeGemm* g, void* stream) {
   // per row block instead of a full and a mostly empty 128-wide one - the store epilogue skips all-empty column units,
   // and with a one-k-block main loop the per-tile epilogue is what the kernel costs
   if (g->block_n == 0 && g->N > 128 && g->N < 256 && p.m_tiles >= num_sms() && p.num_k_blocks <= 4) bn = 256;
+  // N <= 32 with a plain "bias + activation -> dense output" epilogue (MiDaS_small's depthwise-separable pointwise conv
+  // 32 -> 24 and the first projection of a stage): a 64-wide tile runs the TMA-store epilogue - the tensor map clips the
+  // columns beyond N - where the 32-wide tile would take the general epilogue with scattered 8-byte stores
+  // (scripts/narrow_n_probe.py: M 262144, K 32, N 24: 34.6 -> 21.5 us; equal or better on every shape measured)
+  if (g->block_n == 0 && bn == 32 && !g->add1 && !g->add2 && !g->out_relu && !g->head_w && g->out_rowmode == 0 && !g->out_split &&
+      g->epilogue != 1 && (g->ldo * (g->out_dtype == DE_DTYPE_F32 ? 4 : 2)) % 16 == 0 && (reinterpret_cast<uintptr_t>(g->out) & 15) == 0 &&
+      (g->a_mode == 0 || g->ldo == g->N))
+    bn = 64;
   // Split-K for small grids (the batch-1 latency path, the coarse decoder levels): when the tiles cover a fraction of the
   // SMs and K is long, K-slices of a tile run on different SMs and store their fp32 partial tiles into per-slice
   // regions of the caller's workspace; splitk_finalize_kernel adds the slices in a fixed order and applies the epilogue.
