@@ -1138,7 +1138,10 @@ extern "C" int de_gemm(const DeGemm* g, void* stream) {
     if (want > p.num_k_blocks / 2) want = p.num_k_blocks / 2;         // at least two k-blocks per slice
     if (want > 16) want = 16;
     if (slice_bytes > 0 && want > g->splitk_ws_bytes / slice_bytes) want = (int)(g->splitk_ws_bytes / slice_bytes);
-    const bool worth = tiles * 3 <= num_sms() && p.num_k_blocks >= 24;   // the finalize launch must pay for itself
+    // the finalize launch must pay for itself: a third of the SMs busy and a medium K, or half of them and a long K
+    // (DPT_Hybrid batch 1, bf16x3 decoder convolutions at 96x96: 72 tiles, 108 k-blocks)
+    static const int k2 = getenv("DEB_SPLITK_HALF") ? atoi(getenv("DEB_SPLITK_HALF")) : 1;
+    const bool worth = (tiles * 3 <= num_sms() && p.num_k_blocks >= 24) || (k2 && tiles * 2 <= num_sms() && p.num_k_blocks >= 64);
     if (want >= 2 && bn_s >= 64 && (g->k_splits > 1 || worth)) {
       k_splits = want;
       bn = bn_s;                                                      // wide tiles + K-slices instead of narrow tiles
