@@ -5,6 +5,8 @@
 //   * MaxPool 3x3 s2 TF-same (ResNetV2 stem).
 // Restates [UPSTREAM] geffnet Conv2dSame / timm StdConv2dSame+MaxPool2dSame padding rule:
 //   pad_total = max((ceil(i/s)-1)*s + k - i, 0), pad_before = pad_total / 2 (extra pixel bottom/right).
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "depth_b200.h"
 #include "host_util.h"
@@ -115,6 +117,88 @@ __global__ void __launch_bounds__(128) stem_conv_kernel(const void* __restrict__
       op[0] = make_uint4(pack_bf16(r[0], r[1]), pack_bf16(r[2], r[3]), pack_bf16(r[4], r[5]), pack_bf16(r[6], r[7]));
       op[1] = make_uint4(pack_bf16(r[8], r[9]), pack_bf16(r[10], r[11]), pack_bf16(r[12], r[13]), pack_bf16(r[14], r[15]));
     }
+  }
+}
+
+// EfficientNet-Lite3 stem (3x3, stride 2, 3 -> 32 channels, bf16 in / out) staged through shared memory: a CTA owns an
+// 8 x 32-pixel output tile; its 17 x 65 x 3 input window is read once with coalesced loads (zero outside the image =
+// TF-same padding) and kept as fp32, the 27 x 32 filter bank sits next to it.  A thread computes two adjacent pixels x
+// all 32 channels: per (channel, ky) it reads its five window columns with one LDS.128 + one LDS.32, every weight
+// float4 (a warp-wide broadcast) feeds four FFMA2.  The kernel above issues one dependent 2-byte global load per
+// (tap, channel, pixel) behind a bounds branch - 34 us per 32 frames of 128x256 (an 8th of the HBM rate) - this one has
+// no global load inside the tap loops.  Same accumulation order per output (bias, then (ky, kx, c)).
+constexpr int kStTH = 8, kStTW = 32;                      // output tile
+constexpr int kStWH = 2 * (kStTH - 1) + 3, kStWW = 2 * (kStTW - 1) + 3;   // 17 x 65 window
+constexpr int kStWP = 68;                                 // padded window row (16-byte aligned rows)
+__global__ void __launch_bounds__(128) stem3x3s2_tiled_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
+                                                              const float* __restrict__ bias, __nv_bfloat16* __restrict__ out,
+                                                              int B, int H, int W, int Ho, int Wo, int pad_y, int pad_x, int act) {
+  __shared__ __align__(16) float s_in[3 * kStWH * kStWP];
+  __shared__ __align__(16) float s_wt[27 * 32];             // [tap = (ky*3 + kx)*3 + c][32]
+  __shared__ float s_bias[32];
+  const int b = blockIdx.z, oy0 = blockIdx.y * kStTH, ox0 = blockIdx.x * kStTW;
+  const int iy0 = oy0 * 2 - pad_y, ix0 = ox0 * 2 - pad_x;
+  for (int i = threadIdx.x; i < 27 * 32; i += 128) {
+    const int co = i / 27, t = i - co * 27;                 // coalesced read of [32][27], transposed into smem
+    s_wt[t * 32 + co] = __ldg(w + i);
+  }
+  if (threadIdx.x < 32) s_bias[threadIdx.x] = bias ? __ldg(bias + threadIdx.x) : 0.f;
+  const __nv_bfloat16* xb = x + (long long)b * 3 * H * W;
+  for (int i = threadIdx.x; i < 3 * kStWH * kStWP; i += 128) {
+    const int col = i % kStWP, r = i / kStWP;               // r = c * 17 + row
+    const int c = r / kStWH, row = r - c * kStWH;
+    const int iy = iy0 + row, ix = ix0 + col;
+    float v = 0.f;
+    if (col < kStWW && iy >= 0 && iy < H && ix >= 0 && ix < W) v = __bfloat162float(xb[((long long)c * H + iy) * W + ix]);
+    s_in[i] = v;
+  }
+  __syncthreads();
+  const int px = threadIdx.x & 15, ty = threadIdx.x >> 4;  // pixel pair (columns 2px, 2px+1) of tile row ty
+  float2 acc[2][16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) acc[0][j] = acc[1][j] = make_float2(s_bias[2 * j], s_bias[2 * j + 1]);
+#pragma unroll
+  for (int ky = 0; ky < 3; ++ky) {
+    float in[3][5];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const float* rp = s_in + (c * kStWH + 2 * ty + ky) * kStWP + 4 * px;
+      const float4 v4 = *reinterpret_cast<const float4*>(rp);
+      in[c][0] = v4.x; in[c][1] = v4.y; in[c][2] = v4.z; in[c][3] = v4.w; in[c][4] = rp[4];
+    }
+#pragma unroll
+    for (int kx = 0; kx < 3; ++kx)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const float4* wp = reinterpret_cast<const float4*>(s_wt + ((ky * 3 + kx) * 3 + c) * 32);
+        const float2 p0 = make_float2(in[c][kx], in[c][kx]), p1 = make_float2(in[c][kx + 2], in[c][kx + 2]);
+#pragma unroll
+        for (int j4 = 0; j4 < 8; ++j4) {
+          const float4 ww = wp[j4];
+          acc[0][2 * j4] = ffma2(p0, make_float2(ww.x, ww.y), acc[0][2 * j4]);
+          acc[0][2 * j4 + 1] = ffma2(p0, make_float2(ww.z, ww.w), acc[0][2 * j4 + 1]);
+          acc[1][2 * j4] = ffma2(p1, make_float2(ww.x, ww.y), acc[1][2 * j4]);
+          acc[1][2 * j4 + 1] = ffma2(p1, make_float2(ww.z, ww.w), acc[1][2 * j4 + 1]);
+        }
+      }
+  }
+  const int oy = oy0 + ty;
+  if (oy >= Ho) return;
+#pragma unroll
+  for (int q = 0; q < 2; ++q) {
+    const int ox = ox0 + 2 * px + q;
+    if (ox >= Wo) break;
+    uint32_t o[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      float a = acc[q][j].x, c = acc[q][j].y;
+      if (act == DE_ACT_RELU6) { a = fminf(fmaxf(a, 0.f), 6.f); c = fminf(fmaxf(c, 0.f), 6.f); }
+      else if (act == DE_ACT_RELU) { a = fmaxf(a, 0.f); c = fmaxf(c, 0.f); }
+      o[j] = pack_bf16(a, c);
+    }
+    uint4* op = reinterpret_cast<uint4*>(out + (((long long)b * Ho + oy) * Wo + ox) * 32);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) op[j] = make_uint4(o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
   }
 }
 
@@ -240,6 +324,15 @@ extern "C" int de_stem_conv(const void* x_nchw, int x_dtype, const float* w, con
   if (!x_nchw || !w || !out_nhwc || Cout % kStemCo != 0 || k < 1 || k > 7)
     return fail(DE_ERR_INVALID, "de_stem_conv: bad args (Cout %% 16, k <= 7)");
   const int Ho = (H + stride - 1) / stride, Wo = (W + stride - 1) / stride;
+  static const bool direct = getenv("DEB_STEM_UNTILED") && atoi(getenv("DEB_STEM_UNTILED")) != 0;   // A/B switch
+  if (k == 3 && stride == 2 && Cout == 32 && x_dtype != DE_DTYPE_F32 && out_dtype != DE_DTYPE_F32 && B <= 65535 && !direct) {
+    const dim3 grid((Wo + kStTW - 1) / kStTW, (Ho + kStTH - 1) / kStTH, B);
+    stem3x3s2_tiled_kernel<<<grid, 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<const __nv_bfloat16*>(x_nchw), w, bias, reinterpret_cast<__nv_bfloat16*>(out_nhwc), B, H, W, Ho, Wo,
+        same_pad_before(H, k, stride), same_pad_before(W, k, stride), act);
+    count_launch();
+    return cuda_check_launch("stem3x3s2_tiled_kernel");
+  }
   const long long n = (long long)B * Ho * ((Wo + 1) / 2) * (Cout / kStemCo);
   const size_t smem = sizeof(float) * k * k * 3 * Cout;
   stem_conv_kernel<<<(unsigned)((n + 127) / 128), 128, smem, reinterpret_cast<cudaStream_t>(stream)>>>(
