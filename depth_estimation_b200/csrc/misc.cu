@@ -570,11 +570,25 @@ __global__ void __launch_bounds__(256) groupnorm_fused_kernel(const void* __rest
     if (sl < slices) {
       double a = 0.0, q = 0.0;
       const double2* pp = reinterpret_cast<const double2*>(partial) + (long long)b * nblocks * groups + g;
-#pragma unroll 4
-      for (int k = sl; k < (int)nblocks; k += slices) {
-        const double2 t = __ldcg(pp + (long long)k * groups);
-        a += t.x;
-        q += t.y;
+      // all of the thread's partials are requested before the first add (one L2 round trip instead of one per
+      // unrolled batch: ~1.2 us of every batch-1 GroupNorm); the adds run in the same order as before
+      constexpr int kAhead = 20;                                // 148 CTAs / 8 slices = 19 partials per thread
+      double2 t[kAhead];
+#pragma unroll
+      for (int i = 0; i < kAhead; ++i) {
+        const int k = sl + i * slices;
+        t[i] = k < (int)nblocks ? __ldcg(pp + (long long)k * groups) : make_double2(0.0, 0.0);
+      }
+#pragma unroll
+      for (int i = 0; i < kAhead; ++i)
+        if (sl + i * slices < (int)nblocks) {
+          a += t[i].x;
+          q += t[i].y;
+        }
+      for (int k = sl + kAhead * slices; k < (int)nblocks; k += slices) {
+        const double2 u = __ldcg(pp + (long long)k * groups);
+        a += u.x;
+        q += u.y;
       }
       s_red[sl * groups + g] = make_double2(a, q);
     }
