@@ -13,6 +13,10 @@
 //     final ReLU straight from TMEM and write one fp32 per pixel.
 // Roles: warp 0 TMA producer, warp 1 MMA issuer, warp 2 TMEM allocator, warps 4..7 epilogue.  Persistent CTAs, one
 // per SM, tiles handed out round-robin (x fastest, so concurrently running CTAs share halo rows in L2).
+//
+// Three kernels live here: head_conv_kernel (the above, on an activation that already has the output resolution),
+// head_up_conv_kernel (round 1: the x2 bilinear upsample fused in front, three dx copies of the halo tile) and
+// head_up3_kernel (round 2, what de_head_up_conv runs: the horizontal taps in the MMA's N dimension - see its comment).
 #include <cuda.h>
 #include <stdlib.h>
 
