@@ -445,6 +445,10 @@ attention_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const WsParams p)
 
 }  // namespace deb
 
+namespace deb {
+int launch_attention_ws2(const CUtensorMap& tm, __nv_bfloat16* out, int T, int heads, int qtiles, int ntiles, int out_split,
+                         float scale_log2e, cudaStream_t stream);   // attention_ws2.cu: two softmax threads per row
+}
 static int attention_impl(const void* qkv, void* out, int B, int T, int heads, float scale, int out_split, void* stream);
 extern "C" int de_attention(const void* qkv, void* out, int B, int T, int heads, float scale, void* stream) {
   return attention_impl(qkv, out, B, T, heads, scale, 0, stream);
@@ -468,6 +472,10 @@ static int attention_impl(const void* qkv, void* out, int B, int T, int heads, f
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(DE_ERR_CUDA, "de_attention: cuTensorMapEncodeTiled failed (%d)", (int)r);
+  static const int v2 = getenv("DEB_ATTN_V2") ? atoi(getenv("DEB_ATTN_V2")) : 0;
+  if (v2)
+    return launch_attention_ws2(tm, reinterpret_cast<__nv_bfloat16*>(out), T, heads, (T + 127) / 128, B * heads * ((T + 127) / 128),
+                                out_split, scale * 1.4426950408889634f, reinterpret_cast<cudaStream_t>(stream));
   static SmemOptIn optin;
   {
     cudaError_t e = ensure_smem(optin, attention_ws_kernel, (int)kWsSmem);

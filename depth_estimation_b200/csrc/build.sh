@@ -6,7 +6,7 @@ cd "$(dirname "$0")"
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 OUT=${OUT:-../libdepthb200.so}
 OBJ=${OBJ:-build}
-SRCS="api.cu resample_plan.cu preprocess.cu postprocess.cu gemm_tcgen05.cu attention_ws.cu misc.cu conv_direct.cu depthwise.cu head_conv.cu mbconv.cu engine.cu engine_nets.cu $EXTRA_SRCS"
+SRCS="api.cu resample_plan.cu preprocess.cu postprocess.cu gemm_tcgen05.cu attention_ws.cu attention_ws2.cu misc.cu conv_direct.cu depthwise.cu head_conv.cu mbconv.cu engine.cu engine_nets.cu $EXTRA_SRCS"
 FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -I../../include -I. ${NVCC_EXTRA}"
 mkdir -p $OBJ
 echo "$FLAGS" > $OBJ/.flags.new
