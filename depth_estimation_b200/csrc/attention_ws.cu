@@ -472,7 +472,7 @@ static int attention_impl(const void* qkv, void* out, int B, int T, int heads, f
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(DE_ERR_CUDA, "de_attention: cuTensorMapEncodeTiled failed (%d)", (int)r);
-  static const int v2 = getenv("DEB_ATTN_V2") ? atoi(getenv("DEB_ATTN_V2")) : 0;
+  static const int v2 = getenv("DEB_ATTN_V2") ? atoi(getenv("DEB_ATTN_V2")) : 1;   // 0: one softmax thread per row (the kernel below)
   if (v2)
     return launch_attention_ws2(tm, reinterpret_cast<__nv_bfloat16*>(out), T, heads, (T + 127) / 128, B * heads * ((T + 127) / 128),
                                 out_split, scale * 1.4426950408889634f, reinterpret_cast<cudaStream_t>(stream));

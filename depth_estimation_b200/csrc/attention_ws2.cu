@@ -9,7 +9,7 @@
 // S is read from TMEM twice per block in 32-column chunks (once for the maximum, once for the exponentials) so that a
 // thread never holds more than 32 scores: 640 threads leave 96 registers per thread, no setmaxnreg.
 // TMEM columns (512): S0 0-127 | S1 128-255 | O0 256-319 | O1 320-383 | P0 384-447 | P1 448-511 (as attention_ws.cu).
-// Selected with DEB_ATTN_V2=1 (attention_ws.cu::attention_impl).
+// The default since its measurement (profiles/r02_attention_ws2.md); DEB_ATTN_V2=0 selects attention_ws_kernel.
 #include <cuda.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -416,7 +416,7 @@ attention_ws2_kernel(const __grid_constant__ CUtensorMap tmQKV, const W2Params p
   }
 }
 
-// launched by attention_impl (attention_ws.cu) when DEB_ATTN_V2=1
+// launched by attention_impl (attention_ws.cu) unless DEB_ATTN_V2=0
 int launch_attention_ws2(const CUtensorMap& tm, __nv_bfloat16* out, int T, int heads, int qtiles, int ntiles, int out_split,
                          float scale_log2e, cudaStream_t stream) {
   static SmemOptIn optin;
